@@ -1,0 +1,158 @@
+"""Generate tests/golden/*.npz by running the REAL reference from /root/reference (build container only).
+
+    python oracle/make_golden.py
+
+TEST INFRASTRUCTURE.  Inputs come from ``weclip_b200.synth`` seeds (regenerated bit-identically by the tests);
+only the reference's *outputs* (plus the small micro-case inputs) are stored.  Library versions that the
+outputs depend on are recorded in every file (torch / cv2 / numpy are the arithmetic).
+"""
+from __future__ import annotations
+
+import os
+import sys
+import tempfile
+
+import numpy as np
+import torch
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, REPO)
+
+from weclip_b200 import synth  # noqa: E402
+from oracle import ref_harness  # noqa: E402
+
+OUT = os.path.join(REPO, "tests", "golden")
+WECLIP_CASE = dict(weights_seed=0, text_seed=7, label_seed=3, image_seed=1, H=96, W=112, label_hw=(70, 90),
+                   names=("syn0", "syn1"))
+
+
+def _versions():
+    import cv2
+    return dict(torch=torch.__version__, numpy=np.__version__, cv2=cv2.__version__)
+
+
+def _save(name, **arrs):
+    arrs["versions"] = np.array(repr(_versions()))
+    np.savez_compressed(os.path.join(OUT, name), **arrs)
+    print("wrote", name, {k: getattr(v, "shape", None) for k, v in arrs.items()})
+
+
+def golden_par(ref):
+    PAR = ref["PAR"]
+    par = PAR(num_iter=20, dilations=[1, 2, 4, 8, 12, 24])
+    g = torch.Generator().manual_seed(11)
+    cases = {"same": (40, 56, 40, 56, 3), "resize": (33, 47, 52, 38, 2), "tiny": (5, 7, 5, 7, 4)}
+    for tag, (hi, wi, h, w, kc) in cases.items():
+        imgs = synth.make_images(21 + kc, 1, hi, wi)
+        masks = torch.rand(1, kc, h, w, generator=g)
+        with torch.no_grad():
+            out = par(imgs, masks)
+            # affinity tensor, recomputed exactly as PAR.forward does (PAR.py:67-86)
+            im = torch.nn.functional.interpolate(imgs, size=(h, w), mode="bilinear", align_corners=True)
+            nb = par.get_dilated_neighbors(im)
+            ab = torch.abs(nb - im.unsqueeze(2).repeat(1, 1, nb.shape[2], 1, 1))
+            sd = torch.std(nb, dim=2, keepdim=True)
+            aff = (-(ab / (sd + 1e-8) / 0.3) ** 2).mean(dim=1, keepdim=True)
+            pos = par.pos.repeat(1, 1, 1, h, w)
+            pos_aff = -(pos / (torch.std(pos, dim=2, keepdim=True) + 1e-8) / 0.3) ** 2
+            aff = torch.softmax(aff, dim=2) + 0.01 * torch.softmax(pos_aff, dim=2)
+        _save(f"par_{tag}.npz", imgs=imgs.numpy(), masks=masks.numpy(), out=out.numpy(), aff=aff[:, 0].numpy())
+
+
+def golden_small_ops(ref):
+    g = torch.Generator().manual_seed(5)
+    a = torch.rand(30, 30, generator=g) + 0.01
+    _save("transmat.npz", a=a.numpy(), out=ref["compute_trans_mat"](a).numpy())
+
+    rng = np.random.default_rng(9)
+    cams, masks, thrs = [], [], []
+    for i in range(24):
+        h, w = (12, 14) if i % 2 else (20, 20)
+        lo = rng.random((h // 2 + 1, w // 2 + 1)).astype(np.float32)
+        cam = np.kron(lo, np.ones((2, 2), np.float32))[:h, :w] * rng.random((h, w)).astype(np.float32) ** 0.3
+        if i == 0:
+            cam[:] = 0
+        if i == 1:
+            cam[:] = 1
+        if i == 2:
+            cam[:] = 0; cam[-1, :] = 1        # component confined to the last row
+        thr = 0.4 if i % 3 else 0.7
+        box, cnt = ref["scoremap2bbox"](scoremap=cam, threshold=thr, multi_contour_eval=True)
+        m = np.zeros((h, w), np.float32)
+        for j in range(cnt):
+            x0, y0, x1, y1 = box[j]
+            m[y0:y1, x0:x1] = 1
+        pad = np.zeros((20, 20), np.float32); pad[:h, :w] = cam; cams.append(pad)
+        pm = np.zeros((20, 20), np.float32); pm[:h, :w] = m; masks.append(pm)
+        thrs.append((h, w, thr))
+    _save("bbox.npz", cams=np.stack(cams), masks=np.stack(masks), meta=np.array(thrs, dtype=np.float64))
+
+    refined = [torch.rand(6, 7, generator=g) * 3 - 1 for _ in range(3)]
+    outs = {}
+    for tag, (w, h) in {"up": (112, 96), "odd": (90, 70), "down": (5, 4)}.items():
+        outs[tag] = ref["generate_cam_label"](refined, [1, 2, 3], w, h)["refined_cam"].numpy()
+    _save("camlabel.npz", refined=torch.stack(refined).numpy(), **outs)
+
+    gts = [rng.integers(0, 21, (17, 19)).astype(np.int16) for _ in range(3)]
+    gts[0][:3] = 255
+    preds = [rng.integers(0, 21, (17, 19)).astype(np.int16) for _ in range(3)]
+    hist, sc = ref["evaluate"].scores(gts, preds, np.zeros((21, 21)))
+    _save("scores.npz", gts=np.stack(gts), preds=np.stack(preds), hist=hist,
+          summary=np.array([sc["pAcc"], sc["mAcc"], sc["miou"]]), iou=np.array([sc["iou"][i] for i in range(21)]))
+
+
+def golden_weclip(dataset, num_classes, n_fg, n_bg, subdir):
+    c = WECLIP_CASE
+    sd = synth.make_state_dict(c["weights_seed"], num_classes)
+    fg, bg = synth.make_text_features(c["text_seed"], n_fg, n_bg)
+    root = tempfile.mkdtemp()
+    rng = np.random.default_rng(c["label_seed"])
+    labs = []
+    for n in c["names"]:
+        ids = synth.draw_label_set(rng, n_fg)
+        lab = synth.make_label_map(rng, *c["label_hw"], ids)
+        synth.write_label_png(root, subdir, n, lab)
+        labs.append(lab)
+    img = synth.make_images(c["image_seed"], 2, c["H"], c["W"])
+    model = ref_harness.build_reference_model(sd, fg, bg, root, dataset, num_classes)
+    switch = 15000 if dataset == "voc" else 40000
+    runs = {"val": ("val", 0), "train": ("train", 0), "train_rfm": ("train", switch + 5)}
+    for tag, (mode, it) in runs.items():
+        model.iter_num = it
+        seg, cam, ap = model(img, list(c["names"]), mode=mode)
+        arrs = dict(seg=seg.detach().numpy(), attn_pred=ap.detach().numpy(), labels=np.stack(labs))
+        if cam is not None:
+            arrs["cam"] = cam.numpy().astype(np.int16)
+        _save(f"weclip_{dataset}_{tag}.npz", **arrs)
+    if dataset == "voc":
+        # encoder taps / attention and raw Grad-CAMs for image 0 (the pieces the kernels are diffed against)
+        from clip.clip_tool import generate_clip_fts, ClipOutputTarget
+        from oracle.weclip_oracle import label_ids_from_map
+        with torch.no_grad():
+            fts_all, attn_list = generate_clip_fts(img, model.encoder, require_all_fts=True)
+        ids = label_ids_from_map(labs[0])
+        text = torch.cat([fg[ids], bg], dim=0)
+        cams = []
+        for k in range(len(ids)):
+            cam_k, probs, attn_last = model.grad_cam(
+                input_tensor=[fts_all[-1][:, 0:1, :], text, c["H"], c["W"]], targets=[ClipOutputTarget(k)],
+                target_size=None)
+            cams.append(cam_k[0])
+        _save("weclip_voc_parts.npz", tap0=fts_all[0].numpy(), tap10=fts_all[-1].numpy(),
+              attn0=attn_list[0].numpy(), attn10=attn_list[-1].numpy(), cams0=np.stack(cams),
+              probs0=probs.detach().numpy(), attn_last0=attn_last.detach().numpy())
+
+
+def main():
+    assert ref_harness.available(), "/root/reference is required (build container only)"
+    os.makedirs(OUT, exist_ok=True)
+    torch.set_num_threads(8)
+    ref = ref_harness.reference_modules()
+    golden_par(ref)
+    golden_small_ops(ref)
+    golden_weclip("voc", 21, 20, 25, "SegmentationClassAug")
+    golden_weclip("coco", 81, 80, 23, os.path.join("SegmentationClass", "train"))
+
+
+if __name__ == "__main__":
+    main()
