@@ -1,0 +1,428 @@
+// tcgen05 GEMM kernel (sm_100a).  See gemm.cuh for the contract.
+//
+// One CTA per 128 x BN output tile, 192 threads, warp-specialised:
+//   warp 0   TMA producer   — cp.async.bulk.tensor (rank-4 maps, 128B swizzle, OOB zero-fill) into a STAGES-deep ring
+//   warp 1   MMA issuer     — one lane issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BN, K=16) x4 per k-block;
+//                             tcgen05.commit releases the smem stage / signals the epilogue; owns the TMEM allocation
+//   warps 2-5 epilogue      — tcgen05.ld 32x32b.x16 (thread = accumulator row), fused bias / activation / residual /
+//                             layout scatter, direct 128-bit global stores
+// Operands are K-major bf16 (A: [M,K], B: [N,K]); accumulators are fp32 in tensor memory (BN columns).
+#include "gemm.cuh"
+
+#include <cudaTypedefs.h>
+#include <mutex>
+#include <unordered_map>
+
+namespace wc {
+
+constexpr int BM = 128;
+constexpr int BK = 64;               // 64 bf16 = 128 B = one swizzle row
+constexpr int GEMM_THREADS = 192;
+
+// ---------------------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t done = 0;
+    const long long t0 = clock64();
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (done) break;
+        if (clock64() - t0 > 4000000000LL) {   // ~2 s: a protocol bug must fault, never hang the GPU
+            printf("wc gemm: mbarrier timeout (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x);
+            __trap();
+        }
+    }
+}
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major, 128B-swizzled shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
+//   [0,14) start address >> 4 | [16,30) leading byte offset >> 4 (unused for swizzled K-major, 1) |
+//   [32,46) stride byte offset >> 4 (8 rows * 128 B = 1024) | [46,48) version = 1 | [61,64) layout = SWIZZLE_128B (2)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// Instruction descriptor for kind::f16 (cute::UMMA::InstrDescriptor): D=f32, A=B=bf16, both K-major.
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Epilogue
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float apply_act(float x, int act) {
+    switch (act) {
+        case ACT_RELU: return fmaxf(x, 0.f);
+        case ACT_QUICKGELU: return x / (1.f + __expf(-1.702f * x));
+        case ACT_SIGMOID: return 1.f / (1.f + __expf(-x));
+        default: return x;
+    }
+}
+
+struct KernelArgs {
+    int M, N, K, nb0;
+    int a_b0, a_b1, b_b0, b_b1;   // 1 when the operand really has that batch dimension (else coordinate 0)
+    GemmEpilogue e;
+};
+
+__device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, float* v, int row, int col0, int b0, int b1, int bz) {
+    const GemmEpilogue& e = a.e;
+    const int ncol = min(16, a.N - col0);
+    if (e.mode == GM_STORE) {
+        const float* bias = e.bias ? e.bias + b0 * e.bias_bs0 + b1 * e.bias_bs1 + col0 : nullptr;
+        const float* resid = e.resid ? e.resid + b0 * e.resid_bs0 + b1 * e.resid_bs1 + (long)row * e.ldr + col0 : nullptr;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            if (j < ncol) {
+                float x = e.alpha * v[j];
+                if (bias) x += __ldg(bias + j);
+                x = apply_act(x, e.act);
+                if (resid) x += resid[j];
+                v[j] = x;
+            }
+        }
+        const long ob = b0 * e.out_bs0 + b1 * e.out_bs1;
+        if (e.out_trans) {
+            if (e.out_bf16) {
+                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + ob + (long)col0 * e.ldo + row;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) if (j < ncol) o[(long)j * e.ldo] = __float2bfloat16(v[j]);
+            } else {
+                float* o = reinterpret_cast<float*>(e.out) + ob + (long)col0 * e.ldo + row;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) if (j < ncol) o[(long)j * e.ldo] = v[j];
+            }
+        } else if (e.out_bf16) {
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + ob + (long)row * e.ldo + col0;
+            if (ncol == 16 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+                uint4 pk[2];
+                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                reinterpret_cast<uint4*>(o)[0] = pk[0];
+                reinterpret_cast<uint4*>(o)[1] = pk[1];
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) if (j < ncol) o[j] = __float2bfloat16(v[j]);
+            }
+        } else {
+            float* o = reinterpret_cast<float*>(e.out) + ob + (long)row * e.ldo + col0;
+            if (ncol == 16 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    reinterpret_cast<float4*>(o)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) if (j < ncol) o[j] = v[j];
+            }
+        }
+        if (e.out2) {
+            __nv_bfloat16* o = e.out2 + b0 * e.out2_bs0 + b1 * e.out2_bs1 + (long)row * e.ld2 + col0;
+            if (ncol == 16 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+                uint4 pk[2];
+                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                reinterpret_cast<uint4*>(o)[0] = pk[0];
+                reinterpret_cast<uint4*>(o)[1] = pk[1];
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) if (j < ncol) o[j] = __float2bfloat16(v[j]);
+            }
+        }
+    } else if (e.mode == GM_QKV) {
+        // clip/myAtt.py:199-201 (packed in-proj) + :257-268 (head split); q pre-scaled by 1/sqrt(hd) (:54).
+        const int E = e.heads * e.hd;
+        const int which = col0 / E, within = col0 - which * E;
+        const int head = within / e.hd, d0 = within - head * e.hd;
+        const int img = row / e.L, l = row - img * e.L;
+        const float* bias = e.bias + col0;
+        const float sc = (which == 0) ? e.qscale : 1.f;
+        uint4 pk[2];
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            h[j] = __floats2bfloat162_rn((v[2 * j] + __ldg(bias + 2 * j)) * sc, (v[2 * j + 1] + __ldg(bias + 2 * j + 1)) * sc);
+        const long hb = (long)img * e.heads + head;
+        __nv_bfloat16* dst = (which == 0) ? e.q : (which == 1) ? e.k : e.v;
+        if (dst) {
+            uint4* o = reinterpret_cast<uint4*>(dst + (hb * e.L + l) * e.hd + d0);
+            o[0] = pk[0];
+            o[1] = pk[1];
+        }
+        if (which == 2 && e.vt) {
+            __nv_bfloat16* o = e.vt + (hb * e.hd + d0) * (long)e.Lp + l;
+            const __nv_bfloat16* hv = reinterpret_cast<const __nv_bfloat16*>(pk);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) o[(long)j * e.Lp] = hv[j];
+        }
+    } else {   // GM_MUL_QGELU_GRAD
+        const int ab = e.aux_map ? e.aux_map[bz] : bz;
+        const __nv_bfloat16* u = e.aux + (long)ab * e.aux_bs + (long)row * e.ldaux + col0;
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + b0 * e.out_bs0 + b1 * e.out_bs1 + (long)row * e.ldo + col0;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            if (j < ncol) {
+                const float x = __bfloat162float(u[j]);
+                const float s = 1.f / (1.f + __expf(-1.702f * x));
+                o[j] = __float2bfloat16(v[j] * e.alpha * (s * (1.f + 1.702f * x * (1.f - s))));
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Kernel
+// ---------------------------------------------------------------------------------------------------
+template <int BN, int STAGES>
+struct SmemLayout {
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(GEMM_THREADS) gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA,
+                                                               const __grid_constant__ CUtensorMap mapB,
+                                                               const __grid_constant__ KernelArgs args) {
+    using SL = SmemLayout<BN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * SL::STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    const int bz = blockIdx.z, b0 = bz % args.nb0, b1 = bz / args.nb0;
+    const int num_kb = (args.K + BK - 1) / BK;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapB)) : "memory");
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(tmem_full_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (kb / STAGES) & 1;
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                mbar_expect_tx(&full_bar[s], SL::STAGE_BYTES);
+                uint8_t* sa = smem + s * SL::STAGE_BYTES;
+                tma_load_4d(sa, &mapA, &full_bar[s], kb * BK, m0, b0 * args.a_b0, b1 * args.a_b1);
+                tma_load_4d(sa + SL::A_BYTES, &mapB, &full_bar[s], kb * BK, n0, b0 * args.b_b0, b1 * args.b_b1);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc(BM, BN);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (kb / STAGES) & 1;
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + s * SL::STAGE_BYTES);
+                const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + SL::A_BYTES);
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k)   // +32 B per UMMA_K inside the 128 B swizzle row -> +2 in the >>4 field
+                    umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(tmem_full_bar);
+        }
+    } else {
+        const int q = warp & 3;                     // TMEM lane quarter this warp may access
+        const int row = m0 + q * 32 + lane;
+        mbar_wait(tmem_full_bar, 0);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+        for (int c = 0; c < BN / 16; ++c) {
+            const int col0 = n0 + c * 16;
+            if (col0 >= args.N) break;              // warp-uniform
+            float v[16];
+            tmem_ld16(taddr + c * 16, v);
+            if (row < args.M) epilogue_chunk(args, v, row, col0, b0, b1, bz);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, BN);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Host side: tensor maps (driver entry point resolved at run time: no link against libcuda) + launch
+// ---------------------------------------------------------------------------------------------------
+static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+    });
+    return fn;
+}
+
+struct MapKey {
+    const void* ptr; long rows, ld, bs0, bs1; int K, nb0, nb1, box_rows;
+    bool operator==(const MapKey& o) const {
+        return ptr == o.ptr && rows == o.rows && ld == o.ld && bs0 == o.bs0 && bs1 == o.bs1 && K == o.K &&
+               nb0 == o.nb0 && nb1 == o.nb1 && box_rows == o.box_rows;
+    }
+};
+struct MapKeyHash {
+    size_t operator()(const MapKey& k) const {
+        size_t h = reinterpret_cast<size_t>(k.ptr);
+        auto mix = [&](size_t v) { h ^= v + 0x9e3779b97f4a7c15ULL + (h << 6) + (h >> 2); };
+        mix(k.rows); mix(k.ld); mix(k.bs0); mix(k.bs1); mix(k.K); mix(k.nb0); mix(k.nb1); mix(k.box_rows);
+        return h;
+    }
+};
+
+static int make_map(CUtensorMap* out, const GemmOperand& op, int K, int nb0, int nb1, int box_rows, int* use_b0, int* use_b1) {
+    auto enc = get_encode();
+    if (!enc) return fail(WC_ERR_CUDA, "%s: cuTensorMapEncodeTiled entry point unavailable", __func__);
+    if ((reinterpret_cast<uintptr_t>(op.ptr) & 15) || (op.ld & 7) || (op.bs0 & 7) || (op.bs1 & 7))
+        return fail(WC_ERR_ARG, "%s: operand pointer/strides must be 16-byte aligned (ld=%ld)", __func__, op.ld);
+    *use_b0 = (nb0 > 1 && op.bs0 != 0);
+    *use_b1 = (nb1 > 1 && op.bs1 != 0);
+    thread_local std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+    MapKey key{op.ptr, op.rows, op.ld, op.bs0, op.bs1, K, nb0, nb1, box_rows};
+    auto it = cache.find(key);
+    if (it != cache.end()) { *out = it->second; return WC_OK; }
+    const cuuint64_t d2 = *use_b0 ? nb0 : 1, d3 = *use_b1 ? nb1 : 1;
+    cuuint64_t dims[4] = {(cuuint64_t)K, (cuuint64_t)op.rows, d2, d3};
+    const cuuint64_t row_bytes = (cuuint64_t)op.ld * 2;
+    const cuuint64_t s2 = *use_b0 ? (cuuint64_t)op.bs0 * 2 : row_bytes * (cuuint64_t)op.rows;
+    const cuuint64_t s3 = *use_b1 ? (cuuint64_t)op.bs1 * 2 : s2 * d2;
+    cuuint64_t strides[3] = {row_bytes, s2, s3};
+    cuuint32_t box[4] = {(cuuint32_t)BK, (cuuint32_t)box_rows, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<__nv_bfloat16*>(op.ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(WC_ERR_CUDA, "%s: cuTensorMapEncodeTiled failed (%ld) rows=%ld", __func__, (long)r, op.rows);
+    if (cache.size() > 4096) cache.clear();
+    cache.emplace(key, *out);
+    return WC_OK;
+}
+
+template <int BN, int STAGES>
+static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
+    using SL = SmemLayout<BN, STAGES>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        WC_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
+        attr_set = true;
+    }
+    CUtensorMap mA, mB;
+    KernelArgs ka;
+    ka.M = p.M; ka.N = p.N; ka.K = p.K; ka.nb0 = p.nb0; ka.e = p.epi;
+    int rc = make_map(&mA, p.A, p.K, p.nb0, p.nb1, BM, &ka.a_b0, &ka.a_b1);
+    if (rc) return rc;
+    rc = make_map(&mB, p.B, p.K, p.nb0, p.nb1, BN, &ka.b_b0, &ka.b_b1);
+    if (rc) return rc;
+    dim3 grid(ceil_div(p.M, BM), ceil_div(p.N, BN), p.nb0 * p.nb1);
+    gemm_tc_kernel<BN, STAGES><<<grid, GEMM_THREADS, SL::TOTAL, st>>>(mA, mB, ka);
+    WC_LAUNCH_CHECK();
+    return WC_OK;
+}
+
+int launch_gemm(const GemmProblem& p, cudaStream_t st) {
+    WC_CHECK_ARG(p.M > 0 && p.N > 0 && p.K > 0 && p.nb0 > 0 && p.nb1 > 0 && p.A.ptr && p.B.ptr);
+    WC_CHECK_ARG((long)p.nb0 * p.nb1 <= 65535);
+    if (p.epi.mode == GM_QKV) WC_CHECK_ARG(p.N % 16 == 0 && p.epi.hd % 16 == 0 && p.epi.bias);
+    if (p.N <= 32) return launch_cfg<32, 4>(p, st);
+    if (p.N <= 64) return launch_cfg<64, 4>(p, st);
+    return launch_cfg<128, 3>(p, st);
+}
+
+}  // namespace wc
+
+using namespace wc;
+
+// Generic test / micro-bench entry: out[b] = act(alpha * A[b] @ B[b]^T + bias) (+ resid), see include/weclip_b200.h.
+extern "C" int wc_gemm_bf16(const void* A, const void* B, void* out, const float* bias, const float* resid,
+                            int M, int N, int K, int batch, long lda, long ldb, long ldo, long a_bs, long b_bs, long o_bs,
+                            int out_bf16, int out_trans, int act, float alpha, void* stream) {
+    WC_CHECK_ARG(A && B && out);
+    GemmProblem p;
+    p.M = M; p.N = N; p.K = K; p.nb0 = batch; p.nb1 = 1;
+    p.A = {reinterpret_cast<const __nv_bfloat16*>(A), M, lda, a_bs, 0};
+    p.B = {reinterpret_cast<const __nv_bfloat16*>(B), N, ldb, b_bs, 0};
+    p.epi.mode = GM_STORE; p.epi.act = act; p.epi.alpha = alpha; p.epi.bias = bias;
+    p.epi.out = out; p.epi.out_bf16 = out_bf16; p.epi.out_trans = out_trans; p.epi.ldo = ldo; p.epi.out_bs0 = o_bs;
+    p.epi.resid = resid; p.epi.ldr = ldo; p.epi.resid_bs0 = o_bs;
+    return launch_gemm(p, as_stream(stream));
+}
