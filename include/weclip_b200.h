@@ -29,7 +29,7 @@ extern "C" {
 #define WC_ERR_WORKSPACE (-3)
 #define WC_ERR_UNSUPPORTED (-4)
 
-#define WC_ABI_VERSION 1
+#define WC_ABI_VERSION 3
 #define WC_PAR_MAX_DIL 8
 
 /* ABI version (bumped whenever a signature changes) and last error text. */
@@ -81,6 +81,105 @@ int wc_argmax_lut(const float* masks, const int64_t* lut, int64_t* labels,
 int wc_gemm_bf16(const void* A, const void* B, void* out, const float* bias, const float* resid,
                  int M, int N, int K, int batch, long lda, long ldb, long ldo, long a_bs, long b_bs, long o_bs,
                  int out_bf16, int out_trans, int act, float alpha, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Weights.  "bf16" pointers are __nv_bfloat16 row-major [out_features, in_features] (nn.Linear layout,
+ * K contiguous = the GEMM's B operand); biases / LayerNorm parameters are fp32.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct wc_block_weights {           /* one ResidualAttentionBlock, clip/model.py:191-214 */
+    const void* w_in;   const float* b_in;  /* attn.in_proj_weight [3E,E], in_proj_bias [3E] */
+    const void* w_out;  const float* b_out; /* attn.out_proj [E,E] */
+    const void* w_fc;   const float* b_fc;  /* mlp.c_fc [4E,E] */
+    const void* w_proj; const float* b_proj;/* mlp.c_proj [E,4E] */
+    const float *ln1_w, *ln1_b, *ln2_w, *ln2_b;
+} wc_block_weights;
+
+typedef struct wc_vit_weights {             /* VisionTransformer, clip/model.py:246-262 */
+    const void* conv1_w;                    /* bf16 [768, 3*16*16] = conv1.weight flattened */
+    const float* class_emb;                 /* [768] */
+    const float* pos_emb;                   /* [pos_grid^2+1, 768] */
+    int pos_grid;                           /* 14 */
+    const float *ln_pre_w, *ln_pre_b;
+    wc_block_weights blocks[12];
+    const float *ln_post_w, *ln_post_b;
+    const float* proj;                      /* fp32 [768,512] */
+    /* block 12, transposed copies for the Grad-CAM input-gradient GEMMs (dX = dY @ W): */
+    const void* w_proj_t;                   /* bf16 [3072,768] = c_proj.weight^T */
+    const void* w_fc_t;                     /* bf16 [768,3072] = c_fc.weight^T */
+    const void* w_out_t;                    /* bf16 [768,768]  = out_proj.weight^T */
+    const float* w_in_f32;                  /* fp32 [2304,768] = in_proj_weight */
+    float logit_scale_exp;                  /* exp(logit_scale), clip/model.py:422 */
+} wc_vit_weights;
+
+typedef struct wc_decoder_weights {         /* SegFormerHead (segformer_head.py:49-80) + DecoderTransformer */
+    const void* fuse_w1; const float* fuse_b1;   /* bf16 [11,256,768], fp32 [11,256]  (linears_modulelist.i.proj) */
+    const void* fuse_w2; const float* fuse_b2;   /* bf16 [11,256,256], fp32 [11,256]  (.proj_2) */
+    const void* fuse_wf; const float* fuse_bf;   /* bf16 [256,2816],   fp32 [256]     (linear_fuse, 1x1 conv) */
+    wc_block_weights blocks[3];                  /* width 256, 8 heads (TransDecoder.py:104-110) */
+    const void* pred_w;  const float* pred_b;    /* bf16 [C,256], fp32 [C]            (linear_pred, 1x1 conv) */
+    int num_classes;
+} wc_decoder_weights;
+
+/* ------------------------------------------------------------------------------------------------
+ * Encoder: patch embed, class token, resized positional embedding, ln_pre, 11 of the 12 blocks
+ * (clip/model.py:264-287 + :225-243 via clip_tool.py:31-41 / CLIP.encode_image :387-390).
+ *   img       fp32 [N,3,H,W]
+ *   taps      bf16 [11, N*L, 768]   block outputs F_0..F_10 (token-major, image-major rows; L = h*w+1)
+ *   x_last    fp32 [N*L, 768]       F_10 in fp32 (input of block 12 / Grad-CAM)
+ *   attn_avg  fp32 [n_attn(+slack), N, L, L]  head-averaged attention (myAtt.py:323-326) of the LAST n_attn
+ *             encoder blocks, oldest first; may be NULL when n_attn == 0
+ * ---------------------------------------------------------------------------------------------- */
+size_t wc_encoder_workspace_bytes(int N, int H, int W);
+int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, int H, int W, void* taps, float* x_last,
+                   float* attn_avg, int n_attn, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Decoder: 11 per-layer MLPs + concat + linear_fuse (segformer_head.py:69-80), attn_pred = sigmoid(F^T F)
+ * (model_attn_aff_voc.py:134-137), 3 transformer blocks + linear_pred (TransDecoder.py:113-125).
+ *   seg fp32 [N,C,h,w]; attn_pred fp32 [N,P,P]; fts (optional, may be NULL) fp32 [N*P,256] token-major */
+size_t wc_decoder_workspace_bytes(int N, int h, int w, int num_classes);
+int wc_decoder_fwd(const wc_decoder_weights* w, const void* taps, int N, int h, int wd, float* seg, float* attn_pred,
+                   float* fts, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Stand-alone pieces exported for the numerics tests (same kernels the two calls above launch). */
+int wc_layernorm(const float* x, const float* w, const float* b, void* out_bf16, float* out_f32, long rows, int E,
+                 void* stream);
+int wc_softmax_headmean(const float* S, void* P_bf16, float* avg, int n_img, int heads, int L, int Lp, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Grad-CAM head.  Replaces CLIP.forward_last_layer (clip/model.py:407-429) + GradCAM.__call__
+ * (pytorch_grad_cam/base_cam.py:62-108,116-154, grad_cam.py:16-23, activations_and_gradients.py:19-37) as
+ * looped per class by perform_single_voc_cam / perform_single_coco_cam (clip/clip_tool.py:139-147, :261-268).
+ * Block 12 runs forward ONCE per image; the input-gradient to the ln_1 output is evaluated analytically and
+ * batched over all (image, class) instances.
+ *   x11        fp32 [N*L,768]    F_10 (x_last of wc_encoder_fwd)
+ *   text       fp32 [sumT,512]   per image: its K_i foreground rows (fg_text_features[label_ids]) followed by
+ *                                the background rows (clip_tool.py:134-137); rows need not be normalised
+ *   text_off_host int [N+1]      row offsets into text;  k_off_host int [N+1]  instance offsets (K_i = diff)
+ *   cams       fp32 [sumK,h*w]   raw Grad-CAMs, ReLU'd and min-max normalised twice
+ *   attn_last  fp32 [N,L,L]      head-averaged attention of block 12
+ *   probs      fp32 [sumT] or NULL  softmax(logit_scale * cos) per image
+ * ---------------------------------------------------------------------------------------------- */
+size_t wc_gradcam_workspace_bytes(int N, int h, int w, int total_inst, int max_k);
+int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int h, int wd, const float* text,
+               const int* text_off_host, const int* k_off_host, float* cams, float* attn_last, float* probs,
+               void* workspace, size_t workspace_bytes, void* stream);
+
+/* Attention-affinity refinement.  Replaces clip/clip_tool.py:152-191 (VOC) / :274-314 (COCO): RFM layer
+ * selection against attn_pred (use_rfm=1; nl = 6 VOC / 10 COCO) or plain mean of the nl maps (use_rfm=0,
+ * nl = 8), compute_trans_mat (:64-80), scoremap2bbox box mask (clip/utils.py:115-142; box_thr 0.4 / 0.7) and
+ * cam' = (T * mask) @ cam.
+ *   attn fp32 [nl,N,L,L] (oldest first, block 12 last); attn_pred fp32 [N,P,P]; cams / cams_refined fp32 [sumK,P];
+ *   box_masks fp32 [sumK,P] or NULL (exported for the parity tests). */
+size_t wc_affinity_workspace_bytes(int N, int h, int w, int total_inst, int nl);
+int wc_affinity_refine(const float* attn, int nl, const float* attn_pred, int N, int h, int wd, int use_rfm,
+                       const float* cams, const int* k_off_host, float box_thr, float* cams_refined,
+                       float* box_masks, void* workspace, size_t workspace_bytes, void* stream);
+
+/* generate_cam_label (clip/clip_tool.py:202-216: per-class min-max + cv2.resize INTER_LINEAR to Wc x Hc) and the
+ * background channel (model_attn_aff_voc.py:162-163).  out fp32 [sumK+N, Hc, Wc]: image i owns channels
+ * [k_off[i]+i, k_off[i+1]+i+1) = (bg, class 1..K_i) — the packed layout wc_par_fwd takes.  stats_ws: 2*sumK floats. */
+int wc_cam_upsample_bg(const float* cams, const int* k_off_host, int N, int h, int wd, int Hc, int Wc, float bg_pow,
+                       float* out, float* stats_ws, void* stream);
 
 #ifdef __cplusplus
 }

@@ -48,9 +48,8 @@ def lib() -> ctypes.CDLL:
                 "(there is no CPU / PyTorch fallback for the hot path)")
         _lib = ctypes.CDLL(LIB_PATH)
         _lib.wc_last_error.restype = c_char_p
-        _lib.wc_par_workspace_bytes.restype = c_size_t
-        for name in ("wc_gemm_workspace_bytes", "wc_ctx_workspace_bytes"):
-            if hasattr(_lib, name):
+        for name in declared_symbols():
+            if name.endswith("_workspace_bytes") and hasattr(_lib, name):
                 getattr(_lib, name).restype = c_size_t
     return _lib
 

@@ -1,0 +1,373 @@
+// Attention-affinity CAM refinement + CAM post-processing for sm_100a (memory-bound kernels).
+//
+// Replaces clip/clip_tool.py:152-191 (RFM layer selection, compute_trans_mat :64-80, box mask via
+// clip/utils.py:115-142 scoremap2bbox, masked transition) and :202-216 generate_cam_label +
+// model_attn_aff_voc.py:160-163 (cv2 bilinear upsample, background channel).
+//
+// compute_trans_mat is evaluated in factored form.  With B the fused attention [P,P], the three
+// (column, row) normalisation rounds only rescale rows and columns, T = diag(r) B diag(c), so each round is a
+// matrix-vector product with B (r = 1/(B c), c = 1/(B^T r)); the symmetrised square is never materialised:
+//     cam' = T_s (T_s v),  T_s x = (r * (B (c*x)) + c * (B^T (r*x))) / 2,  v = mask * cam
+// which is algebraically (T_s T_s) v of clip_tool.py:73-76,186-191 with 4 passes over B instead of a P^3 GEMM.
+#include "common.cuh"
+
+#include <math.h>
+
+namespace wc {
+
+constexpr int AFF_MAX_IMG = 64;
+constexpr int AFF_KMAX = 8;
+
+struct AffTable {
+    int n;
+    int k_off[AFF_MAX_IMG + 1];
+};
+
+__device__ __forceinline__ const float* attn_row(const float* attn, int l, int img, int N, int L, int i) {
+    return attn + (((size_t)l * N + img) * L + 1 + i) * L + 1;   // [:, 1:, 1:] (clip_tool.py:155)
+}
+
+// sums[img][l] = sum_ij W_l[i][j] (l < nl), sums[img][nl] = sum_ij attn_pred[i][j]
+__global__ void __launch_bounds__(256) aff_layer_sums_kernel(const float* __restrict__ attn, const float* __restrict__ ap,
+                                                             double* __restrict__ sums, int nl, int N, int L) {
+    __shared__ float red[32];
+    const int P = L - 1, img = blockIdx.z, l = blockIdx.y, r0 = blockIdx.x * 32, r1 = min(r0 + 32, P);
+    float s = 0.f;
+    for (int i = r0; i < r1; ++i) {
+        const float* row = (l < nl) ? attn_row(attn, l, img, N, L, i) : ap + ((size_t)img * P + i) * P;
+        for (int j = threadIdx.x; j < P; j += 256) s += row[j];
+    }
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) atomicAdd(sums + (size_t)img * (nl + 1) + l, (double)s);
+}
+
+// B = RFM fusion (clip_tool.py:158-170) or the plain layer mean (:173-174); also the first column sums.
+__global__ void __launch_bounds__(256) aff_build_kernel(const float* __restrict__ attn, const float* __restrict__ ap,
+                                                        const double* __restrict__ sums, float* __restrict__ Bm,
+                                                        float* __restrict__ colz, int nl, int N, int L, int use_rfm) {
+    __shared__ float wl[16];
+    const int P = L - 1, img = blockIdx.y, r0 = blockIdx.x * 16, r1 = min(r0 + 16, P);
+    if (threadIdx.x == 0) {
+        if (use_rfm) {
+            // attn_diff_l = sum(seg_attn - W_l); keep layers with diff <= mean(diff)
+            float d[16], mean = 0.f;
+            const double sap = sums[(size_t)img * (nl + 1) + nl];
+            for (int l = 0; l < nl; ++l) { d[l] = (float)(sap - sums[(size_t)img * (nl + 1) + l]); mean += d[l]; }
+            mean /= (float)nl;
+            float cnt = 0.f;
+            for (int l = 0; l < nl; ++l) { wl[l] = (d[l] <= mean) ? 1.f : 0.f; cnt += wl[l]; }
+            for (int l = 0; l < nl; ++l) wl[l] /= (cnt + 1e-5f);
+        } else {
+            for (int l = 0; l < nl; ++l) wl[l] = 1.f / (float)nl;
+        }
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < P; j += 256) {
+        float cs = 0.f;
+        for (int i = r0; i < r1; ++i) {
+            float v = 0.f;
+            for (int l = 0; l < nl; ++l) v = fmaf(wl[l], attn_row(attn, l, img, N, L, i)[j], v);
+            if (use_rfm) v *= ap[((size_t)img * P + i) * P + j];
+            Bm[((size_t)img * P + i) * P + j] = v;
+            cs += v;
+        }
+        atomicAdd(colz + (size_t)img * P + j, cs);
+    }
+}
+
+// r_i = 1 / sum_j B_ij / z_j      (row normalisation with c = 1/z)
+__global__ void __launch_bounds__(256) aff_row_pass_kernel(const float* __restrict__ Bm, const float* __restrict__ z,
+                                                           float* __restrict__ r, int P) {
+    const int img = blockIdx.y, i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (i >= P) return;
+    const float* row = Bm + ((size_t)img * P + i) * P;
+    const float* zz = z + (size_t)img * P;
+    float s = 0.f;
+    for (int j = lane; j < P; j += 32) s += row[j] / zz[j];
+    s = warp_sum(s);
+    if (lane == 0) r[(size_t)img * P + i] = 1.f / s;
+}
+
+// z_j += sum_{i in chunk} r_i B_ij      (column sums of diag(r) B)
+__global__ void __launch_bounds__(256) aff_col_pass_kernel(const float* __restrict__ Bm, const float* __restrict__ r,
+                                                           float* __restrict__ z, int P) {
+    __shared__ float rr[32];
+    const int img = blockIdx.y, r0 = blockIdx.x * 32, n = min(32, P - r0);
+    if (threadIdx.x < n) rr[threadIdx.x] = r[(size_t)img * P + r0 + threadIdx.x];
+    __syncthreads();
+    for (int j = threadIdx.x; j < P; j += 256) {
+        float s = 0.f;
+        for (int i = 0; i < n; ++i) s = fmaf(rr[i], Bm[((size_t)img * P + r0 + i) * P + j], s);
+        atomicAdd(z + (size_t)img * P + j, s);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Box mask (clip/utils.py:115-142 + clip_tool.py:179-185), one CTA per class instance, grid <= 64x64 cells:
+// uint8 quantisation, strict '>' threshold against int(thr*max), 8-connected component labelling by iterated
+// min-label propagation in shared memory, per-component bounding box, cv2's min(x+w, W-1) clip and the
+// exclusive-upper slice fill.  Output v = mask * cam (the masked CAM that multiplies the transition matrix).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) box_mask_kernel(const float* __restrict__ cams, float* __restrict__ v,
+                                                       float* __restrict__ mask_out, int h, int w, double thr) {
+    extern __shared__ int sm[];
+    const int P = h * w, tid = threadIdx.x, inst = blockIdx.x;
+    int* label = sm;                 // [P]
+    int* x0 = sm + P; int* x1 = x0 + P; int* y0 = x1 + P; int* y1 = y0 + P;
+    unsigned char* msk = reinterpret_cast<unsigned char*>(y1 + P);   // [P]
+    __shared__ int s_max, s_changed;
+    const float* cam = cams + (size_t)inst * P;
+    if (tid == 0) s_max = 0;
+    __syncthreads();
+    int lmax = 0;
+    for (int p = tid; p < P; p += 256) lmax = max(lmax, (int)(unsigned char)(int)(cam[p] * 255.f));
+    atomicMax(&s_max, lmax);
+    __syncthreads();
+    const int t = (int)(thr * (double)s_max);
+    for (int p = tid; p < P; p += 256) {
+        const int u8 = (int)(unsigned char)(int)(cam[p] * 255.f);
+        label[p] = (u8 > t) ? p : -1;
+        x0[p] = w; x1[p] = -1; y0[p] = h; y1[p] = -1; msk[p] = 0;
+    }
+    __syncthreads();
+    for (int iter = 0; iter < 4 * P; ++iter) {
+        if (tid == 0) s_changed = 0;
+        __syncthreads();
+        for (int p = tid; p < P; p += 256) {
+            int l = label[p];
+            if (l < 0) continue;
+            const int y = p / w, x = p - y * w;
+            int m = l;
+            for (int dy = -1; dy <= 1; ++dy)
+                for (int dx = -1; dx <= 1; ++dx) {
+                    const int yy = y + dy, xx = x + dx;
+                    if (yy < 0 || yy >= h || xx < 0 || xx >= w) continue;
+                    const int q = label[yy * w + xx];
+                    if (q >= 0) m = min(m, q);
+                }
+            m = min(m, label[m]);           // pointer jumping
+            if (m < l) { label[p] = m; s_changed = 1; }
+        }
+        __syncthreads();
+        if (!s_changed) break;
+        __syncthreads();
+    }
+    for (int p = tid; p < P; p += 256) {
+        const int l = label[p];
+        if (l < 0) continue;
+        const int y = p / w, x = p - y * w;
+        atomicMin(&x0[l], x); atomicMax(&x1[l], x); atomicMin(&y0[l], y); atomicMax(&y1[l], y);
+    }
+    __syncthreads();
+    for (int p = tid; p < P; p += 256) {
+        if (label[p] != p) continue;   // component root
+        const int xa = x0[p], ya = y0[p], xb = min(x1[p] + 1, w - 1), yb = min(y1[p] + 1, h - 1);
+        for (int y = ya; y < yb; ++y)
+            for (int x = xa; x < xb; ++x) msk[y * w + x] = 1;
+    }
+    __syncthreads();
+    for (int p = tid; p < P; p += 256) {
+        const float m = msk[p] ? 1.f : 0.f;
+        v[(size_t)inst * P + p] = m * cam[p];
+        if (mask_out) mask_out[(size_t)inst * P + p] = m;
+    }
+}
+
+// out_ik = 0.5 * r_i * sum_j B_ij (x_jk / z_j)          (row half of T_s x; writes)
+__global__ void __launch_bounds__(256) tsym_row_kernel(const float* __restrict__ Bm, const float* __restrict__ r,
+                                                       const float* __restrict__ z, const float* __restrict__ x,
+                                                       float* __restrict__ out, const __grid_constant__ AffTable tab,
+                                                       int P, int kbase) {
+    const int img = blockIdx.y, i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int k0 = tab.k_off[img] + kbase, kn = min(AFF_KMAX, tab.k_off[img + 1] - k0);
+    if (i >= P || kn <= 0) return;
+    const float* row = Bm + ((size_t)img * P + i) * P;
+    const float* zz = z + (size_t)img * P;
+    float acc[AFF_KMAX];
+#pragma unroll
+    for (int k = 0; k < AFF_KMAX; ++k) acc[k] = 0.f;
+    for (int j = lane; j < P; j += 32) {
+        const float b = row[j] / zz[j];
+#pragma unroll
+        for (int k = 0; k < AFF_KMAX; ++k)
+            if (k < kn) acc[k] = fmaf(b, x[(size_t)(k0 + k) * P + j], acc[k]);
+    }
+    const float ri = r[(size_t)img * P + i];
+#pragma unroll
+    for (int k = 0; k < AFF_KMAX; ++k) {
+        if (k < kn) {
+            const float s = warp_sum(acc[k]);
+            if (lane == 0) out[(size_t)(k0 + k) * P + i] = 0.5f * ri * s;
+        }
+    }
+}
+
+// out_jk += 0.5 / z_j * sum_{i in chunk} B_ij r_i x_ik   (column half of T_s x; accumulates)
+__global__ void __launch_bounds__(256) tsym_col_kernel(const float* __restrict__ Bm, const float* __restrict__ r,
+                                                       const float* __restrict__ z, const float* __restrict__ x,
+                                                       float* __restrict__ out, const __grid_constant__ AffTable tab,
+                                                       int P, int kbase) {
+    __shared__ float rx[32][AFF_KMAX];
+    const int img = blockIdx.y, r0 = blockIdx.x * 32, n = min(32, P - r0);
+    const int k0 = tab.k_off[img] + kbase, kn = min(AFF_KMAX, tab.k_off[img + 1] - k0);
+    if (kn <= 0) return;
+    for (int t = threadIdx.x; t < 32 * AFF_KMAX; t += 256) {
+        const int i = t / AFF_KMAX, k = t % AFF_KMAX;
+        rx[i][k] = (i < n && k < kn) ? r[(size_t)img * P + r0 + i] * x[(size_t)(k0 + k) * P + r0 + i] : 0.f;
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < P; j += 256) {
+        float acc[AFF_KMAX];
+#pragma unroll
+        for (int k = 0; k < AFF_KMAX; ++k) acc[k] = 0.f;
+        for (int i = 0; i < n; ++i) {
+            const float b = Bm[((size_t)img * P + r0 + i) * P + j];
+#pragma unroll
+            for (int k = 0; k < AFF_KMAX; ++k) acc[k] = fmaf(b, rx[i][k], acc[k]);
+        }
+        const float cj = 0.5f / z[(size_t)img * P + j];
+#pragma unroll
+        for (int k = 0; k < AFF_KMAX; ++k)
+            if (k < kn) atomicAdd(out + (size_t)(k0 + k) * P + j, cj * acc[k]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// generate_cam_label (clip_tool.py:202-216): per class min-max (scale_cam_image) then cv2.resize INTER_LINEAR
+// (half-pixel centres, border taps clamped with zero weight), and the background channel
+// bg = (1 - max_k)^cam_bg_thres in front (model_attn_aff_voc.py:162-163).  Output packed [sumK + N, Hc, Wc]:
+// image i owns channels [k_off[i]+i, k_off[i+1]+i+1): bg first, then its K classes.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) cam_minmax_kernel(const float* __restrict__ cams, float* __restrict__ stats, int P) {
+    __shared__ float red[32];
+    const int inst = blockIdx.x;
+    const float* c = cams + (size_t)inst * P;
+    float mn = INFINITY;
+    for (int p = threadIdx.x; p < P; p += 256) mn = fminf(mn, c[p]);
+    mn = block_min(mn, red);
+    float mx = -INFINITY;
+    for (int p = threadIdx.x; p < P; p += 256) mx = fmaxf(mx, c[p] - mn);
+    mx = block_max(mx, red);
+    if (threadIdx.x == 0) { stats[2 * inst] = mn; stats[2 * inst + 1] = 1e-7f + mx; }
+}
+
+__global__ void __launch_bounds__(256) cam_upsample_bg_kernel(const float* __restrict__ cams, const float* __restrict__ stats,
+                                                              float* __restrict__ out, const __grid_constant__ AffTable tab,
+                                                              int h, int w, int Hc, int Wc, float bg_pow) {
+    const int X = blockIdx.x * 32 + threadIdx.x, Y = blockIdx.y * 8 + threadIdx.y, img = blockIdx.z;
+    if (X >= Wc || Y >= Hc) return;
+    const int P = h * w;
+    // cv2 resize.cpp: fx = (float)((dx+0.5)*scale - 0.5); sx = floor(fx); fx -= sx; clamp with zero weight
+    float fx = (float)(((double)X + 0.5) * ((double)w / (double)Wc) - 0.5);
+    float fy = (float)(((double)Y + 0.5) * ((double)h / (double)Hc) - 0.5);
+    int sx = (int)floorf(fx), sy = (int)floorf(fy);
+    fx -= sx; fy -= sy;
+    if (sx < 0) { sx = 0; fx = 0.f; }
+    if (sx >= w - 1) { sx = w - 1; fx = 0.f; }
+    if (sy < 0) { sy = 0; fy = 0.f; }
+    if (sy >= h - 1) { sy = h - 1; fy = 0.f; }
+    const int sx1 = min(sx + 1, w - 1), sy1 = min(sy + 1, h - 1);
+    const int k0 = tab.k_off[img], K = tab.k_off[img + 1] - k0;
+    const size_t hw = (size_t)Hc * Wc;
+    float* o = out + (size_t)(k0 + img) * hw + (size_t)Y * Wc + X;
+    float mx = -INFINITY;
+    for (int k = 0; k < K; ++k) {
+        const float* c = cams + (size_t)(k0 + k) * P;
+        const float mn = stats[2 * (k0 + k)], den = stats[2 * (k0 + k) + 1];
+        const float v00 = (c[sy * w + sx] - mn) / den, v01 = (c[sy * w + sx1] - mn) / den;
+        const float v10 = (c[sy1 * w + sx] - mn) / den, v11 = (c[sy1 * w + sx1] - mn) / den;
+        const float r0 = v00 * (1.f - fx) + v01 * fx, r1 = v10 * (1.f - fx) + v11 * fx;
+        const float val = r0 * (1.f - fy) + r1 * fy;
+        o[(size_t)(k + 1) * hw] = val;
+        mx = fmaxf(mx, val);
+    }
+    o[0] = (bg_pow == 1.f) ? (1.f - mx) : powf(1.f - mx, bg_pow);
+}
+
+}  // namespace wc
+
+using namespace wc;
+
+extern "C" size_t wc_affinity_workspace_bytes(int N, int h, int w, int total_inst, int nl) {
+    const size_t P = (size_t)h * w;
+    return sizeof(float) * ((size_t)N * P * P + 3 * (size_t)N * P + 2 * (size_t)total_inst * P) +
+           sizeof(double) * (size_t)N * (nl + 1) + 2048;
+}
+
+extern "C" int wc_affinity_refine(const float* attn, int nl, const float* attn_pred, int N, int h, int wd, int use_rfm,
+                                  const float* cams, const int* k_off_host, float box_thr, float* cams_refined,
+                                  float* box_masks, void* workspace, size_t workspace_bytes, void* stream) {
+    WC_CHECK_ARG(attn && cams && k_off_host && cams_refined && workspace && nl >= 1 && nl <= 16);
+    WC_CHECK_ARG(N > 0 && N <= AFF_MAX_IMG && h > 0 && wd > 0 && (!use_rfm || attn_pred));
+    cudaStream_t st = as_stream(stream);
+    const int P = h * wd, L = P + 1, total = k_off_host[N];
+    WC_CHECK_ARG((size_t)P * 21 + 64 <= 200 * 1024);
+    if (workspace_bytes < wc_affinity_workspace_bytes(N, h, wd, total, nl))
+        return fail(WC_ERR_WORKSPACE, "%s: workspace too small (%ld bytes)", __func__, (long)workspace_bytes);
+    AffTable tab; tab.n = N;
+    int max_k = 0;
+    for (int i = 0; i <= N; ++i) tab.k_off[i] = k_off_host[i];
+    for (int i = 0; i < N; ++i) max_k = max(max_k, k_off_host[i + 1] - k_off_host[i]);
+    uint8_t* wsb = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~(uintptr_t)255);
+    double* sums = reinterpret_cast<double*>(wsb);
+    float* Bm = reinterpret_cast<float*>(wsb + (((size_t)N * (nl + 1) * sizeof(double) + 255) & ~(size_t)255));
+    float* z = Bm + (size_t)N * P * P;
+    float* r = z + (size_t)N * P;
+    float* v0 = r + (size_t)N * P;
+    float* v1 = v0 + (size_t)total * P;
+    const size_t NP = (size_t)N * P;
+    if (use_rfm) {
+        WC_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * N * (nl + 1), st));
+        aff_layer_sums_kernel<<<dim3(ceil_div(P, 32), nl + 1, N), 256, 0, st>>>(attn, attn_pred, sums, nl, N, L);
+        WC_LAUNCH_CHECK();
+    }
+    WC_CUDA(cudaMemsetAsync(z, 0, sizeof(float) * NP, st));
+    aff_build_kernel<<<dim3(ceil_div(P, 16), N), 256, 0, st>>>(attn, attn_pred, sums, Bm, z, nl, N, L, use_rfm);
+    WC_LAUNCH_CHECK();
+    for (int round = 0; round < 3; ++round) {   // clip_tool.py:67-72
+        if (round > 0) {
+            WC_CUDA(cudaMemsetAsync(z, 0, sizeof(float) * NP, st));
+            aff_col_pass_kernel<<<dim3(ceil_div(P, 32), N), 256, 0, st>>>(Bm, r, z, P);
+            WC_LAUNCH_CHECK();
+        }
+        aff_row_pass_kernel<<<dim3(ceil_div(P, 8), N), 256, 0, st>>>(Bm, z, r, P);
+        WC_LAUNCH_CHECK();
+    }
+    // box masks -> v0 = mask * cam
+    const size_t box_smem = (size_t)P * 21 + 16;
+    static bool attr_set = false;
+    if (!attr_set) {
+        WC_CUDA(cudaFuncSetAttribute(box_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set = true;
+    }
+    box_mask_kernel<<<total, 256, box_smem, st>>>(cams, v0, box_masks, h, wd, (double)box_thr);
+    WC_LAUNCH_CHECK();
+    // cam' = T_s (T_s v0)
+    const float* src = v0;
+    float* dsts[2] = {v1, cams_refined};
+    for (int pass = 0; pass < 2; ++pass) {
+        for (int kb = 0; kb < max_k; kb += AFF_KMAX) {
+            tsym_row_kernel<<<dim3(ceil_div(P, 8), N), 256, 0, st>>>(Bm, r, z, src, dsts[pass], tab, P, kb);
+            WC_LAUNCH_CHECK();
+            tsym_col_kernel<<<dim3(ceil_div(P, 32), N), 256, 0, st>>>(Bm, r, z, src, dsts[pass], tab, P, kb);
+            WC_LAUNCH_CHECK();
+        }
+        src = v1;
+    }
+    return WC_OK;
+}
+
+extern "C" int wc_cam_upsample_bg(const float* cams, const int* k_off_host, int N, int h, int wd, int Hc, int Wc,
+                                  float bg_pow, float* out, float* stats_ws, void* stream) {
+    WC_CHECK_ARG(cams && k_off_host && out && stats_ws && N > 0 && N <= AFF_MAX_IMG && h > 0 && wd > 0 && Hc > 0 && Wc > 0);
+    cudaStream_t st = as_stream(stream);
+    AffTable tab; tab.n = N;
+    for (int i = 0; i <= N; ++i) tab.k_off[i] = k_off_host[i];
+    const int total = k_off_host[N];
+    cam_minmax_kernel<<<total, 256, 0, st>>>(cams, stats_ws, h * wd);
+    WC_LAUNCH_CHECK();
+    cam_upsample_bg_kernel<<<dim3(ceil_div(Wc, 32), ceil_div(Hc, 8), N), dim3(32, 8), 0, st>>>(cams, stats_ws, out, tab, h, wd,
+                                                                                              Hc, Wc, bg_pow);
+    WC_LAUNCH_CHECK();
+    return WC_OK;
+}

@@ -125,16 +125,39 @@ __device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, float* v, in
     if (e.mode == GM_STORE) {
         const float* bias = e.bias ? e.bias + b0 * e.bias_bs0 + b1 * e.bias_bs1 + col0 : nullptr;
         const float* resid = e.resid ? e.resid + b0 * e.resid_bs0 + b1 * e.resid_bs1 + (long)row * e.ldr + col0 : nullptr;
+        __nv_bfloat16* o2 = e.out2 ? e.out2 + b0 * e.out2_bs0 + b1 * e.out2_bs1 + (long)row * e.ld2 + col0 : nullptr;
+        const bool o2_vec = o2 && ncol == 16 && (reinterpret_cast<uintptr_t>(o2) & 15) == 0;
+        auto store_o2 = [&]() {
+            if (o2_vec) {
+                uint4 pk[2];
+                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                reinterpret_cast<uint4*>(o2)[0] = pk[0];
+                reinterpret_cast<uint4*>(o2)[1] = pk[1];
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) if (j < ncol) o2[j] = __float2bfloat16(v[j]);
+            }
+        };
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
             if (j < ncol) {
                 float x = e.alpha * v[j];
                 if (bias) x += __ldg(bias + j);
-                x = apply_act(x, e.act);
+                v[j] = x;
+            }
+        }
+        if (o2 && e.out2_preact) store_o2();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            if (j < ncol) {
+                float x = apply_act(v[j], e.act);
                 if (resid) x += resid[j];
                 v[j] = x;
             }
         }
+        if (o2 && !e.out2_preact) store_o2();
         const long ob = b0 * e.out_bs0 + b1 * e.out_bs1;
         if (e.out_trans) {
             if (e.out_bf16) {
@@ -168,20 +191,6 @@ __device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, float* v, in
             } else {
 #pragma unroll
                 for (int j = 0; j < 16; ++j) if (j < ncol) o[j] = v[j];
-            }
-        }
-        if (e.out2) {
-            __nv_bfloat16* o = e.out2 + b0 * e.out2_bs0 + b1 * e.out2_bs1 + (long)row * e.ld2 + col0;
-            if (ncol == 16 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
-                uint4 pk[2];
-                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(pk);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-                reinterpret_cast<uint4*>(o)[0] = pk[0];
-                reinterpret_cast<uint4*>(o)[1] = pk[1];
-            } else {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) if (j < ncol) o[j] = __float2bfloat16(v[j]);
             }
         }
     } else if (e.mode == GM_QKV) {

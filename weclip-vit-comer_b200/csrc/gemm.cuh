@@ -29,7 +29,7 @@ struct GemmEpilogue {
     const float* bias = nullptr; long bias_bs0 = 0, bias_bs1 = 0;
     void* out = nullptr; int out_bf16 = 0; int out_trans = 0; long ldo = 0, out_bs0 = 0, out_bs1 = 0;
     const float* resid = nullptr; long ldr = 0, resid_bs0 = 0, resid_bs1 = 0;
-    __nv_bfloat16* out2 = nullptr; long ld2 = 0, out2_bs0 = 0, out2_bs1 = 0;
+    __nv_bfloat16* out2 = nullptr; long ld2 = 0, out2_bs0 = 0, out2_bs1 = 0; int out2_preact = 0;   // bf16 copy (before act+resid if preact)
     const __nv_bfloat16* aux = nullptr; long ldaux = 0; long aux_bs = 0; const int* aux_map = nullptr;
     // GM_QKV
     __nv_bfloat16 *q = nullptr, *k = nullptr, *v = nullptr, *vt = nullptr;

@@ -1,0 +1,484 @@
+// Grad-CAM head for sm_100a: block 12 forward + pooled cosine-softmax head + the ANALYTIC input-gradient
+// backward to the ln_1 output, batched over (image, class) instances.
+//
+// Replaces: CLIP.forward_last_layer (clip/model.py:407-429), GradCAM/BaseCAM.forward
+// (pytorch_grad_cam/base_cam.py:62-108,116-154), get_cam_weights (grad_cam.py:16-23), the ln_1 hooks
+// (activations_and_gradients.py:19-37), reshape_transform (model_attn_aff_voc.py:23-30), ClipOutputTarget
+// (clip_tool.py:20-26) and scale_cam_image (utils/image.py:51-61), as driven per class by clip_tool.py:139-147.
+//
+// Math.  With A = ln_1(x11) the hook tensor, only the q/k/v branch carries gradient
+// to A, and Grad-CAM only needs  w = mean_{patch rows}(dp_k/dA) = (1/P) * [sum_rows dQ | sum_rows dK | sum_rows dV] @ W_in.
+// The three row sums follow from the attention backward without materialising dQ/dK/dV:
+//     dP = dO V^T,  delta_i = sum_j dP_ij P_ij,  dS = P * (dP - delta)
+//     sum_{i>=1} dQs_i = sum_j (sum_{i>=1} dS_ij) K_j          (column sums of dS over patch rows)
+//     sum_{j>=1} dK_j  = sum_i (-dS_i0) Qs_i                   (rows of dS sum to zero)
+//     sum_{j>=1} dV_j  = sum_i (1 - P_i0) dO_i
+// so the only L x L work per (instance, head) is the dP GEMM (tcgen05) and one fused reduction pass.
+#include "encoder.cuh"
+
+#include <math.h>
+
+namespace wc {
+
+constexpr int GC_MAX_IMG = 64;
+constexpr int GC_MAX_INST = 64;      // instances processed per backward chunk
+constexpr int GC_MAX_T = 128;        // text rows per image (VOC 20+25, COCO 80+23)
+constexpr int GC_E = 768, GC_HEADS = 12, GC_HD = 64, GC_EMB = 512;
+
+struct ImgTable {
+    int n;
+    int text_off[GC_MAX_IMG + 1];
+    int k_off[GC_MAX_IMG + 1];
+};
+struct InstTable {
+    int n;                   // instances in this chunk
+    int inst0;               // global index of the first instance of the chunk
+    short img[GC_MAX_INST];  // image of each instance
+};
+
+// ---------------------------------------------------------------------------------------------------
+// ln_post + column sums over the patch rows (clip/model.py:411-412).  msum[img][c] += sum_rows LN(x2)[row][c]
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) lnpost_mean_kernel(const float* __restrict__ x2, const float* __restrict__ gw,
+                                                          const float* __restrict__ gb, float* __restrict__ msum, int L) {
+    __shared__ float part[8][GC_E];
+    const int img = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float acc[24];
+#pragma unroll
+    for (int i = 0; i < 24; ++i) acc[i] = 0.f;
+    for (int r = 0; r < 4; ++r) {
+        const int l = 1 + blockIdx.x * 32 + warp * 4 + r;
+        if (l >= L) break;
+        const float4* xr = reinterpret_cast<const float4*>(x2 + ((size_t)img * L + l) * GC_E);
+        float4 v[6];
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) { v[i] = xr[lane + 32 * i]; s += v[i].x + v[i].y + v[i].z + v[i].w; }
+        const float mean = warp_sum(s) / GC_E;
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+            q += a * a + b * b + c * c + d * d;
+        }
+        const float rstd = rsqrtf(warp_sum(q) / GC_E + 1e-5f);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            const float4 ww = __ldg(reinterpret_cast<const float4*>(gw) + lane + 32 * i);
+            const float4 bb = __ldg(reinterpret_cast<const float4*>(gb) + lane + 32 * i);
+            acc[4 * i + 0] += (v[i].x - mean) * rstd * ww.x + bb.x;
+            acc[4 * i + 1] += (v[i].y - mean) * rstd * ww.y + bb.y;
+            acc[4 * i + 2] += (v[i].z - mean) * rstd * ww.z + bb.z;
+            acc[4 * i + 3] += (v[i].w - mean) * rstd * ww.w + bb.w;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) part[warp][(lane + 32 * i) * 4 + j] = acc[4 * i + j];
+    __syncthreads();
+    for (int c = threadIdx.x; c < GC_E; c += 256) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += part[w][c];
+        atomicAdd(msum + (size_t)img * GC_E + c, s);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Pooled head forward + its backward to d(mean-pooled ln_post output) for every class of the image
+// (clip/model.py:411-427 and the softmax / L2-norm / proj Jacobians).  One CTA (512 threads) per image.
+//   dm[inst][c] = d p_k / d y[l][c] for every patch row l  ( = (proj @ dg)[c] / P )
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msum, const float* __restrict__ proj,
+                                                   const float* __restrict__ text, const __grid_constant__ ImgTable tab,
+                                                   float logit_scale, int P, float* __restrict__ dm,
+                                                   float* __restrict__ probs_out) {
+    __shared__ float mvec[GC_E];
+    __shared__ float g[GC_EMB], dgh[GC_EMB];
+    __shared__ float logit[GC_MAX_T], tnorm[GC_MAX_T], dl[GC_MAX_T];
+    __shared__ float red[32];
+    const int img = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int t0 = tab.text_off[img], T = tab.text_off[img + 1] - t0;
+    const int K = tab.k_off[img + 1] - tab.k_off[img];
+    for (int c = tid; c < GC_E; c += 512) mvec[c] = msum[(size_t)img * GC_E + c] / (float)P;
+    __syncthreads();
+    {   // g = mean @ proj  (model.py:414-415)
+        float s = 0.f;
+        for (int c = 0; c < GC_E; ++c) s = fmaf(mvec[c], __ldg(proj + (size_t)c * GC_EMB + tid), s);
+        g[tid] = s;
+    }
+    __syncthreads();
+    const float gn = sqrtf(block_sum(g[tid] * g[tid], red));
+    __syncthreads();
+    g[tid] = g[tid] / gn;          // normalised image feature (model.py:420)
+    __syncthreads();
+    for (int t = warp; t < T; t += 16) {   // cosine logits (model.py:421-424)
+        const float* tr = text + (size_t)(t0 + t) * GC_EMB;
+        float dot = 0.f, nn = 0.f;
+        for (int j = lane; j < GC_EMB; j += 32) { const float v = __ldg(tr + j); dot = fmaf(v, g[j], dot); nn = fmaf(v, v, nn); }
+        dot = warp_sum(dot); nn = warp_sum(nn);
+        if (lane == 0) { tnorm[t] = sqrtf(nn); logit[t] = logit_scale * dot / sqrtf(nn); }
+    }
+    __syncthreads();
+    if (warp == 0) {   // softmax over the T texts (model.py:427)
+        float mx = -INFINITY;
+        for (int t = lane; t < T; t += 32) mx = fmaxf(mx, logit[t]);
+        mx = warp_max(mx);
+        float s = 0.f;
+        for (int t = lane; t < T; t += 32) s += expf(logit[t] - mx);
+        s = warp_sum(s);
+        for (int t = lane; t < T; t += 32) logit[t] = expf(logit[t] - mx) / s;   // now probabilities
+    }
+    __syncthreads();
+    if (probs_out) for (int t = tid; t < T; t += 512) probs_out[t0 + t] = logit[t];
+    for (int k = 0; k < K; ++k) {
+        const int inst = tab.k_off[img] + k;
+        const float pk = logit[k];
+        for (int t = tid; t < T; t += 512) dl[t] = pk * ((t == k ? 1.f : 0.f) - logit[t]);   // d p_k / d logit_t
+        __syncthreads();
+        float s = 0.f;   // d p_k / d ghat_j
+        for (int t = 0; t < T; ++t) s = fmaf(dl[t] / tnorm[t], __ldg(text + (size_t)(t0 + t) * GC_EMB + tid), s);
+        s *= logit_scale;
+        const float dot = block_sum(s * g[tid], red);
+        dgh[tid] = (s - g[tid] * dot) / gn;          // through the L2 normalisation
+        __syncthreads();
+        for (int c = warp; c < GC_E; c += 16) {      // d / d mean = proj @ dg ; every patch row gets 1/P of it
+            const float* pr = proj + (size_t)c * GC_EMB;
+            float a = 0.f;
+            for (int j = lane; j < GC_EMB; j += 32) a = fmaf(__ldg(pr + j), dgh[j], a);
+            a = warp_sum(a);
+            if (lane == 0) dm[(size_t)inst * GC_E + c] = a / (float)P;
+        }
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// LayerNorm input-gradient.  out[r] = add[r] + rstd * (g - mean(g) - xhat * mean(g*xhat)),  g = gamma * dy.
+// dy is either a matrix [rows,768] (dy_mat) or one vector per instance broadcast over the patch rows with the
+// class-token row receiving zero (dy_vec; ln_post feeds only x[:,1:], model.py:412).  One warp per row.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                     const float* __restrict__ dy_mat, const float* __restrict__ dy_vec,
+                                                     const float* __restrict__ add, float* __restrict__ out_f,
+                                                     __nv_bfloat16* __restrict__ out_bf, const __grid_constant__ InstTable it,
+                                                     int L) {
+    const long row = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= (long)it.n * L) return;
+    const int inst = (int)(row / L), l = (int)(row % L);
+    const float4* xr = reinterpret_cast<const float4*>(x + ((size_t)it.img[inst] * L + l) * GC_E);
+    float4 v[6], gg[6];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) { v[i] = xr[lane + 32 * i]; s += v[i].x + v[i].y + v[i].z + v[i].w; }
+    const float mean = warp_sum(s) / GC_E;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        v[i].x -= mean; v[i].y -= mean; v[i].z -= mean; v[i].w -= mean;
+        q += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+    }
+    const float rstd = rsqrtf(warp_sum(q) / GC_E + 1e-5f);
+    const bool zero = (dy_vec != nullptr && l == 0);
+    const float4* dyr = dy_mat ? reinterpret_cast<const float4*>(dy_mat + (size_t)row * GC_E)
+                               : reinterpret_cast<const float4*>(dy_vec + (size_t)(it.inst0 + inst) * GC_E);
+    float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        const float4 w = __ldg(reinterpret_cast<const float4*>(gamma) + lane + 32 * i);
+        float4 d = zero ? make_float4(0.f, 0.f, 0.f, 0.f) : dyr[lane + 32 * i];
+        v[i].x *= rstd; v[i].y *= rstd; v[i].z *= rstd; v[i].w *= rstd;      // xhat
+        gg[i] = make_float4(w.x * d.x, w.y * d.y, w.z * d.z, w.w * d.w);
+        c1 += gg[i].x + gg[i].y + gg[i].z + gg[i].w;
+        c2 += gg[i].x * v[i].x + gg[i].y * v[i].y + gg[i].z * v[i].z + gg[i].w * v[i].w;
+    }
+    c1 = warp_sum(c1) / GC_E;
+    c2 = warp_sum(c2) / GC_E;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        const int c4 = lane + 32 * i;
+        float4 o;
+        o.x = rstd * (gg[i].x - c1 - v[i].x * c2);
+        o.y = rstd * (gg[i].y - c1 - v[i].y * c2);
+        o.z = rstd * (gg[i].z - c1 - v[i].z * c2);
+        o.w = rstd * (gg[i].w - c1 - v[i].w * c2);
+        if (add) {
+            const float4 a = reinterpret_cast<const float4*>(add + (size_t)row * GC_E)[c4];
+            o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+        }
+        if (out_f) reinterpret_cast<float4*>(out_f + (size_t)row * GC_E)[c4] = o;
+        if (out_bf) {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t*>(&lo);
+            pk.y = *reinterpret_cast<uint32_t*>(&hi);
+            reinterpret_cast<uint2*>(out_bf + (size_t)row * GC_E)[c4] = pk;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Fused softmax-backward reduction.  For (instance, head, 32-row chunk):  delta_i, dS = P*(dP-delta),
+//   colsum[j] += sum_{i>=1 in chunk} dS_ij ;  ds0[i] = dS_i0.
+// dP fp32 [n_inst*12, L, Lp] (chunk-local instances), P bf16 [N*12, L, Lp] (per image).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) attn_bwd_reduce_kernel(const float* __restrict__ dP, const __nv_bfloat16* __restrict__ Pm,
+                                                              float* __restrict__ colsum, float* __restrict__ ds0,
+                                                              const __grid_constant__ InstTable it, int L, int Lp) {
+    extern __shared__ float colacc[];   // [L]
+    __shared__ float red[32];
+    const int inst = blockIdx.z, h = blockIdx.y, tid = threadIdx.x;
+    const int img = it.img[inst];
+    for (int c = tid; c < L; c += 256) colacc[c] = 0.f;
+    const int r0 = blockIdx.x * 32, r1 = min(r0 + 32, L);
+    for (int i = r0; i < r1; ++i) {
+        const float* dp = dP + ((size_t)(inst * GC_HEADS + h) * L + i) * Lp;
+        const __nv_bfloat16* p = Pm + ((size_t)(img * GC_HEADS + h) * L + i) * Lp;
+        float d = 0.f;
+        for (int c = tid; c < L; c += 256) d = fmaf(dp[c], __bfloat162float(p[c]), d);
+        d = block_sum(d, red);
+        for (int c = tid; c < L; c += 256) {
+            const float ds = __bfloat162float(p[c]) * (dp[c] - d);
+            if (i >= 1) colacc[c] += ds;
+            if (c == 0) ds0[(size_t)(inst * GC_HEADS + h) * L + i] = ds;
+        }
+    }
+    __syncthreads();
+    float* cs = colsum + (size_t)(inst * GC_HEADS + h) * L;
+    for (int c = tid; c < L; c += 256) atomicAdd(cs + c, colacc[c]);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Row sums of dQ, dK, dV over the patch tokens -> dqkv[inst][2304] (see file header).  One CTA per (head, inst).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) qkv_grad_sum_kernel(const float* __restrict__ colsum, const float* __restrict__ ds0,
+                                                           const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k,
+                                                           const __nv_bfloat16* __restrict__ Pm, const __nv_bfloat16* __restrict__ dO,
+                                                           float* __restrict__ dqkv, const __grid_constant__ InstTable it,
+                                                           int L, int Lp, float qscale) {
+    __shared__ float part[3][4][GC_HD];
+    const int h = blockIdx.x, inst = blockIdx.y, d = threadIdx.x & 63, grp = threadIdx.x >> 6;
+    const int img = it.img[inst];
+    const size_t hb = (size_t)(img * GC_HEADS + h);
+    const float* cs = colsum + (size_t)(inst * GC_HEADS + h) * L;
+    const float* d0 = ds0 + (size_t)(inst * GC_HEADS + h) * L;
+    float gq = 0.f, gk = 0.f, gv = 0.f;
+    for (int i = grp; i < L; i += 4) {
+        gq = fmaf(cs[i], __bfloat162float(k[(hb * L + i) * GC_HD + d]), gq);
+        gk = fmaf(-d0[i], __bfloat162float(q[(hb * L + i) * GC_HD + d]), gk);
+        const float pi0 = __bfloat162float(Pm[(hb * L + i) * Lp]);
+        gv = fmaf(1.f - pi0, __bfloat162float(dO[((size_t)inst * L + i) * GC_E + h * GC_HD + d]), gv);
+    }
+    part[0][grp][d] = gq; part[1][grp][d] = gk; part[2][grp][d] = gv;
+    __syncthreads();
+    if (grp < 3) {
+        const float s = part[grp][0][d] + part[grp][1][d] + part[grp][2][d] + part[grp][3][d];
+        dqkv[(size_t)inst * 3 * GC_E + grp * GC_E + h * GC_HD + d] = (grp == 0) ? s * qscale : s;
+    }
+}
+
+// w[inst][c] = (1/P) * sum_r dqkv[inst][r] * W_in[r][c]   (mean over patch tokens of the hooked gradient, grad_cam.py:23)
+__global__ void __launch_bounds__(128) cam_weight_kernel(const float* __restrict__ dqkv, const float* __restrict__ w_in,
+                                                         float* __restrict__ wvec, int P) {
+    __shared__ float dq[3 * GC_E];
+    const int inst = blockIdx.y, c = blockIdx.x * 128 + threadIdx.x;
+    for (int r = threadIdx.x; r < 3 * GC_E; r += 128) dq[r] = dqkv[(size_t)inst * 3 * GC_E + r];
+    __syncthreads();
+    float s = 0.f;
+#pragma unroll 8
+    for (int r = 0; r < 3 * GC_E; ++r) s = fmaf(dq[r], __ldg(w_in + (size_t)r * GC_E + c), s);
+    wvec[(size_t)inst * GC_E + c] = s / (float)P;
+}
+
+// cam = relu(sum_c w_c A_c) over the patch tokens, then scale_cam_image twice (base_cam.py:55-59,144-145,150-154).
+__global__ void __launch_bounds__(256) cam_kernel(const float* __restrict__ A32, const float* __restrict__ wvec,
+                                                  float* __restrict__ cams, const __grid_constant__ InstTable it, int L) {
+    extern __shared__ float cam[];   // [P]
+    __shared__ float wv[GC_E];
+    __shared__ float red[32];
+    const int inst = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int P = L - 1, img = it.img[inst];
+    for (int c = tid; c < GC_E; c += 256) wv[c] = wvec[(size_t)(it.inst0 + inst) * GC_E + c];
+    __syncthreads();
+    for (int p = warp; p < P; p += 8) {
+        const float* a = A32 + ((size_t)img * L + 1 + p) * GC_E;
+        float s = 0.f;
+        for (int c = lane; c < GC_E; c += 32) s = fmaf(wv[c], a[c], s);
+        s = warp_sum(s);
+        if (lane == 0) cam[p] = fmaxf(s, 0.f);
+    }
+    __syncthreads();
+    for (int rep = 0; rep < 2; ++rep) {
+        float mn = INFINITY;
+        for (int p = tid; p < P; p += 256) mn = fminf(mn, cam[p]);
+        mn = block_min(mn, red);
+        float mx = -INFINITY;
+        for (int p = tid; p < P; p += 256) mx = fmaxf(mx, cam[p] - mn);
+        mx = block_max(mx, red);
+        const float den = 1e-7f + mx;
+        for (int p = tid; p < P; p += 256) cam[p] = (cam[p] - mn) / den;
+        __syncthreads();
+    }
+    float* o = cams + (size_t)(it.inst0 + inst) * P;
+    for (int p = tid; p < P; p += 256) o[p] = cam[p];
+}
+
+// ---------------------------------------------------------------------------------------------------
+struct GcLayout {
+    // forward (per call)
+    float *a32, *x1, *x2, *S, *msum, *dm, *dqkv, *wvec;
+    bf16 *a, *q, *k, *v, *vt, *P, *o, *u, *upre;
+    // backward (per chunk of <= chunk instances)
+    float *dx2, *da2, *dP, *colsum, *ds0;
+    bf16 *dx2b, *dh, *dx1b, *dO;
+};
+
+static void gc_layout(Arena& ar, GcLayout& g, int N, int L, int total_inst, int chunk) {
+    const long M = (long)N * L, Lp = round8(L), E = GC_E;
+    g.a32 = ar.get<float>(M * E); g.x1 = ar.get<float>(M * E); g.x2 = ar.get<float>(M * E);
+    g.S = ar.get<float>((long)N * GC_HEADS * L * Lp);
+    g.msum = ar.get<float>((long)N * E); g.dm = ar.get<float>((long)total_inst * E);
+    g.dqkv = ar.get<float>((long)total_inst * 3 * E); g.wvec = ar.get<float>((long)total_inst * E);
+    g.a = ar.get<bf16>(M * E); g.q = ar.get<bf16>(M * E); g.k = ar.get<bf16>(M * E); g.v = ar.get<bf16>(M * E);
+    g.vt = ar.get<bf16>((long)N * GC_HEADS * GC_HD * Lp);
+    g.P = ar.get<bf16>((long)N * GC_HEADS * L * Lp);
+    g.o = ar.get<bf16>(M * E); g.u = ar.get<bf16>(M * 4 * E); g.upre = ar.get<bf16>(M * 4 * E);
+    const long R = (long)chunk * L;
+    g.dx2 = ar.get<float>(R * E); g.da2 = ar.get<float>(R * E);
+    g.dP = ar.get<float>((long)chunk * GC_HEADS * L * Lp);
+    g.colsum = ar.get<float>((long)chunk * GC_HEADS * L); g.ds0 = ar.get<float>((long)chunk * GC_HEADS * L);
+    g.dx2b = ar.get<bf16>(R * E); g.dh = ar.get<bf16>(R * 4 * E); g.dx1b = ar.get<bf16>(R * E); g.dO = ar.get<bf16>(R * E);
+}
+
+// instances per backward chunk: 16 (bounds the dP scratch), but never less than the largest image's class count
+static int chunk_size(int total_inst, int max_k) {
+    int c = total_inst < 16 ? total_inst : 16;
+    if (c < max_k) c = max_k;
+    return c < 1 ? 1 : c;
+}
+
+}  // namespace wc
+
+using namespace wc;
+
+extern "C" size_t wc_gradcam_workspace_bytes(int N, int h, int w, int total_inst, int max_k) {
+    Arena ar(nullptr, 0);
+    GcLayout g;
+    gc_layout(ar, g, N, h * w + 1, total_inst, chunk_size(total_inst, max_k));
+    return ar.off + 512;
+}
+
+extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int h, int wd, const float* text,
+                          const int* text_off_host, const int* k_off_host, float* cams, float* attn_last, float* probs,
+                          void* workspace, size_t workspace_bytes, void* stream) {
+    WC_CHECK_ARG(w && x11 && text && text_off_host && k_off_host && cams && attn_last && workspace);
+    WC_CHECK_ARG(N > 0 && N <= GC_MAX_IMG && h > 0 && wd > 0);
+    cudaStream_t st = as_stream(stream);
+    const int P = h * wd, L = P + 1, E = GC_E;
+    const long M = (long)N * L, Lp = round8(L);
+    ImgTable tab; tab.n = N;
+    for (int i = 0; i <= N; ++i) { tab.text_off[i] = text_off_host[i]; tab.k_off[i] = k_off_host[i]; }
+    const int total = k_off_host[N];
+    int max_k = 0;
+    for (int i = 0; i < N; ++i) {
+        const int K = k_off_host[i + 1] - k_off_host[i], T = text_off_host[i + 1] - text_off_host[i];
+        WC_CHECK_ARG(K >= 1 && K <= T && T <= GC_MAX_T);
+        max_k = K > max_k ? K : max_k;
+    }
+    const int chunk = chunk_size(total, max_k);
+    WC_CHECK_ARG(chunk <= GC_MAX_INST);
+    WC_CHECK_ARG(L * (int)sizeof(float) <= 48 * 1024);
+    Arena ar(workspace, workspace_bytes);
+    GcLayout g;
+    gc_layout(ar, g, N, L, total, chunk);
+    if (!ar.ok) return fail(WC_ERR_WORKSPACE, "%s: workspace too small (%ld bytes)", __func__, (long)workspace_bytes);
+    int rc;
+    // ---- block 12 forward, keeping what the backward needs (clip/model.py:408)
+    {
+        BlockBuffers b{};
+        b.x_in = x11; b.x_mid = g.x1; b.x_out = g.x2;
+        b.a = g.a; b.a_f32 = g.a32; b.q = g.q; b.k = g.k; b.v = g.v; b.vt = g.vt; b.S = g.S; b.P = g.P; b.o = g.o;
+        b.u = g.u; b.u_pre = g.upre; b.attn_avg = attn_last;
+        if ((rc = run_block(w->blocks[11], b, N, L, E, GC_HEADS, st))) return rc;
+    }
+    // ---- pooled head + its Jacobian for every (image, class)
+    WC_CUDA(cudaMemsetAsync(g.msum, 0, sizeof(float) * N * E, st));
+    lnpost_mean_kernel<<<dim3(ceil_div(P, 32), N), 256, 0, st>>>(g.x2, w->ln_post_w, w->ln_post_b, g.msum, L);
+    WC_LAUNCH_CHECK();
+    head_kernel<<<N, 512, 0, st>>>(g.msum, w->proj, text, tab, w->logit_scale_exp, P, g.dm, probs);
+    WC_LAUNCH_CHECK();
+    // ---- backward, in chunks of whole images holding <= chunk instances
+    const float qscale = 1.f / sqrtf((float)GC_HD);
+    int img0 = 0;
+    while (img0 < N) {
+        int img1 = img0, n_inst = 0;
+        while (img1 < N && n_inst + (k_off_host[img1 + 1] - k_off_host[img1]) <= chunk) {
+            n_inst += k_off_host[img1 + 1] - k_off_host[img1];
+            ++img1;
+        }
+        if (img1 == img0) return fail(WC_ERR_UNSUPPORTED, "%s: more than %ld classes in one image", __func__, (long)chunk);
+        InstTable it; it.n = n_inst; it.inst0 = k_off_host[img0];
+        for (int i = img0, c = 0; i < img1; ++i)
+            for (int k = k_off_host[i]; k < k_off_host[i + 1]; ++k) it.img[c++] = (short)i;
+        const long R = (long)n_inst * L;
+        const unsigned ln_grid = (unsigned)ceil_div(R, 8L);
+        // ln_post backward (dy = dm broadcast over patch rows, class row zero)
+        ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x2, w->ln_post_w, nullptr, g.dm, nullptr, g.dx2, g.dx2b, it, L);
+        WC_LAUNCH_CHECK();
+        // c_proj^T and the QuickGELU derivative (model.py:198-203); per image because the saved pre-activation
+        // u_pre belongs to the image, shared by its classes
+        for (int i = img0; i < img1; ++i) {
+            const int li = k_off_host[i] - it.inst0, K = k_off_host[i + 1] - k_off_host[i];
+            GemmProblem p; p.M = L; p.N = 4 * E; p.K = E; p.nb0 = K;
+            p.A = GemmOperand{g.dx2b + (long)li * L * E, L, E, (long)L * E, 0};
+            p.B = GemmOperand{reinterpret_cast<const bf16*>(w->w_proj_t), 4 * E, E, 0, 0};
+            p.epi.mode = GM_MUL_QGELU_GRAD; p.epi.out = g.dh + (long)li * L * 4 * E; p.epi.ldo = 4 * E;
+            p.epi.out_bs0 = (long)L * 4 * E; p.epi.aux = g.upre + (long)i * L * 4 * E; p.epi.ldaux = 4 * E; p.epi.aux_bs = 0;
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
+        {   // c_fc^T
+            GemmProblem p; p.M = (int)R; p.N = E; p.K = 4 * E;
+            p.A = GemmOperand{g.dh, R, 4 * E, 0, 0};
+            p.B = GemmOperand{reinterpret_cast<const bf16*>(w->w_fc_t), E, 4 * E, 0, 0};
+            p.epi.out = g.da2; p.epi.ldo = E;
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
+        // ln_2 backward + the residual branch: dx1 = dx2 + LN2'(da2)
+        ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x1, w->blocks[11].ln2_w, g.da2, nullptr, g.dx2, nullptr, g.dx1b, it, L);
+        WC_LAUNCH_CHECK();
+        {   // out_proj^T (myAtt.py:321)
+            GemmProblem p; p.M = (int)R; p.N = E; p.K = E;
+            p.A = GemmOperand{g.dx1b, R, E, 0, 0};
+            p.B = GemmOperand{reinterpret_cast<const bf16*>(w->w_out_t), E, E, 0, 0};
+            p.epi.out = g.dO; p.epi.out_bf16 = 1; p.epi.ldo = E;
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
+        // dP = dO V^T per head; V is shared by the classes of an image
+        for (int i = img0; i < img1; ++i) {
+            const int li = k_off_host[i] - it.inst0, K = k_off_host[i + 1] - k_off_host[i];
+            GemmProblem p; p.M = L; p.N = L; p.K = GC_HD; p.nb0 = GC_HEADS; p.nb1 = K;
+            p.A = GemmOperand{g.dO + (long)li * L * E, L, E, GC_HD, (long)L * E};
+            p.B = GemmOperand{g.v + (long)i * GC_HEADS * L * GC_HD, L, GC_HD, (long)L * GC_HD, 0};
+            p.epi.out = g.dP + (long)li * GC_HEADS * L * Lp; p.epi.ldo = Lp; p.epi.out_bs0 = (long)L * Lp;
+            p.epi.out_bs1 = (long)GC_HEADS * L * Lp;
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
+        WC_CUDA(cudaMemsetAsync(g.colsum, 0, sizeof(float) * n_inst * GC_HEADS * L, st));
+        attn_bwd_reduce_kernel<<<dim3(ceil_div(L, 32), GC_HEADS, n_inst), 256, sizeof(float) * L, st>>>(
+            g.dP, g.P, g.colsum, g.ds0, it, L, (int)Lp);
+        WC_LAUNCH_CHECK();
+        qkv_grad_sum_kernel<<<dim3(GC_HEADS, n_inst), 256, 0, st>>>(g.colsum, g.ds0, g.q, g.k, g.P, g.dO,
+                                                                    g.dqkv + (long)it.inst0 * 3 * E, it, L, (int)Lp, qscale);
+        WC_LAUNCH_CHECK();
+        cam_weight_kernel<<<dim3(E / 128, n_inst), 128, 0, st>>>(g.dqkv + (long)it.inst0 * 3 * E, w->w_in_f32,
+                                                                 g.wvec + (long)it.inst0 * E, P);
+        WC_LAUNCH_CHECK();
+        cam_kernel<<<n_inst, 256, sizeof(float) * P, st>>>(g.a32, g.wvec, cams, it, L);
+        WC_LAUNCH_CHECK();
+        img0 = img1;
+    }
+    (void)M;
+    return WC_OK;
+}

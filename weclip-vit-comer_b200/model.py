@@ -1,0 +1,165 @@
+"""WeCLIP model wrapper — CUDA (sm_100a) drop-in for WeCLIP_model/model_attn_aff_voc.py:60-175 and its COCO twin
+model_attn_aff_coco.py:56-170.
+
+Same ``forward(img, img_names, mode) -> (seg, cam_labels, attn_pred)`` contract, same attributes callers touch
+(``iter_num``, ``par``, ``cam_bg_thres``, ``root_path``, ``fg_text_features``, ``bg_text_features``) and the same
+``state_dict`` key names (``encoder.visual.*``, ``decoder_fts_fuse.*``, ``decoder.*``, ``par.kernel``).
+
+Out of scope by SURVEY.md §2 (init-time only): the CLIP text tower / tokenizer.  ``fg_text_features`` /
+``bg_text_features`` are therefore inputs (ctor kwargs or attributes), not computed here.
+Forward-only: ``seg`` / ``attn_pred`` carry no autograd graph (training the decoder through this module is
+SURVEY.md §8f-2, "next").
+"""
+from __future__ import annotations
+
+import os
+from collections import OrderedDict
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib
+from .engine import Engine
+from .par import PAR, argmax_lut
+
+_DATASETS = {
+    # window, box threshold, RFM switch iteration, label sub-directory   (clip_tool.py:155,179 / :277,301;
+    # model_attn_aff_voc.py:86,146 / model_attn_aff_coco.py:78,135,141)
+    "voc": dict(window=6, box_thr=0.4, switch=15000, subdir="SegmentationClassAug"),
+    "coco": dict(window=10, box_thr=0.7, switch=40000, subdir=os.path.join("SegmentationClass", "train")),
+}
+
+
+class LabelReader:
+    """clip_tool.py:111-118: the image-level label set is read from the ground-truth PNG inside forward().
+    The decoded (ids, height, width) are memoised per path + mtime: msc+flip evaluation opens the same PNG
+    2 x n_scales times per dataset image."""
+
+    def __init__(self):
+        self._cache: Dict[str, Tuple[float, List[int], int, int]] = {}
+
+    def __call__(self, path: str):
+        from PIL import Image
+        mtime = os.path.getmtime(path)          # FileNotFoundError like the reference's Image.open
+        hit = self._cache.get(path)
+        if hit is not None and hit[0] == mtime:
+            return hit[1], hit[2], hit[3]
+        lab = np.asarray(Image.open(path))
+        ids = (np.unique(lab) - 1).tolist()     # uint8 wrap: 0 -> 255 (bg), 255 -> 254 (ignore)
+        ids = [int(i) for i in ids if i not in (254, 255)]
+        if len(self._cache) > 4096:
+            self._cache.clear()
+        self._cache[path] = (mtime, ids, lab.shape[0], lab.shape[1])
+        return ids, lab.shape[0], lab.shape[1]
+
+
+class WeCLIP(nn.Module):
+    def __init__(self, num_classes=None, clip_model=None, embedding_dim=256, in_channels=512, dataset_root_path=None,
+                 device="cuda", dataset: str = "voc", fg_text_features: Optional[torch.Tensor] = None,
+                 bg_text_features: Optional[torch.Tensor] = None, state_dict: Optional[dict] = None):
+        """``clip_model``: path to a state dict with the reference's CLIP keys (``visual.*``) — or pass a full
+        WeCLIP ``state_dict`` directly.  ``dataset`` selects the VOC / COCO constants."""
+        super().__init__()
+        assert embedding_dim == 256, "the decoder kernels are instantiated for embedding_dim=256"
+        self.num_classes = num_classes
+        self.embedding_dim = embedding_dim
+        self.in_channels = in_channels
+        self.dataset = dataset
+        self.cfg = _DATASETS[dataset]
+        self.root_path = os.path.join(dataset_root_path or "", self.cfg["subdir"].split(os.sep)[0])
+        self._label_subdir = os.sep.join(self.cfg["subdir"].split(os.sep)[1:])
+        self.cam_bg_thres = 1
+        self.iter_num = 0
+        self.require_all_fts = True
+        self.fg_text_features = fg_text_features
+        self.bg_text_features = bg_text_features
+        self.par = PAR(num_iter=20, dilations=[1, 2, 4, 8, 12, 24])
+        self.label_reader = LabelReader()
+        self._device = torch.device(device)
+        self._sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+        self.engine: Optional[Engine] = None
+        if state_dict is None and clip_model is not None:
+            clip_sd = torch.load(clip_model, map_location="cpu")
+            state_dict = {("encoder." + k.replace("module.", "")): v for k, v in clip_sd.items()
+                          if k.replace("module.", "").startswith(("visual.", "logit_scale"))}
+        if state_dict is not None:
+            self.load_state_dict(state_dict, strict=False)
+
+    # ---- state dict with the reference's key names -------------------------------------------------------
+    def state_dict(self, *args, **kwargs):
+        sd = OrderedDict(self._sd)
+        sd["par.kernel"] = self.par.kernel
+        return sd
+
+    def load_state_dict(self, state_dict, strict: bool = False):
+        """test_msc_flip_voc.py:196 loads with strict=False; encoder keys may come from the CLIP checkpoint."""
+        known = {k: v for k, v in state_dict.items() if k.startswith(("encoder.visual.", "encoder.logit_scale",
+                                                                      "decoder_fts_fuse.", "decoder."))}
+        self._sd.update({k: v.detach().float().cpu() for k, v in known.items()})
+        need = ("encoder.visual.conv1.weight", "decoder.linear_pred.weight", "decoder_fts_fuse.linear_fuse.weight")
+        if all(k in self._sd for k in need) and torch.cuda.is_available():
+            self.engine = Engine(self._sd, self.num_classes, self._device)
+            self.num_classes = self.engine.num_classes
+        missing = [k for k in need if k not in self._sd]
+        unexpected = [k for k in state_dict if k not in known and k != "par.kernel"]
+        if strict and (missing or unexpected):
+            raise RuntimeError(f"missing {missing}, unexpected {unexpected}")
+        return nn.modules.module._IncompatibleKeys(missing, unexpected)
+
+    def get_param_groups(self):
+        """model_attn_aff_voc.py:94-103: [[], [], [], decoder + fuse parameters]."""
+        groups = [[], [], [], []]
+        for k, v in self._sd.items():
+            if k.startswith(("decoder.", "decoder_fts_fuse.")):
+                groups[3].append(v)
+        return groups
+
+    # ---- forward ---------------------------------------------------------------------------------------------
+    def _label_path(self, name) -> str:
+        return os.path.join(self.root_path, self._label_subdir, str(name) + ".png")
+
+    @torch.no_grad()
+    def forward(self, img, img_names="2007_000032", mode="train"):
+        _lib.require_device()
+        if self.engine is None:
+            raise _lib.WeclipError("WeCLIP weights are not loaded (encoder + decoder state dict required)")
+        eng, cfg = self.engine, self.cfg
+        img = img.to(eng.device, torch.float32)
+        N, _, H, W = img.shape
+        h, w = H // 16, W // 16
+        self.iter_num += 1
+        cam_path = not (self.dataset == "coco" and mode == "val")     # model_attn_aff_coco.py:131-132
+        require_seg_trans = self.iter_num > cfg["switch"] or mode == "val"
+        nl = cfg["window"] if require_seg_trans else 8                 # clip_tool.py:155 / :173
+        taps, x_last, attn = eng.encoder(img, n_attn=(nl - 1) if cam_path else 0, attn_slots=nl if cam_path else 0)
+        seg, attn_pred, _ = eng.decoder(taps, N, h, w)
+        if not cam_path:
+            return seg, None, attn_pred
+
+        ids_all, sizes, text_off, k_off, rows = [], [], [0], [0], []
+        fg = self.fg_text_features.to(eng.device, torch.float32)
+        bg = self.bg_text_features.to(eng.device, torch.float32)
+        for name in img_names:
+            ids, oh, ow = self.label_reader(self._label_path(name))
+            ids_all.append(ids)
+            sizes.append((H, W) if mode == "train" else (oh, ow))     # clip_tool.py:194-197
+            rows += [fg[ids], bg]
+            text_off.append(text_off[-1] + len(ids) + bg.shape[0])
+            k_off.append(k_off[-1] + len(ids))
+        assert len(ids_all) == N, "one name per image"
+        if any(len(i) == 0 for i in ids_all):
+            raise RuntimeError("image without foreground label (torch.stack([]) in the reference, clip_tool.py:212)")
+        text = torch.cat(rows, dim=0)
+        cams, _, _ = eng.gradcam(x_last, N, h, w, text, text_off, k_off, attn_last_out=attn[nl - 1])
+        refined, _ = eng.affinity_refine(attn, nl, attn_pred, N, h, w, require_seg_trans, cams, k_off, cfg["box_thr"])
+        if len(set(sizes)) != 1:
+            raise RuntimeError("stack expects each tensor to be equal size (model_attn_aff_voc.py:173)")
+        Hc, Wc = sizes[0]
+        par_in = eng.cam_upsample_bg(refined, k_off, N, h, w, Hc, Wc, float(self.cam_bg_thres))
+        ch_off = [k_off[i] + i for i in range(N + 1)]
+        par_out = self.par.refine_ragged(img, par_in, ch_off)
+        lut = torch.tensor([v for ids in ids_all for v in [0] + [i + 1 for i in ids]], dtype=torch.int64)
+        labels = argmax_lut(par_out, lut, ch_off)
+        return seg, labels, attn_pred
