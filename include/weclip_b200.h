@@ -29,7 +29,7 @@ extern "C" {
 #define WC_ERR_WORKSPACE (-3)
 #define WC_ERR_UNSUPPORTED (-4)
 
-#define WC_ABI_VERSION 3
+#define WC_ABI_VERSION 4
 #define WC_PAR_MAX_DIL 8
 
 /* ABI version (bumped whenever a signature changes) and last error text. */
@@ -37,6 +37,16 @@ int wc_abi_version(void);
 const char* wc_last_error(void);
 /* 1 when the current device is compute capability 10.x (the only target); 0 otherwise. */
 int wc_device_ok(void);
+
+/* Opt-in per-kernel-class device timing (no reference counterpart: the reference has no profiling).
+ * While enabled, every launch is bracketed by CUDA events on its stream; wc_prof_summary synchronises the device
+ * and sums device milliseconds, algorithmic work (flops for gemm_tc, bytes for the memory-bound classes) and
+ * launch counts per class into arrays of wc_prof_kinds() entries.  bench.py uses it for the roofline object. */
+int wc_prof_kinds(void);
+const char* wc_prof_kind_name(int kind);
+int wc_prof_enable(int on);
+int wc_prof_reset(void);
+int wc_prof_summary(double* ms, double* work, long* launches);
 
 /* ------------------------------------------------------------------------------------------------
  * PAR — pixel-adaptive refinement.  Replaces WeCLIP_model/PAR.py:64-92 (PAR.forward), incl.
@@ -180,6 +190,30 @@ int wc_affinity_refine(const float* attn, int nl, const float* attn_pred, int N,
  * [k_off[i]+i, k_off[i+1]+i+1) = (bg, class 1..K_i) — the packed layout wc_par_fwd takes.  stats_ws: 2*sumK floats. */
 int wc_cam_upsample_bg(const float* cams, const int* k_off_host, int N, int h, int wd, int Hc, int Wc, float bg_pow,
                        float* out, float* stats_ws, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * msc+flip fusion and scoring (the caller that defines the metric).  Replaces the ATen
+ * calls of validate(), test_msc_flip_voc.py:60-96 (COCO twin test_msc_flip_coco.py:61-96), and
+ * utils/evaluate.py:9-15 (_fast_hist).
+ * ---------------------------------------------------------------------------------------------- */
+/* F.interpolate(mode='bilinear', align_corners=False) on [planes,Hi,Wi] -> [planes,Ho,Wo]
+ * (test_msc_flip_voc.py:63 with size=, :80 with scale_factor=).  scale_factor_{y,x} > 0 reproduces torch's
+ * scale_factor= call (source step 1/scale_factor); 0 means the size= call (source step in/out). */
+int wc_resize_bilinear(const float* in, float* out, int planes, int Hi, int Wi, int Ho, int Wo,
+                       float scale_factor_y, float scale_factor_x, void* stream);
+/* torch.cat([x, x.flip(-1)], dim=0) (test_msc_flip_voc.py:68,82): in [planes,H,W] -> out [2,planes,H,W]. */
+int wc_flip_concat(const float* in, float* out, int planes, int H, int W, void* stream);
+/* One scale of the msc fusion (test_msc_flip_voc.py:74,86-88,90): seg2 [2,C,hs,ws] (plain, flipped input) ->
+ * acc[C,h,w] = (first ? 0 : acc) + weight * (R(seg2[0]) + flip(R(seg2[1]))) / 2, R = bilinear resize to h x w. */
+int wc_msc_accumulate(const float* seg2, float* acc, int C, int hs, int ws, int h, int w, float weight,
+                      int first, void* stream);
+/* argmax_c of the bilinear resize of logits [C,h,w] to Ho x Wo (test_msc_flip_voc.py:93-96) -> pred int32 [Ho,Wo]
+ * (may be NULL) and, when gt (int16 [Ho,Wo]) and hist (int64 [C,C]) are given, hist[gt*C+pred] += 1 for 0<=gt<C. */
+int wc_upsample_argmax_hist(const float* logits, int C, int h, int w, int Ho, int Wo, int32_t* pred,
+                            const int16_t* gt, int64_t* hist, void* stream);
+/* _fast_hist over flat label arrays (the CAM pseudo-label histogram, test_msc_flip_voc.py:107):
+ * pred int64 [n], gt int16 [n], hist int64 [C,C] accumulated in place. */
+int wc_confusion_hist(const int64_t* pred, const int16_t* gt, long n, int C, int64_t* hist, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,90 @@
+"""msc+flip fusion / scoring kernels (csrc/evalops.cu) against torch's own ops and the oracle's restated
+evaluation loop (oracle.msc_flip_image <- test_msc_flip_voc.py:60-96)."""
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import weclip_oracle as O
+from weclip_b200 import ops, synth
+from weclip_b200.evaluate import MscFlipEvaluator
+from weclip_b200.model import WeCLIP
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("shape,size,sf", [((2, 3, 37, 53), (64, 41), None), ((1, 21, 20, 20), (333, 500), None),
+                                           ((1, 3, 96, 128), None, 0.75), ((1, 3, 96, 128), None, 1.25),
+                                           ((1, 3, 375, 500), (384, 512), None), ((1, 5, 9, 7), (3, 2), None)])
+def test_resize_bilinear_matches_torch(shape, size, sf):
+    x = torch.randn(*shape, generator=torch.Generator().manual_seed(1))
+    want = F.interpolate(x, size=size, scale_factor=sf, mode="bilinear", align_corners=False)
+    got = ops.resize_bilinear(x.cuda(), size=size, scale_factor=sf).cpu()
+    assert got.shape == want.shape
+    assert (got - want).abs().max().item() < 1e-5
+
+
+def test_flip_concat_is_exact():
+    x = torch.randn(1, 3, 45, 67)
+    assert torch.equal(ops.flip_concat(x.cuda()).cpu(), torch.cat([x, x.flip(-1)], 0))
+
+
+def test_msc_accumulate_matches_torch():
+    g = torch.Generator().manual_seed(2)
+    C, h, w = 21, 20, 27
+    segs = [torch.randn(2, C, h, w, generator=g), torch.randn(2, C, 15, 20, generator=g), torch.randn(2, C, 25, 33, generator=g)]
+    acc = torch.empty(C, h, w, device="cuda")
+    lst = []
+    for i, s in enumerate(segs):
+        ops.msc_accumulate(s.cuda(), acc, 1.0 / 3, i == 0)
+        r = F.interpolate(s, size=(h, w), mode="bilinear", align_corners=False) if i else s
+        lst.append((r[0] + r[1].flip(-1)) / 2)
+    want = torch.stack(lst).mean(0)
+    assert (acc.cpu() - want).abs().max().item() < 1e-5
+
+
+@pytest.mark.parametrize("C", [21, 81, 150])
+def test_upsample_argmax_hist_matches_torch_and_fast_hist(C):
+    g = torch.Generator().manual_seed(C)
+    logits = torch.randn(C, 23, 31, generator=g)
+    Ho, Wo = 181, 250
+    gt = torch.randint(0, C, (Ho, Wo), generator=g).to(torch.int16)
+    gt[torch.rand(Ho, Wo, generator=g) < 0.1] = 255            # ignore label
+    hist = torch.zeros(C, C, dtype=torch.int64, device="cuda")
+    pred = ops.upsample_argmax_hist(logits.cuda(), (Ho, Wo), gt.cuda(), hist).cpu()
+    want = F.interpolate(logits[None], size=(Ho, Wo), mode="bilinear", align_corners=False)[0].argmax(0)
+    assert (pred == want).float().mean().item() >= 0.9995     # ties / last-bit interpolation differences only
+    # integer work is bit-exact: the histogram of OUR predictions equals _fast_hist of the same arrays
+    assert np.array_equal(hist.cpu().numpy(), O.fast_hist(gt.numpy(), pred.numpy(), C))
+    hist2 = torch.zeros(C, C, dtype=torch.int64, device="cuda")
+    ops.confusion_hist(pred.long().cuda(), gt.cuda(), hist2)
+    assert torch.equal(hist, hist2)
+
+
+def test_msc_flip_image_matches_oracle():
+    """One dataset image through the whole evaluation loop, small enough for the CPU oracle (long side -> 160)."""
+    sd = synth.make_state_dict(0, 21)
+    fg, bg = synth.make_text_features(7, 20, 25)
+    rng = np.random.default_rng(4)
+    lab = synth.make_label_map(rng, 93, 130, [4, 14])
+    root = tempfile.mkdtemp()
+    synth.write_label_png(root, "SegmentationClassAug", "e0", lab)
+    img = synth.make_images(9, 1, 93, 130)
+    model = WeCLIP(num_classes=21, dataset_root_path=root, device="cuda", state_dict=sd, fg_text_features=fg,
+                   bg_text_features=bg)
+    ev = MscFlipEvaluator(model, 21, (1.0, 0.75, 1.25), resize_long=160)
+    gt = torch.from_numpy(lab.astype(np.int16)).cuda()
+    seg_pred, msc_pred, cam, msc = ev.process("e0", img.cuda(), gt, want_preds=True)
+    seg_o, msc_o, cam_o, msc_segs_o = O.msc_flip_image(img, lab, sd, fg, bg, (1.0, 0.75, 1.25), resize_long=160)
+    assert ((msc.cpu() - msc_segs_o[0]).abs().max() / msc_segs_o.abs().max()).item() < 2e-2
+    assert (seg_pred.cpu() == seg_o).float().mean().item() >= 0.995
+    assert (msc_pred.cpu() == msc_o).float().mean().item() >= 0.995
+    assert (cam.cpu() == cam_o).float().mean().item() >= 0.995
+    h = ev.hist.cpu().numpy()
+    assert np.array_equal(h[0], O.fast_hist(lab, seg_pred.cpu().numpy(), 21))
+    assert np.array_equal(h[1], O.fast_hist(lab, msc_pred.cpu().numpy(), 21))
+    assert np.array_equal(h[2], O.fast_hist(lab, cam.cpu().numpy(), 21))
+    sc = ev.scores()
+    assert 0.0 <= sc["msc_seg"]["miou"] <= 1.0

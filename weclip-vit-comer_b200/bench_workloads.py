@@ -1,0 +1,159 @@
+"""Full-path bench workloads (registered into bench.py's WORKLOADS table).
+
+``mscflip`` = BASELINE.json configs[2]: test_msc_flip_voc inference, scales 1.0/0.75/1.25 + flip at 512x512,
+21 classes, images sharded across ranks.  One step = IMAGES_PER_STEP dataset images through
+``evaluate.MscFlipEvaluator.process`` (6 WeCLIP forwards each: encoder, decoder, Grad-CAM, affinity refinement,
+CAM upsample, PAR at label resolution, then fusion + argmax + 3 confusion matrices).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import tempfile
+import time
+
+import numpy as np
+import torch
+
+from . import _lib, synth
+
+IMAGES_PER_STEP = 8
+KINDS_TENSOR = ("gemm_tc", "attention")
+
+
+def prof_summary():
+    L = _lib.lib()
+    n = L.wc_prof_kinds()
+    ms, work, cnt = (ctypes.c_double * n)(), (ctypes.c_double * n)(), (ctypes.c_long * n)()
+    L.wc_prof_kind_name.restype = ctypes.c_char_p
+    _lib.check(L.wc_prof_summary(ms, work, cnt), "wc_prof_summary")
+    return {L.wc_prof_kind_name(i).decode(): (ms[i], work[i], cnt[i]) for i in range(n)}
+
+
+class MscFlipVoc:
+    name = ("cfg3: test_msc_flip_voc val, scales 1.0/0.75/1.25 + flip, 512x512 images and labels, 21 classes, "
+            "K per image from the VOC histogram")
+    dtype = "bf16"
+    n_classes, n_fg, n_bg, dataset, subdir = 21, 20, 25, "voc", "SegmentationClassAug"
+    scales = (1.0, 0.75, 1.25)
+    H = W = 512
+
+    def _make_data(self, seed, n_img, root):
+        rng = np.random.default_rng(seed)
+        names, labs = [], []
+        for i in range(n_img):
+            ids = synth.draw_label_set(rng, self.n_fg)
+            lab = synth.make_label_map(rng, self.H, self.W, ids)
+            synth.write_label_png(root, self.subdir, f"b{seed}_{i}", lab)
+            names.append(f"b{seed}_{i}")
+            labs.append(lab)
+        imgs = synth.make_images(1000 + seed, n_img, self.H, self.W)
+        return names, labs, imgs
+
+    def __init__(self, rank: int, device):
+        from .evaluate import MscFlipEvaluator
+        from .model import WeCLIP
+        self.dev = device
+        self.root = tempfile.mkdtemp(prefix="wcbench")
+        self.sd = synth.make_state_dict(0, self.n_classes)
+        self.fg, self.bg = synth.make_text_features(7, self.n_fg, self.n_bg)
+        self.names, labs, imgs = self._make_data(100 + rank, IMAGES_PER_STEP, self.root)
+        self.model = WeCLIP(num_classes=self.n_classes, dataset_root_path=self.root, device=device,
+                            dataset=self.dataset, state_dict=self.sd, fg_text_features=self.fg,
+                            bg_text_features=self.bg)
+        self.ev = MscFlipEvaluator(self.model, self.n_classes, self.scales, 512, device)
+        self.imgs_h = imgs.pin_memory()
+        self.labs_h = torch.from_numpy(np.stack(labs).astype(np.int16)).pin_memory()
+        self.imgs_d = self.imgs_h.to(device)
+        self.labs_d = self.labs_h.to(device)
+        self.hist_h = torch.empty(3, self.n_classes, self.n_classes, dtype=torch.int64).pin_memory()
+        self.units = IMAGES_PER_STEP
+        self.h2d = self.imgs_h.numel() * 4 + self.labs_h.numel() * 2
+        self.d2h = self.hist_h.numel() * 8
+        self.launches = None
+        # per forward pair at 512x512 the attention scores alone are 2*12*1025*1032*4 B = 101 MB, rewritten by each
+        # of the 12 blocks; with taps, MLP activations and PAR affinities the working set per image is > 126 MB
+        self.l2_note = "working set larger than L2 (>= 101 MB of attention scores per block at 512x512, x3 scales)"
+
+    def step_device(self, record=False):
+        for i in range(self.units):
+            self.ev.process(self.names[i], self.imgs_d[i:i + 1], self.labs_d[i])
+
+    def step_e2e(self):
+        for i in range(self.units):
+            img = self.imgs_h[i:i + 1].to(self.dev, non_blocking=True)
+            lab = self.labs_h[i].to(self.dev, non_blocking=True)
+            self.ev.process(self.names[i], img, lab)
+        self.hist_h.copy_(self.ev.hist, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self.hist_h
+
+    def profile(self, steps: int):
+        """Separate pass with the C-side profiler on: per-kernel-class device time and algorithmic work."""
+        L = _lib.lib()
+        L.wc_prof_reset(); L.wc_prof_enable(1)
+        for _ in range(steps):
+            self.step_device()
+        summ = prof_summary()
+        L.wc_prof_enable(0); L.wc_prof_reset()
+        self._prof = {k: (ms / steps, work / steps, cnt // steps) for k, (ms, work, cnt) in summ.items()}
+        self.launches = sum(c for _, _, c in self._prof.values())
+        return self._prof
+
+    def roofline(self, peaks):
+        prof = self._prof
+        total = sum(ms for ms, _, _ in prof.values()) or 1.0
+        top = max(prof, key=lambda k: prof[k][0])
+        rows = {}
+        for k, (ms, work, cnt) in prof.items():
+            if cnt == 0:
+                continue
+            row = {"ms_per_step": round(ms, 3), "share": round(ms / total, 4), "launches_per_step": cnt}
+            if work > 0 and ms > 0:
+                if k in KINDS_TENSOR:
+                    a = work / (ms * 1e-3) / 1e12
+                    row.update(achieved=round(a, 1), unit="TFLOP/s", frac=round(a / peaks["bf16_tflops_sustained"], 4))
+                else:
+                    a = work / (ms * 1e-3) / 1e9
+                    row.update(achieved=round(a, 1), unit="GB/s", frac=round(a / peaks["hbm_gbs"], 4))
+            rows[k] = row
+        ms, work, cnt = prof[top]
+        tensor = top in KINDS_TENSOR
+        peak = peaks["bf16_tflops_sustained"] if tensor else peaks["hbm_gbs"]
+        ach = (work / (ms * 1e-3) / (1e12 if tensor else 1e9)) if work > 0 else None
+        return {"bound": "tensor" if tensor else "hbm", "kernel": top, "achieved": round(ach, 1) if ach else None,
+                "peak": peak, "peak_source": peaks["source"] + (" (sustained cuBLAS bf16)" if tensor else " (copy)"),
+                "unit": "TFLOP/s" if tensor else "GB/s", "frac": round(ach / peak, 4) if ach else None,
+                "traffic": None, "kernel_ms_per_launch": round(ms / max(cnt, 1), 4), "kernels": rows}
+
+    # ---- CPU baseline / reference arm (oracle port of the evaluation loop; bounded sample) ---------------
+    @classmethod
+    def cpu(cls):
+        wl = cls.__new__(cls)
+        wl.root = tempfile.mkdtemp(prefix="wcbench")
+        wl.sd = synth.make_state_dict(0, cls.n_classes)
+        wl.fg, wl.bg = synth.make_text_features(7, cls.n_fg, cls.n_bg)
+        wl.names, wl.labs, wl.imgs_h = wl._make_data(100, 1, wl.root)
+        return wl
+
+    def cpu_sample(self, n_img=1):
+        from oracle import weclip_oracle as O
+        if not hasattr(self, "labs"):
+            self.labs = [self.labs_h[i].numpy().astype(np.uint8) for i in range(n_img)]
+        t0 = time.perf_counter()
+        for i in range(n_img):
+            O.msc_flip_image(self.imgs_h[i:i + 1].clone(), self.labs[i], self.sd, self.fg, self.bg, self.scales, 512,
+                             self.dataset)
+        dt = time.perf_counter() - t0
+        return n_img / dt, (f"{n_img} of the step's {IMAGES_PER_STEP} dataset images (6 forwards + fusion each), "
+                            "oracle port of the reference loop, torch CPU fp32")
+
+
+class MscFlipCoco(MscFlipVoc):
+    name = ("cfg4: test_msc_flip_coco val, scales 1.0/0.75/1.25 + flip, 512x512, 81 classes "
+            "(val mode returns before CAM/PAR, model_attn_aff_coco.py:131-132)")
+    n_classes, n_fg, n_bg, dataset = 81, 80, 23, "coco"
+    subdir = os.path.join("SegmentationClass", "train")
+
+
+WORKLOADS = {"mscflip": MscFlipVoc, "mscflip_coco": MscFlipCoco}

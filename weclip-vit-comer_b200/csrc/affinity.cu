@@ -300,6 +300,7 @@ extern "C" int wc_affinity_refine(const float* attn, int nl, const float* attn_p
     WC_CHECK_ARG(attn && cams && k_off_host && cams_refined && workspace && nl >= 1 && nl <= 16);
     WC_CHECK_ARG(N > 0 && N <= AFF_MAX_IMG && h > 0 && wd > 0 && (!use_rfm || attn_pred));
     cudaStream_t st = as_stream(stream);
+    ProfScope prof(PK_AFFINITY, 0.0, st);
     const int P = h * wd, L = P + 1, total = k_off_host[N];
     WC_CHECK_ARG((size_t)P * 21 + 64 <= 200 * 1024);
     if (workspace_bytes < wc_affinity_workspace_bytes(N, h, wd, total, nl))
@@ -361,6 +362,7 @@ extern "C" int wc_cam_upsample_bg(const float* cams, const int* k_off_host, int 
                                   float bg_pow, float* out, float* stats_ws, void* stream) {
     WC_CHECK_ARG(cams && k_off_host && out && stats_ws && N > 0 && N <= AFF_MAX_IMG && h > 0 && wd > 0 && Hc > 0 && Wc > 0);
     cudaStream_t st = as_stream(stream);
+    ProfScope prof(PK_CAM_UPSAMPLE, 0.0, st);
     AffTable tab; tab.n = N;
     for (int i = 0; i <= N; ++i) tab.k_off[i] = k_off_host[i];
     const int total = k_off_host[N];

@@ -81,4 +81,28 @@ __device__ __forceinline__ float block_min(float v, float* scratch) {
     return warp_min(r);
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Opt-in per-kernel-class device timing (wc_prof_*): CUDA events recorded on the launching stream around each
+// launch, summed per class after a synchronise.  Off by default; bench.py turns it on for a separate pass so the
+// headline timed region is never perturbed.
+// ---------------------------------------------------------------------------------------------------
+enum ProfKind : int {
+    PK_GEMM = 0, PK_LAYERNORM, PK_SOFTMAX, PK_PAR_AFF, PK_PAR_ITER, PK_AFFINITY, PK_GRADCAM_MISC, PK_ENC_MISC,
+    PK_CAM_UPSAMPLE, PK_EVAL, PK_ATTENTION, PK_COUNT
+};
+extern bool g_prof_on;
+void prof_begin(int kind, double work, cudaStream_t st);
+void prof_end(cudaStream_t st);
+struct ProfScope {
+    cudaStream_t st; bool on;
+    ProfScope(int kind, double work, cudaStream_t s) : st(s), on(g_prof_on) { if (on) prof_begin(kind, work, st); }
+    ~ProfScope() { if (on) prof_end(st); }
+};
+
+#define WC_PROF_LAUNCH(kind, work, st, ...)            \
+    do {                                               \
+        ::wc::ProfScope ps__(kind, work, st);          \
+        __VA_ARGS__;                                   \
+    } while (0)
+
 }  // namespace wc

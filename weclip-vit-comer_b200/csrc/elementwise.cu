@@ -56,6 +56,7 @@ int launch_layernorm(const float* x, const float* w, const float* b, __nv_bfloat
                      int E, cudaStream_t st) {
     WC_CHECK_ARG(x && w && b && rows > 0 && (out_bf || out_f));
     const unsigned grid = (unsigned)ceil_div(rows, 8L);
+    ProfScope prof(PK_LAYERNORM, (double)rows * E * (4.0 + (out_bf ? 2.0 : 0.0) + (out_f ? 4.0 : 0.0)), st);
     switch (E) {
         case 256: layernorm_kernel<2><<<grid, 256, 0, st>>>(x, w, b, out_bf, out_f, rows, E); break;
         case 512: layernorm_kernel<4><<<grid, 256, 0, st>>>(x, w, b, out_bf, out_f, rows, E); break;
@@ -107,6 +108,7 @@ __global__ void __launch_bounds__(256) softmax_headmean_kernel(const float* __re
 int launch_softmax_headmean(const float* S, __nv_bfloat16* P, float* avg, int n_img, int heads, int L, int Lp, cudaStream_t st) {
     WC_CHECK_ARG(S && P && n_img > 0 && heads > 0 && L > 0 && Lp >= L && n_img <= 65535);
     dim3 grid(L, n_img);
+    ProfScope prof(PK_SOFTMAX, (double)n_img * L * L * (6.0 * heads + (avg ? 4.0 : 0.0)), st);
     softmax_headmean_kernel<<<grid, 256, sizeof(float) * L, st>>>(S, P, avg, heads, L, Lp);
     WC_LAUNCH_CHECK();
     return WC_OK;
@@ -133,6 +135,7 @@ __global__ void __launch_bounds__(256) im2col16_kernel(const float* __restrict__
 int launch_im2col16(const float* img, __nv_bfloat16* out, int N, int H, int W, cudaStream_t st) {
     const int h = H / 16, w = W / 16;
     WC_CHECK_ARG(img && out && N > 0 && h > 0 && w > 0 && N <= 65535);
+    ProfScope prof(PK_ENC_MISC, 0.0, st);
     im2col16_kernel<<<dim3(h, N), 256, 0, st>>>(img, out, H, W, h, w);
     WC_LAUNCH_CHECK();
     return WC_OK;
@@ -173,12 +176,14 @@ __global__ void cls_row_kernel(float* __restrict__ x, const float* __restrict__ 
 
 int launch_posemb_resize(const float* pos, float* out, int gs, int h, int w, int E, cudaStream_t st) {
     WC_CHECK_ARG(pos && out && gs > 0 && h > 0 && w > 0);
+    ProfScope prof(PK_ENC_MISC, 0.0, st);
     posemb_resize_kernel<<<h * w + 1, 256, 0, st>>>(pos, out, gs, h, w, E);
     WC_LAUNCH_CHECK();
     return WC_OK;
 }
 
 int launch_cls_row(float* x, const float* cls, const float* pos, int N, int L, int E, cudaStream_t st) {
+    ProfScope prof(PK_ENC_MISC, 0.0, st);
     cls_row_kernel<<<N, 256, 0, st>>>(x, cls, pos, L, E);
     WC_LAUNCH_CHECK();
     return WC_OK;
@@ -190,6 +195,7 @@ __global__ void cast_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __r
     if (i < n) y[i] = __float2bfloat16(x[i]);
 }
 int launch_cast_bf16(const float* x, __nv_bfloat16* y, size_t n, cudaStream_t st) {
+    ProfScope prof(PK_ENC_MISC, 0.0, st);
     cast_bf16_kernel<<<(unsigned)ceil_div(n, (size_t)256), 256, 0, st>>>(x, y, n);
     WC_LAUNCH_CHECK();
     return WC_OK;

@@ -403,6 +403,7 @@ static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
     rc = make_map(&mB, p.B, p.K, p.nb0, p.nb1, BN, &ka.b_b0, &ka.b_b1);
     if (rc) return rc;
     dim3 grid(ceil_div(p.M, BM), ceil_div(p.N, BN), p.nb0 * p.nb1);
+    ProfScope prof(PK_GEMM, 2.0 * p.M * p.N * p.K * p.nb0 * p.nb1, st);
     gemm_tc_kernel<BN, STAGES><<<grid, GEMM_THREADS, SL::TOTAL, st>>>(mA, mB, ka);
     WC_LAUNCH_CHECK();
     return WC_OK;

@@ -405,9 +405,9 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
     }
     // ---- pooled head + its Jacobian for every (image, class)
     WC_CUDA(cudaMemsetAsync(g.msum, 0, sizeof(float) * N * E, st));
-    lnpost_mean_kernel<<<dim3(ceil_div(P, 32), N), 256, 0, st>>>(g.x2, w->ln_post_w, w->ln_post_b, g.msum, L);
+    WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, lnpost_mean_kernel<<<dim3(ceil_div(P, 32), N), 256, 0, st>>>(g.x2, w->ln_post_w, w->ln_post_b, g.msum, L));
     WC_LAUNCH_CHECK();
-    head_kernel<<<N, 512, 0, st>>>(g.msum, w->proj, text, tab, w->logit_scale_exp, P, g.dm, probs);
+    WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, head_kernel<<<N, 512, 0, st>>>(g.msum, w->proj, text, tab, w->logit_scale_exp, P, g.dm, probs));
     WC_LAUNCH_CHECK();
     // ---- backward, in chunks of whole images holding <= chunk instances
     const float qscale = 1.f / sqrtf((float)GC_HD);
@@ -425,7 +425,7 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
         const long R = (long)n_inst * L;
         const unsigned ln_grid = (unsigned)ceil_div(R, 8L);
         // ln_post backward (dy = dm broadcast over patch rows, class row zero)
-        ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x2, w->ln_post_w, nullptr, g.dm, nullptr, g.dx2, g.dx2b, it, L);
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x2, w->ln_post_w, nullptr, g.dm, nullptr, g.dx2, g.dx2b, it, L));
         WC_LAUNCH_CHECK();
         // c_proj^T and the QuickGELU derivative (model.py:198-203); per image because the saved pre-activation
         // u_pre belongs to the image, shared by its classes
@@ -446,7 +446,7 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
             if ((rc = launch_gemm(p, st))) return rc;
         }
         // ln_2 backward + the residual branch: dx1 = dx2 + LN2'(da2)
-        ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x1, w->blocks[11].ln2_w, g.da2, nullptr, g.dx2, nullptr, g.dx1b, it, L);
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x1, w->blocks[11].ln2_w, g.da2, nullptr, g.dx2, nullptr, g.dx1b, it, L));
         WC_LAUNCH_CHECK();
         {   // out_proj^T (myAtt.py:321)
             GemmProblem p; p.M = (int)R; p.N = E; p.K = E;
@@ -466,16 +466,16 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
             if ((rc = launch_gemm(p, st))) return rc;
         }
         WC_CUDA(cudaMemsetAsync(g.colsum, 0, sizeof(float) * n_inst * GC_HEADS * L, st));
-        attn_bwd_reduce_kernel<<<dim3(ceil_div(L, 32), GC_HEADS, n_inst), 256, sizeof(float) * L, st>>>(
-            g.dP, g.P, g.colsum, g.ds0, it, L, (int)Lp);
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, attn_bwd_reduce_kernel<<<dim3(ceil_div(L, 32), GC_HEADS, n_inst), 256, sizeof(float) * L, st>>>(
+            g.dP, g.P, g.colsum, g.ds0, it, L, (int)Lp));
         WC_LAUNCH_CHECK();
-        qkv_grad_sum_kernel<<<dim3(GC_HEADS, n_inst), 256, 0, st>>>(g.colsum, g.ds0, g.q, g.k, g.P, g.dO,
-                                                                    g.dqkv + (long)it.inst0 * 3 * E, it, L, (int)Lp, qscale);
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, qkv_grad_sum_kernel<<<dim3(GC_HEADS, n_inst), 256, 0, st>>>(g.colsum, g.ds0, g.q, g.k, g.P, g.dO,
+                                                                    g.dqkv + (long)it.inst0 * 3 * E, it, L, (int)Lp, qscale));
         WC_LAUNCH_CHECK();
-        cam_weight_kernel<<<dim3(E / 128, n_inst), 128, 0, st>>>(g.dqkv + (long)it.inst0 * 3 * E, w->w_in_f32,
-                                                                 g.wvec + (long)it.inst0 * E, P);
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, cam_weight_kernel<<<dim3(E / 128, n_inst), 128, 0, st>>>(g.dqkv + (long)it.inst0 * 3 * E, w->w_in_f32,
+                                                                 g.wvec + (long)it.inst0 * E, P));
         WC_LAUNCH_CHECK();
-        cam_kernel<<<n_inst, 256, sizeof(float) * P, st>>>(g.a32, g.wvec, cams, it, L);
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, cam_kernel<<<n_inst, 256, sizeof(float) * P, st>>>(g.a32, g.wvec, cams, it, L));
         WC_LAUNCH_CHECK();
         img0 = img1;
     }

@@ -233,8 +233,13 @@ static int propagate(const float* aff, const float* masks, float* out, float* sc
             }
             if (n == 0) break;
             dim3 grid(ceil_div(g.W, PAR_TX), ceil_div(g.H, PAR_TY), n);
-            if (g.nn == 48) par_iter_kernel<48><<<grid, block, 0, st>>>(aff, src, dst, g, chunks);
-            else par_iter_kernel<0><<<grid, block, 0, st>>>(aff, src, dst, g, chunks);
+            {
+                int chs = 0;
+                for (int i = 0; i < n; ++i) chs += chunks.cnt[i];
+                ProfScope prof(PK_PAR_ITER, (double)hw * (4.0 * g.nn * n + 8.0 * chs), st);
+                if (g.nn == 48) par_iter_kernel<48><<<grid, block, 0, st>>>(aff, src, dst, g, chunks);
+                else par_iter_kernel<0><<<grid, block, 0, st>>>(aff, src, dst, g, chunks);
+            }
             WC_LAUNCH_CHECK();
             done += n;
         }
@@ -264,6 +269,7 @@ extern "C" int wc_par_affinity(const float* img, float* aff, int B, int H, int W
     ParGeom g; ParPos pos;
     WC_CHECK_ARG(make_geom(g, &pos, H, W, dil, n_dil) == 0);
     dim3 block(32, 8), grid(ceil_div(W, 32), ceil_div(H, 8), B);
+    ProfScope prof(PK_PAR_AFF, (double)B * H * W * (12.0 + 4.0 * g.nn), as_stream(stream));
     if (g.nn == 48) par_aff_kernel<48><<<grid, block, 0, as_stream(stream)>>>(img, aff, g, pos);
     else par_aff_kernel<0><<<grid, block, 0, as_stream(stream)>>>(img, aff, g, pos);
     WC_LAUNCH_CHECK();
@@ -297,6 +303,7 @@ extern "C" int wc_par_fwd(const float* imgs, int Hi, int Wi, const float* masks,
     if (Hi != H || Wi != W) {
         dim3 block(32, 8), grid(ceil_div(W, 32), ceil_div(H, 8), B * 3);
         WC_CHECK_ARG(B * 3 <= 65535);
+        ProfScope prof(PK_PAR_AFF, 0.0, st);
         par_resize_kernel<<<grid, block, 0, st>>>(imgs, img_r, B * 3, Hi, Wi, H, W);
         WC_LAUNCH_CHECK();
         img = img_r;
@@ -313,6 +320,7 @@ extern "C" int wc_argmax_lut(const float* masks, const int64_t* lut, int64_t* la
     WC_CHECK_ARG(masks && lut && labels && H > 0 && W > 0);
     WC_CHECK_ARG(check_ragged(ch_off, B) == 0);
     const size_t hw = (size_t)H * W;
+    ProfScope prof(PK_CAM_UPSAMPLE, 0.0, as_stream(stream));
     for (int b = 0; b < B; ++b) {
         argmax_lut_kernel<<<(unsigned)ceil_div(hw, (size_t)256), 256, 0, as_stream(stream)>>>(
             masks, lut, labels, ch_off[b], ch_off[b + 1] - ch_off[b], b, hw);

@@ -2,6 +2,7 @@
 from __future__ import annotations
 
 import ctypes
+import math
 
 import torch
 
@@ -38,3 +39,72 @@ def gemm_bf16(A: torch.Tensor, B: torch.Tensor, bias=None, resid=None, act: str 
         ctypes.c_float(alpha), _lib.stream_ptr())
     _lib.check(rc, "wc_gemm_bf16")
     return out[0] if squeeze and out.dim() == 3 else out
+
+
+def resize_bilinear(x: torch.Tensor, size=None, scale_factor: float = None) -> torch.Tensor:
+    """F.interpolate(x, size=|scale_factor=, mode='bilinear', align_corners=False) for fp32 [N,C,H,W]
+    (test_msc_flip_voc.py:63,80)."""
+    _lib.require_device()
+    x = x.contiguous().float()
+    N, C, Hi, Wi = x.shape
+    if size is not None:
+        Ho, Wo, sf = int(size[0]), int(size[1]), 0.0
+    else:
+        Ho, Wo, sf = int(math.floor(Hi * scale_factor)), int(math.floor(Wi * scale_factor)), float(scale_factor)
+    out = torch.empty(N, C, Ho, Wo, dtype=torch.float32, device=x.device)
+    rc = _lib.lib().wc_resize_bilinear(_lib.ptr(x), _lib.ptr(out), N * C, Hi, Wi, Ho, Wo, ctypes.c_float(sf),
+                                       ctypes.c_float(sf), _lib.stream_ptr())
+    _lib.check(rc, "wc_resize_bilinear")
+    return out
+
+
+def flip_concat(x: torch.Tensor) -> torch.Tensor:
+    """torch.cat([x, x.flip(-1)], dim=0) for fp32 [1,C,H,W] (test_msc_flip_voc.py:68,82)."""
+    _lib.require_device()
+    x = x.contiguous().float()
+    n, C, H, W = x.shape
+    out = torch.empty(2 * n, C, H, W, dtype=torch.float32, device=x.device)
+    rc = _lib.lib().wc_flip_concat(_lib.ptr(x), _lib.ptr(out), n * C, H, W, _lib.stream_ptr())
+    _lib.check(rc, "wc_flip_concat")
+    return out
+
+
+def msc_accumulate(seg2: torch.Tensor, acc: torch.Tensor, weight: float, first: bool) -> torch.Tensor:
+    """acc (+)= weight * (R(seg2[0]) + flip(R(seg2[1]))) / 2 with R the bilinear resize to acc's size."""
+    _lib.require_device()
+    seg2 = seg2.contiguous()
+    two, C, hs, ws = seg2.shape
+    assert two == 2 and acc.is_contiguous() and acc.shape[0] == C
+    rc = _lib.lib().wc_msc_accumulate(_lib.ptr(seg2), _lib.ptr(acc), C, hs, ws, acc.shape[1], acc.shape[2],
+                                      ctypes.c_float(weight), int(first), _lib.stream_ptr())
+    _lib.check(rc, "wc_msc_accumulate")
+    return acc
+
+
+def upsample_argmax_hist(logits: torch.Tensor, size, gt: torch.Tensor = None, hist: torch.Tensor = None,
+                         want_pred: bool = True):
+    """argmax over classes of the bilinear resize of logits [C,h,w] to `size`; optional confusion-matrix update."""
+    _lib.require_device()
+    logits = logits.contiguous()
+    C, h, w = logits.shape
+    Ho, Wo = int(size[0]), int(size[1])
+    pred = torch.empty(Ho, Wo, dtype=torch.int32, device=logits.device) if want_pred else None
+    if gt is not None:
+        assert gt.dtype == torch.int16 and gt.is_contiguous() and tuple(gt.shape) == (Ho, Wo)
+        assert hist.dtype == torch.int64 and hist.is_contiguous() and hist.numel() == C * C
+    rc = _lib.lib().wc_upsample_argmax_hist(_lib.ptr(logits), C, h, w, Ho, Wo, _lib.ptr(pred), _lib.ptr(gt),
+                                            _lib.ptr(hist), _lib.stream_ptr())
+    _lib.check(rc, "wc_upsample_argmax_hist")
+    return pred
+
+
+def confusion_hist(pred: torch.Tensor, gt: torch.Tensor, hist: torch.Tensor) -> torch.Tensor:
+    """hist[gt*C+pred] += 1 for valid gt (utils/evaluate.py:9-15); pred int64, gt int16, hist int64 [C,C]."""
+    _lib.require_device()
+    assert pred.dtype == torch.int64 and gt.dtype == torch.int16 and hist.dtype == torch.int64
+    pred, gt = pred.contiguous(), gt.contiguous()
+    assert pred.numel() == gt.numel()
+    rc = _lib.lib().wc_confusion_hist(_lib.ptr(pred), _lib.ptr(gt), ctypes.c_long(pred.numel()), hist.shape[0],
+                                      _lib.ptr(hist), _lib.stream_ptr())
+    _lib.check(rc, "wc_confusion_hist")
+    return hist
