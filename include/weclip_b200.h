@@ -11,7 +11,8 @@
  *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises
  *     the device and nothing allocates device memory (callers pass workspaces sized by *_workspace_bytes);
  *   - return value: 0 = OK, negative = error (WC_ERR_*); wc_last_error() returns a thread-local message;
- *   - tensors are dense row-major with the shapes given; fp32 unless stated; "bf16" = __nv_bfloat16 bits.
+ *   - tensors are dense row-major with the shapes given; fp32 unless stated; "h16" = IEEE fp16 (__half) bits,
+ *     the 16-bit tensor-core operand type of this library (fp32 accumulation everywhere).
  */
 #ifndef WECLIP_B200_H_
 #define WECLIP_B200_H_
@@ -78,22 +79,22 @@ int wc_argmax_lut(const float* masks, const int64_t* lut, int64_t* labels,
                   const int* ch_off_host, int B, int H, int W, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
- * Tensor-core GEMM (tcgen05 + TMEM + TMA), bf16 inputs, fp32 accumulation:
+ * Tensor-core GEMM (tcgen05 + TMEM + TMA), h16 inputs, fp32 accumulation:
  *     out[b] = act(alpha * A[b] @ B[b]^T + bias) (+ resid[b])
- * A [batch,M,K] and B [batch,N,K] are bf16, K contiguous (lda/ldb/a_bs/b_bs in elements, multiples of 8;
- * b_bs = 0 broadcasts B).  out is fp32 or bf16 (out_bf16), row-major [M,N] with row stride ldo, or
+ * A [batch,M,K] and B [batch,N,K] are h16, K contiguous (lda/ldb/a_bs/b_bs in elements, multiples of 8;
+ * b_bs = 0 broadcasts B).  out is fp32 or h16 (out_f16), row-major [M,N] with row stride ldo, or
  * transposed [N,M] (out_trans: element (m,n) at n*ldo+m).  bias is fp32 [N] or NULL; resid is fp32 with the
  * layout of out (may alias a fp32 out) or NULL.  act: 0 none, 1 ReLU, 2 QuickGELU, 3 sigmoid.
  * This is the building block behind every nn.Linear / F.linear / bmm on the path (clip/model.py:198-213,
  * clip/myAtt.py:53-64,199-201,320-321, segformer_head.py:13-28,69-80, model_attn_aff_voc.py:134-137); it is
  * exported for the numerics tests and the tensor-pipe roofline micro-bench.
  * ---------------------------------------------------------------------------------------------- */
-int wc_gemm_bf16(const void* A, const void* B, void* out, const float* bias, const float* resid,
+int wc_gemm_f16(const void* A, const void* B, void* out, const float* bias, const float* resid,
                  int M, int N, int K, int batch, long lda, long ldb, long ldo, long a_bs, long b_bs, long o_bs,
-                 int out_bf16, int out_trans, int act, float alpha, void* stream);
+                 int out_f16, int out_trans, int act, float alpha, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
- * Weights.  "bf16" pointers are __nv_bfloat16 row-major [out_features, in_features] (nn.Linear layout,
+ * Weights.  "h16" pointers are h16 row-major [out_features, in_features] (nn.Linear layout,
  * K contiguous = the GEMM's B operand); biases / LayerNorm parameters are fp32.
  * ---------------------------------------------------------------------------------------------- */
 typedef struct wc_block_weights {           /* one ResidualAttentionBlock, clip/model.py:191-214 */
@@ -105,7 +106,7 @@ typedef struct wc_block_weights {           /* one ResidualAttentionBlock, clip/
 } wc_block_weights;
 
 typedef struct wc_vit_weights {             /* VisionTransformer, clip/model.py:246-262 */
-    const void* conv1_w;                    /* bf16 [768, 3*16*16] = conv1.weight flattened */
+    const void* conv1_w;                    /* h16 [768, 3*16*16] = conv1.weight flattened */
     const float* class_emb;                 /* [768] */
     const float* pos_emb;                   /* [pos_grid^2+1, 768] */
     int pos_grid;                           /* 14 */
@@ -114,19 +115,19 @@ typedef struct wc_vit_weights {             /* VisionTransformer, clip/model.py:
     const float *ln_post_w, *ln_post_b;
     const float* proj;                      /* fp32 [768,512] */
     /* block 12, transposed copies for the Grad-CAM input-gradient GEMMs (dX = dY @ W): */
-    const void* w_proj_t;                   /* bf16 [3072,768] = c_proj.weight^T */
-    const void* w_fc_t;                     /* bf16 [768,3072] = c_fc.weight^T */
-    const void* w_out_t;                    /* bf16 [768,768]  = out_proj.weight^T */
+    const void* w_proj_t;                   /* h16 [3072,768] = c_proj.weight^T */
+    const void* w_fc_t;                     /* h16 [768,3072] = c_fc.weight^T */
+    const void* w_out_t;                    /* h16 [768,768]  = out_proj.weight^T */
     const float* w_in_f32;                  /* fp32 [2304,768] = in_proj_weight */
     float logit_scale_exp;                  /* exp(logit_scale), clip/model.py:422 */
 } wc_vit_weights;
 
 typedef struct wc_decoder_weights {         /* SegFormerHead (segformer_head.py:49-80) + DecoderTransformer */
-    const void* fuse_w1; const float* fuse_b1;   /* bf16 [11,256,768], fp32 [11,256]  (linears_modulelist.i.proj) */
-    const void* fuse_w2; const float* fuse_b2;   /* bf16 [11,256,256], fp32 [11,256]  (.proj_2) */
-    const void* fuse_wf; const float* fuse_bf;   /* bf16 [256,2816],   fp32 [256]     (linear_fuse, 1x1 conv) */
+    const void* fuse_w1; const float* fuse_b1;   /* h16 [11,256,768], fp32 [11,256]  (linears_modulelist.i.proj) */
+    const void* fuse_w2; const float* fuse_b2;   /* h16 [11,256,256], fp32 [11,256]  (.proj_2) */
+    const void* fuse_wf; const float* fuse_bf;   /* h16 [256,2816],   fp32 [256]     (linear_fuse, 1x1 conv) */
     wc_block_weights blocks[3];                  /* width 256, 8 heads (TransDecoder.py:104-110) */
-    const void* pred_w;  const float* pred_b;    /* bf16 [C,256], fp32 [C]            (linear_pred, 1x1 conv) */
+    const void* pred_w;  const float* pred_b;    /* h16 [C,256], fp32 [C]            (linear_pred, 1x1 conv) */
     int num_classes;
 } wc_decoder_weights;
 
@@ -134,7 +135,7 @@ typedef struct wc_decoder_weights {         /* SegFormerHead (segformer_head.py:
  * Encoder: patch embed, class token, resized positional embedding, ln_pre, 11 of the 12 blocks
  * (clip/model.py:264-287 + :225-243 via clip_tool.py:31-41 / CLIP.encode_image :387-390).
  *   img       fp32 [N,3,H,W]
- *   taps      bf16 [11, N*L, 768]   block outputs F_0..F_10 (token-major, image-major rows; L = h*w+1)
+ *   taps      h16 [11, N*L, 768]   block outputs F_0..F_10 (token-major, image-major rows; L = h*w+1)
  *   x_last    fp32 [N*L, 768]       F_10 in fp32 (input of block 12 / Grad-CAM)
  *   attn_avg  fp32 [n_attn(+slack), N, L, L]  head-averaged attention (myAtt.py:323-326) of the LAST n_attn
  *             encoder blocks, oldest first; may be NULL when n_attn == 0
@@ -151,9 +152,9 @@ int wc_decoder_fwd(const wc_decoder_weights* w, const void* taps, int N, int h, 
                    float* fts, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Stand-alone pieces exported for the numerics tests (same kernels the two calls above launch). */
-int wc_layernorm(const float* x, const float* w, const float* b, void* out_bf16, float* out_f32, long rows, int E,
+int wc_layernorm(const float* x, const float* w, const float* b, void* out_f16, float* out_f32, long rows, int E,
                  void* stream);
-int wc_softmax_headmean(const float* S, void* P_bf16, float* avg, int n_img, int heads, int L, int Lp, void* stream);
+int wc_softmax_headmean(const float* S, void* P_f16, float* avg, int n_img, int heads, int L, int Lp, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Grad-CAM head.  Replaces CLIP.forward_last_layer (clip/model.py:407-429) + GradCAM.__call__

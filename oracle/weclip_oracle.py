@@ -239,12 +239,14 @@ def box_mask(cam: np.ndarray, threshold: float) -> np.ndarray:
     return mask
 
 
-def refine_cams(cams: np.ndarray, trans_mat: Tensor, threshold: float) -> List[Tensor]:
-    """clip/clip_tool.py:179-191 — cam' = (T * mask[None,:]) @ cam, per class."""
+def refine_cams(cams: np.ndarray, trans_mat: Tensor, threshold: float, masks=None) -> List[Tensor]:
+    """clip/clip_tool.py:179-191 — cam' = (T * mask[None,:]) @ cam, per class.  ``masks`` (test hook) overrides the
+    box masks so that a test can hold the discontinuous threshold decision fixed."""
     out = []
-    for cam in cams:
+    for k, cam in enumerate(cams):
         h, w = cam.shape
-        m = torch.from_numpy(box_mask(cam, threshold)).view(1, h * w)
+        bm = box_mask(cam, threshold) if masks is None else np.asarray(masks[k], dtype=np.float32)
+        m = torch.from_numpy(bm).view(1, h * w)
         out.append(torch.matmul(trans_mat * m, torch.from_numpy(cam).view(-1, 1)).reshape(h, w))
     return out
 
@@ -356,7 +358,7 @@ def label_ids_from_map(lab: np.ndarray) -> List[int]:
 
 def weclip_forward(img: Tensor, label_maps: Sequence[np.ndarray], sd: Dict[str, Tensor], fg_text: Tensor,
                    bg_text: Tensor, mode: str = "val", iter_num: int = 1, dataset: str = "voc",
-                   mimic_fp16: bool = True, return_intermediates: bool = False):
+                   mimic_fp16: bool = True, return_intermediates: bool = False, box_masks=None):
     """WeCLIP_model/model_attn_aff_voc.py:107-175 (COCO twin model_attn_aff_coco.py:100-170) with
     clip/clip_tool.py:106-197 inlined.  ``label_maps[i]`` is the decoded label PNG of image i.
     Returns (seg [N,C,h,w], cam_labels [N,Hc,Wc] int64 | None, attn_pred [N,P,P])."""
@@ -383,7 +385,7 @@ def weclip_forward(img: Tensor, label_maps: Sequence[np.ndarray], sd: Dict[str, 
         stack = torch.cat([attn_stack[i], attn_last], dim=0)
         aff = rfm_attention(stack, attn_pred[i:i + 1], require_seg_trans, window)
         tm = compute_trans_mat(aff)
-        refined = refine_cams(cams, tm, thr)
+        refined = refine_cams(cams, tm, thr, None if box_masks is None else box_masks[i])
         size_wh = (W, H) if mode == "train" else (ori_w, ori_h)
         up = generate_cam_label(refined, size_wh)
         full = cams_with_bg(up)
@@ -391,6 +393,7 @@ def weclip_forward(img: Tensor, label_maps: Sequence[np.ndarray], sd: Dict[str, 
         labels_out.append(refine_labels(img[i], full, valid_key))
         inter["cams"].append(cams); inter["cams_refined"].append(torch.stack(refined)); inter["cams_up"].append(up)
         inter["trans_mat"].append(tm); inter["keys"].append(ids); inter["par_in"].append(full)
+        inter.setdefault("box_masks", []).append(np.stack([box_mask(c, thr) for c in cams]))
     out = (seg, torch.stack(labels_out, dim=0), attn_pred)
     return out + (inter,) if return_intermediates else out
 

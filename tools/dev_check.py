@@ -35,7 +35,7 @@ def main():
     stat("seg", seg, seg_o)
     print("seg argmax agree", (seg.argmax(1).cpu() == seg_o.argmax(1)).float().mean().item())
     # decoder in isolation: feed the oracle's taps (bf16) so that encoder error does not enter
-    taps_in = torch.stack([t.permute(1, 0, 2).reshape(N * L, 768) for t in taps_o]).cuda().bfloat16().contiguous()
+    taps_in = torch.stack([t.permute(1, 0, 2).reshape(N * L, 768) for t in taps_o]).cuda().half().contiguous()
     seg2, ap2, fts2 = eng.decoder(taps_in, N, h, w, want_fts=True)
     stat("fts (oracle taps)", fts2.view(N, h * w, 256), fts_o.flatten(2).permute(0, 2, 1))
     stat("attn_pred (oracle taps)", ap2, ap_o)

@@ -33,7 +33,7 @@ def prof_summary():
 class MscFlipVoc:
     name = ("cfg3: test_msc_flip_voc val, scales 1.0/0.75/1.25 + flip, 512x512 images and labels, 21 classes, "
             "K per image from the VOC histogram")
-    dtype = "bf16"
+    dtype = "f16"
     n_classes, n_fg, n_bg, dataset, subdir = 21, 20, 25, "voc", "SegmentationClassAug"
     scales = (1.0, 0.75, 1.25)
     H = W = 512

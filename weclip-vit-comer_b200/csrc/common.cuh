@@ -1,7 +1,7 @@
 // Shared helpers for libweclip_sm100.so (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
@@ -9,6 +9,12 @@
 #include "../../include/weclip_b200.h"
 
 namespace wc {
+
+// 16-bit GEMM operand type.  fp16, not bf16: the reference's own GPU weights are fp16 (clip/model.py:461-476), so real
+// checkpoints load bit-exactly, and the 11-bit significand keeps activations 4x closer to the fp32 oracle at the same
+// tensor-core rate.  Accumulation is always fp32 (TMEM); gradients are power-of-two scaled (gradcam.cu).
+using h16 = __half;
+using h16x2 = __half2;
 
 extern thread_local char g_err[512];
 

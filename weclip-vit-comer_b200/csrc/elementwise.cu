@@ -6,11 +6,11 @@ namespace wc {
 
 // ---------------------------------------------------------------------------------------------------
 // LayerNorm over the last dim (clip/model.py:177-183: fp32 statistics, eps 1e-5).  One warp per row,
-// the row lives in registers (E <= 1024), 128-bit loads.  Writes bf16 (GEMM operand) and/or fp32.
+// the row lives in registers (E <= 1024), 128-bit loads.  Writes h16 (GEMM operand) and/or fp32.
 // ---------------------------------------------------------------------------------------------------
 template <int VPL>   // float4 vectors per lane: E = 128 * VPL
 __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w,
-                                                        const float* __restrict__ b, __nv_bfloat16* __restrict__ out_bf,
+                                                        const float* __restrict__ b, h16* __restrict__ out_h,
                                                         float* __restrict__ out_f, long rows, int E) {
     const long row = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
@@ -42,26 +42,26 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
         y.z = (v[i].z - mean) * rstd * ww.z + bb.z;
         y.w = (v[i].w - mean) * rstd * ww.w + bb.w;
         if (out_f) reinterpret_cast<float4*>(out_f + row * E)[c4] = y;
-        if (out_bf) {
-            __nv_bfloat162 lo = __floats2bfloat162_rn(y.x, y.y), hi = __floats2bfloat162_rn(y.z, y.w);
+        if (out_h) {
+            h16x2 lo = __floats2half2_rn(y.x, y.y), hi = __floats2half2_rn(y.z, y.w);
             uint2 pk;
             pk.x = *reinterpret_cast<uint32_t*>(&lo);
             pk.y = *reinterpret_cast<uint32_t*>(&hi);
-            reinterpret_cast<uint2*>(out_bf + row * E)[c4] = pk;
+            reinterpret_cast<uint2*>(out_h + row * E)[c4] = pk;
         }
     }
 }
 
-int launch_layernorm(const float* x, const float* w, const float* b, __nv_bfloat16* out_bf, float* out_f, long rows,
+int launch_layernorm(const float* x, const float* w, const float* b, h16* out_h, float* out_f, long rows,
                      int E, cudaStream_t st) {
-    WC_CHECK_ARG(x && w && b && rows > 0 && (out_bf || out_f));
+    WC_CHECK_ARG(x && w && b && rows > 0 && (out_h || out_f));
     const unsigned grid = (unsigned)ceil_div(rows, 8L);
-    ProfScope prof(PK_LAYERNORM, (double)rows * E * (4.0 + (out_bf ? 2.0 : 0.0) + (out_f ? 4.0 : 0.0)), st);
+    ProfScope prof(PK_LAYERNORM, (double)rows * E * (4.0 + (out_h ? 2.0 : 0.0) + (out_f ? 4.0 : 0.0)), st);
     switch (E) {
-        case 256: layernorm_kernel<2><<<grid, 256, 0, st>>>(x, w, b, out_bf, out_f, rows, E); break;
-        case 512: layernorm_kernel<4><<<grid, 256, 0, st>>>(x, w, b, out_bf, out_f, rows, E); break;
-        case 768: layernorm_kernel<6><<<grid, 256, 0, st>>>(x, w, b, out_bf, out_f, rows, E); break;
-        case 1024: layernorm_kernel<8><<<grid, 256, 0, st>>>(x, w, b, out_bf, out_f, rows, E); break;
+        case 256: layernorm_kernel<2><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, rows, E); break;
+        case 512: layernorm_kernel<4><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, rows, E); break;
+        case 768: layernorm_kernel<6><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, rows, E); break;
+        case 1024: layernorm_kernel<8><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, rows, E); break;
         default: return fail(WC_ERR_UNSUPPORTED, "%s: LayerNorm width %ld not instantiated", __func__, (long)E);
     }
     WC_LAUNCH_CHECK();
@@ -70,11 +70,11 @@ int launch_layernorm(const float* x, const float* w, const float* b, __nv_bfloat
 
 // ---------------------------------------------------------------------------------------------------
 // Row softmax of the attention scores for all heads of one (image, query row) + mean over heads
-// (clip/myAtt.py:57 softmax, :323-326 head average).  S fp32 [N*heads, L, Lp] -> P bf16 same layout,
+// (clip/myAtt.py:57 softmax, :323-326 head average).  S fp32 [N*heads, L, Lp] -> P h16 same layout,
 // avg fp32 [N, L, L] (optional).  One CTA per (row, image); the head-mean accumulates in shared memory so
 // each output element is written once (4*L^2 bytes per image instead of 12x).
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) softmax_headmean_kernel(const float* __restrict__ S, __nv_bfloat16* __restrict__ P,
+__global__ void __launch_bounds__(256) softmax_headmean_kernel(const float* __restrict__ S, h16* __restrict__ P,
                                                                float* __restrict__ avg, int heads, int L, int Lp) {
     extern __shared__ float sm_avg[];   // [L]
     __shared__ float red[32];
@@ -92,10 +92,10 @@ __global__ void __launch_bounds__(256) softmax_headmean_kernel(const float* __re
         for (int c = tid; c < L; c += 256) sum += __expf(s[c] - mx);
         sum = block_sum(sum, red);
         const float inv = 1.f / sum;
-        __nv_bfloat16* p = P + base;
+        h16* p = P + base;
         for (int c = tid; c < L; c += 256) {
             const float v = __expf(s[c] - mx) * inv;
-            p[c] = __float2bfloat16(v);
+            p[c] = __float2half_rn(v);
             if (avg) sm_avg[c] += v * inv_h;   // each thread owns its columns: no race
         }
     }
@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(256) softmax_headmean_kernel(const float* __re
     }
 }
 
-int launch_softmax_headmean(const float* S, __nv_bfloat16* P, float* avg, int n_img, int heads, int L, int Lp, cudaStream_t st) {
+int launch_softmax_headmean(const float* S, h16* P, float* avg, int n_img, int heads, int L, int Lp, cudaStream_t st) {
     WC_CHECK_ARG(S && P && n_img > 0 && heads > 0 && L > 0 && Lp >= L && n_img <= 65535);
     dim3 grid(L, n_img);
     ProfScope prof(PK_SOFTMAX, (double)n_img * L * L * (6.0 * heads + (avg ? 4.0 : 0.0)), st);
@@ -115,10 +115,10 @@ int launch_softmax_headmean(const float* S, __nv_bfloat16* P, float* avg, int n_
 }
 
 // ---------------------------------------------------------------------------------------------------
-// Patch gather: img fp32 [N,3,H,W] -> patches bf16 [N*P, 768], k = c*256 + ky*16 + kx (the flattening of
+// Patch gather: img fp32 [N,3,H,W] -> patches h16 [N*P, 768], k = c*256 + ky*16 + kx (the flattening of
 // conv1.weight [768,3,16,16], clip/model.py:246,267).  The conv floors: only h*16 x w*16 pixels are used.
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) im2col16_kernel(const float* __restrict__ img, __nv_bfloat16* __restrict__ out,
+__global__ void __launch_bounds__(256) im2col16_kernel(const float* __restrict__ img, h16* __restrict__ out,
                                                        int H, int W, int h, int w) {
     // one CTA per (patch row py, image): 16 image rows x (w*16) pixels x 3 channels
     const int py = blockIdx.x, n = blockIdx.y;
@@ -128,11 +128,11 @@ __global__ void __launch_bounds__(256) im2col16_kernel(const float* __restrict__
         const int c = r >> 4, ky = r & 15;
         const float v = img[((size_t)(n * 3 + c) * H + (py * 16 + ky)) * W + x];
         const int px = x >> 4, kx = x & 15;
-        out[((size_t)(n * h + py) * w + px) * 768 + c * 256 + ky * 16 + kx] = __float2bfloat16(v);
+        out[((size_t)(n * h + py) * w + px) * 768 + c * 256 + ky * 16 + kx] = __float2half_rn(v);
     }
 }
 
-int launch_im2col16(const float* img, __nv_bfloat16* out, int N, int H, int W, cudaStream_t st) {
+int launch_im2col16(const float* img, h16* out, int N, int H, int W, cudaStream_t st) {
     const int h = H / 16, w = W / 16;
     WC_CHECK_ARG(img && out && N > 0 && h > 0 && w > 0 && N <= 65535);
     ProfScope prof(PK_ENC_MISC, 0.0, st);
@@ -189,12 +189,12 @@ int launch_cls_row(float* x, const float* cls, const float* pos, int N, int L, i
     return WC_OK;
 }
 
-// fp32 -> bf16 cast (contiguous)
-__global__ void cast_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, size_t n) {
+// fp32 -> h16 cast (contiguous)
+__global__ void cast_bf16_kernel(const float* __restrict__ x, h16* __restrict__ y, size_t n) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) y[i] = __float2bfloat16(x[i]);
+    if (i < n) y[i] = __float2half_rn(x[i]);
 }
-int launch_cast_bf16(const float* x, __nv_bfloat16* y, size_t n, cudaStream_t st) {
+int launch_cast_bf16(const float* x, h16* y, size_t n, cudaStream_t st) {
     ProfScope prof(PK_ENC_MISC, 0.0, st);
     cast_bf16_kernel<<<(unsigned)ceil_div(n, (size_t)256), 256, 0, st>>>(x, y, n);
     WC_LAUNCH_CHECK();

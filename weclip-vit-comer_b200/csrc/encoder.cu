@@ -6,7 +6,7 @@
 
 namespace wc {
 
-static GemmOperand op(const bf16* p, long rows, long ld, long bs0 = 0, long bs1 = 0) { return GemmOperand{p, rows, ld, bs0, bs1}; }
+static GemmOperand op(const h16* p, long rows, long ld, long bs0 = 0, long bs1 = 0) { return GemmOperand{p, rows, ld, bs0, bs1}; }
 
 int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L, int E, int heads, cudaStream_t st) {
     const int M = n_img * L, hd = E / heads;
@@ -17,7 +17,7 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
     // packed in-proj + head split, q pre-scaled by 1/sqrt(hd) (myAtt.py:199-201,257-268,54)
     {
         GemmProblem p; p.M = M; p.N = 3 * E; p.K = E;
-        p.A = op(b.a, M, E); p.B = op(reinterpret_cast<const bf16*>(w.w_in), 3 * E, E);
+        p.A = op(b.a, M, E); p.B = op(reinterpret_cast<const h16*>(w.w_in), 3 * E, E);
         p.epi.mode = GM_QKV; p.epi.bias = w.b_in; p.epi.q = b.q; p.epi.k = b.k; p.epi.v = b.v; p.epi.vt = b.vt;
         p.epi.L = L; p.epi.Lp = (int)Lp; p.epi.heads = heads; p.epi.hd = hd; p.epi.qscale = 1.f / sqrtf((float)hd);
         if ((rc = launch_gemm(p, st))) return rc;
@@ -36,13 +36,13 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
         GemmProblem p; p.M = L; p.N = hd; p.K = L; p.nb0 = heads; p.nb1 = n_img;
         p.A = op(b.P, L, Lp, (long)L * Lp, (long)heads * L * Lp);
         p.B = op(b.vt, hd, Lp, (long)hd * Lp, (long)heads * hd * Lp);
-        p.epi.out = b.o; p.epi.out_bf16 = 1; p.epi.ldo = E; p.epi.out_bs0 = hd; p.epi.out_bs1 = (long)L * E;
+        p.epi.out = b.o; p.epi.out_f16 = 1; p.epi.ldo = E; p.epi.out_bs0 = hd; p.epi.out_bs1 = (long)L * E;
         if ((rc = launch_gemm(p, st))) return rc;
     }
     // out-proj + residual (myAtt.py:321, model.py:212)
     {
         GemmProblem p; p.M = M; p.N = E; p.K = E;
-        p.A = op(b.o, M, E); p.B = op(reinterpret_cast<const bf16*>(w.w_out), E, E);
+        p.A = op(b.o, M, E); p.B = op(reinterpret_cast<const h16*>(w.w_out), E, E);
         p.epi.bias = w.b_out; p.epi.out = b.x_mid; p.epi.ldo = E; p.epi.resid = b.x_in; p.epi.ldr = E;
         if ((rc = launch_gemm(p, st))) return rc;
     }
@@ -50,14 +50,14 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
     if ((rc = launch_layernorm(b.x_mid, w.ln2_w, w.ln2_b, b.a, nullptr, M, E, st))) return rc;
     {
         GemmProblem p; p.M = M; p.N = 4 * E; p.K = E;
-        p.A = op(b.a, M, E); p.B = op(reinterpret_cast<const bf16*>(w.w_fc), 4 * E, E);
-        p.epi.bias = w.b_fc; p.epi.act = ACT_QUICKGELU; p.epi.out = b.u; p.epi.out_bf16 = 1; p.epi.ldo = 4 * E;
+        p.A = op(b.a, M, E); p.B = op(reinterpret_cast<const h16*>(w.w_fc), 4 * E, E);
+        p.epi.bias = w.b_fc; p.epi.act = ACT_QUICKGELU; p.epi.out = b.u; p.epi.out_f16 = 1; p.epi.ldo = 4 * E;
         if (b.u_pre) { p.epi.out2 = b.u_pre; p.epi.ld2 = 4 * E; p.epi.out2_preact = 1; }
         if ((rc = launch_gemm(p, st))) return rc;
     }
     {
         GemmProblem p; p.M = M; p.N = E; p.K = 4 * E;
-        p.A = op(b.u, M, 4 * E); p.B = op(reinterpret_cast<const bf16*>(w.w_proj), E, 4 * E);
+        p.A = op(b.u, M, 4 * E); p.B = op(reinterpret_cast<const h16*>(w.w_proj), E, 4 * E);
         p.epi.bias = w.b_proj; p.epi.out = b.x_out; p.epi.ldo = E; p.epi.resid = b.x_mid; p.epi.ldr = E;
         if (b.tap) { p.epi.out2 = b.tap; p.epi.ld2 = E; }
         if ((rc = launch_gemm(p, st))) return rc;
@@ -66,37 +66,37 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
 }
 
 // Attention scratch shared by every block of one call.
-struct AttnScratch { bf16 *a, *q, *k, *vt, *P, *o, *u; float* S; };
+struct AttnScratch { h16 *a, *q, *k, *vt, *P, *o, *u; float* S; };
 
 static AttnScratch carve_block(Arena& ar, int n_img, int L, int E, int heads) {
     const long M = (long)n_img * L, Lp = round8(L), hd = E / heads;
     AttnScratch s;
-    s.a = ar.get<bf16>(M * E);
-    s.q = ar.get<bf16>(M * E);
-    s.k = ar.get<bf16>(M * E);
-    s.vt = ar.get<bf16>((long)n_img * heads * hd * Lp);
+    s.a = ar.get<h16>(M * E);
+    s.q = ar.get<h16>(M * E);
+    s.k = ar.get<h16>(M * E);
+    s.vt = ar.get<h16>((long)n_img * heads * hd * Lp);
     s.S = ar.get<float>((long)n_img * heads * L * Lp);
-    s.P = ar.get<bf16>((long)n_img * heads * L * Lp);
-    s.o = ar.get<bf16>(M * E);
-    s.u = ar.get<bf16>(M * 4 * E);
+    s.P = ar.get<h16>((long)n_img * heads * L * Lp);
+    s.o = ar.get<h16>(M * E);
+    s.u = ar.get<h16>(M * 4 * E);
     return s;
 }
 
-static size_t encoder_layout(Arena& ar, int N, int H, int W, float** x, float** pos, bf16** patches, AttnScratch* s) {
+static size_t encoder_layout(Arena& ar, int N, int H, int W, float** x, float** pos, h16** patches, AttnScratch* s) {
     const int h = H / 16, w = W / 16, P = h * w, L = P + 1, E = 768;
     *x = ar.get<float>((long)N * L * E);
     *pos = ar.get<float>((long)L * E);
-    *patches = ar.get<bf16>((long)N * P * E);
+    *patches = ar.get<h16>((long)N * P * E);
     *s = carve_block(ar, N, L, E, 12);
     return ar.off;
 }
 
-static size_t decoder_layout(Arena& ar, int N, int P, int C, bf16** z1, bf16** cat, float** x, bf16** x_bf, AttnScratch* s) {
+static size_t decoder_layout(Arena& ar, int N, int P, int C, h16** z1, h16** cat, float** x, h16** x_bf, AttnScratch* s) {
     const int D = 256;
-    *z1 = ar.get<bf16>((long)11 * N * P * D);
-    *cat = ar.get<bf16>((long)N * P * 11 * D);
+    *z1 = ar.get<h16>((long)11 * N * P * D);
+    *cat = ar.get<h16>((long)N * P * 11 * D);
     *x = ar.get<float>((long)N * P * D);
-    *x_bf = ar.get<bf16>((long)N * P * D);
+    *x_bf = ar.get<h16>((long)N * P * D);
     *s = carve_block(ar, N, P, D, 8);
     return ar.off;
 }
@@ -107,7 +107,7 @@ using namespace wc;
 
 extern "C" size_t wc_encoder_workspace_bytes(int N, int H, int W) {
     Arena ar(nullptr, 0);
-    float *x, *pos; bf16* patches; AttnScratch s;
+    float *x, *pos; h16* patches; AttnScratch s;
     return encoder_layout(ar, N, H, W, &x, &pos, &patches, &s) + 512;
 }
 
@@ -119,10 +119,10 @@ extern "C" int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, 
     const int h = H / 16, wd = W / 16, P = h * wd, L = P + 1, E = 768;
     const long M = (long)N * L;
     Arena ar(workspace, workspace_bytes);
-    float *x, *pos; bf16* patches; AttnScratch s;
+    float *x, *pos; h16* patches; AttnScratch s;
     encoder_layout(ar, N, H, W, &x, &pos, &patches, &s);
     if (!ar.ok) return fail(WC_ERR_WORKSPACE, "%s: workspace too small (%ld bytes)", __func__, (long)workspace_bytes);
-    bf16* taps = reinterpret_cast<bf16*>(taps_);
+    h16* taps = reinterpret_cast<h16*>(taps_);
     int rc;
     // clip/model.py:266 positional embedding resized every forward; :267 conv1 as a GEMM over gathered patches;
     // :270 class token; :271 + pos; :272 ln_pre
@@ -130,7 +130,7 @@ extern "C" int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, 
     if ((rc = launch_im2col16(img, patches, N, H, W, st))) return rc;
     {
         GemmProblem p; p.M = P; p.N = E; p.K = E; p.nb0 = N;
-        p.A = op(patches, P, E, (long)P * E); p.B = op(reinterpret_cast<const bf16*>(w->conv1_w), E, E);
+        p.A = op(patches, P, E, (long)P * E); p.B = op(reinterpret_cast<const h16*>(w->conv1_w), E, E);
         p.epi.out = x + E; p.epi.ldo = E; p.epi.out_bs0 = (long)L * E;
         p.epi.resid = pos + E; p.epi.ldr = E; p.epi.resid_bs0 = 0;
         if ((rc = launch_gemm(p, st))) return rc;
@@ -151,7 +151,7 @@ extern "C" int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, 
 
 extern "C" size_t wc_decoder_workspace_bytes(int N, int h, int w, int num_classes) {
     Arena ar(nullptr, 0);
-    bf16 *z1, *cat, *xb; float* x; AttnScratch s;
+    h16 *z1, *cat, *xb; float* x; AttnScratch s;
     return decoder_layout(ar, N, h * w, num_classes, &z1, &cat, &x, &xb, &s) + 512;
 }
 
@@ -162,32 +162,32 @@ extern "C" int wc_decoder_fwd(const wc_decoder_weights* w, const void* taps_, in
     const int P = h * wd, L = P + 1, E = 768, D = 256, C = w->num_classes;
     const long M = (long)N * L, MP = (long)N * P;
     Arena ar(workspace, workspace_bytes);
-    bf16 *z1, *cat, *xb; float* x; AttnScratch s;
+    h16 *z1, *cat, *xb; float* x; AttnScratch s;
     decoder_layout(ar, N, P, C, &z1, &cat, &x, &xb, &s);
     if (!ar.ok) return fail(WC_ERR_WORKSPACE, "%s: workspace too small (%ld bytes)", __func__, (long)workspace_bytes);
-    const bf16* taps = reinterpret_cast<const bf16*>(taps_);
+    const h16* taps = reinterpret_cast<const h16*>(taps_);
     int rc;
     // segformer_head.py:13-28,69-76: per-layer MLP on the patch tokens (cls row skipped via the +E pointer offset);
     // one grouped launch for all 11 layers x N images
     {
         GemmProblem p; p.M = P; p.N = D; p.K = E; p.nb0 = N; p.nb1 = 11;
         p.A = op(taps + E, P, E, (long)L * E, M * E);
-        p.B = op(reinterpret_cast<const bf16*>(w->fuse_w1), D, E, 0, (long)D * E);
+        p.B = op(reinterpret_cast<const h16*>(w->fuse_w1), D, E, 0, (long)D * E);
         p.epi.bias = w->fuse_b1; p.epi.bias_bs1 = D; p.epi.act = ACT_RELU;
-        p.epi.out = z1; p.epi.out_bf16 = 1; p.epi.ldo = D; p.epi.out_bs0 = (long)P * D; p.epi.out_bs1 = MP * D;
+        p.epi.out = z1; p.epi.out_f16 = 1; p.epi.ldo = D; p.epi.out_bs0 = (long)P * D; p.epi.out_bs1 = MP * D;
         if ((rc = launch_gemm(p, st))) return rc;
     }
     {   // proj_2, written straight into the channel-concatenated layout (segformer_head.py:77: cat on dim=1)
         GemmProblem p; p.M = (int)MP; p.N = D; p.K = D; p.nb0 = 11;
         p.A = op(z1, MP, D, MP * D);
-        p.B = op(reinterpret_cast<const bf16*>(w->fuse_w2), D, D, (long)D * D);
+        p.B = op(reinterpret_cast<const h16*>(w->fuse_w2), D, D, (long)D * D);
         p.epi.bias = w->fuse_b2; p.epi.bias_bs0 = D;
-        p.epi.out = cat; p.epi.out_bf16 = 1; p.epi.ldo = 11 * D; p.epi.out_bs0 = D;
+        p.epi.out = cat; p.epi.out_f16 = 1; p.epi.ldo = 11 * D; p.epi.out_bs0 = D;
         if ((rc = launch_gemm(p, st))) return rc;
     }
     {   // linear_fuse 1x1 conv (segformer_head.py:78); Dropout2d is identity in eval
         GemmProblem p; p.M = (int)MP; p.N = D; p.K = 11 * D;
-        p.A = op(cat, MP, 11 * D); p.B = op(reinterpret_cast<const bf16*>(w->fuse_wf), D, 11 * D);
+        p.A = op(cat, MP, 11 * D); p.B = op(reinterpret_cast<const h16*>(w->fuse_wf), D, 11 * D);
         p.epi.bias = w->fuse_bf; p.epi.out = x; p.epi.ldo = D; p.epi.out2 = xb; p.epi.ld2 = D;
         if ((rc = launch_gemm(p, st))) return rc;
     }
@@ -207,18 +207,18 @@ extern "C" int wc_decoder_fwd(const wc_decoder_weights* w, const void* taps_, in
     }
     {   // linear_pred 1x1 conv -> [N,C,h,w] (TransDecoder.py:121-122): transposed store
         GemmProblem p; p.M = P; p.N = C; p.K = D; p.nb0 = N;
-        p.A = op(xb, P, D, (long)P * D); p.B = op(reinterpret_cast<const bf16*>(w->pred_w), C, D);
+        p.A = op(xb, P, D, (long)P * D); p.B = op(reinterpret_cast<const h16*>(w->pred_w), C, D);
         p.epi.bias = w->pred_b; p.epi.out = seg; p.epi.out_trans = 1; p.epi.ldo = P; p.epi.out_bs0 = (long)C * P;
         if ((rc = launch_gemm(p, st))) return rc;
     }
     return WC_OK;
 }
 
-extern "C" int wc_layernorm(const float* x, const float* w, const float* b, void* out_bf16, float* out_f32, long rows,
+extern "C" int wc_layernorm(const float* x, const float* w, const float* b, void* out_f16, float* out_f32, long rows,
                             int E, void* stream) {
-    return launch_layernorm(x, w, b, reinterpret_cast<bf16*>(out_bf16), out_f32, rows, E, as_stream(stream));
+    return launch_layernorm(x, w, b, reinterpret_cast<h16*>(out_f16), out_f32, rows, E, as_stream(stream));
 }
 
 extern "C" int wc_softmax_headmean(const float* S, void* P, float* avg, int n_img, int heads, int L, int Lp, void* stream) {
-    return launch_softmax_headmean(S, reinterpret_cast<bf16*>(P), avg, n_img, heads, L, Lp, as_stream(stream));
+    return launch_softmax_headmean(S, reinterpret_cast<h16*>(P), avg, n_img, heads, L, Lp, as_stream(stream));
 }

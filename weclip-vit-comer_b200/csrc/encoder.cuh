@@ -5,7 +5,6 @@
 
 namespace wc {
 
-using bf16 = __nv_bfloat16;
 
 inline long round8(long v) { return (v + 7) & ~7L; }
 
@@ -28,17 +27,17 @@ struct Arena {
 struct BlockBuffers {
     // residual stream, fp32 [M,E]: x_in -> (attention) x_mid -> (MLP) x_out; pointers may alias
     const float* x_in; float* x_mid; float* x_out;
-    bf16* a;            // [M,E]   LayerNorm output (GEMM operand)
+    h16* a;            // [M,E]   LayerNorm output (GEMM operand)
     float* a_f32;       // optional fp32 copy of the ln_1 output (Grad-CAM hook tensor)
-    bf16 *q, *k, *vt;   // [N*heads, L, hd], [N*heads, L, hd], [N*heads, hd, Lp]
-    bf16* v;            // optional [N*heads, L, hd]
+    h16 *q, *k, *vt;   // [N*heads, L, hd], [N*heads, L, hd], [N*heads, hd, Lp]
+    h16* v;            // optional [N*heads, L, hd]
     float* S;           // [N*heads, L, Lp]
-    bf16* P;            // [N*heads, L, Lp]
-    bf16* o;            // [M,E]
-    bf16* u;            // [M,4E]  QuickGELU(c_fc)
-    bf16* u_pre;        // optional [M,4E] pre-activation
+    h16* P;            // [N*heads, L, Lp]
+    h16* o;            // [M,E]
+    h16* u;            // [M,4E]  QuickGELU(c_fc)
+    h16* u_pre;        // optional [M,4E] pre-activation
     float* attn_avg;    // optional [N,L,L]
-    bf16* tap;          // optional bf16 copy of x_out
+    h16* tap;          // optional h16 copy of x_out
 };
 
 // clip/model.py:210-214 with clip/myAtt.py:199-326 inside.

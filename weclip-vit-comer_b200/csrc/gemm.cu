@@ -6,7 +6,7 @@
 //                             tcgen05.commit releases the smem stage / signals the epilogue; owns the TMEM allocation
 //   warps 2-5 epilogue      — tcgen05.ld 32x32b.x16 (thread = accumulator row), fused bias / activation / residual /
 //                             layout scatter, direct 128-bit global stores
-// Operands are K-major bf16 (A: [M,K], B: [N,K]); accumulators are fp32 in tensor memory (BN columns).
+// Operands are K-major h16 (A: [M,K], B: [N,K]); accumulators are fp32 in tensor memory (BN columns).
 #include "gemm.cuh"
 
 #include <cudaTypedefs.h>
@@ -16,7 +16,7 @@
 namespace wc {
 
 constexpr int BM = 128;
-constexpr int BK = 64;               // 64 bf16 = 128 B = one swizzle row
+constexpr int BK = 64;               // 64 h16 = 128 B = one swizzle row
 constexpr int GEMM_THREADS = 192;
 
 // ---------------------------------------------------------------------------------------------------
@@ -96,9 +96,10 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
     d |= (uint64_t)2 << 61;
     return d;
 }
-// Instruction descriptor for kind::f16 (cute::UMMA::InstrDescriptor): D=f32, A=B=bf16, both K-major.
+// Instruction descriptor for kind::f16 (cute::UMMA::InstrDescriptor): c_format[4,6)=1 (f32), a_format[7,10)=0 and
+// b_format[10,13)=0 (fp16; 1 would be bf16), a/b major bits 15/16 = 0 (K-major), n>>3 at [17,23), m>>4 at [24,29).
 __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -125,19 +126,19 @@ __device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, float* v, in
     if (e.mode == GM_STORE) {
         const float* bias = e.bias ? e.bias + b0 * e.bias_bs0 + b1 * e.bias_bs1 + col0 : nullptr;
         const float* resid = e.resid ? e.resid + b0 * e.resid_bs0 + b1 * e.resid_bs1 + (long)row * e.ldr + col0 : nullptr;
-        __nv_bfloat16* o2 = e.out2 ? e.out2 + b0 * e.out2_bs0 + b1 * e.out2_bs1 + (long)row * e.ld2 + col0 : nullptr;
+        h16* o2 = e.out2 ? e.out2 + b0 * e.out2_bs0 + b1 * e.out2_bs1 + (long)row * e.ld2 + col0 : nullptr;
         const bool o2_vec = o2 && ncol == 16 && (reinterpret_cast<uintptr_t>(o2) & 15) == 0;
         auto store_o2 = [&]() {
             if (o2_vec) {
                 uint4 pk[2];
-                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(pk);
+                h16x2* h = reinterpret_cast<h16x2*>(pk);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                for (int j = 0; j < 8; ++j) h[j] = __floats2half2_rn(v[2 * j], v[2 * j + 1]);
                 reinterpret_cast<uint4*>(o2)[0] = pk[0];
                 reinterpret_cast<uint4*>(o2)[1] = pk[1];
             } else {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) if (j < ncol) o2[j] = __float2bfloat16(v[j]);
+                for (int j = 0; j < 16; ++j) if (j < ncol) o2[j] = __float2half_rn(v[j]);
             }
         };
 #pragma unroll
@@ -160,27 +161,27 @@ __device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, float* v, in
         if (o2 && !e.out2_preact) store_o2();
         const long ob = b0 * e.out_bs0 + b1 * e.out_bs1;
         if (e.out_trans) {
-            if (e.out_bf16) {
-                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + ob + (long)col0 * e.ldo + row;
+            if (e.out_f16) {
+                h16* o = reinterpret_cast<h16*>(e.out) + ob + (long)col0 * e.ldo + row;
 #pragma unroll
-                for (int j = 0; j < 16; ++j) if (j < ncol) o[(long)j * e.ldo] = __float2bfloat16(v[j]);
+                for (int j = 0; j < 16; ++j) if (j < ncol) o[(long)j * e.ldo] = __float2half_rn(v[j]);
             } else {
                 float* o = reinterpret_cast<float*>(e.out) + ob + (long)col0 * e.ldo + row;
 #pragma unroll
                 for (int j = 0; j < 16; ++j) if (j < ncol) o[(long)j * e.ldo] = v[j];
             }
-        } else if (e.out_bf16) {
-            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + ob + (long)row * e.ldo + col0;
+        } else if (e.out_f16) {
+            h16* o = reinterpret_cast<h16*>(e.out) + ob + (long)row * e.ldo + col0;
             if (ncol == 16 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
                 uint4 pk[2];
-                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(pk);
+                h16x2* h = reinterpret_cast<h16x2*>(pk);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                for (int j = 0; j < 8; ++j) h[j] = __floats2half2_rn(v[2 * j], v[2 * j + 1]);
                 reinterpret_cast<uint4*>(o)[0] = pk[0];
                 reinterpret_cast<uint4*>(o)[1] = pk[1];
             } else {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) if (j < ncol) o[j] = __float2bfloat16(v[j]);
+                for (int j = 0; j < 16; ++j) if (j < ncol) o[j] = __float2half_rn(v[j]);
             }
         } else {
             float* o = reinterpret_cast<float*>(e.out) + ob + (long)row * e.ldo + col0;
@@ -202,33 +203,33 @@ __device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, float* v, in
         const float* bias = e.bias + col0;
         const float sc = (which == 0) ? e.qscale : 1.f;
         uint4 pk[2];
-        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(pk);
+        h16x2* h = reinterpret_cast<h16x2*>(pk);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-            h[j] = __floats2bfloat162_rn((v[2 * j] + __ldg(bias + 2 * j)) * sc, (v[2 * j + 1] + __ldg(bias + 2 * j + 1)) * sc);
+            h[j] = __floats2half2_rn((v[2 * j] + __ldg(bias + 2 * j)) * sc, (v[2 * j + 1] + __ldg(bias + 2 * j + 1)) * sc);
         const long hb = (long)img * e.heads + head;
-        __nv_bfloat16* dst = (which == 0) ? e.q : (which == 1) ? e.k : e.v;
+        h16* dst = (which == 0) ? e.q : (which == 1) ? e.k : e.v;
         if (dst) {
             uint4* o = reinterpret_cast<uint4*>(dst + (hb * e.L + l) * e.hd + d0);
             o[0] = pk[0];
             o[1] = pk[1];
         }
         if (which == 2 && e.vt) {
-            __nv_bfloat16* o = e.vt + (hb * e.hd + d0) * (long)e.Lp + l;
-            const __nv_bfloat16* hv = reinterpret_cast<const __nv_bfloat16*>(pk);
+            h16* o = e.vt + (hb * e.hd + d0) * (long)e.Lp + l;
+            const h16* hv = reinterpret_cast<const h16*>(pk);
 #pragma unroll
             for (int j = 0; j < 16; ++j) o[(long)j * e.Lp] = hv[j];
         }
     } else {   // GM_MUL_QGELU_GRAD
         const int ab = e.aux_map ? e.aux_map[bz] : bz;
-        const __nv_bfloat16* u = e.aux + (long)ab * e.aux_bs + (long)row * e.ldaux + col0;
-        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + b0 * e.out_bs0 + b1 * e.out_bs1 + (long)row * e.ldo + col0;
+        const h16* u = e.aux + (long)ab * e.aux_bs + (long)row * e.ldaux + col0;
+        h16* o = reinterpret_cast<h16*>(e.out) + b0 * e.out_bs0 + b1 * e.out_bs1 + (long)row * e.ldo + col0;
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
             if (j < ncol) {
-                const float x = __bfloat162float(u[j]);
+                const float x = __half2float(u[j]);
                 const float s = 1.f / (1.f + __expf(-1.702f * x));
-                o[j] = __float2bfloat16(v[j] * e.alpha * (s * (1.f + 1.702f * x * (1.f - s))));
+                o[j] = __float2half_rn(v[j] * e.alpha * (s * (1.f + 1.702f * x * (1.f - s))));
             }
         }
     }
@@ -378,7 +379,7 @@ static int make_map(CUtensorMap* out, const GemmOperand& op, int K, int nb0, int
     cuuint64_t strides[3] = {row_bytes, s2, s3};
     cuuint32_t box[4] = {(cuuint32_t)BK, (cuuint32_t)box_rows, 1, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
-    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<__nv_bfloat16*>(op.ptr), dims, strides, box, estr,
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<h16*>(op.ptr), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(WC_ERR_CUDA, "%s: cuTensorMapEncodeTiled failed (%ld) rows=%ld", __func__, (long)r, op.rows);
@@ -423,16 +424,16 @@ int launch_gemm(const GemmProblem& p, cudaStream_t st) {
 using namespace wc;
 
 // Generic test / micro-bench entry: out[b] = act(alpha * A[b] @ B[b]^T + bias) (+ resid), see include/weclip_b200.h.
-extern "C" int wc_gemm_bf16(const void* A, const void* B, void* out, const float* bias, const float* resid,
+extern "C" int wc_gemm_f16(const void* A, const void* B, void* out, const float* bias, const float* resid,
                             int M, int N, int K, int batch, long lda, long ldb, long ldo, long a_bs, long b_bs, long o_bs,
-                            int out_bf16, int out_trans, int act, float alpha, void* stream) {
+                            int out_f16, int out_trans, int act, float alpha, void* stream) {
     WC_CHECK_ARG(A && B && out);
     GemmProblem p;
     p.M = M; p.N = N; p.K = K; p.nb0 = batch; p.nb1 = 1;
-    p.A = {reinterpret_cast<const __nv_bfloat16*>(A), M, lda, a_bs, 0};
-    p.B = {reinterpret_cast<const __nv_bfloat16*>(B), N, ldb, b_bs, 0};
+    p.A = {reinterpret_cast<const h16*>(A), M, lda, a_bs, 0};
+    p.B = {reinterpret_cast<const h16*>(B), N, ldb, b_bs, 0};
     p.epi.mode = GM_STORE; p.epi.act = act; p.epi.alpha = alpha; p.epi.bias = bias;
-    p.epi.out = out; p.epi.out_bf16 = out_bf16; p.epi.out_trans = out_trans; p.epi.ldo = ldo; p.epi.out_bs0 = o_bs;
+    p.epi.out = out; p.epi.out_f16 = out_f16; p.epi.out_trans = out_trans; p.epi.ldo = ldo; p.epi.out_bs0 = o_bs;
     p.epi.resid = resid; p.epi.ldr = ldo; p.epi.resid_bs0 = o_bs;
     return launch_gemm(p, as_stream(stream));
 }

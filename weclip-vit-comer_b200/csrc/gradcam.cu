@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(256) lnpost_mean_kernel(const float* __restric
 __global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msum, const float* __restrict__ proj,
                                                    const float* __restrict__ text, const __grid_constant__ ImgTable tab,
                                                    float logit_scale, int P, float* __restrict__ dm,
-                                                   float* __restrict__ probs_out) {
+                                                   float* __restrict__ gscale, float* __restrict__ probs_out) {
     __shared__ float mvec[GC_E];
     __shared__ float g[GC_EMB], dgh[GC_EMB];
     __shared__ float logit[GC_MAX_T], tnorm[GC_MAX_T], dl[GC_MAX_T];
@@ -151,6 +151,14 @@ __global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msu
             if (lane == 0) dm[(size_t)inst * GC_E + c] = a / (float)P;
         }
         __syncthreads();
+        // power-of-two gradient scale: the backward chain runs through fp16 GEMM operands and dp_k/dy is ~1e-6 for
+        // near-uniform p (below fp16's normal range); the chain is linear in the gradient, so scaling by 2^e here and
+        // dividing the channel weights by 2^e in cam_weight_kernel is exact in fp32.
+        float mx = 0.f;
+        for (int c = tid; c < GC_E; c += 512) mx = fmaxf(mx, fabsf(dm[(size_t)inst * GC_E + c]));
+        mx = block_max(mx, red);
+        if (tid == 0) gscale[inst] = (mx > 0.f && isfinite(mx)) ? exp2f(3.f - ceilf(log2f(mx))) : 1.f;
+        __syncthreads();
     }
 }
 
@@ -162,8 +170,8 @@ __global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msu
 __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                      const float* __restrict__ dy_mat, const float* __restrict__ dy_vec,
                                                      const float* __restrict__ add, float* __restrict__ out_f,
-                                                     __nv_bfloat16* __restrict__ out_bf, const __grid_constant__ InstTable it,
-                                                     int L) {
+                                                     h16* __restrict__ out_h, const __grid_constant__ InstTable it,
+                                                     int L, const float* __restrict__ gscale) {
     const long row = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= (long)it.n * L) return;
@@ -182,6 +190,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
     }
     const float rstd = rsqrtf(warp_sum(q) / GC_E + 1e-5f);
     const bool zero = (dy_vec != nullptr && l == 0);
+    const float gs = (dy_vec != nullptr && gscale != nullptr) ? gscale[it.inst0 + inst] : 1.f;
     const float4* dyr = dy_mat ? reinterpret_cast<const float4*>(dy_mat + (size_t)row * GC_E)
                                : reinterpret_cast<const float4*>(dy_vec + (size_t)(it.inst0 + inst) * GC_E);
     float c1 = 0.f, c2 = 0.f;
@@ -190,7 +199,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
         const float4 w = __ldg(reinterpret_cast<const float4*>(gamma) + lane + 32 * i);
         float4 d = zero ? make_float4(0.f, 0.f, 0.f, 0.f) : dyr[lane + 32 * i];
         v[i].x *= rstd; v[i].y *= rstd; v[i].z *= rstd; v[i].w *= rstd;      // xhat
-        gg[i] = make_float4(w.x * d.x, w.y * d.y, w.z * d.z, w.w * d.w);
+        gg[i] = make_float4(w.x * d.x * gs, w.y * d.y * gs, w.z * d.z * gs, w.w * d.w * gs);
         c1 += gg[i].x + gg[i].y + gg[i].z + gg[i].w;
         c2 += gg[i].x * v[i].x + gg[i].y * v[i].y + gg[i].z * v[i].z + gg[i].w * v[i].w;
     }
@@ -209,12 +218,12 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
             o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
         }
         if (out_f) reinterpret_cast<float4*>(out_f + (size_t)row * GC_E)[c4] = o;
-        if (out_bf) {
-            __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
+        if (out_h) {
+            h16x2 lo = __floats2half2_rn(o.x, o.y), hi = __floats2half2_rn(o.z, o.w);
             uint2 pk;
             pk.x = *reinterpret_cast<uint32_t*>(&lo);
             pk.y = *reinterpret_cast<uint32_t*>(&hi);
-            reinterpret_cast<uint2*>(out_bf + (size_t)row * GC_E)[c4] = pk;
+            reinterpret_cast<uint2*>(out_h + (size_t)row * GC_E)[c4] = pk;
         }
     }
 }
@@ -222,9 +231,9 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
 // ---------------------------------------------------------------------------------------------------
 // Fused softmax-backward reduction.  For (instance, head, 32-row chunk):  delta_i, dS = P*(dP-delta),
 //   colsum[j] += sum_{i>=1 in chunk} dS_ij ;  ds0[i] = dS_i0.
-// dP fp32 [n_inst*12, L, Lp] (chunk-local instances), P bf16 [N*12, L, Lp] (per image).
+// dP fp32 [n_inst*12, L, Lp] (chunk-local instances), P h16 [N*12, L, Lp] (per image).
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) attn_bwd_reduce_kernel(const float* __restrict__ dP, const __nv_bfloat16* __restrict__ Pm,
+__global__ void __launch_bounds__(256) attn_bwd_reduce_kernel(const float* __restrict__ dP, const h16* __restrict__ Pm,
                                                               float* __restrict__ colsum, float* __restrict__ ds0,
                                                               const __grid_constant__ InstTable it, int L, int Lp) {
     extern __shared__ float colacc[];   // [L]
@@ -235,12 +244,12 @@ __global__ void __launch_bounds__(256) attn_bwd_reduce_kernel(const float* __res
     const int r0 = blockIdx.x * 32, r1 = min(r0 + 32, L);
     for (int i = r0; i < r1; ++i) {
         const float* dp = dP + ((size_t)(inst * GC_HEADS + h) * L + i) * Lp;
-        const __nv_bfloat16* p = Pm + ((size_t)(img * GC_HEADS + h) * L + i) * Lp;
+        const h16* p = Pm + ((size_t)(img * GC_HEADS + h) * L + i) * Lp;
         float d = 0.f;
-        for (int c = tid; c < L; c += 256) d = fmaf(dp[c], __bfloat162float(p[c]), d);
+        for (int c = tid; c < L; c += 256) d = fmaf(dp[c], __half2float(p[c]), d);
         d = block_sum(d, red);
         for (int c = tid; c < L; c += 256) {
-            const float ds = __bfloat162float(p[c]) * (dp[c] - d);
+            const float ds = __half2float(p[c]) * (dp[c] - d);
             if (i >= 1) colacc[c] += ds;
             if (c == 0) ds0[(size_t)(inst * GC_HEADS + h) * L + i] = ds;
         }
@@ -254,8 +263,8 @@ __global__ void __launch_bounds__(256) attn_bwd_reduce_kernel(const float* __res
 // Row sums of dQ, dK, dV over the patch tokens -> dqkv[inst][2304] (see file header).  One CTA per (head, inst).
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) qkv_grad_sum_kernel(const float* __restrict__ colsum, const float* __restrict__ ds0,
-                                                           const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k,
-                                                           const __nv_bfloat16* __restrict__ Pm, const __nv_bfloat16* __restrict__ dO,
+                                                           const h16* __restrict__ q, const h16* __restrict__ k,
+                                                           const h16* __restrict__ Pm, const h16* __restrict__ dO,
                                                            float* __restrict__ dqkv, const __grid_constant__ InstTable it,
                                                            int L, int Lp, float qscale) {
     __shared__ float part[3][4][GC_HD];
@@ -266,10 +275,10 @@ __global__ void __launch_bounds__(256) qkv_grad_sum_kernel(const float* __restri
     const float* d0 = ds0 + (size_t)(inst * GC_HEADS + h) * L;
     float gq = 0.f, gk = 0.f, gv = 0.f;
     for (int i = grp; i < L; i += 4) {
-        gq = fmaf(cs[i], __bfloat162float(k[(hb * L + i) * GC_HD + d]), gq);
-        gk = fmaf(-d0[i], __bfloat162float(q[(hb * L + i) * GC_HD + d]), gk);
-        const float pi0 = __bfloat162float(Pm[(hb * L + i) * Lp]);
-        gv = fmaf(1.f - pi0, __bfloat162float(dO[((size_t)inst * L + i) * GC_E + h * GC_HD + d]), gv);
+        gq = fmaf(cs[i], __half2float(k[(hb * L + i) * GC_HD + d]), gq);
+        gk = fmaf(-d0[i], __half2float(q[(hb * L + i) * GC_HD + d]), gk);
+        const float pi0 = __half2float(Pm[(hb * L + i) * Lp]);
+        gv = fmaf(1.f - pi0, __half2float(dO[((size_t)inst * L + i) * GC_E + h * GC_HD + d]), gv);
     }
     part[0][grp][d] = gq; part[1][grp][d] = gk; part[2][grp][d] = gv;
     __syncthreads();
@@ -281,7 +290,7 @@ __global__ void __launch_bounds__(256) qkv_grad_sum_kernel(const float* __restri
 
 // w[inst][c] = (1/P) * sum_r dqkv[inst][r] * W_in[r][c]   (mean over patch tokens of the hooked gradient, grad_cam.py:23)
 __global__ void __launch_bounds__(128) cam_weight_kernel(const float* __restrict__ dqkv, const float* __restrict__ w_in,
-                                                         float* __restrict__ wvec, int P) {
+                                                         float* __restrict__ wvec, const float* __restrict__ gscale, int P) {
     __shared__ float dq[3 * GC_E];
     const int inst = blockIdx.y, c = blockIdx.x * 128 + threadIdx.x;
     for (int r = threadIdx.x; r < 3 * GC_E; r += 128) dq[r] = dqkv[(size_t)inst * 3 * GC_E + r];
@@ -289,7 +298,7 @@ __global__ void __launch_bounds__(128) cam_weight_kernel(const float* __restrict
     float s = 0.f;
 #pragma unroll 8
     for (int r = 0; r < 3 * GC_E; ++r) s = fmaf(dq[r], __ldg(w_in + (size_t)r * GC_E + c), s);
-    wvec[(size_t)inst * GC_E + c] = s / (float)P;
+    wvec[(size_t)inst * GC_E + c] = s / (float)P / gscale[inst];
 }
 
 // cam = relu(sum_c w_c A_c) over the patch tokens, then scale_cam_image twice (base_cam.py:55-59,144-145,150-154).
@@ -328,11 +337,11 @@ __global__ void __launch_bounds__(256) cam_kernel(const float* __restrict__ A32,
 // ---------------------------------------------------------------------------------------------------
 struct GcLayout {
     // forward (per call)
-    float *a32, *x1, *x2, *S, *msum, *dm, *dqkv, *wvec;
-    bf16 *a, *q, *k, *v, *vt, *P, *o, *u, *upre;
+    float *a32, *x1, *x2, *S, *msum, *dm, *dqkv, *wvec, *gscale;
+    h16 *a, *q, *k, *v, *vt, *P, *o, *u, *upre;
     // backward (per chunk of <= chunk instances)
     float *dx2, *da2, *dP, *colsum, *ds0;
-    bf16 *dx2b, *dh, *dx1b, *dO;
+    h16 *dx2b, *dh, *dx1b, *dO;
 };
 
 static void gc_layout(Arena& ar, GcLayout& g, int N, int L, int total_inst, int chunk) {
@@ -341,15 +350,16 @@ static void gc_layout(Arena& ar, GcLayout& g, int N, int L, int total_inst, int 
     g.S = ar.get<float>((long)N * GC_HEADS * L * Lp);
     g.msum = ar.get<float>((long)N * E); g.dm = ar.get<float>((long)total_inst * E);
     g.dqkv = ar.get<float>((long)total_inst * 3 * E); g.wvec = ar.get<float>((long)total_inst * E);
-    g.a = ar.get<bf16>(M * E); g.q = ar.get<bf16>(M * E); g.k = ar.get<bf16>(M * E); g.v = ar.get<bf16>(M * E);
-    g.vt = ar.get<bf16>((long)N * GC_HEADS * GC_HD * Lp);
-    g.P = ar.get<bf16>((long)N * GC_HEADS * L * Lp);
-    g.o = ar.get<bf16>(M * E); g.u = ar.get<bf16>(M * 4 * E); g.upre = ar.get<bf16>(M * 4 * E);
+    g.gscale = ar.get<float>((long)total_inst);
+    g.a = ar.get<h16>(M * E); g.q = ar.get<h16>(M * E); g.k = ar.get<h16>(M * E); g.v = ar.get<h16>(M * E);
+    g.vt = ar.get<h16>((long)N * GC_HEADS * GC_HD * Lp);
+    g.P = ar.get<h16>((long)N * GC_HEADS * L * Lp);
+    g.o = ar.get<h16>(M * E); g.u = ar.get<h16>(M * 4 * E); g.upre = ar.get<h16>(M * 4 * E);
     const long R = (long)chunk * L;
     g.dx2 = ar.get<float>(R * E); g.da2 = ar.get<float>(R * E);
     g.dP = ar.get<float>((long)chunk * GC_HEADS * L * Lp);
     g.colsum = ar.get<float>((long)chunk * GC_HEADS * L); g.ds0 = ar.get<float>((long)chunk * GC_HEADS * L);
-    g.dx2b = ar.get<bf16>(R * E); g.dh = ar.get<bf16>(R * 4 * E); g.dx1b = ar.get<bf16>(R * E); g.dO = ar.get<bf16>(R * E);
+    g.dx2b = ar.get<h16>(R * E); g.dh = ar.get<h16>(R * 4 * E); g.dx1b = ar.get<h16>(R * E); g.dO = ar.get<h16>(R * E);
 }
 
 // instances per backward chunk: 16 (bounds the dP scratch), but never less than the largest image's class count
@@ -407,7 +417,7 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
     WC_CUDA(cudaMemsetAsync(g.msum, 0, sizeof(float) * N * E, st));
     WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, lnpost_mean_kernel<<<dim3(ceil_div(P, 32), N), 256, 0, st>>>(g.x2, w->ln_post_w, w->ln_post_b, g.msum, L));
     WC_LAUNCH_CHECK();
-    WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, head_kernel<<<N, 512, 0, st>>>(g.msum, w->proj, text, tab, w->logit_scale_exp, P, g.dm, probs));
+    WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, head_kernel<<<N, 512, 0, st>>>(g.msum, w->proj, text, tab, w->logit_scale_exp, P, g.dm, g.gscale, probs));
     WC_LAUNCH_CHECK();
     // ---- backward, in chunks of whole images holding <= chunk instances
     const float qscale = 1.f / sqrtf((float)GC_HD);
@@ -425,7 +435,7 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
         const long R = (long)n_inst * L;
         const unsigned ln_grid = (unsigned)ceil_div(R, 8L);
         // ln_post backward (dy = dm broadcast over patch rows, class row zero)
-        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x2, w->ln_post_w, nullptr, g.dm, nullptr, g.dx2, g.dx2b, it, L));
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x2, w->ln_post_w, nullptr, g.dm, nullptr, g.dx2, g.dx2b, it, L, g.gscale));
         WC_LAUNCH_CHECK();
         // c_proj^T and the QuickGELU derivative (model.py:198-203); per image because the saved pre-activation
         // u_pre belongs to the image, shared by its classes
@@ -433,7 +443,7 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
             const int li = k_off_host[i] - it.inst0, K = k_off_host[i + 1] - k_off_host[i];
             GemmProblem p; p.M = L; p.N = 4 * E; p.K = E; p.nb0 = K;
             p.A = GemmOperand{g.dx2b + (long)li * L * E, L, E, (long)L * E, 0};
-            p.B = GemmOperand{reinterpret_cast<const bf16*>(w->w_proj_t), 4 * E, E, 0, 0};
+            p.B = GemmOperand{reinterpret_cast<const h16*>(w->w_proj_t), 4 * E, E, 0, 0};
             p.epi.mode = GM_MUL_QGELU_GRAD; p.epi.out = g.dh + (long)li * L * 4 * E; p.epi.ldo = 4 * E;
             p.epi.out_bs0 = (long)L * 4 * E; p.epi.aux = g.upre + (long)i * L * 4 * E; p.epi.ldaux = 4 * E; p.epi.aux_bs = 0;
             if ((rc = launch_gemm(p, st))) return rc;
@@ -441,18 +451,18 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
         {   // c_fc^T
             GemmProblem p; p.M = (int)R; p.N = E; p.K = 4 * E;
             p.A = GemmOperand{g.dh, R, 4 * E, 0, 0};
-            p.B = GemmOperand{reinterpret_cast<const bf16*>(w->w_fc_t), E, 4 * E, 0, 0};
+            p.B = GemmOperand{reinterpret_cast<const h16*>(w->w_fc_t), E, 4 * E, 0, 0};
             p.epi.out = g.da2; p.epi.ldo = E;
             if ((rc = launch_gemm(p, st))) return rc;
         }
         // ln_2 backward + the residual branch: dx1 = dx2 + LN2'(da2)
-        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x1, w->blocks[11].ln2_w, g.da2, nullptr, g.dx2, nullptr, g.dx1b, it, L));
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x1, w->blocks[11].ln2_w, g.da2, nullptr, g.dx2, nullptr, g.dx1b, it, L, nullptr));
         WC_LAUNCH_CHECK();
         {   // out_proj^T (myAtt.py:321)
             GemmProblem p; p.M = (int)R; p.N = E; p.K = E;
             p.A = GemmOperand{g.dx1b, R, E, 0, 0};
-            p.B = GemmOperand{reinterpret_cast<const bf16*>(w->w_out_t), E, E, 0, 0};
-            p.epi.out = g.dO; p.epi.out_bf16 = 1; p.epi.ldo = E;
+            p.B = GemmOperand{reinterpret_cast<const h16*>(w->w_out_t), E, E, 0, 0};
+            p.epi.out = g.dO; p.epi.out_f16 = 1; p.epi.ldo = E;
             if ((rc = launch_gemm(p, st))) return rc;
         }
         // dP = dO V^T per head; V is shared by the classes of an image
@@ -473,7 +483,7 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
                                                                     g.dqkv + (long)it.inst0 * 3 * E, it, L, (int)Lp, qscale));
         WC_LAUNCH_CHECK();
         WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, cam_weight_kernel<<<dim3(E / 128, n_inst), 128, 0, st>>>(g.dqkv + (long)it.inst0 * 3 * E, w->w_in_f32,
-                                                                 g.wvec + (long)it.inst0 * E, P));
+                                                                 g.wvec + (long)it.inst0 * E, g.gscale + it.inst0, P));
         WC_LAUNCH_CHECK();
         WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, cam_kernel<<<n_inst, 256, sizeof(float) * P, st>>>(g.a32, g.wvec, cams, it, L));
         WC_LAUNCH_CHECK();

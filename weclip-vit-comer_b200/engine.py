@@ -52,7 +52,7 @@ class Engine:
 
     # ------------------------------------------------------------------ weights
     def _bf(self, t):
-        t = t.detach().to(self.device, torch.float32).contiguous().to(torch.bfloat16).contiguous()
+        t = t.detach().to(self.device, torch.float32).contiguous().to(torch.float16).contiguous()
         self._keep.append(t)
         return t.data_ptr()
 
@@ -123,7 +123,7 @@ class Engine:
         N, _, H, W = img.shape
         h, w = H // 16, W // 16
         Lt = h * w + 1
-        taps = torch.empty(N_TAPS, N * Lt, E_VIT, dtype=torch.bfloat16, device=self.device)
+        taps = torch.empty(N_TAPS, N * Lt, E_VIT, dtype=torch.float16, device=self.device)
         x_last = torch.empty(N * Lt, E_VIT, dtype=torch.float32, device=self.device)
         slots = attn_slots if attn_slots is not None else n_attn
         attn = torch.empty(max(slots, 1), N, Lt, Lt, dtype=torch.float32, device=self.device) if slots else None

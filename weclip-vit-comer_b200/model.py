@@ -77,6 +77,8 @@ class WeCLIP(nn.Module):
         self.bg_text_features = bg_text_features
         self.par = PAR(num_iter=20, dilations=[1, 2, 4, 8, 12, 24])
         self.label_reader = LabelReader()
+        self.keep_intermediates = False      # debugging / test hook: keep raw CAMs, box masks, refined CAMs in self.last
+        self.last: dict = {}
         self._device = torch.device(device)
         self._sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
         self.engine: Optional[Engine] = None
@@ -153,7 +155,10 @@ class WeCLIP(nn.Module):
             raise RuntimeError("image without foreground label (torch.stack([]) in the reference, clip_tool.py:212)")
         text = torch.cat(rows, dim=0)
         cams, _, _ = eng.gradcam(x_last, N, h, w, text, text_off, k_off, attn_last_out=attn[nl - 1])
-        refined, _ = eng.affinity_refine(attn, nl, attn_pred, N, h, w, require_seg_trans, cams, k_off, cfg["box_thr"])
+        refined, bmasks = eng.affinity_refine(attn, nl, attn_pred, N, h, w, require_seg_trans, cams, k_off,
+                                              cfg["box_thr"], want_masks=self.keep_intermediates)
+        if self.keep_intermediates:
+            self.last = dict(cams=cams, box_masks=bmasks, refined=refined, k_off=k_off, ids=ids_all)
         if len(set(sizes)) != 1:
             raise RuntimeError("stack expects each tensor to be equal size (model_attn_aff_voc.py:173)")
         Hc, Wc = sizes[0]
