@@ -30,7 +30,7 @@ extern "C" {
 #define WC_ERR_WORKSPACE (-3)
 #define WC_ERR_UNSUPPORTED (-4)
 
-#define WC_ABI_VERSION 4
+#define WC_ABI_VERSION 5
 #define WC_PAR_MAX_DIL 8
 
 /* ABI version (bumped whenever a signature changes) and last error text. */
@@ -48,6 +48,8 @@ const char* wc_prof_kind_name(int kind);
 int wc_prof_enable(int on);
 int wc_prof_reset(void);
 int wc_prof_summary(double* ms, double* work, long* launches);
+/* Raw per-launch records (call after wc_prof_summary): kind, device ms, work, 4 tags (GEMM: M, N, K, batch). */
+long wc_prof_records(int* kind, double* ms, double* work, int* tags, long cap);
 
 /* ------------------------------------------------------------------------------------------------
  * PAR — pixel-adaptive refinement.  Replaces WeCLIP_model/PAR.py:64-92 (PAR.forward), incl.
@@ -204,13 +206,14 @@ int wc_resize_bilinear(const float* in, float* out, int planes, int Hi, int Wi, 
                        float scale_factor_y, float scale_factor_x, void* stream);
 /* torch.cat([x, x.flip(-1)], dim=0) (test_msc_flip_voc.py:68,82): in [planes,H,W] -> out [2,planes,H,W]. */
 int wc_flip_concat(const float* in, float* out, int planes, int H, int W, void* stream);
-/* One scale of the msc fusion (test_msc_flip_voc.py:74,86-88,90): seg2 [2,C,hs,ws] (plain, flipped input) ->
- * acc[C,h,w] = (first ? 0 : acc) + weight * (R(seg2[0]) + flip(R(seg2[1]))) / 2, R = bilinear resize to h x w. */
-int wc_msc_accumulate(const float* seg2, float* acc, int C, int hs, int ws, int h, int w, float weight,
+/* One scale of the msc fusion (test_msc_flip_voc.py:74,86-88,90) for B same-size dataset images at once:
+ * seg2 [2,B,C,hs,ws] (plain inputs, then their flipped twins) ->
+ * acc[B,C,h,w] = (first ? 0 : acc) + weight * (R(seg2[0]) + flip(R(seg2[1]))) / 2, R = bilinear resize to h x w. */
+int wc_msc_accumulate(const float* seg2, float* acc, int B, int C, int hs, int ws, int h, int w, float weight,
                       int first, void* stream);
-/* argmax_c of the bilinear resize of logits [C,h,w] to Ho x Wo (test_msc_flip_voc.py:93-96) -> pred int32 [Ho,Wo]
- * (may be NULL) and, when gt (int16 [Ho,Wo]) and hist (int64 [C,C]) are given, hist[gt*C+pred] += 1 for 0<=gt<C. */
-int wc_upsample_argmax_hist(const float* logits, int C, int h, int w, int Ho, int Wo, int32_t* pred,
+/* argmax_c of the bilinear resize of logits [B,C,h,w] to Ho x Wo (test_msc_flip_voc.py:93-96) -> pred int32 [B,Ho,Wo]
+ * (may be NULL) and, when gt (int16 [B,Ho,Wo]) and hist (int64 [C,C]) are given, hist[gt*C+pred] += 1 for 0<=gt<C. */
+int wc_upsample_argmax_hist(const float* logits, int B, int C, int h, int w, int Ho, int Wo, int32_t* pred,
                             const int16_t* gt, int64_t* hist, void* stream);
 /* _fast_hist over flat label arrays (the CAM pseudo-label histogram, test_msc_flip_voc.py:107):
  * pred int64 [n], gt int16 [n], hist int64 [C,C] accumulated in place. */

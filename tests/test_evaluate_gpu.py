@@ -35,14 +35,22 @@ def test_msc_accumulate_matches_torch():
     g = torch.Generator().manual_seed(2)
     C, h, w = 21, 20, 27
     segs = [torch.randn(2, C, h, w, generator=g), torch.randn(2, C, 15, 20, generator=g), torch.randn(2, C, 25, 33, generator=g)]
-    acc = torch.empty(C, h, w, device="cuda")
+    acc = torch.empty(1, C, h, w, device="cuda")
     lst = []
     for i, s in enumerate(segs):
         ops.msc_accumulate(s.cuda(), acc, 1.0 / 3, i == 0)
         r = F.interpolate(s, size=(h, w), mode="bilinear", align_corners=False) if i else s
         lst.append((r[0] + r[1].flip(-1)) / 2)
     want = torch.stack(lst).mean(0)
-    assert (acc.cpu() - want).abs().max().item() < 1e-5
+    assert (acc[0].cpu() - want).abs().max().item() < 1e-5
+    # batched form: [2B,C,hs,ws] = B plain then B flipped
+    B = 3
+    sb = torch.randn(2 * B, C, 15, 20, generator=g)
+    accb = torch.empty(B, C, h, w, device="cuda")
+    ops.msc_accumulate(sb.cuda(), accb, 0.5, True)
+    r = F.interpolate(sb, size=(h, w), mode="bilinear", align_corners=False)
+    wantb = 0.5 * (r[:B] + r[B:].flip(-1)) / 2
+    assert (accb.cpu() - wantb).abs().max().item() < 1e-5
 
 
 @pytest.mark.parametrize("C", [21, 81, 150])
@@ -88,3 +96,30 @@ def test_msc_flip_image_matches_oracle():
     assert np.array_equal(h[2], O.fast_hist(lab, cam.cpu().numpy(), 21))
     sc = ev.scores()
     assert 0.0 <= sc["msc_seg"]["miou"] <= 1.0
+
+
+def test_batched_bucket_equals_image_by_image():
+    """A (H,W) bucket of B dataset images run as one [2B,...] forward per scale gives the same three confusion
+    matrices as the reference's image-by-image loop (images are independent)."""
+    sd = synth.make_state_dict(0, 21)
+    fg, bg = synth.make_text_features(7, 20, 25)
+    rng = np.random.default_rng(6)
+    root = tempfile.mkdtemp()
+    B, H, W = 3, 96, 128
+    labs, names = [], []
+    for i in range(B):
+        lab = synth.make_label_map(rng, H, W, synth.draw_label_set(rng, 20))
+        synth.write_label_png(root, "SegmentationClassAug", f"q{i}", lab)
+        labs.append(lab); names.append(f"q{i}")
+    img = synth.make_images(10, B, H, W).cuda()
+    gt = torch.from_numpy(np.stack(labs).astype(np.int16)).cuda()
+    model = WeCLIP(num_classes=21, dataset_root_path=root, device="cuda", state_dict=sd, fg_text_features=fg,
+                   bg_text_features=bg)
+    one = MscFlipEvaluator(model, 21, (1.0, 0.75, 1.25), resize_long=128)
+    for i in range(B):
+        one.process(names[i], img[i:i + 1], gt[i])
+    bat = MscFlipEvaluator(model, 21, (1.0, 0.75, 1.25), resize_long=128)
+    bat.process_batch(names, img, gt)
+    assert bat.n_images == one.n_images == B
+    assert torch.equal(one.hist, bat.hist)
+    assert int(bat.hist[0].sum()) == int((gt >= 0).logical_and(gt < 21).sum())

@@ -1,0 +1,35 @@
+"""Developer script (GPU box): per-launch device times of one msc+flip step, grouped by kernel class / GEMM shape."""
+import sys, os, ctypes, collections
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from weclip_b200 import _lib
+from weclip_b200.bench_workloads import WORKLOADS, prof_summary
+
+def main():
+    name = sys.argv[1] if len(sys.argv) > 1 else "mscflip"
+    wl = WORKLOADS[name](0, torch.device("cuda", 0))
+    for _ in range(2):
+        wl.step_device()
+    torch.cuda.synchronize()
+    L = _lib.lib()
+    L.wc_prof_reset(); L.wc_prof_enable(1)
+    wl.step_device()
+    summ = prof_summary()
+    cap = 1 << 16
+    kind = (ctypes.c_int * cap)(); ms = (ctypes.c_double * cap)(); work = (ctypes.c_double * cap)(); tags = (ctypes.c_int * (4 * cap))()
+    L.wc_prof_records.restype = ctypes.c_long
+    n = L.wc_prof_records(kind, ms, work, tags, ctypes.c_long(cap))
+    L.wc_prof_enable(0)
+    for k, (m, w, c) in summ.items():
+        if c: print(f"{k:18s} {m:9.3f} ms  {c:5d} launches")
+    groups = collections.defaultdict(lambda: [0, 0.0, 0.0])
+    for i in range(n):
+        if kind[i] == 0:
+            key = tuple(tags[4 * i:4 * i + 4])
+            g = groups[key]; g[0] += 1; g[1] += ms[i]; g[2] += work[i]
+    print("GEMM shapes (M,N,K,batch): count, total ms, TFLOP/s")
+    for key, (c, m, w) in sorted(groups.items(), key=lambda kv: -kv[1][1]):
+        print(f"  {str(key):32s} x{c:4d} {m:9.3f} ms {w / (m * 1e-3) / 1e12:8.1f} TF/s")
+
+if __name__ == "__main__":
+    main()

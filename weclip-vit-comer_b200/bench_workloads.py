@@ -76,14 +76,13 @@ class MscFlipVoc:
         self.l2_note = "working set larger than L2 (>= 101 MB of attention scores per block at 512x512, x3 scales)"
 
     def step_device(self, record=False):
-        for i in range(self.units):
-            self.ev.process(self.names[i], self.imgs_d[i:i + 1], self.labs_d[i])
+        # the step's images share one (H,W) bucket: one [2B,3,H,W] forward per scale
+        self.ev.process_batch(self.names, self.imgs_d, self.labs_d)
 
     def step_e2e(self):
-        for i in range(self.units):
-            img = self.imgs_h[i:i + 1].to(self.dev, non_blocking=True)
-            lab = self.labs_h[i].to(self.dev, non_blocking=True)
-            self.ev.process(self.names[i], img, lab)
+        img = self.imgs_h.to(self.dev, non_blocking=True)
+        lab = self.labs_h.to(self.dev, non_blocking=True)
+        self.ev.process_batch(self.names, img, lab)
         self.hist_h.copy_(self.ev.hist, non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return self.hist_h

@@ -7,7 +7,7 @@ namespace wc {
 thread_local char g_err[512] = "";
 bool g_prof_on = false;
 
-struct ProfRec { int kind; double work; cudaEvent_t e0, e1; };
+struct ProfRec { int kind; double work; cudaEvent_t e0, e1; int tag[4]; };
 static std::vector<ProfRec> g_recs;
 static std::vector<cudaEvent_t> g_pool;
 static size_t g_pool_used = 0;
@@ -24,11 +24,16 @@ static cudaEvent_t pool_event() {
 
 void prof_begin(int kind, double work, cudaStream_t st) {
     if (g_open || g_recs.size() >= (1u << 20)) return;
-    ProfRec r{kind, work, pool_event(), pool_event()};
+    ProfRec r{kind, work, pool_event(), pool_event(), {0, 0, 0, 0}};
     if (!r.e0 || !r.e1) return;
     cudaEventRecord(r.e0, st);
     g_recs.push_back(r);
     g_open = true;
+}
+void prof_tag(int a, int b, int c, int d) {
+    if (!g_open) return;
+    int* t = g_recs.back().tag;
+    t[0] = a; t[1] = b; t[2] = c; t[3] = d;
 }
 void prof_end(cudaStream_t st) {
     if (!g_open) return;
@@ -77,4 +82,18 @@ extern "C" int wc_prof_summary(double* ms, double* work, long* launches) {
         ms[r.kind] += t; work[r.kind] += r.work; launches[r.kind] += 1;
     }
     return WC_OK;
+}
+
+// Raw records (after wc_prof_summary has synchronised): up to cap entries of {kind, ms, work, tag[4]}; returns the count.
+extern "C" long wc_prof_records(int* kind, double* ms, double* work, int* tags, long cap) {
+    long n = 0;
+    for (const ProfRec& r : g_recs) {
+        if (n >= cap) break;
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, r.e0, r.e1) != cudaSuccess) continue;
+        kind[n] = r.kind; ms[n] = t; work[n] = r.work;
+        for (int i = 0; i < 4; ++i) tags[4 * n + i] = r.tag[i];
+        ++n;
+    }
+    return n;
 }

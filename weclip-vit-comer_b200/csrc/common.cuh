@@ -98,6 +98,7 @@ enum ProfKind : int {
 };
 extern bool g_prof_on;
 void prof_begin(int kind, double work, cudaStream_t st);
+void prof_tag(int a, int b, int c, int d);   // annotate the open record (GEMM: M, N, K, batch)
 void prof_end(cudaStream_t st);
 struct ProfScope {
     cudaStream_t st; bool on;

@@ -48,9 +48,11 @@ __global__ void __launch_bounds__(256) flip_concat_kernel(const float* __restric
 
 // acc[c,y,x] (+)= weight * 0.5 * (R(seg[0])[c,y,x] + R(seg[1])[c,y,w-1-x]),  R = bilinear resize hs x ws -> h x w
 __global__ void __launch_bounds__(256) msc_accumulate_kernel(const float* __restrict__ seg2, float* __restrict__ acc,
-                                                             int C, int hs, int ws, int h, int w, float sy, float sx,
+                                                             int BC, int hs, int ws, int h, int w, float sy, float sx,
                                                              float weight, int first) {
+    // c runs over B*C planes; the flipped half of seg2 [2,B,C,hs,ws] starts BC planes later
     const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y, c = blockIdx.z;
+    const int C = BC;
     if (x >= w || y >= h) return;
     float a, b;
     if (hs == h && ws == w) {
@@ -77,6 +79,9 @@ __global__ void __launch_bounds__(256) upsample_argmax_hist_kernel(const float* 
     if (smem_hist) for (int i = tid; i < C * C; i += 256) sh[i] = 0u;
     if (smem_hist) __syncthreads();
     const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+    logits += (size_t)blockIdx.z * C * h * w;
+    if (pred) pred += (size_t)blockIdx.z * Ho * Wo;
+    if (gt) gt += (size_t)blockIdx.z * Ho * Wo;
     if (x < Wo && y < Ho) {
         const Tap ty = make_tap(y, sy, h), tx = make_tap(x, sx, w);
         float best = bilerp(logits, w, ty, tx);
@@ -141,9 +146,10 @@ extern "C" int wc_flip_concat(const float* in, float* out, int planes, int H, in
     return WC_OK;
 }
 
-extern "C" int wc_msc_accumulate(const float* seg2, float* acc, int C, int hs, int ws, int h, int w, float weight,
+extern "C" int wc_msc_accumulate(const float* seg2, float* acc, int B, int C_, int hs, int ws, int h, int w, float weight,
                                  int first, void* stream) {
-    WC_CHECK_ARG(seg2 && acc && C > 0 && C <= 65535 && hs > 0 && ws > 0 && h > 0 && w > 0);
+    WC_CHECK_ARG(seg2 && acc && B > 0 && C_ > 0 && (long)B * C_ <= 65535 && hs > 0 && ws > 0 && h > 0 && w > 0);
+    const int C = B * C_;
     ProfScope prof(PK_EVAL, 0.0, as_stream(stream));
     dim3 block(32, 8), grid(ceil_div(w, 32), ceil_div(h, 8), C);
     msc_accumulate_kernel<<<grid, block, 0, as_stream(stream)>>>(seg2, acc, C, hs, ws, h, w, torch_scale(hs, h, 0.f),
@@ -152,12 +158,12 @@ extern "C" int wc_msc_accumulate(const float* seg2, float* acc, int C, int hs, i
     return WC_OK;
 }
 
-extern "C" int wc_upsample_argmax_hist(const float* logits, int C, int h, int w, int Ho, int Wo, int32_t* pred,
+extern "C" int wc_upsample_argmax_hist(const float* logits, int B, int C, int h, int w, int Ho, int Wo, int32_t* pred,
                                        const int16_t* gt, int64_t* hist, void* stream) {
-    WC_CHECK_ARG(logits && C > 0 && h > 0 && w > 0 && Ho > 0 && Wo > 0 && (pred || (gt && hist)));
+    WC_CHECK_ARG(logits && B > 0 && B <= 65535 && C > 0 && h > 0 && w > 0 && Ho > 0 && Wo > 0 && (pred || (gt && hist)));
     const int smem_hist = (gt && hist && (size_t)C * C * 4 <= 40 * 1024) ? 1 : 0;
     ProfScope prof(PK_EVAL, 0.0, as_stream(stream));
-    dim3 block(32, 8), grid(ceil_div(Wo, 32), ceil_div(Ho, 8));
+    dim3 block(32, 8), grid(ceil_div(Wo, 32), ceil_div(Ho, 8), B);
     upsample_argmax_hist_kernel<<<grid, block, smem_hist ? (size_t)C * C * 4 : 0, as_stream(stream)>>>(
         logits, C, h, w, Ho, Wo, torch_scale(h, Ho, 0.f), torch_scale(w, Wo, 0.f), pred, gt,
         reinterpret_cast<unsigned long long*>(hist), smem_hist);

@@ -1,13 +1,18 @@
-// tcgen05 GEMM kernel (sm_100a).  See gemm.cuh for the contract.
+// tcgen05 GEMM kernel (sm_100a), persistent and warp-specialised.  See gemm.cuh for the contract.
 //
-// One CTA per 128 x BN output tile, 192 threads, warp-specialised:
-//   warp 0   TMA producer   — cp.async.bulk.tensor (rank-4 maps, 128B swizzle, OOB zero-fill) into a STAGES-deep ring
-//   warp 1   MMA issuer     — one lane issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BN, K=16) x4 per k-block;
-//                             tcgen05.commit releases the smem stage / signals the epilogue; owns the TMEM allocation
-//   warps 2-5 epilogue      — tcgen05.ld 32x32b.x16 (thread = accumulator row), fused bias / activation / residual /
-//                             layout scatter, direct 128-bit global stores
-// Operands are K-major h16 (A: [M,K], B: [N,K]); accumulators are fp32 in tensor memory (BN columns).
+// grid = min(#tiles, #SMs) CTAs of 192 threads; each CTA walks output tiles t = blockIdx.x + i*gridDim.x
+// (m-block fastest, so concurrently running CTAs share the same weight tile in L2).  Tile = 128 x BN, BN in {256,128,64,32}.
+//   warp 0     TMA producer  — cp.async.bulk.tensor (rank-4 maps, 128B swizzle, OOB zero-fill) into a STAGES-deep smem ring
+//                              (192 KB: 4 stages at BN=256 ... 8 stages at BN<=64), running ahead across tile boundaries
+//   warp 1     MMA issuer    — one lane issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BN, K=16) x4 per 64-wide k-block;
+//                              tcgen05.commit frees the smem stage; accumulators are DOUBLE-BUFFERED in tensor memory
+//                              (2 x BN fp32 columns) so the next tile's mainloop overlaps this tile's epilogue
+//   warps 2-5  epilogue      — tcgen05.ld 32x32b.x32 (thread = accumulator row), transposed through a per-warp padded smem
+//                              block so that global traffic is row-contiguous 128-bit accesses (8 lanes = 128 B of one row),
+//                              fused bias / activation / residual / fp16 copy / head-major QKV scatter
+// Operands are K-major fp16 (A: [M,K], B: [N,K]); accumulators are fp32.
 #include "gemm.cuh"
+#include "tc_ptx.cuh"
 
 #include <cudaTypedefs.h>
 #include <mutex>
@@ -16,95 +21,11 @@
 namespace wc {
 
 constexpr int BM = 128;
-constexpr int BK = 64;               // 64 h16 = 128 B = one swizzle row
+constexpr int BK = 64;               // 64 fp16 = 128 B = one swizzle row
 constexpr int GEMM_THREADS = 192;
+constexpr int STG_LD = 36;           // staging row stride in floats (32 + 4: conflict-free 128-bit rows)
+constexpr int RING_BYTES = 192 * 1024;
 
-// ---------------------------------------------------------------------------------------------------
-// PTX wrappers
-// ---------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    const uint32_t addr = smem_u32(bar);
-    uint32_t done = 0;
-    const long long t0 = clock64();
-    while (true) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done) : "r"(addr), "r"(parity) : "memory");
-        if (done) break;
-        if (clock64() - t0 > 4000000000LL) {   // ~2 s: a protocol bug must fault, never hang the GPU
-            printf("wc gemm: mbarrier timeout (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x);
-            __trap();
-        }
-    }
-}
-__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
-    uint32_t r[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// K-major, 128B-swizzled shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
-//   [0,14) start address >> 4 | [16,30) leading byte offset >> 4 (unused for swizzled K-major, 1) |
-//   [32,46) stride byte offset >> 4 (8 rows * 128 B = 1024) | [46,48) version = 1 | [61,64) layout = SWIZZLE_128B (2)
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
-    d |= (uint64_t)1 << 16;
-    d |= (uint64_t)(1024 >> 4) << 32;
-    d |= (uint64_t)1 << 46;
-    d |= (uint64_t)2 << 61;
-    return d;
-}
-// Instruction descriptor for kind::f16 (cute::UMMA::InstrDescriptor): c_format[4,6)=1 (f32), a_format[7,10)=0 and
-// b_format[10,13)=0 (fp16; 1 would be bf16), a/b major bits 15/16 = 0 (K-major), n>>3 at [17,23), m>>4 at [24,29).
-__host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
-    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
-}
-
-// ---------------------------------------------------------------------------------------------------
-// Epilogue
-// ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float apply_act(float x, int act) {
     switch (act) {
         case ACT_RELU: return fmaxf(x, 0.f);
@@ -117,160 +38,288 @@ __device__ __forceinline__ float apply_act(float x, int act) {
 struct KernelArgs {
     int M, N, K, nb0;
     int a_b0, a_b1, b_b0, b_b1;   // 1 when the operand really has that batch dimension (else coordinate 0)
+    int tiles_m, tiles_n, total_tiles;
+    int vec_ok;                   // every pointer / stride of the epilogue allows 4-element vector access
+    int variant;                  // variant_id() of the GM_STORE flags (fast epilogue dispatch)
     GemmEpilogue e;
 };
 
-__device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, float* v, int row, int col0, int b0, int b1, int bz) {
+__device__ __forceinline__ void store_h4(h16* p, const float* x) {
+    h16x2 lo = __floats2half2_rn(x[0], x[1]), hi = __floats2half2_rn(x[2], x[3]);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(p) = pk;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Fast epilogue paths.  The flags are template parameters (no per-row branches) and the 8 row iterations are fully
+// unrolled so that the 8 LDS.128, the 8 residual LDG.128 and the 8 STG are each issued back to back.
+// Preconditions (checked by the caller): full 32-column chunk, 4-element vector access allowed.
+// ---------------------------------------------------------------------------------------------------
+constexpr int variant_id(int f16, int act, int bias, int resid, int out2) {
+    return f16 | (act << 1) | (bias << 3) | (resid << 4) | (out2 << 5);     // out2: 0 none, 1 after act+resid, 2 before
+}
+
+template <int F16, int ACT, int BIAS, int RESID, int OUT2>
+__device__ __forceinline__ void fast_store(const KernelArgs& a, const float* stg, int lane, int row0, int col0, int b0, int b1) {
     const GemmEpilogue& e = a.e;
-    const int ncol = min(16, a.N - col0);
-    if (e.mode == GM_STORE) {
-        const float* bias = e.bias ? e.bias + b0 * e.bias_bs0 + b1 * e.bias_bs1 + col0 : nullptr;
-        const float* resid = e.resid ? e.resid + b0 * e.resid_bs0 + b1 * e.resid_bs1 + (long)row * e.ldr + col0 : nullptr;
-        h16* o2 = e.out2 ? e.out2 + b0 * e.out2_bs0 + b1 * e.out2_bs1 + (long)row * e.ld2 + col0 : nullptr;
-        const bool o2_vec = o2 && ncol == 16 && (reinterpret_cast<uintptr_t>(o2) & 15) == 0;
-        auto store_o2 = [&]() {
-            if (o2_vec) {
-                uint4 pk[2];
-                h16x2* h = reinterpret_cast<h16x2*>(pk);
+    const int cc = (lane & 7) * 4, rsub = lane >> 3, col = col0 + cc;
+    const int r_first = row0 + rsub;
+    float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (BIAS) bias = __ldg(reinterpret_cast<const float4*>(e.bias + b0 * e.bias_bs0 + b1 * e.bias_bs1 + col));
+    float4 x[8], rs[8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) h[j] = __floats2half2_rn(v[2 * j], v[2 * j + 1]);
-                reinterpret_cast<uint4*>(o2)[0] = pk[0];
-                reinterpret_cast<uint4*>(o2)[1] = pk[1];
-            } else {
+    for (int i = 0; i < 8; ++i) x[i] = *reinterpret_cast<const float4*>(stg + (i * 4 + rsub) * STG_LD + cc);
+    if (RESID) {
+        const float* rp = e.resid + b0 * e.resid_bs0 + b1 * e.resid_bs1 + (long)r_first * e.ldr + col;
 #pragma unroll
-                for (int j = 0; j < 16; ++j) if (j < ncol) o2[j] = __float2half_rn(v[j]);
-            }
-        };
+        for (int i = 0; i < 8; ++i)
+            rs[i] = (r_first + 4 * i < a.M) ? *reinterpret_cast<const float4*>(rp + (long)(4 * i) * e.ldr) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const long ob = b0 * e.out_bs0 + b1 * e.out_bs1 + (long)r_first * e.ldo + col;
+    const long o2b = OUT2 ? b0 * e.out2_bs0 + b1 * e.out2_bs1 + (long)r_first * e.ld2 + col : 0;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            if (j < ncol) {
-                float x = e.alpha * v[j];
-                if (bias) x += __ldg(bias + j);
-                v[j] = x;
+    for (int i = 0; i < 8; ++i) {
+        if (r_first + 4 * i >= a.M) break;
+        float v[4] = {e.alpha * x[i].x + bias.x, e.alpha * x[i].y + bias.y, e.alpha * x[i].z + bias.z, e.alpha * x[i].w + bias.w};
+        if (OUT2 == 2) store_h4(e.out2 + o2b + (long)(4 * i) * e.ld2, v);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) v[t] = apply_act(v[t], ACT);
+        if (RESID) { v[0] += rs[i].x; v[1] += rs[i].y; v[2] += rs[i].z; v[3] += rs[i].w; }
+        if (OUT2 == 1) store_h4(e.out2 + o2b + (long)(4 * i) * e.ld2, v);
+        if (F16) store_h4(reinterpret_cast<h16*>(e.out) + ob + (long)(4 * i) * e.ldo, v);
+        else *reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + ob + (long)(4 * i) * e.ldo) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+}
+
+// returns false when the variant is not instantiated (caller falls back to the generic path)
+__device__ __forceinline__ bool fast_store_dispatch(const KernelArgs& a, const float* stg, int lane, int row0, int col0, int b0, int b1) {
+#define WC_V(f, ac, bi, re, o2) \
+    case variant_id(f, ac, bi, re, o2): fast_store<f, ac, bi, re, o2>(a, stg, lane, row0, col0, b0, b1); return true;
+    switch (a.variant) {
+        WC_V(0, ACT_NONE, 0, 1, 0)        // patch embed + positional embedding
+        WC_V(0, ACT_NONE, 0, 0, 0)        // plain fp32 (scores, dP, c_fc^T)
+        WC_V(1, ACT_NONE, 0, 0, 0)        // plain fp16 (P V, out_proj^T)
+        WC_V(0, ACT_NONE, 1, 1, 0)        // out-proj / c_proj + residual
+        WC_V(0, ACT_NONE, 1, 1, 1)        // c_proj + residual + fp16 feature tap
+        WC_V(1, ACT_QUICKGELU, 1, 0, 0)   // c_fc
+        WC_V(1, ACT_QUICKGELU, 1, 0, 2)   // c_fc keeping the pre-activation (Grad-CAM block)
+        WC_V(1, ACT_RELU, 1, 0, 0)        // decoder fuse MLP layer 1
+        WC_V(1, ACT_NONE, 1, 0, 0)        // decoder fuse MLP layer 2
+        WC_V(0, ACT_NONE, 1, 0, 1)        // linear_fuse (+ fp16 copy)
+        WC_V(0, ACT_SIGMOID, 0, 0, 0)     // attn_pred
+        default: return false;
+    }
+#undef WC_V
+}
+
+__device__ __forceinline__ void fast_qkv(const KernelArgs& a, const float* stg, int lane, int row0, int col0, int which,
+                                         int head, int d0) {
+    const GemmEpilogue& e = a.e;
+    const int cc = (lane & 7) * 4, rsub = lane >> 3;
+    const float4 bias = __ldg(reinterpret_cast<const float4*>(e.bias + col0 + cc));
+    const float sc = (which == 0) ? e.qscale : 1.f;     // q pre-scaled by 1/sqrt(hd) (myAtt.py:54)
+    h16* dst = (which == 0) ? e.q : (which == 1) ? e.k : e.v;
+    float4 x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = *reinterpret_cast<const float4*>(stg + (i * 4 + rsub) * STG_LD + cc);
+    int row = row0 + rsub;
+    int img = row / e.L, l = row - img * e.L;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        if (row >= a.M) break;
+        float v[4] = {(x[i].x + bias.x) * sc, (x[i].y + bias.y) * sc, (x[i].z + bias.z) * sc, (x[i].w + bias.w) * sc};
+        store_h4(dst + (((long)img * e.heads + head) * e.L + l) * e.hd + d0 + cc, v);
+        row += 4; l += 4;
+        if (l >= e.L) { l -= e.L; ++img; }          // L >= 4 is guaranteed by the caller
+    }
+}
+
+// One 32-row x 32-column block of the accumulator owned by this warp (thread `lane` holds row row0+lane, r[j] = column
+// col0+j).  `stg` is the warp's private [32][STG_LD] fp32 staging block.
+__device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, const uint32_t* r, float* stg, int lane, int row0,
+                                               int col0, int b0, int b1, int bz) {
+    const GemmEpilogue& e = a.e;
+    const int ncol = min(32, a.N - col0);       // warp-uniform
+    const int myrow = row0 + lane;
+
+    if (e.mode == GM_STORE && e.out_trans) {
+        // transposed output (element (m,n) at n*ldo+m): lanes are consecutive m -> already coalesced, no staging
+        if (myrow < a.M) {
+            const long ob = b0 * e.out_bs0 + b1 * e.out_bs1;
+            const float* bias = e.bias ? e.bias + b0 * e.bias_bs0 + b1 * e.bias_bs1 + col0 : nullptr;
+            const float* resid = e.resid ? e.resid + b0 * e.resid_bs0 + b1 * e.resid_bs1 + (long)col0 * e.ldr + myrow : nullptr;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                if (j < ncol) {
+                    float x = e.alpha * __uint_as_float(r[j]);
+                    if (bias) x += __ldg(bias + j);
+                    x = apply_act(x, e.act);
+                    if (resid) x += resid[(long)j * e.ldr];
+                    if (e.out_f16) reinterpret_cast<h16*>(e.out)[ob + (long)(col0 + j) * e.ldo + myrow] = __float2half_rn(x);
+                    else reinterpret_cast<float*>(e.out)[ob + (long)(col0 + j) * e.ldo + myrow] = x;
+                }
             }
         }
-        if (o2 && e.out2_preact) store_o2();
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            if (j < ncol) {
-                float x = apply_act(v[j], e.act);
-                if (resid) x += resid[j];
-                v[j] = x;
-            }
-        }
-        if (o2 && !e.out2_preact) store_o2();
-        const long ob = b0 * e.out_bs0 + b1 * e.out_bs1;
-        if (e.out_trans) {
-            if (e.out_f16) {
-                h16* o = reinterpret_cast<h16*>(e.out) + ob + (long)col0 * e.ldo + row;
-#pragma unroll
-                for (int j = 0; j < 16; ++j) if (j < ncol) o[(long)j * e.ldo] = __float2half_rn(v[j]);
-            } else {
-                float* o = reinterpret_cast<float*>(e.out) + ob + (long)col0 * e.ldo + row;
-#pragma unroll
-                for (int j = 0; j < 16; ++j) if (j < ncol) o[(long)j * e.ldo] = v[j];
-            }
-        } else if (e.out_f16) {
-            h16* o = reinterpret_cast<h16*>(e.out) + ob + (long)row * e.ldo + col0;
-            if (ncol == 16 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
-                uint4 pk[2];
-                h16x2* h = reinterpret_cast<h16x2*>(pk);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) h[j] = __floats2half2_rn(v[2 * j], v[2 * j + 1]);
-                reinterpret_cast<uint4*>(o)[0] = pk[0];
-                reinterpret_cast<uint4*>(o)[1] = pk[1];
-            } else {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) if (j < ncol) o[j] = __float2half_rn(v[j]);
-            }
-        } else {
-            float* o = reinterpret_cast<float*>(e.out) + ob + (long)row * e.ldo + col0;
-            if (ncol == 16 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    reinterpret_cast<float4*>(o)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) if (j < ncol) o[j] = v[j];
-            }
-        }
-    } else if (e.mode == GM_QKV) {
-        // clip/myAtt.py:199-201 (packed in-proj) + :257-268 (head split); q pre-scaled by 1/sqrt(hd) (:54).
+        return;
+    }
+
+    int which = 0, head = 0, d0 = 0;
+    if (e.mode == GM_QKV) {
+        // clip/myAtt.py:199-201 (packed in-proj) + :257-268 (head split); a 32-column block never straddles a head
         const int E = e.heads * e.hd;
-        const int which = col0 / E, within = col0 - which * E;
-        const int head = within / e.hd, d0 = within - head * e.hd;
-        const int img = row / e.L, l = row - img * e.L;
-        const float* bias = e.bias + col0;
-        const float sc = (which == 0) ? e.qscale : 1.f;
-        uint4 pk[2];
-        h16x2* h = reinterpret_cast<h16x2*>(pk);
+        which = col0 / E;
+        const int within = col0 - which * E;
+        head = within / e.hd;
+        d0 = within - head * e.hd;
+        if (which == 2 && e.vt && myrow < a.M) {
+            // V^T [N*heads, hd, Lp]: lanes are consecutive tokens -> coalesced along l
+            const int img = myrow / e.L, l = myrow - img * e.L;
+            h16* o = e.vt + (((long)img * e.heads + head) * e.hd + d0) * (long)e.Lp + l;
+            const float* bias = e.bias + col0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) o[(long)j * e.Lp] = __float2half_rn(__uint_as_float(r[j]) + __ldg(bias + j));
+        }
+        if ((which == 0 && !e.q) || (which == 1 && !e.k) || (which == 2 && !e.v)) return;
+    }
+
+    // ---- transpose through shared memory: row-per-thread -> 8 lanes x float4 per row
+    {
+        float4* srow = reinterpret_cast<float4*>(stg + lane * STG_LD);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-            h[j] = __floats2half2_rn((v[2 * j] + __ldg(bias + 2 * j)) * sc, (v[2 * j + 1] + __ldg(bias + 2 * j + 1)) * sc);
-        const long hb = (long)img * e.heads + head;
-        h16* dst = (which == 0) ? e.q : (which == 1) ? e.k : e.v;
-        if (dst) {
-            uint4* o = reinterpret_cast<uint4*>(dst + (hb * e.L + l) * e.hd + d0);
-            o[0] = pk[0];
-            o[1] = pk[1];
-        }
-        if (which == 2 && e.vt) {
-            h16* o = e.vt + (hb * e.hd + d0) * (long)e.Lp + l;
-            const h16* hv = reinterpret_cast<const h16*>(pk);
+            srow[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                                  __uint_as_float(r[4 * j + 3]));
+    }
+    __syncwarp();
+    if (ncol == 32) {
+        if (e.mode == GM_STORE && a.vec_ok && fast_store_dispatch(a, stg, lane, row0, col0, b0, b1)) { __syncwarp(); return; }
+        if (e.mode == GM_QKV && e.L >= 4) { fast_qkv(a, stg, lane, row0, col0, which, head, d0); __syncwarp(); return; }
+    }
+    const int cc = (lane & 7) * 4, rsub = lane >> 3;
+    const int nv = min(4, ncol - cc);           // valid columns of this lane's group (<= 0: nothing)
+    if (nv > 0) {
+        const int col = col0 + cc;
+        const bool vec = a.vec_ok && nv == 4;
+        float bias4[4] = {0.f, 0.f, 0.f, 0.f};
+        if (e.bias) {
+            const float* bp = e.bias + (e.mode == GM_STORE ? b0 * e.bias_bs0 + b1 * e.bias_bs1 : 0) + col;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) o[(long)j * e.Lp] = hv[j];
+            for (int t = 0; t < 4; ++t) if (t < nv) bias4[t] = __ldg(bp + t);
         }
-    } else {   // GM_MUL_QGELU_GRAD
-        const int ab = e.aux_map ? e.aux_map[bz] : bz;
-        const h16* u = e.aux + (long)ab * e.aux_bs + (long)row * e.ldaux + col0;
-        h16* o = reinterpret_cast<h16*>(e.out) + b0 * e.out_bs0 + b1 * e.out_bs1 + (long)row * e.ldo + col0;
+#pragma unroll 2
+        for (int i = 0; i < 8; ++i) {
+            const int rr = i * 4 + rsub, row = row0 + rr;
+            if (row >= a.M) break;
+            const float4 xv = *reinterpret_cast<const float4*>(stg + rr * STG_LD + cc);
+            float x[4] = {xv.x, xv.y, xv.z, xv.w};
+            if (e.mode == GM_STORE) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            if (j < ncol) {
-                const float x = __half2float(u[j]);
-                const float s = 1.f / (1.f + __expf(-1.702f * x));
-                o[j] = __float2half_rn(v[j] * e.alpha * (s * (1.f + 1.702f * x * (1.f - s))));
+                for (int t = 0; t < 4; ++t) x[t] = e.alpha * x[t] + bias4[t];
+                h16* o2 = e.out2 ? e.out2 + b0 * e.out2_bs0 + b1 * e.out2_bs1 + (long)row * e.ld2 + col : nullptr;
+                if (o2 && e.out2_preact) {
+                    if (vec) store_h4(o2, x);
+                    else for (int t = 0; t < nv; ++t) o2[t] = __float2half_rn(x[t]);
+                }
+#pragma unroll
+                for (int t = 0; t < 4; ++t) x[t] = apply_act(x[t], e.act);
+                if (e.resid) {
+                    const float* rp = e.resid + b0 * e.resid_bs0 + b1 * e.resid_bs1 + (long)row * e.ldr + col;
+                    if (vec) {
+                        const float4 rv = *reinterpret_cast<const float4*>(rp);
+                        x[0] += rv.x; x[1] += rv.y; x[2] += rv.z; x[3] += rv.w;
+                    } else {
+                        for (int t = 0; t < nv; ++t) x[t] += rp[t];
+                    }
+                }
+                if (o2 && !e.out2_preact) {
+                    if (vec) store_h4(o2, x);
+                    else for (int t = 0; t < nv; ++t) o2[t] = __float2half_rn(x[t]);
+                }
+                const long ob = b0 * e.out_bs0 + b1 * e.out_bs1 + (long)row * e.ldo + col;
+                if (e.out_f16) {
+                    h16* o = reinterpret_cast<h16*>(e.out) + ob;
+                    if (vec) store_h4(o, x);
+                    else for (int t = 0; t < nv; ++t) o[t] = __float2half_rn(x[t]);
+                } else {
+                    float* o = reinterpret_cast<float*>(e.out) + ob;
+                    if (vec) *reinterpret_cast<float4*>(o) = make_float4(x[0], x[1], x[2], x[3]);
+                    else for (int t = 0; t < nv; ++t) o[t] = x[t];
+                }
+            } else if (e.mode == GM_QKV) {
+                const float sc = (which == 0) ? e.qscale : 1.f;     // q pre-scaled by 1/sqrt(hd) (myAtt.py:54)
+#pragma unroll
+                for (int t = 0; t < 4; ++t) x[t] = (x[t] + bias4[t]) * sc;
+                const int img = row / e.L, l = row - img * e.L;
+                h16* dst = (which == 0) ? e.q : (which == 1) ? e.k : e.v;
+                store_h4(dst + (((long)img * e.heads + head) * e.L + l) * e.hd + d0 + cc, x);
+            } else {   // GM_MUL_QGELU_GRAD: out = acc * alpha * quickgelu'(u)
+                const int ab = e.aux_map ? e.aux_map[bz] : bz;
+                const h16* u = e.aux + (long)ab * e.aux_bs + (long)row * e.ldaux + col;
+                h16* o = reinterpret_cast<h16*>(e.out) + b0 * e.out_bs0 + b1 * e.out_bs1 + (long)row * e.ldo + col;
+                float uu[4] = {0.f, 0.f, 0.f, 0.f};
+                if (vec) {
+                    const uint2 pk = *reinterpret_cast<const uint2*>(u);
+                    const float2 f0 = __half22float2(*reinterpret_cast<const h16x2*>(&pk.x));
+                    const float2 f1 = __half22float2(*reinterpret_cast<const h16x2*>(&pk.y));
+                    uu[0] = f0.x; uu[1] = f0.y; uu[2] = f1.x; uu[3] = f1.y;
+                } else {
+                    for (int t = 0; t < nv; ++t) uu[t] = __half2float(u[t]);
+                }
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const float s = 1.f / (1.f + __expf(-1.702f * uu[t]));
+                    x[t] = x[t] * e.alpha * (s * (1.f + 1.702f * uu[t] * (1.f - s)));
+                }
+                if (vec) store_h4(o, x);
+                else for (int t = 0; t < nv; ++t) o[t] = __float2half_rn(x[t]);
             }
         }
     }
+    __syncwarp();
 }
 
 // ---------------------------------------------------------------------------------------------------
 // Kernel
 // ---------------------------------------------------------------------------------------------------
-template <int BN, int STAGES>
-struct SmemLayout {
+template <int BN>
+struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int STAGES = (RING_BYTES / STAGE_BYTES) < 8 ? (RING_BYTES / STAGE_BYTES) : 8;
+    static constexpr int STG_BYTES = 4 * 32 * STG_LD * 4;                 // 4 epilogue warps
+    static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;         // double-buffered accumulator (power of two)
+    static constexpr int TOTAL = STAGES * STAGE_BYTES + STG_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(GEMM_THREADS) gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA,
-                                                               const __grid_constant__ CUtensorMap mapB,
-                                                               const __grid_constant__ KernelArgs args) {
-    using SL = SmemLayout<BN, STAGES>;
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA,
+                                                                  const __grid_constant__ CUtensorMap mapB,
+                                                                  const __grid_constant__ KernelArgs args) {
+    using C = Cfg<BN>;
+    constexpr int STAGES = C::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * SL::STAGE_BYTES);
+    float* stg_all = reinterpret_cast<float*>(smem + STAGES * C::STAGE_BYTES);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES + C::STG_BYTES);
     uint64_t* empty_bar = full_bar + STAGES;
-    uint64_t* tmem_full_bar = empty_bar + STAGES;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+    uint64_t* tfull_bar = empty_bar + STAGES;      // [2] accumulator ready   (MMA -> epilogue)
+    uint64_t* tempty_bar = tfull_bar + 2;          // [2] accumulator drained (epilogue -> MMA)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
-    const int bz = blockIdx.z, b0 = bz % args.nb0, b1 = bz / args.nb0;
     const int num_kb = (args.K + BK - 1) / BK;
 
     if (warp == 0 && lane == 0) {
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapB)) : "memory");
+        prefetch_tmap(&mapA);
+        prefetch_tmap(&mapB);
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        mbar_init(tmem_full_bar, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], 4); }
+        mbar_fence_init();
     }
-    if (warp == 1) tmem_alloc(tmem_slot, BN);
+    if (warp == 1) tmem_alloc(tmem_slot, C::TMEM_COLS);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -278,53 +327,83 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_tc_kernel(const __grid_cons
 
     if (warp == 0) {
         if (lane == 0) {
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % STAGES;
-                const uint32_t ph = (kb / STAGES) & 1;
-                mbar_wait(&empty_bar[s], ph ^ 1);
-                mbar_expect_tx(&full_bar[s], SL::STAGE_BYTES);
-                uint8_t* sa = smem + s * SL::STAGE_BYTES;
-                tma_load_4d(sa, &mapA, &full_bar[s], kb * BK, m0, b0 * args.a_b0, b1 * args.a_b1);
-                tma_load_4d(sa + SL::A_BYTES, &mapB, &full_bar[s], kb * BK, n0, b0 * args.b_b0, b1 * args.b_b1);
+            uint32_t it = 0;     // running k-block counter across tiles
+            for (int t = blockIdx.x; t < args.total_tiles; t += gridDim.x) {
+                const int mb = t % args.tiles_m, rest = t / args.tiles_m;
+                const int nb = rest % args.tiles_n, bz = rest / args.tiles_n;
+                const int b0 = bz % args.nb0, b1 = bz / args.nb0;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    mbar_expect_tx(&full_bar[s], C::STAGE_BYTES);
+                    uint8_t* sa = smem + s * C::STAGE_BYTES;
+                    tma_load_4d(sa, &mapA, &full_bar[s], kb * BK, mb * BM, b0 * args.a_b0, b1 * args.a_b1);
+                    tma_load_4d(sa + C::A_BYTES, &mapB, &full_bar[s], kb * BK, nb * BN, b0 * args.b_b0, b1 * args.b_b1);
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = make_idesc(BM, BN);
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % STAGES;
-                const uint32_t ph = (kb / STAGES) & 1;
-                mbar_wait(&full_bar[s], ph);
+            uint32_t it = 0, tl = 0;
+            for (int t = blockIdx.x; t < args.total_tiles; t += gridDim.x, ++tl) {
+                const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
+                mbar_wait(&tempty_bar[as], aph ^ 1);            // epilogue has drained this accumulator
                 tc_fence_after();
-                const uint32_t sa = smem_u32(smem + s * SL::STAGE_BYTES);
-                const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + SL::A_BYTES);
+                const uint32_t tacc = tmem_base + as * BN;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait(&full_bar[s], ph);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + s * C::STAGE_BYTES);
+                    const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + C::A_BYTES);
 #pragma unroll
-                for (int k = 0; k < BK / 16; ++k)   // +32 B per UMMA_K inside the 128 B swizzle row -> +2 in the >>4 field
-                    umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-                umma_commit(&empty_bar[s]);
+                    for (int k = 0; k < BK / 16; ++k)   // +32 B per UMMA_K inside the 128 B swizzle row -> +2 in the >>4 field
+                        umma_f16(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                    umma_commit(&empty_bar[s]);
+                }
+                umma_commit(&tfull_bar[as]);
             }
-            umma_commit(tmem_full_bar);
         }
     } else {
-        const int q = warp & 3;                     // TMEM lane quarter this warp may access
-        const int row = m0 + q * 32 + lane;
-        mbar_wait(tmem_full_bar, 0);
-        tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-#pragma unroll 1
-        for (int c = 0; c < BN / 16; ++c) {
-            const int col0 = n0 + c * 16;
-            if (col0 >= args.N) break;              // warp-uniform
-            float v[16];
-            tmem_ld16(taddr + c * 16, v);
-            if (row < args.M) epilogue_chunk(args, v, row, col0, b0, b1, bz);
+        const int q = warp & 3;                     // TMEM lane quarter this warp may access (warps 2,3,4,5 -> 2,3,0,1)
+        float* stg = stg_all + (warp - 2) * 32 * STG_LD;
+        uint32_t tl = 0;
+        for (int t = blockIdx.x; t < args.total_tiles; t += gridDim.x, ++tl) {
+            const int mb = t % args.tiles_m, rest = t / args.tiles_m;
+            const int nb = rest % args.tiles_n, bz = rest / args.tiles_n;
+            const int b0 = bz % args.nb0, b1 = bz / args.nb0;
+            const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
+            mbar_wait(&tfull_bar[as], aph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
+            const int row0 = mb * BM + q * 32;
+            if (row0 < args.M) {
+                // software-pipelined TMEM reads: chunk c+1 is in flight while chunk c goes through the epilogue
+                uint32_t r[2][32];
+                tmem_ld32_issue(taddr, r[0]);
+#pragma unroll
+                for (int c = 0; c < BN / 32; ++c) {
+                    const int col0 = nb * BN + c * 32;
+                    if (col0 >= args.N) break;          // warp-uniform
+                    tmem_ld_wait();
+                    if (c + 1 < BN / 32 && col0 + 32 < args.N) tmem_ld32_issue(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+                    epilogue_chunk(args, r[c & 1], stg, lane, row0, col0, b0, b1, bz);
+                }
+                tmem_ld_wait();
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[as]);
         }
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, BN);
+        tmem_dealloc(tmem_base, C::TMEM_COLS);
     }
 }
 
@@ -388,12 +467,41 @@ static int make_map(CUtensorMap* out, const GemmOperand& op, int K, int nb0, int
     return WC_OK;
 }
 
-template <int BN, int STAGES>
+static int num_sms() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+    }
+    return n;
+}
+
+static bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
+
+// 4-element vector access in the epilogue needs every touched pointer 16 B (fp32) / 8 B (fp16) aligned and every stride
+// a multiple of 4 elements; otherwise the kernel falls back to scalar accesses (same results).
+static int epilogue_vec_ok(const GemmEpilogue& e) {
+    auto m4 = [](long v) { return (v & 3) == 0; };
+    bool ok = true;
+    if (e.mode == GM_STORE) {
+        if (e.out_trans) return 0;
+        ok = ok && aligned(e.out, e.out_f16 ? 8 : 16) && m4(e.ldo) && m4(e.out_bs0) && m4(e.out_bs1);
+        if (e.bias) ok = ok && aligned(e.bias, 16) && m4(e.bias_bs0) && m4(e.bias_bs1);
+        if (e.resid) ok = ok && aligned(e.resid, 16) && m4(e.ldr) && m4(e.resid_bs0) && m4(e.resid_bs1);
+        if (e.out2) ok = ok && aligned(e.out2, 8) && m4(e.ld2) && m4(e.out2_bs0) && m4(e.out2_bs1);
+    } else if (e.mode == GM_MUL_QGELU_GRAD) {
+        ok = ok && aligned(e.out, 8) && m4(e.ldo) && m4(e.out_bs0) && m4(e.out_bs1) && aligned(e.aux, 8) && m4(e.ldaux) && m4(e.aux_bs);
+    }
+    return ok ? 1 : 0;
+}
+
+template <int BN>
 static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
-    using SL = SmemLayout<BN, STAGES>;
+    using C = Cfg<BN>;
     static bool attr_set = false;
     if (!attr_set) {
-        WC_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
+        WC_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::TOTAL));
         attr_set = true;
     }
     CUtensorMap mA, mB;
@@ -403,20 +511,33 @@ static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
     if (rc) return rc;
     rc = make_map(&mB, p.B, p.K, p.nb0, p.nb1, BN, &ka.b_b0, &ka.b_b1);
     if (rc) return rc;
-    dim3 grid(ceil_div(p.M, BM), ceil_div(p.N, BN), p.nb0 * p.nb1);
+    ka.tiles_m = ceil_div(p.M, BM);
+    ka.tiles_n = ceil_div(p.N, BN);
+    const long total = (long)ka.tiles_m * ka.tiles_n * p.nb0 * p.nb1;
+    if (total > 0x7fffffffL) return fail(WC_ERR_ARG, "%s: too many tiles", __func__);
+    ka.total_tiles = (int)total;
+    ka.vec_ok = epilogue_vec_ok(p.epi);
+    ka.variant = variant_id(p.epi.out_f16 ? 1 : 0, p.epi.act, p.epi.bias ? 1 : 0, p.epi.resid ? 1 : 0,
+                            p.epi.out2 ? (p.epi.out2_preact ? 2 : 1) : 0);
+    const int grid = (int)(total < num_sms() ? total : num_sms());
     ProfScope prof(PK_GEMM, 2.0 * p.M * p.N * p.K * p.nb0 * p.nb1, st);
-    gemm_tc_kernel<BN, STAGES><<<grid, GEMM_THREADS, SL::TOTAL, st>>>(mA, mB, ka);
+    if (g_prof_on) prof_tag(p.M, p.N, p.K, p.nb0 * p.nb1);
+    gemm_tc_kernel<BN><<<grid, GEMM_THREADS, C::TOTAL, st>>>(mA, mB, ka);
     WC_LAUNCH_CHECK();
     return WC_OK;
 }
 
 int launch_gemm(const GemmProblem& p, cudaStream_t st) {
     WC_CHECK_ARG(p.M > 0 && p.N > 0 && p.K > 0 && p.nb0 > 0 && p.nb1 > 0 && p.A.ptr && p.B.ptr);
-    WC_CHECK_ARG((long)p.nb0 * p.nb1 <= 65535);
-    if (p.epi.mode == GM_QKV) WC_CHECK_ARG(p.N % 16 == 0 && p.epi.hd % 16 == 0 && p.epi.bias);
-    if (p.N <= 32) return launch_cfg<32, 4>(p, st);
-    if (p.N <= 64) return launch_cfg<64, 4>(p, st);
-    return launch_cfg<128, 3>(p, st);
+    if (p.epi.mode == GM_QKV) WC_CHECK_ARG(p.N % 32 == 0 && p.epi.hd % 32 == 0 && p.epi.bias && aligned(p.epi.bias, 16));
+    if (p.N <= 32) return launch_cfg<32>(p, st);
+    if (p.N <= 64) return launch_cfg<64>(p, st);
+    if (p.N <= 128) return launch_cfg<128>(p, st);
+    // widest tile that still gives every SM at least one tile (tile quantisation matters more than tile shape on small M)
+    const long per_n = (long)ceil_div(p.M, BM) * p.nb0 * p.nb1;
+    if (per_n * ceil_div(p.N, 256) >= num_sms()) return launch_cfg<256>(p, st);
+    if (per_n * ceil_div(p.N, 128) >= num_sms()) return launch_cfg<128>(p, st);
+    return launch_cfg<64>(p, st);
 }
 
 }  // namespace wc

@@ -51,27 +51,39 @@ class MscFlipEvaluator:
     def process(self, name: str, inputs: torch.Tensor, labels: torch.Tensor, want_preds: bool = False):
         """One dataset image (test_msc_flip_voc.py:50-101).  inputs fp32 [1,3,H0,W0]; labels int16 [Hl,Wl]
         (both already on the device).  Returns (seg_pred, msc_pred, cam, msc_segs) when want_preds."""
-        names = [name, name]
+        out = self.process_batch([name], inputs, labels.unsqueeze(0), want_preds)
+        if want_preds:
+            seg_pred, msc_pred, cam, msc = out
+            return seg_pred[0], msc_pred[0], (cam[0] if cam is not None else None), msc[0]
+        return None
+
+    def process_batch(self, names: Sequence[str], inputs: torch.Tensor, labels: torch.Tensor, want_preds: bool = False):
+        """B same-size dataset images per model call (the reference loops image by image; images are independent,
+        so a (H,W) bucket is run as one [2B,3,H,W] forward per scale: B plain images followed by their B flipped
+        twins).  inputs fp32 [B,3,H0,W0]; labels int16 [B,Hl,Wl]."""
+        B = inputs.shape[0]
+        names2 = list(names) + list(names)
         _, _, h0, w0 = inputs.shape
         ratio = self.resize_long / max(h0, w0)
         base = ops.resize_bilinear(inputs, size=(int(h0 * ratio), int(w0 * ratio)))          # :60-63
-        segs_cat, cam, _ = self.model(ops.flip_concat(base), names, mode="val")              # :68-69
+        segs_cat, cam, _ = self.model(ops.flip_concat(base), names2, mode="val")             # :68-69
         C, h, w = segs_cat.shape[1:]
         n_scales = 1 + sum(1 for s in self.scales if s != 1.0)
-        msc = torch.empty(C, h, w, dtype=torch.float32, device=self.device)
+        msc = torch.empty(B, C, h, w, dtype=torch.float32, device=self.device)
         ops.msc_accumulate(segs_cat, msc, 1.0 / n_scales, True)                              # :74
         for s in self.scales:                                                                # :79-88
             if s != 1.0:
-                sc, _, _ = self.model(ops.flip_concat(ops.resize_bilinear(base, scale_factor=s)), names, mode="val")
+                sc, _, _ = self.model(ops.flip_concat(ops.resize_bilinear(base, scale_factor=s)), names2, mode="val")
                 ops.msc_accumulate(sc, msc, 1.0 / n_scales, False)
         size = labels.shape[-2:]
-        seg_pred = ops.upsample_argmax_hist(segs_cat[0], size, labels, self.hist[0], want_preds)   # :93-94
+        labels = labels.contiguous()
+        seg_pred = ops.upsample_argmax_hist(segs_cat[:B], size, labels, self.hist[0], want_preds)  # :93-94
         msc_pred = ops.upsample_argmax_hist(msc, size, labels, self.hist[1], want_preds)           # :95-96
         if cam is not None:                                                                  # :71, :107
-            ops.confusion_hist(cam[0], labels, self.hist[2])
-        self.n_images += 1
+            ops.confusion_hist(cam[:B], labels, self.hist[2])
+        self.n_images += B
         if want_preds:
-            return seg_pred, msc_pred, (cam[0] if cam is not None else None), msc
+            return seg_pred, msc_pred, (cam[:B] if cam is not None else None), msc
         return None
 
     def all_reduce(self):

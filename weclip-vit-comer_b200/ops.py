@@ -59,7 +59,7 @@ def resize_bilinear(x: torch.Tensor, size=None, scale_factor: float = None) -> t
 
 
 def flip_concat(x: torch.Tensor) -> torch.Tensor:
-    """torch.cat([x, x.flip(-1)], dim=0) for fp32 [1,C,H,W] (test_msc_flip_voc.py:68,82)."""
+    """torch.cat([x, x.flip(-1)], dim=0) for fp32 [B,C,H,W] (test_msc_flip_voc.py:68,82)."""
     _lib.require_device()
     x = x.contiguous().float()
     n, C, H, W = x.shape
@@ -70,12 +70,13 @@ def flip_concat(x: torch.Tensor) -> torch.Tensor:
 
 
 def msc_accumulate(seg2: torch.Tensor, acc: torch.Tensor, weight: float, first: bool) -> torch.Tensor:
-    """acc (+)= weight * (R(seg2[0]) + flip(R(seg2[1]))) / 2 with R the bilinear resize to acc's size."""
+    """acc[B,C,h,w] (+)= weight * (R(seg2[:B]) + flip(R(seg2[B:]))) / 2 with R the bilinear resize to acc's size."""
     _lib.require_device()
     seg2 = seg2.contiguous()
-    two, C, hs, ws = seg2.shape
-    assert two == 2 and acc.is_contiguous() and acc.shape[0] == C
-    rc = _lib.lib().wc_msc_accumulate(_lib.ptr(seg2), _lib.ptr(acc), C, hs, ws, acc.shape[1], acc.shape[2],
+    n2, C, hs, ws = seg2.shape                  # [2B,C,hs,ws]: B plain images followed by their B flipped twins
+    B = n2 // 2
+    assert n2 == 2 * B and acc.is_contiguous() and tuple(acc.shape[:2]) == (B, C)
+    rc = _lib.lib().wc_msc_accumulate(_lib.ptr(seg2), _lib.ptr(acc), B, C, hs, ws, acc.shape[2], acc.shape[3],
                                       ctypes.c_float(weight), int(first), _lib.stream_ptr())
     _lib.check(rc, "wc_msc_accumulate")
     return acc
@@ -86,16 +87,19 @@ def upsample_argmax_hist(logits: torch.Tensor, size, gt: torch.Tensor = None, hi
     """argmax over classes of the bilinear resize of logits [C,h,w] to `size`; optional confusion-matrix update."""
     _lib.require_device()
     logits = logits.contiguous()
-    C, h, w = logits.shape
+    squeeze = logits.dim() == 3
+    if squeeze:
+        logits = logits.unsqueeze(0)
+    B, C, h, w = logits.shape
     Ho, Wo = int(size[0]), int(size[1])
-    pred = torch.empty(Ho, Wo, dtype=torch.int32, device=logits.device) if want_pred else None
+    pred = torch.empty(B, Ho, Wo, dtype=torch.int32, device=logits.device) if want_pred else None
     if gt is not None:
-        assert gt.dtype == torch.int16 and gt.is_contiguous() and tuple(gt.shape) == (Ho, Wo)
+        assert gt.dtype == torch.int16 and gt.is_contiguous() and gt.numel() == B * Ho * Wo
         assert hist.dtype == torch.int64 and hist.is_contiguous() and hist.numel() == C * C
-    rc = _lib.lib().wc_upsample_argmax_hist(_lib.ptr(logits), C, h, w, Ho, Wo, _lib.ptr(pred), _lib.ptr(gt),
+    rc = _lib.lib().wc_upsample_argmax_hist(_lib.ptr(logits), B, C, h, w, Ho, Wo, _lib.ptr(pred), _lib.ptr(gt),
                                             _lib.ptr(hist), _lib.stream_ptr())
     _lib.check(rc, "wc_upsample_argmax_hist")
-    return pred
+    return pred[0] if (squeeze and pred is not None) else pred
 
 
 def confusion_hist(pred: torch.Tensor, gt: torch.Tensor, hist: torch.Tensor) -> torch.Tensor:
