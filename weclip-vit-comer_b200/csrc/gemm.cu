@@ -1,13 +1,14 @@
 // tcgen05 GEMM kernel (sm_100a), persistent and warp-specialised.  See gemm.cuh for the contract.
 //
-// grid = min(#tiles, #SMs) CTAs of 192 threads; each CTA walks output tiles t = blockIdx.x + i*gridDim.x
+// grid = min(#tiles, #SMs) CTAs of 320 threads; each CTA walks output tiles t = blockIdx.x + i*gridDim.x
 // (m-block fastest, so concurrently running CTAs share the same weight tile in L2).  Tile = 128 x BN, BN in {256,128,64,32}.
 //   warp 0     TMA producer  — cp.async.bulk.tensor (rank-4 maps, 128B swizzle, OOB zero-fill) into a STAGES-deep smem ring
 //                              (192 KB: 4 stages at BN=256 ... 8 stages at BN<=64), running ahead across tile boundaries
 //   warp 1     MMA issuer    — one lane issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BN, K=16) x4 per 64-wide k-block;
 //                              tcgen05.commit frees the smem stage; accumulators are DOUBLE-BUFFERED in tensor memory
 //                              (2 x BN fp32 columns) so the next tile's mainloop overlaps this tile's epilogue
-//   warps 2-5  epilogue      — tcgen05.ld 32x32b.x32 (thread = accumulator row), transposed through a per-warp padded smem
+//   warps 2-9  epilogue      — two warps per TMEM lane quarter, each draining half of the tile's columns:
+//                              tcgen05.ld 32x32b.x32 (thread = accumulator row), transposed through a per-warp swizzled smem
 //                              block so that global traffic is row-contiguous 128-bit accesses (8 lanes = 128 B of one row),
 //                              fused bias / activation / residual / fp16 copy / head-major QKV scatter
 // Operands are K-major fp16 (A: [M,K], B: [N,K]); accumulators are fp32.
@@ -22,15 +23,18 @@ namespace wc {
 
 constexpr int BM = 128;
 constexpr int BK = 64;               // 64 fp16 = 128 B = one swizzle row
-constexpr int GEMM_THREADS = 192;
-constexpr int STG_LD = 36;           // staging row stride in floats (32 + 4: conflict-free 128-bit rows)
+constexpr int EPI_WARPS = 8;         // two warps per TMEM lane quarter, each taking half of the tile's columns
+constexpr int GEMM_THREADS = 64 + 32 * EPI_WARPS;
+// Per-warp staging block: [32 rows][32 floats], 128-bit vectors XOR-swizzled by (row & 7) -> conflict-free row-per-thread
+// writes and 8-lanes-per-row reads without padding (8 warps x 4 KB fit beside the 192 KB operand ring).
+__device__ __forceinline__ int stg_off(int row, int vec) { return row * 32 + ((vec ^ (row & 7)) << 2); }
 constexpr int RING_BYTES = 192 * 1024;
 
 __device__ __forceinline__ float apply_act(float x, int act) {
     switch (act) {
         case ACT_RELU: return fmaxf(x, 0.f);
-        case ACT_QUICKGELU: return x / (1.f + __expf(-1.702f * x));
-        case ACT_SIGMOID: return 1.f / (1.f + __expf(-x));
+        case ACT_QUICKGELU: return __fdividef(x, 1.f + __expf(-1.702f * x));     // 2 MUFU (ex2, rcp) + 3 FP32 ops
+        case ACT_SIGMOID: return __fdividef(1.f, 1.f + __expf(-x));
         default: return x;
     }
 }
@@ -70,7 +74,7 @@ __device__ __forceinline__ void fast_store(const KernelArgs& a, const float* stg
     if (BIAS) bias = __ldg(reinterpret_cast<const float4*>(e.bias + b0 * e.bias_bs0 + b1 * e.bias_bs1 + col));
     float4 x[8], rs[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) x[i] = *reinterpret_cast<const float4*>(stg + (i * 4 + rsub) * STG_LD + cc);
+    for (int i = 0; i < 8; ++i) x[i] = *reinterpret_cast<const float4*>(stg + stg_off(i * 4 + rsub, lane & 7));
     if (RESID) {
         const float* rp = e.resid + b0 * e.resid_bs0 + b1 * e.resid_bs1 + (long)r_first * e.ldr + col;
 #pragma unroll
@@ -123,7 +127,7 @@ __device__ __forceinline__ void fast_qkv(const KernelArgs& a, const float* stg, 
     h16* dst = (which == 0) ? e.q : (which == 1) ? e.k : e.v;
     float4 x[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) x[i] = *reinterpret_cast<const float4*>(stg + (i * 4 + rsub) * STG_LD + cc);
+    for (int i = 0; i < 8; ++i) x[i] = *reinterpret_cast<const float4*>(stg + stg_off(i * 4 + rsub, lane & 7));
     int row = row0 + rsub;
     int img = row / e.L, l = row - img * e.L;
 #pragma unroll
@@ -137,7 +141,7 @@ __device__ __forceinline__ void fast_qkv(const KernelArgs& a, const float* stg, 
 }
 
 // One 32-row x 32-column block of the accumulator owned by this warp (thread `lane` holds row row0+lane, r[j] = column
-// col0+j).  `stg` is the warp's private [32][STG_LD] fp32 staging block.
+// col0+j).  `stg` is the warp's private swizzled 32x32 fp32 staging block (stg_off).
 __device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, const uint32_t* r, float* stg, int lane, int row0,
                                                int col0, int b0, int b1, int bz) {
     const GemmEpilogue& e = a.e;
@@ -186,10 +190,9 @@ __device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, const uint32
 
     // ---- transpose through shared memory: row-per-thread -> 8 lanes x float4 per row
     {
-        float4* srow = reinterpret_cast<float4*>(stg + lane * STG_LD);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-            srow[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+            *reinterpret_cast<float4*>(stg + stg_off(lane, j)) = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
                                   __uint_as_float(r[4 * j + 3]));
     }
     __syncwarp();
@@ -212,7 +215,7 @@ __device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, const uint32
         for (int i = 0; i < 8; ++i) {
             const int rr = i * 4 + rsub, row = row0 + rr;
             if (row >= a.M) break;
-            const float4 xv = *reinterpret_cast<const float4*>(stg + rr * STG_LD + cc);
+            const float4 xv = *reinterpret_cast<const float4*>(stg + stg_off(rr, lane & 7));
             float x[4] = {xv.x, xv.y, xv.z, xv.w};
             if (e.mode == GM_STORE) {
 #pragma unroll
@@ -289,7 +292,7 @@ struct Cfg {
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int STAGES = (RING_BYTES / STAGE_BYTES) < 8 ? (RING_BYTES / STAGE_BYTES) : 8;
-    static constexpr int STG_BYTES = 4 * 32 * STG_LD * 4;                 // 4 epilogue warps
+    static constexpr int STG_BYTES = EPI_WARPS * 32 * 32 * 4;
     static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;         // double-buffered accumulator (power of two)
     static constexpr int TOTAL = STAGES * STAGE_BYTES + STG_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
@@ -316,7 +319,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         prefetch_tmap(&mapA);
         prefetch_tmap(&mapB);
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], 4); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], EPI_WARPS); }
         mbar_fence_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, C::TMEM_COLS);
@@ -368,8 +371,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
             }
         }
     } else {
-        const int q = warp & 3;                     // TMEM lane quarter this warp may access (warps 2,3,4,5 -> 2,3,0,1)
-        float* stg = stg_all + (warp - 2) * 32 * STG_LD;
+        const int q = warp & 3;                     // TMEM lane quarter this warp may access (warp id % 4)
+        const int half = (warp - 2) >> 2;           // which half of the tile's 32-column chunks this warp drains
+        constexpr int CH = BN / 32, NCH = (CH >= 2) ? CH / 2 : 1;
+        const int c_begin = half * NCH;
+        const bool has_work = (CH >= 2) || half == 0;
+        float* stg = stg_all + (warp - 2) * 32 * 32;
         uint32_t tl = 0;
         for (int t = blockIdx.x; t < args.total_tiles; t += gridDim.x, ++tl) {
             const int mb = t % args.tiles_m, rest = t / args.tiles_m;
@@ -378,18 +385,18 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
             const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
             mbar_wait(&tfull_bar[as], aph);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
+            const uint32_t taddr = tmem_base + as * BN + c_begin * 32 + ((uint32_t)(q * 32) << 16);
             const int row0 = mb * BM + q * 32;
-            if (row0 < args.M) {
+            if (has_work && row0 < args.M && nb * BN + c_begin * 32 < args.N) {
                 // software-pipelined TMEM reads: chunk c+1 is in flight while chunk c goes through the epilogue
                 uint32_t r[2][32];
                 tmem_ld32_issue(taddr, r[0]);
 #pragma unroll
-                for (int c = 0; c < BN / 32; ++c) {
-                    const int col0 = nb * BN + c * 32;
+                for (int c = 0; c < NCH; ++c) {
+                    const int col0 = nb * BN + (c_begin + c) * 32;
                     if (col0 >= args.N) break;          // warp-uniform
                     tmem_ld_wait();
-                    if (c + 1 < BN / 32 && col0 + 32 < args.N) tmem_ld32_issue(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+                    if (c + 1 < NCH && col0 + 32 < args.N) tmem_ld32_issue(taddr + (c + 1) * 32, r[(c + 1) & 1]);
                     epilogue_chunk(args, r[c & 1], stg, lane, row0, col0, b0, b1, bz);
                 }
                 tmem_ld_wait();
