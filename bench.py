@@ -94,7 +94,8 @@ class ClockSampler:
 class ParPseudoLabel:
     """Interim round-1 workload: the PAR + argmax/LUT tail of BASELINE.json configs[1] (batch 32 crops of
     320x320, K+1 = 3 CAM channels per image, dilations 1/2/4/8/12/24, 20 iterations)."""
-    name = "cfg2-tail: PAR(20 it, 6 dil)+argmax on 32 x 320x320 crops, K+1=3"
+    name = "cfg2-tail: PAR(20 it, 6 dil, fp16 affinity)+argmax on 32 x 320x320 crops, K+1=3"
+    aff_dtype, s_a = torch.float16, 2
 
     def __init__(self, rank: int, device):
         from weclip_b200 import synth
@@ -108,7 +109,7 @@ class ParPseudoLabel:
         self.masks_h = torch.cat([bg, cams], 1).reshape(self.B * self.Kc, self.H, self.W).contiguous().pin_memory()
         self.ch_off = [b * self.Kc for b in range(self.B + 1)]
         self.lut = torch.tensor([0, 3, 7] * self.B, dtype=torch.int64, device=device)
-        self.par = PAR([1, 2, 4, 8, 12, 24], 20).to(device)
+        self.par = PAR([1, 2, 4, 8, 12, 24], 20, affinity_dtype=self.aff_dtype).to(device)
         self.imgs_d = self.imgs_h.to(device)
         self.masks_d = self.masks_h.to(device)
         self.labels_h = torch.empty(self.B, self.H, self.W, dtype=torch.int64).pin_memory()
@@ -118,7 +119,7 @@ class ParPseudoLabel:
         self.d2h = self.labels_h.numel() * 8
         self.kernel_events = []
         # aff (614 MB) + masks > 126 MB L2: every iteration streams from HBM
-        self.l2_note = "inputs larger than L2 (affinity 590 MB per step)"
+        self.l2_note = f"inputs larger than L2 (affinity {self.B * 48 * self.H * self.W * self.s_a / 1e6:.0f} MB per step)"
 
     def step_device(self, record=False):
         from weclip_b200.par import argmax_lut
@@ -142,13 +143,14 @@ class ParPseudoLabel:
         return self.labels_h
 
     def roofline(self, peaks):
-        """Dominant kernel: par_iter_kernel.  Algorithmic bytes per launch = H*W*B*(48*4 + 2*4*Kc) (SURVEY §8d);
-        the bracketed region holds 1 affinity launch (12+192 B/px) + 20 iteration launches."""
+        """Dominant kernel: par_iter_tile_kernel.  Algorithmic bytes per launch = H*W*B*(48*s_a + 2*4*Kc) (SURVEY §8d,
+        s_a = bytes per stored affinity); the bracketed region holds 1 affinity launch (12+48*s_a B/px) + 20 iteration
+        launches."""
         px = self.B * self.H * self.W
-        alg = px * (12 + 192) + 20 * px * (192 + 8 * self.Kc)
+        alg = px * (12 + 48 * self.s_a) + 20 * px * (48 * self.s_a + 8 * self.Kc)
         ms = statistics.mean(a.elapsed_time(b) for a, b in self.kernel_events)
         ach = alg / (ms * 1e-3) / 1e9
-        return {"bound": "hbm", "kernel": "par_aff_kernel<48> + 20 x par_iter_kernel<48>", "achieved": round(ach, 1),
+        return {"bound": "hbm", "kernel": "par_aff_tile_kernel + 20 x par_iter_tile_kernel", "achieved": round(ach, 1),
                 "peak": peaks["hbm_gbs"], "peak_source": peaks["source"] + " (burst copy)", "unit": "GB/s",
                 "frac": round(ach / peaks["hbm_gbs"], 4), "traffic": None,
                 "algorithmic_bytes_per_step": alg, "kernel_ms_per_step": round(ms, 4)}
@@ -178,7 +180,12 @@ class ParPseudoLabel:
         return n_img / dt, f"{n_img} of the step's {self.B} images (PAR+argmax), torch CPU fp32"
 
 
-WORKLOADS = {"par": ParPseudoLabel}
+class ParPseudoLabelF32(ParPseudoLabel):
+    name = "cfg2-tail: PAR(20 it, 6 dil, fp32 affinity)+argmax on 32 x 320x320 crops, K+1=3"
+    aff_dtype, s_a = torch.float32, 4
+
+
+WORKLOADS = {"par": ParPseudoLabel, "par32": ParPseudoLabelF32}
 try:
     from weclip_b200.bench_workloads import WORKLOADS as _MORE  # full-path workloads register themselves here
     WORKLOADS.update(_MORE)

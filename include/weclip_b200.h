@@ -30,7 +30,7 @@ extern "C" {
 #define WC_ERR_WORKSPACE (-3)
 #define WC_ERR_UNSUPPORTED (-4)
 
-#define WC_ABI_VERSION 5
+#define WC_ABI_VERSION 6
 #define WC_PAR_MAX_DIL 8
 
 /* ABI version (bumped whenever a signature changes) and last error text. */
@@ -61,16 +61,21 @@ long wc_prof_records(int* kind, double* ms, double* work, int* tags, long cap);
  * sizes differ.  w1=0.3, w2=0.01 as PAR.py:36-37.
  * ---------------------------------------------------------------------------------------------- */
 size_t wc_par_workspace_bytes(int B, int sum_kc, int H, int W, int n_dil);
+/* aff_f16: storage type of the materialised affinity inside the workspace.  0 = fp32 (exact path: results within 2e-5
+ * of PAR.py in fp32); 1 = fp16 (pipeline path: halves the bytes each propagation step streams; pseudo-labels agree
+ * with the fp32 path on >= 99.5 % of pixels, masks within 5e-3). */
 int wc_par_fwd(const float* imgs, int Hi, int Wi, const float* masks, float* out,
                const int* ch_off_host, int B, int H, int W,
-               const int* dilations_host, int n_dil, int num_iter,
+               const int* dilations_host, int n_dil, int num_iter, int aff_f16,
                void* workspace, size_t workspace_bytes, void* stream);
 /* The two halves of wc_par_fwd, exposed for the roofline micro-bench (BASELINE.json configs[4]):
- * affinity build (PAR.py:70-86) -> aff [B, 8*n_dil, H, W]; img must already be HxW. */
-int wc_par_affinity(const float* img, float* aff, int B, int H, int W,
+ * affinity build (PAR.py:70-86) -> aff [B, 8*n_dil, H, wc_par_aff_pitch(W)] fp32 or fp16 (aff_f16);
+ * img must already be HxW. */
+int wc_par_aff_pitch(int W);
+int wc_par_affinity(const float* img, void* aff, int aff_f16, int B, int H, int W,
                     const int* dilations_host, int n_dil, void* stream);
-/* num_iter propagation steps (PAR.py:88-90); scratch holds 2*sum_kc*H*W floats. */
-int wc_par_propagate(const float* aff, const float* masks, float* out, float* scratch,
+/* num_iter propagation steps (PAR.py:88-90); scratch holds 2*sum_kc*H*wc_par_aff_pitch(W) floats. */
+int wc_par_propagate(const void* aff, int aff_f16, const float* masks, float* out, float* scratch,
                      const int* ch_off_host, int B, int H, int W,
                      const int* dilations_host, int n_dil, int num_iter, void* stream);
 
@@ -157,6 +162,13 @@ int wc_decoder_fwd(const wc_decoder_weights* w, const void* taps, int N, int h, 
 int wc_layernorm(const float* x, const float* w, const float* b, void* out_f16, float* out_f32, long rows, int E,
                  void* stream);
 int wc_softmax_headmean(const float* S, void* P_f16, float* avg, int n_img, int heads, int L, int Lp, void* stream);
+/* Fused attention of the encoder blocks (head_dim 64): softmax(q k^T) v without materialising the scores
+ * (clip/myAtt.py:53-64), output head-interleaved (myAtt.py:320), plus the head-mean probability map (myAtt.py:323-326).
+ *   q, k fp16 [N*heads, L, 64] (q pre-scaled by 1/8); vt fp16 [N*heads, 64, Lp] (V transposed, Lp = round_up(L,8));
+ *   o fp16 [N*L, heads*64]; lse2 fp32 [N*heads, L] or NULL (log2-domain row log-sum-exp);
+ *   attn_avg fp32 [N, L, L] or NULL (needs lse2). */
+int wc_attention_fwd(const void* q, const void* k, const void* vt, void* o, float* lse2, float* attn_avg,
+                     int n_img, int heads, int L, int Lp, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Grad-CAM head.  Replaces CLIP.forward_last_layer (clip/model.py:407-429) + GradCAM.__call__

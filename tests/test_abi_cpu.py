@@ -27,7 +27,7 @@ def test_abi_version_matches_header(L):
 
 
 def test_bad_arguments_are_rejected_without_a_device(L):
-    rc = L.wc_par_fwd(None, 4, 4, None, None, None, 1, 4, 4, None, 6, 20, None, ctypes.c_size_t(0), None)
+    rc = L.wc_par_fwd(None, 4, 4, None, None, None, 1, 4, 4, None, 6, 20, 0, None, ctypes.c_size_t(0), None)
     assert rc == -1
     assert b"bad argument" in L.wc_last_error()
     assert L.wc_par_workspace_bytes(1, 3, 8, 8, 6) >= 4 * 64 * (3 + 48 + 6)

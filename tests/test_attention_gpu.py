@@ -1,0 +1,45 @@
+"""Fused tcgen05 attention (wc_attention_fwd through the C ABI) against a plain PyTorch fp32 reference of the same op
+(clip/myAtt.py:53-64 scaled-dot-product attention and :323-326 head-mean map)."""
+import pytest
+import torch
+
+from weclip_b200 import ops
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(q, k, v):
+    s = torch.matmul(q.float(), k.float().transpose(-1, -2))
+    p = torch.softmax(s, dim=-1)
+    o = torch.matmul(p, v.float())                       # [N,heads,L,64]
+    N, h, L, d = o.shape
+    return o.permute(0, 2, 1, 3).reshape(N, L, h * d), p.mean(1)
+
+
+@pytest.mark.parametrize("N,heads,L", [(1, 1, 128), (1, 2, 401), (2, 12, 577), (1, 3, 1025), (1, 2, 1601), (2, 1, 50)])
+def test_attention_matches_torch(N, heads, L):
+    g = torch.Generator(device="cuda").manual_seed(L + heads)
+    q = (torch.randn(N, heads, L, 64, device="cuda", generator=g) * 0.125 * 2.0).half()
+    k = (torch.randn(N, heads, L, 64, device="cuda", generator=g) * 1.5).half()
+    v = torch.randn(N, heads, L, 64, device="cuda", generator=g).half()
+    o, avg = ops.attention_fwd(q, k, v)
+    o_ref, avg_ref = _ref(q, k, v)
+    # P is rounded to fp16 before the P V product (as the reference's fp16 bmm does): 2^-11 relative on each term
+    assert (o.float() - o_ref).abs().max().item() < 4e-3
+    assert (avg - avg_ref).abs().max().item() < 2e-5
+    assert (avg.sum(-1) - 1).abs().max().item() < 1e-4
+
+
+def test_attention_peaked_rows_and_large_scores():
+    """Rows dominated by one key (scores ~ +-60): the two-pass log-sum-exp must not overflow or lose the small terms."""
+    torch.manual_seed(0)
+    N, heads, L = 1, 2, 300
+    q = torch.randn(N, heads, L, 64, device="cuda").half()
+    k = (torch.randn(N, heads, L, 64, device="cuda") * 1.0).half()
+    k[:, :, 7] *= 6
+    v = torch.randn(N, heads, L, 64, device="cuda").half()
+    o, avg = ops.attention_fwd(q, k, v)
+    o_ref, avg_ref = _ref(q, k, v)
+    assert torch.isfinite(o.float()).all() and torch.isfinite(avg).all()
+    assert (o.float() - o_ref).abs().max().item() < 8e-3
+    assert (avg - avg_ref).abs().max().item() < 5e-5

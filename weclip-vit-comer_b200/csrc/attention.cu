@@ -1,0 +1,452 @@
+// Fused multi-head attention forward (head_dim 64) for sm_100a.  See attention.cuh for the contract.
+//
+// attn_fwd_kernel — one CTA per (128-query tile, head, image), 192 threads, TWO passes over the key tiles:
+//   pass 1  S = Q K^T per 128-key tile (tcgen05.mma, fp32 in TMEM) -> running row max / sum of exp2 (registers)
+//   pass 2  S again, P = exp2(S*log2e - lse2) is the EXACT softmax probability (no rescaling of the output accumulator),
+//           rounded to fp16 into a 128B-swizzled shared-memory tile, O += P V (tcgen05.mma, O stays in TMEM)
+//   warp 0     TMA producer: Q once, then a 4-stage ring of K (pass 1) / K + V^T (pass 2) tiles, OOB rows zero-filled
+//   warp 1     MMA issuer (one lane): S double-buffered in TMEM so QK^T of tile j+1 overlaps the softmax of tile j
+//   warps 2-5  softmax: thread = query row (TMEM lane), tcgen05.ld 32 columns at a time, ex2.approx
+// The score matrix never leaves the SM: HBM traffic is q, k, v once per query tile (L2-resident) + o.
+//
+// attn_headmean_kernel — the head-averaged probability map the CAM refinement consumes (myAtt.py:323-326): one CTA per
+//   (key tile, query tile, image) loops over the heads, recomputes S = Q_h K_h^T on the tensor cores and accumulates
+//   exp2(S*log2e - lse2_h) in registers; each [N,L,L] element is written once (4 L^2 bytes per image, not 12x).
+#include "attention.cuh"
+#include "gemm.cuh"
+#include "tc_ptx.cuh"
+
+namespace wc {
+
+constexpr int AT_BM = 128, AT_BN = 128, AT_HD = 64;
+constexpr int AT_STAGES = 4;
+constexpr int AT_THREADS = 192;
+constexpr int AT_TILE_BYTES = 128 * 64 * 2;          // one [128][64] fp16 operand tile (Q, K, V^T pair, half of P)
+constexpr float AT_LOG2E = 1.4426950408889634f;
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+struct AttnArgs {
+    int L, heads, n_kt;
+    h16* o;
+    float* lse2;
+};
+
+// ---------------------------------------------------------------------------------------------------
+struct FwdSmem {
+    static constexpr int Q = 0;
+    static constexpr int RING = AT_TILE_BYTES;                               // stage s: K at +s*32K, V^T at +s*32K+16K
+    static constexpr int P = RING + AT_STAGES * 2 * AT_TILE_BYTES;           // two P buffers of 32 KB
+    static constexpr int BARS = P + 2 * 2 * AT_TILE_BYTES;
+    static constexpr int TOTAL = BARS + 256 + 1024;                          // + alignment slack
+};
+
+__global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap mapQ,
+                                                                  const __grid_constant__ CUtensorMap mapK,
+                                                                  const __grid_constant__ CUtensorMap mapV,
+                                                                  const __grid_constant__ AttnArgs a) {
+    extern __shared__ uint8_t at_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FwdSmem::BARS);
+    uint64_t* q_full = bars;                       // [1]
+    uint64_t* kv_full = bars + 1;                  // [STAGES]
+    uint64_t* kv_empty = kv_full + AT_STAGES;      // [STAGES]
+    uint64_t* s_full = kv_empty + AT_STAGES;       // [2]  S[b] computed            (MMA -> softmax)
+    uint64_t* s_empty = s_full + 2;                // [2]  S[b] read into registers (softmax -> MMA)
+    uint64_t* p_full = s_empty + 2;                // [2]  P[b] written             (softmax -> MMA)
+    uint64_t* p_empty = p_full + 2;                // [2]  P[b] consumed by P V     (MMA -> softmax)
+    uint64_t* o_full = p_empty + 2;                // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int qt = blockIdx.x, head = blockIdx.y, img = blockIdx.z;
+    const int bh = img * a.heads + head;
+    const int n_kt = a.n_kt;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&mapQ); prefetch_tmap(&mapK); prefetch_tmap(&mapV);
+        mbar_init(q_full, 1);
+        for (int s = 0; s < AT_STAGES; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], 4);
+            mbar_init(&p_full[b], 4); mbar_init(&p_empty[b], 1);
+        }
+        mbar_init(o_full, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_o = tmem_base + 256;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(q_full, AT_TILE_BYTES);
+            tma_load_4d(smem + FwdSmem::Q, &mapQ, q_full, 0, qt * AT_BM, bh, 0);
+            uint32_t it = 0;
+            for (int pass = 0; pass < 2; ++pass) {
+                for (int j = 0; j < n_kt; ++j, ++it) {
+                    const int s = it % AT_STAGES;
+                    mbar_wait(&kv_empty[s], ((it / AT_STAGES) & 1) ^ 1);
+                    uint8_t* sk = smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES;
+                    mbar_expect_tx(&kv_full[s], pass == 0 ? AT_TILE_BYTES : 2 * AT_TILE_BYTES);
+                    tma_load_4d(sk, &mapK, &kv_full[s], 0, j * AT_BN, bh, 0);
+                    if (pass == 1) {
+                        // V^T [64 dims][128 keys] as two K-major [64][64] blocks (box = 64 keys x 64 dims)
+                        tma_load_4d(sk + AT_TILE_BYTES, &mapV, &kv_full[s], j * AT_BN, 0, bh, 0);
+                        tma_load_4d(sk + AT_TILE_BYTES + AT_TILE_BYTES / 2, &mapV, &kv_full[s], j * AT_BN + 64, 0, bh, 0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_s = make_idesc(AT_BM, AT_BN), idesc_o = make_idesc(AT_BM, AT_HD);
+            const uint64_t dq = make_smem_desc(smem_u32(smem + FwdSmem::Q));
+            mbar_wait(q_full, 0);
+            uint32_t it = 0, sc = 0;
+            auto issue_s = [&](uint32_t it_) {     // S[sc & 1] = Q K^T for ring slot it_
+                const int s = it_ % AT_STAGES, b = sc & 1;
+                mbar_wait(&kv_full[s], (it_ / AT_STAGES) & 1);
+                mbar_wait(&s_empty[b], ((sc >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint64_t dk = make_smem_desc(smem_u32(smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES));
+#pragma unroll
+                for (int k = 0; k < AT_HD / 16; ++k) umma_f16(tmem_base + b * AT_BN, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+                umma_commit(&s_full[b]);
+                ++sc;
+            };
+            for (int j = 0; j < n_kt; ++j, ++it) {          // pass 1: scores only
+                issue_s(it);
+                umma_commit(&kv_empty[it % AT_STAGES]);
+            }
+            uint32_t pc = 0;
+            issue_s(it);                                     // pass 2, software-pipelined by one tile
+            for (int j = 0; j < n_kt; ++j, ++it, ++pc) {
+                if (j + 1 < n_kt) issue_s(it + 1);
+                const int s = it % AT_STAGES, pb = pc & 1;
+                mbar_wait(&p_full[pb], (pc >> 1) & 1);
+                tc_fence_after();
+                const uint32_t sp = smem_u32(smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES);
+                const uint32_t sv = smem_u32(smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES + AT_TILE_BYTES);
+#pragma unroll
+                for (int kb = 0; kb < 2; ++kb) {
+                    const uint64_t dp = make_smem_desc(sp + kb * AT_TILE_BYTES), dv = make_smem_desc(sv + kb * (AT_TILE_BYTES / 2));
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_f16(tmem_o, dp + 2 * k, dv + 2 * k, idesc_o, (j | kb | k) != 0);
+                }
+                umma_commit(&p_empty[pb]);
+                umma_commit(&kv_empty[s]);
+            }
+            umma_commit(o_full);
+        }
+    } else {
+        const int q = warp & 3;                              // TMEM lane quarter
+        const int row = q * 32 + lane, grow = qt * AT_BM + row;
+        const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
+        uint32_t sc = 0;
+        uint32_t r[32];
+        // ---- pass 1: row max and sum of exp2 in the log2 domain
+        float m = -INFINITY, l = 0.f;
+        for (int j = 0; j < n_kt; ++j, ++sc) {
+            const int b = sc & 1;
+            const int nvalid = a.L - j * AT_BN;              // keys of this tile that exist
+            mbar_wait(&s_full[b], (sc >> 1) & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                if (c * 32 >= nvalid) break;
+                tmem_ld32_issue(tlane + b * AT_BN + c * 32, r);
+                tmem_ld_wait();
+                float cm = -INFINITY;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    float v = __uint_as_float(r[i]) * AT_LOG2E;
+                    if (c * 32 + i >= nvalid) v = -INFINITY;
+                    r[i] = __float_as_uint(v);
+                    cm = fmaxf(cm, v);
+                }
+                const float mn = fmaxf(m, cm);
+                float acc = 0.f;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc += ex2_approx(__uint_as_float(r[i]) - mn);
+                l = l * ex2_approx(m - mn) + acc;
+                m = mn;
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_empty[b]);
+        }
+        const float lse2 = m + __log2f(l);
+        if (a.lse2 && grow < a.L) a.lse2[(size_t)bh * a.L + grow] = lse2;
+        // ---- pass 2: exact probabilities -> fp16 P tile in shared memory (K-major, 128B swizzle)
+        uint32_t pc = 0;
+        for (int j = 0; j < n_kt; ++j, ++sc, ++pc) {
+            const int b = sc & 1, pb = pc & 1;
+            const int nvalid = a.L - j * AT_BN;
+            mbar_wait(&s_full[b], (sc >> 1) & 1);
+            mbar_wait(&p_empty[pb], ((pc >> 1) & 1) ^ 1);
+            tc_fence_after();
+            uint8_t* sp = smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES + row * 128;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t pk[16];
+                if (c * 32 < nvalid) {
+                    tmem_ld32_issue(tlane + b * AT_BN + c * 32, r);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * i]), AT_LOG2E, -lse2));
+                        float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * i + 1]), AT_LOG2E, -lse2));
+                        if (c * 32 + 2 * i >= nvalid) p0 = 0.f;
+                        if (c * 32 + 2 * i + 1 >= nvalid) p1 = 0.f;
+                        const h16x2 h = __floats2half2_rn(p0, p1);
+                        pk[i] = *reinterpret_cast<const uint32_t*>(&h);
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) pk[i] = 0u;
+                }
+                uint8_t* blk = sp + (c >> 1) * AT_TILE_BYTES;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int cc = (c & 1) * 4 + t;
+                    *reinterpret_cast<uint4*>(blk + ((cc ^ (row & 7)) << 4)) = make_uint4(pk[4 * t], pk[4 * t + 1], pk[4 * t + 2], pk[4 * t + 3]);
+                }
+            }
+            fence_async_smem();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { mbar_arrive(&s_empty[b]); mbar_arrive(&p_full[pb]); }
+        }
+        // ---- epilogue: O (already normalised) -> fp16, head-interleaved [N*L, heads*64]
+        mbar_wait(o_full, 0);
+        tc_fence_after();
+        h16* orow = a.o + ((size_t)img * a.L + grow) * (size_t)(a.heads * AT_HD) + head * AT_HD;
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+            tmem_ld32_issue(tlane + 256 + c * 32, r);
+            tmem_ld_wait();
+            if (grow < a.L) {
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    uint32_t w[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const h16x2 h = __floats2half2_rn(__uint_as_float(r[8 * t + 2 * i]), __uint_as_float(r[8 * t + 2 * i + 1]));
+                        w[i] = *reinterpret_cast<const uint32_t*>(&h);
+                    }
+                    *reinterpret_cast<uint4*>(orow + c * 32 + t * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+            }
+        }
+        tc_fence_before();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+struct MeanSmem {
+    static constexpr int RING = 0;                                           // stage s: Q_h at +s*32K, K_h at +s*32K+16K
+    static constexpr int STG = AT_STAGES * 2 * AT_TILE_BYTES;                // 4 warps x 4 KB transposition blocks
+    static constexpr int BARS = STG + 4 * 32 * 32 * 4;
+    static constexpr int TOTAL = BARS + 256 + 1024;
+};
+struct MeanArgs {
+    int L, heads;
+    const float* lse2;
+    float* avg;
+};
+
+__global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __grid_constant__ CUtensorMap mapQ,
+                                                                       const __grid_constant__ CUtensorMap mapK,
+                                                                       const __grid_constant__ MeanArgs a) {
+    extern __shared__ uint8_t at_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + MeanSmem::BARS);
+    uint64_t* full = bars;                         // [STAGES]
+    uint64_t* empty = full + AT_STAGES;            // [STAGES]
+    uint64_t* s_full = empty + AT_STAGES;          // [2]
+    uint64_t* s_empty = s_full + 2;                // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int kt = blockIdx.x, qt = blockIdx.y, img = blockIdx.z;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&mapQ); prefetch_tmap(&mapK);
+        for (int s = 0; s < AT_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], 4); }
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int h = 0; h < a.heads; ++h) {
+                const int s = h % AT_STAGES;
+                mbar_wait(&empty[s], ((h / AT_STAGES) & 1) ^ 1);
+                uint8_t* sq = smem + MeanSmem::RING + s * 2 * AT_TILE_BYTES;
+                mbar_expect_tx(&full[s], 2 * AT_TILE_BYTES);
+                tma_load_4d(sq, &mapQ, &full[s], 0, qt * AT_BM, img * a.heads + h, 0);
+                tma_load_4d(sq + AT_TILE_BYTES, &mapK, &full[s], 0, kt * AT_BN, img * a.heads + h, 0);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_s = make_idesc(AT_BM, AT_BN);
+            for (int h = 0; h < a.heads; ++h) {
+                const int s = h % AT_STAGES, b = h & 1;
+                mbar_wait(&full[s], (h / AT_STAGES) & 1);
+                mbar_wait(&s_empty[b], ((h >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t sq = smem_u32(smem + MeanSmem::RING + s * 2 * AT_TILE_BYTES);
+                const uint64_t dq = make_smem_desc(sq), dk = make_smem_desc(sq + AT_TILE_BYTES);
+#pragma unroll
+                for (int k = 0; k < AT_HD / 16; ++k) umma_f16(tmem_base + b * AT_BN, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+                umma_commit(&s_full[b]);
+                umma_commit(&empty[s]);
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        const int row = q * 32 + lane, grow = qt * AT_BM + row;
+        const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
+        float* stg = reinterpret_cast<float*>(smem + MeanSmem::STG) + (warp - 2) * 32 * 32;
+        float acc[AT_BN];
+#pragma unroll
+        for (int i = 0; i < AT_BN; ++i) acc[i] = 0.f;
+        uint32_t r[32];
+        for (int h = 0; h < a.heads; ++h) {
+            const int b = h & 1;
+            const float lse = (grow < a.L) ? __ldg(a.lse2 + (size_t)(img * a.heads + h) * a.L + grow) : 0.f;
+            mbar_wait(&s_full[b], (h >> 1) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                tmem_ld32_issue(tlane + b * AT_BN + c * 32, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[c * 32 + i] += ex2_approx(fmaf(__uint_as_float(r[i]), AT_LOG2E, -lse));
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_empty[b]);
+        }
+        // mean over heads, transposed through the warp's swizzled 32x32 block so that each store is one row x 32 keys
+        const float inv_h = 1.f / (float)a.heads;
+        const int row0 = qt * AT_BM + q * 32;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int key = kt * AT_BN + c * 32 + lane;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<float4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) =
+                    make_float4(acc[c * 32 + 4 * j] * inv_h, acc[c * 32 + 4 * j + 1] * inv_h, acc[c * 32 + 4 * j + 2] * inv_h,
+                                acc[c * 32 + 4 * j + 3] * inv_h);
+            __syncwarp();
+            if (key < a.L) {
+                float* dst = a.avg + ((size_t)img * a.L + row0) * a.L + key;
+#pragma unroll 4
+                for (int rr = 0; rr < 32; ++rr) {
+                    if (row0 + rr >= a.L) break;
+                    dst[(size_t)rr * a.L] = stg[rr * 32 + (((lane >> 2) ^ (rr & 7)) << 2) + (lane & 3)];
+                }
+            }
+            __syncwarp();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 256);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+static int attn_maps(const h16* q, const h16* k, const h16* vt, int nh, int L, int Lp, CUtensorMap* mq, CUtensorMap* mk,
+                     CUtensorMap* mv) {
+    int u0, u1, rc;
+    GemmOperand oq{q, L, AT_HD, (long)L * AT_HD, 0}, ok{k, L, AT_HD, (long)L * AT_HD, 0};
+    if ((rc = make_tma_map(mq, oq, AT_HD, nh, 1, AT_BM, &u0, &u1))) return rc;
+    if ((rc = make_tma_map(mk, ok, AT_HD, nh, 1, AT_BN, &u0, &u1))) return rc;
+    if (vt && mv) {
+        // V^T rows = head dims, K extent = L keys (NOT Lp): columns L..Lp-1 are never written and must read as zero
+        GemmOperand ov{vt, AT_HD, Lp, (long)AT_HD * Lp, 0};
+        if ((rc = make_tma_map(mv, ov, L, nh, 1, AT_HD, &u0, &u1))) return rc;
+    }
+    return WC_OK;
+}
+
+int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, float* lse2, int n_img, int heads, int L, int Lp,
+                         cudaStream_t st) {
+    WC_CHECK_ARG(q && k && vt && o && n_img > 0 && heads > 0 && L > 0 && Lp >= L && (Lp & 7) == 0);
+    WC_CHECK_ARG(heads <= 65535 && n_img <= 65535);
+    static bool attr_set = false;
+    if (!attr_set) {
+        WC_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::TOTAL));
+        attr_set = true;
+    }
+    CUtensorMap mq, mk, mv;
+    int rc = attn_maps(q, k, vt, n_img * heads, L, Lp, &mq, &mk, &mv);
+    if (rc) return rc;
+    // a batch of 1 collapses the map's batch dimension; the kernel's batch coordinate is then 0 anyway
+    AttnArgs a{L, heads, ceil_div(L, AT_BN), o, lse2};
+    dim3 grid(ceil_div(L, AT_BM), heads, n_img);
+    ProfScope prof(PK_ATTENTION, 4.0 * L * L * AT_HD * heads * n_img, st);
+    attn_fwd_kernel<<<grid, AT_THREADS, FwdSmem::TOTAL, st>>>(mq, mk, mv, a);
+    WC_LAUNCH_CHECK();
+    return WC_OK;
+}
+
+int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* avg, int n_img, int heads, int L,
+                         cudaStream_t st) {
+    WC_CHECK_ARG(q && k && lse2 && avg && n_img > 0 && heads > 0 && L > 0 && n_img <= 65535);
+    static bool attr_set = false;
+    if (!attr_set) {
+        WC_CUDA(cudaFuncSetAttribute(attn_headmean_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MeanSmem::TOTAL));
+        attr_set = true;
+    }
+    CUtensorMap mq, mk;
+    int rc = attn_maps(q, k, nullptr, n_img * heads, L, 0, &mq, &mk, nullptr);
+    if (rc) return rc;
+    MeanArgs a{L, heads, lse2, avg};
+    dim3 grid(ceil_div(L, AT_BN), ceil_div(L, AT_BM), n_img);
+    ProfScope prof(PK_SOFTMAX, 4.0 * n_img * (double)L * L, st);
+    attn_headmean_kernel<<<grid, AT_THREADS, MeanSmem::TOTAL, st>>>(mq, mk, a);
+    WC_LAUNCH_CHECK();
+    return WC_OK;
+}
+
+}  // namespace wc
+
+using namespace wc;
+
+// Test / micro-bench entry for the fused attention pair (see include/weclip_b200.h).
+extern "C" int wc_attention_fwd(const void* q, const void* k, const void* vt, void* o, float* lse2, float* attn_avg,
+                                int n_img, int heads, int L, int Lp, void* stream) {
+    WC_CHECK_ARG(lse2 || !attn_avg);
+    int rc = launch_attention_fwd(reinterpret_cast<const h16*>(q), reinterpret_cast<const h16*>(k),
+                                  reinterpret_cast<const h16*>(vt), reinterpret_cast<h16*>(o), lse2, n_img, heads, L, Lp,
+                                  as_stream(stream));
+    if (rc || !attn_avg) return rc;
+    return launch_attn_headmean(reinterpret_cast<const h16*>(q), reinterpret_cast<const h16*>(k), lse2, attn_avg, n_img,
+                                heads, L, as_stream(stream));
+}

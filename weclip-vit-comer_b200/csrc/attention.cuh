@@ -1,0 +1,19 @@
+// Fused multi-head attention forward for sm_100a (tcgen05 + TMEM + TMA), head_dim 64.
+// Replaces the materialised [N*heads, L, L] score tensor of clip/myAtt.py:53-64 on the encoder blocks.
+#pragma once
+#include "common.cuh"
+
+namespace wc {
+
+// q, k: [N*heads, L, 64] fp16 (q pre-scaled by 1/sqrt(64), myAtt.py:54); vt: [N*heads, 64, Lp] fp16 (V transposed).
+// o: [N*L, heads*64] fp16, head-interleaved (myAtt.py:320).  lse2 (optional): [N*heads, L] fp32, log2-domain
+// log-sum-exp of each score row (input of launch_attn_headmean).
+int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, float* lse2, int n_img, int heads, int L, int Lp,
+                         cudaStream_t st);
+
+// avg[n, i, j] = mean over heads of softmax(q k^T)[n, h, i, j] (myAtt.py:323-326), fp32 [N, L, L], each element written
+// once.  Needs lse2 from launch_attention_fwd.
+int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* avg, int n_img, int heads, int L,
+                         cudaStream_t st);
+
+}  // namespace wc

@@ -22,22 +22,30 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
         p.epi.L = L; p.epi.Lp = (int)Lp; p.epi.heads = heads; p.epi.hd = hd; p.epi.qscale = 1.f / sqrtf((float)hd);
         if ((rc = launch_gemm(p, st))) return rc;
     }
-    // S = q k^T (myAtt.py:56), fp32 [N*heads, L, Lp]
-    {
-        GemmProblem p; p.M = L; p.N = L; p.K = hd; p.nb0 = n_img * heads;
-        p.A = op(b.q, L, hd, (long)L * hd); p.B = op(b.k, L, hd, (long)L * hd);
-        p.epi.out = b.S; p.epi.ldo = Lp; p.epi.out_bs0 = (long)L * Lp;
-        if ((rc = launch_gemm(p, st))) return rc;
-    }
-    // softmax (myAtt.py:59) + mean over heads (myAtt.py:323-326)
-    if ((rc = launch_softmax_headmean(b.S, b.P, b.attn_avg, n_img, heads, L, (int)Lp, st))) return rc;
-    // O = P V (myAtt.py:63) written head-interleaved into [M,E] (myAtt.py:320)
-    {
-        GemmProblem p; p.M = L; p.N = hd; p.K = L; p.nb0 = heads; p.nb1 = n_img;
-        p.A = op(b.P, L, Lp, (long)L * Lp, (long)heads * L * Lp);
-        p.B = op(b.vt, hd, Lp, (long)hd * Lp, (long)heads * hd * Lp);
-        p.epi.out = b.o; p.epi.out_f16 = 1; p.epi.ldo = E; p.epi.out_bs0 = hd; p.epi.out_bs1 = (long)L * E;
-        if ((rc = launch_gemm(p, st))) return rc;
+    if (!b.S) {
+        // fused path: scores and probabilities never leave the SM (attention.cu); softmax(q k^T) v written
+        // head-interleaved into [M,E] (myAtt.py:53-64,320), then the head-mean map from the row log-sum-exps (:323-326)
+        if (hd != 64 || !b.lse) return fail(WC_ERR_UNSUPPORTED, "%s: fused attention needs head_dim 64 and an lse buffer", __func__);
+        if ((rc = launch_attention_fwd(b.q, b.k, b.vt, b.o, b.lse, n_img, heads, L, (int)Lp, st))) return rc;
+        if (b.attn_avg && (rc = launch_attn_headmean(b.q, b.k, b.lse, b.attn_avg, n_img, heads, L, st))) return rc;
+    } else {
+        // S = q k^T (myAtt.py:56), fp32 [N*heads, L, Lp]
+        {
+            GemmProblem p; p.M = L; p.N = L; p.K = hd; p.nb0 = n_img * heads;
+            p.A = op(b.q, L, hd, (long)L * hd); p.B = op(b.k, L, hd, (long)L * hd);
+            p.epi.out = b.S; p.epi.ldo = Lp; p.epi.out_bs0 = (long)L * Lp;
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
+        // softmax (myAtt.py:59) + mean over heads (myAtt.py:323-326)
+        if ((rc = launch_softmax_headmean(b.S, b.P, b.attn_avg, n_img, heads, L, (int)Lp, st))) return rc;
+        // O = P V (myAtt.py:63) written head-interleaved into [M,E] (myAtt.py:320)
+        {
+            GemmProblem p; p.M = L; p.N = hd; p.K = L; p.nb0 = heads; p.nb1 = n_img;
+            p.A = op(b.P, L, Lp, (long)L * Lp, (long)heads * L * Lp);
+            p.B = op(b.vt, hd, Lp, (long)hd * Lp, (long)heads * hd * Lp);
+            p.epi.out = b.o; p.epi.out_f16 = 1; p.epi.ldo = E; p.epi.out_bs0 = hd; p.epi.out_bs1 = (long)L * E;
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
     }
     // out-proj + residual (myAtt.py:321, model.py:212)
     {
@@ -66,17 +74,19 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
 }
 
 // Attention scratch shared by every block of one call.
-struct AttnScratch { h16 *a, *q, *k, *vt, *P, *o, *u; float* S; };
+struct AttnScratch { h16 *a, *q, *k, *vt, *P, *o, *u; float *S, *lse; };
 
-static AttnScratch carve_block(Arena& ar, int n_img, int L, int E, int heads) {
+// fused: no materialised score / probability tensors, a [N*heads, L] log-sum-exp vector instead
+static AttnScratch carve_block(Arena& ar, int n_img, int L, int E, int heads, bool fused) {
     const long M = (long)n_img * L, Lp = round8(L), hd = E / heads;
     AttnScratch s;
     s.a = ar.get<h16>(M * E);
     s.q = ar.get<h16>(M * E);
     s.k = ar.get<h16>(M * E);
     s.vt = ar.get<h16>((long)n_img * heads * hd * Lp);
-    s.S = ar.get<float>((long)n_img * heads * L * Lp);
-    s.P = ar.get<h16>((long)n_img * heads * L * Lp);
+    s.S = fused ? nullptr : ar.get<float>((long)n_img * heads * L * Lp);
+    s.P = fused ? nullptr : ar.get<h16>((long)n_img * heads * L * Lp);
+    s.lse = fused ? ar.get<float>((long)n_img * heads * L) : nullptr;
     s.o = ar.get<h16>(M * E);
     s.u = ar.get<h16>(M * 4 * E);
     return s;
@@ -87,7 +97,7 @@ static size_t encoder_layout(Arena& ar, int N, int H, int W, float** x, float** 
     *x = ar.get<float>((long)N * L * E);
     *pos = ar.get<float>((long)L * E);
     *patches = ar.get<h16>((long)N * P * E);
-    *s = carve_block(ar, N, L, E, 12);
+    *s = carve_block(ar, N, L, E, 12, true);
     return ar.off;
 }
 
@@ -97,7 +107,7 @@ static size_t decoder_layout(Arena& ar, int N, int P, int C, h16** z1, h16** cat
     *cat = ar.get<h16>((long)N * P * 11 * D);
     *x = ar.get<float>((long)N * P * D);
     *x_bf = ar.get<h16>((long)N * P * D);
-    *s = carve_block(ar, N, P, D, 8);
+    *s = carve_block(ar, N, P, D, 8, false);
     return ar.off;
 }
 
@@ -140,7 +150,7 @@ extern "C" int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, 
     for (int i = 0; i < 11; ++i) {
         BlockBuffers b{};
         b.x_in = x; b.x_mid = x; b.x_out = (i == 10) ? x_last : x;
-        b.a = s.a; b.q = s.q; b.k = s.k; b.vt = s.vt; b.S = s.S; b.P = s.P; b.o = s.o; b.u = s.u;
+        b.a = s.a; b.q = s.q; b.k = s.k; b.vt = s.vt; b.S = s.S; b.P = s.P; b.lse = s.lse; b.o = s.o; b.u = s.u;
         const int slot = i - (11 - n_attn);
         b.attn_avg = (slot >= 0) ? attn_avg + (size_t)slot * N * L * L : nullptr;
         b.tap = taps + (size_t)i * M * E;
@@ -201,7 +211,7 @@ extern "C" int wc_decoder_fwd(const wc_decoder_weights* w, const void* taps_, in
     for (int i = 0; i < 3; ++i) {   // TransDecoder.py:113-119 (the three attention maps are unused downstream)
         BlockBuffers b{};
         b.x_in = x; b.x_mid = x; b.x_out = x;
-        b.a = s.a; b.q = s.q; b.k = s.k; b.vt = s.vt; b.S = s.S; b.P = s.P; b.o = s.o; b.u = s.u;
+        b.a = s.a; b.q = s.q; b.k = s.k; b.vt = s.vt; b.S = s.S; b.P = s.P; b.lse = s.lse; b.o = s.o; b.u = s.u;
         b.tap = (i == 2) ? xb : nullptr;
         if ((rc = run_block(w->blocks[i], b, N, P, D, 8, st))) return rc;
     }

@@ -2,6 +2,7 @@
 #pragma once
 #include "gemm.cuh"
 #include "elementwise.cuh"
+#include "attention.cuh"
 
 namespace wc {
 
@@ -31,8 +32,9 @@ struct BlockBuffers {
     float* a_f32;       // optional fp32 copy of the ln_1 output (Grad-CAM hook tensor)
     h16 *q, *k, *vt;   // [N*heads, L, hd], [N*heads, L, hd], [N*heads, hd, Lp]
     h16* v;            // optional [N*heads, L, hd]
-    float* S;           // [N*heads, L, Lp]
-    h16* P;            // [N*heads, L, Lp]
+    float* S;           // [N*heads, L, Lp]   materialised scores (unfused path only)
+    h16* P;            // [N*heads, L, Lp]   materialised probabilities (unfused path only; Grad-CAM's backward reads them)
+    float* lse;         // [N*heads, L]       fused path (S == nullptr, head_dim 64): log2-domain row log-sum-exp
     h16* o;            // [M,E]
     h16* u;            // [M,4E]  QuickGELU(c_fc)
     h16* u_pre;        // optional [M,4E] pre-activation

@@ -446,7 +446,7 @@ struct MapKeyHash {
     }
 };
 
-static int make_map(CUtensorMap* out, const GemmOperand& op, int K, int nb0, int nb1, int box_rows, int* use_b0, int* use_b1) {
+int make_tma_map(CUtensorMap* out, const GemmOperand& op, int K, int nb0, int nb1, int box_rows, int* use_b0, int* use_b1) {
     auto enc = get_encode();
     if (!enc) return fail(WC_ERR_CUDA, "%s: cuTensorMapEncodeTiled entry point unavailable", __func__);
     if ((reinterpret_cast<uintptr_t>(op.ptr) & 15) || (op.ld & 7) || (op.bs0 & 7) || (op.bs1 & 7))
@@ -514,9 +514,9 @@ static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
     CUtensorMap mA, mB;
     KernelArgs ka;
     ka.M = p.M; ka.N = p.N; ka.K = p.K; ka.nb0 = p.nb0; ka.e = p.epi;
-    int rc = make_map(&mA, p.A, p.K, p.nb0, p.nb1, BM, &ka.a_b0, &ka.a_b1);
+    int rc = make_tma_map(&mA, p.A, p.K, p.nb0, p.nb1, BM, &ka.a_b0, &ka.a_b1);
     if (rc) return rc;
-    rc = make_map(&mB, p.B, p.K, p.nb0, p.nb1, BN, &ka.b_b0, &ka.b_b1);
+    rc = make_tma_map(&mB, p.B, p.K, p.nb0, p.nb1, BN, &ka.b_b0, &ka.b_b1);
     if (rc) return rc;
     ka.tiles_m = ceil_div(p.M, BM);
     ka.tiles_n = ceil_div(p.N, BN);

@@ -43,6 +43,10 @@ struct GemmProblem {
     GemmEpilogue epi;
 };
 
+// Rank-4 K-major tensor map (k, row, b0, b1) over `op` with a (64 x box_rows) box and 128-byte swizzle (cached per
+// thread).  use_b0 / use_b1 report whether the batch coordinates are live (0: pass coordinate 0).
+int make_tma_map(CUtensorMap* out, const GemmOperand& op, int K, int nb0, int nb1, int box_rows, int* use_b0, int* use_b1);
+
 // Enqueue on `st`.  Returns WC_OK or a negative error (message in wc_last_error()).
 int launch_gemm(const GemmProblem& p, cudaStream_t st);
 

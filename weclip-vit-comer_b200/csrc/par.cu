@@ -1,30 +1,37 @@
 // PAR (pixel-adaptive refinement) for sm_100a.  Reference: WeCLIP_model/PAR.py:26-92.
 //
 // Memory-bound stencil family.  Data layout in HBM:
-//   img   [B,3,H,W]   fp32 planar (resized copy lives in the workspace when Hi,Wi != H,W)
-//   aff   [B,NN,H,W]  fp32 planar, NN = 8*n_dil (48): one coalesced stream per neighbour
-//   masks [sumKc,H,W] fp32 planar, ragged over images; two ping-pong buffers in the workspace
-// Kernels:
-//   par_resize_kernel   bilinear align_corners=True (PAR.py:67)
-//   par_aff_kernel      per pixel: 3-pass over the NN x 3 neighbour values (mean, centred sum of squares,
-//                       logits) -> softmax + w2*softmax(pos)   (PAR.py:70-86).  Algorithmic bytes/pixel: 12 + 4*NN.
-//   par_iter_kernel     one propagation step (PAR.py:88-90): streams NN affinities per pixel with
-//                       L1::no_allocate loads so that L1 keeps the (re-used) mask neighbourhood.
-//                       Algorithmic bytes/pixel/iteration: 4*NN + 2*4*Kc.
+//   img   [B,3,H,W]    fp32 planar (resized copy lives in the workspace when Hi,Wi != H,W)
+//   aff   [B,NN,H,Wp]  planar, NN = 8*n_dil (48), row pitch Wp = round_up(W,8); stored as fp32 (exact path) or
+//                      fp16 (pipeline path: halves the bytes every propagation step streams)
+//   masks [sumKc,H,W]  fp32 planar, ragged over images; two ping-pong buffers [sumKc,H,Wp] in the workspace
+// Kernels (fast path = the module's own dilation set 1/2/4/8/12/24):
+//   par_resize_kernel     bilinear align_corners=True (PAR.py:67)
+//   par_aff_tile_kernel   64x32-pixel tile + 24-pixel replicate halo of the 3 image planes in shared memory; per pixel
+//                         mean / unbiased std / logits over the 48 neighbours from shared memory, softmax +
+//                         w2*softmax(pos) (PAR.py:70-86).  Algorithmic bytes/pixel: 12 + s_a*NN.
+//   par_iter_tile_kernel  one propagation step (PAR.py:88-90): 64xTH tile + halo of the KC mask planes in shared
+//                         memory (filled with 128-bit loads, clamped = replicate padding), each thread owns 4 consecutive
+//                         pixels: per neighbour ONE 128/64-bit streaming affinity load (L1 no-allocate, L2 evict-first) and
+//                         aligned LDS.128 mask vectors (shifted neighbours are register renames).
+//                         Algorithmic bytes/pixel/iteration: s_a*NN + 2*4*Kc.
+//   par_aff_kernel / par_iter_kernel   generic dilation sets (any n_dil <= 8), L1-cached gathers.
 #include "common.cuh"
 
 #include <math.h>
+#include <vector>
 
 namespace wc {
 
 constexpr int PAR_MAX_NN = 8 * WC_PAR_MAX_DIL;
-constexpr int PAR_TX = 32;   // one warp = 32 consecutive pixels of a row
-constexpr int PAR_TY = 16;   // 512 threads; large tiles keep the 24-px neighbourhood L1-resident
-constexpr int PAR_KC = 4;    // mask channels per thread
+constexpr int PAR_TX = 32;   // generic kernels: one warp = 32 consecutive pixels of a row
+constexpr int PAR_TY = 16;
+constexpr int PAR_KC = 4;    // mask channels per thread / per chunk
 constexpr int PAR_MAX_CHUNKS = 240;
 
 struct ParGeom {
     int H, W, nn;
+    int wp;                  // row pitch of the affinity / ping-pong planes
     short dy[PAR_MAX_NN];
     short dx[PAR_MAX_NN];
 };
@@ -37,11 +44,13 @@ struct ParChunks {
     short cnt[PAR_MAX_CHUNKS];   // channels in this chunk (1..PAR_KC)
 };
 
+inline int par_pitch(int W) { return (W + 7) & ~7; }
+
 static int make_geom(ParGeom& g, ParPos* pos, int H, int W, const int* dil, int n_dil) {
     if (n_dil < 1 || n_dil > WC_PAR_MAX_DIL) return -1;
     static const int by[8] = {-1, -1, -1, 0, 0, 1, 1, 1};   // PAR.py:10-24 raster order without the centre
     static const int bx[8] = {-1, 0, 1, -1, 1, -1, 0, 1};
-    g.H = H; g.W = W; g.nn = 8 * n_dil;
+    g.H = H; g.W = W; g.nn = 8 * n_dil; g.wp = par_pitch(W);
     for (int d = 0; d < n_dil; ++d)
         for (int j = 0; j < 8; ++j) {
             g.dy[d * 8 + j] = (short)(by[j] * dil[d]);
@@ -66,11 +75,58 @@ static int make_geom(ParGeom& g, ParPos* pos, int H, int W, const int* dil, int 
     return 0;
 }
 
-__device__ __forceinline__ float ldg_stream(const float* p) {
-    float v;
-    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
-    return v;
+static bool is_standard_dilations(const int* dil, int n_dil) {
+    static const int std_d[6] = {1, 2, 4, 8, 12, 24};
+    if (n_dil != 6) return false;
+    for (int i = 0; i < 6; ++i) if (dil[i] != std_d[i]) return false;
+    return true;
 }
+
+// ---- affinity storage: fp32 (exact path) or fp16 (pipeline path) ---------------------------------------
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+template <typename T> struct AffIO;
+template <> struct AffIO<float> {
+    static __device__ __forceinline__ void st(float* p, float v) { *p = v; }
+    static __device__ __forceinline__ float ld(const float* p) {
+        float v;
+        asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+        return v;
+    }
+    using Raw = float4;               // 4 consecutive pixels' weights as loaded
+    static constexpr int LOOKAHEAD = 1;   // dilations prefetched ahead of the one being accumulated
+    static __device__ __forceinline__ Raw ld4(const float* p, uint64_t pol) {
+        float4 v;
+        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p), "l"(pol));
+        return v;
+    }
+    static __device__ __forceinline__ float4 unpack(const Raw& r) { return r; }
+};
+template <> struct AffIO<__half> {
+    static __device__ __forceinline__ void st(__half* p, float v) { *p = __float2half_rn(v); }
+    static __device__ __forceinline__ float ld(const __half* p) {
+        unsigned short u;
+        asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(u) : "l"(p));
+        return __half2float(__ushort_as_half(u));
+    }
+    using Raw = uint2;                // 4 x fp16 stay packed until they are used (2 registers per neighbour)
+    static constexpr int LOOKAHEAD = 2;
+    static __device__ __forceinline__ Raw ld4(const __half* p, uint64_t pol) {
+        uint2 v;
+        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u32 {%0, %1}, [%2], %3;"
+                     : "=r"(v.x), "=r"(v.y) : "l"(p), "l"(pol));
+        return v;
+    }
+    static __device__ __forceinline__ float4 unpack(const Raw& r) {
+        const float2 lo = __half22float2(*reinterpret_cast<const __half2*>(&r.x));
+        const float2 hi = __half22float2(*reinterpret_cast<const __half2*>(&r.y));
+        return make_float4(lo.x, lo.y, hi.x, hi.y);
+    }
+};
 
 // ---------------------------------------------------------------------------------------------------
 __global__ void par_resize_kernel(const float* __restrict__ src, float* __restrict__ dst, int planes,
@@ -93,8 +149,10 @@ __global__ void par_resize_kernel(const float* __restrict__ src, float* __restri
 }
 
 // ---------------------------------------------------------------------------------------------------
-template <int NN>   // NN > 0: compile-time neighbour count (48); NN == 0: runtime g.nn (<= PAR_MAX_NN)
-__global__ void __launch_bounds__(256) par_aff_kernel(const float* __restrict__ img, float* __restrict__ aff,
+// Generic dilation sets (runtime neighbour table).  Neighbour gathers go through L1.
+// ---------------------------------------------------------------------------------------------------
+template <typename AffT>
+__global__ void __launch_bounds__(256) par_aff_kernel(const float* __restrict__ img, AffT* __restrict__ aff,
                                                       const __grid_constant__ ParGeom g,
                                                       const __grid_constant__ ParPos pos) {
     const int x = blockIdx.x * 32 + threadIdx.x;
@@ -102,7 +160,7 @@ __global__ void __launch_bounds__(256) par_aff_kernel(const float* __restrict__ 
     const int b = blockIdx.z;
     const int H = g.H, W = g.W;
     if (x >= W || y >= H) return;
-    const int nn = NN > 0 ? NN : g.nn;
+    const int nn = g.nn;
     const size_t hw = (size_t)H * W;
     const float* im = img + (size_t)b * 3 * hw;
     const float c0 = im[(size_t)y * W + x], c1 = im[hw + (size_t)y * W + x], c2 = im[2 * hw + (size_t)y * W + x];
@@ -140,22 +198,21 @@ __global__ void __launch_bounds__(256) par_aff_kernel(const float* __restrict__ 
     float mx = -INFINITY;
 #pragma unroll 8
     for (int n = 0; n < nn; ++n) mx = fmaxf(mx, logit(n));
-    // pass 4: softmax denominator; pass 5: write softmax + w2*softmax(pos) (PAR.py:86).  Logits are
-    // recomputed instead of kept (48 live registers spill); the re-reads are L1 hits.
+    // pass 4: softmax denominator; pass 5: write softmax + w2*softmax(pos) (PAR.py:86)
     float sum = 0.f;
 #pragma unroll 8
     for (int n = 0; n < nn; ++n) sum += expf(logit(n) - mx);
     const float inv = 1.f / sum;
-    float* a = aff + (size_t)b * nn * hw + (size_t)y * W + x;
+    const size_t plane = (size_t)H * g.wp;
+    AffT* a = aff + (size_t)b * nn * plane + (size_t)y * g.wp + x;
 #pragma unroll 8
-    for (int n = 0; n < nn; ++n) a[(size_t)n * hw] = expf(logit(n) - mx) * inv + pos.v[n];
+    for (int n = 0; n < nn; ++n) AffIO<AffT>::st(a + (size_t)n * plane, expf(logit(n) - mx) * inv + pos.v[n]);
 }
 
-// ---------------------------------------------------------------------------------------------------
-template <int NN>
-__global__ void __launch_bounds__(PAR_TX* PAR_TY) par_iter_kernel(const float* __restrict__ aff,
-                                                                   const float* __restrict__ in,
-                                                                   float* __restrict__ out,
+template <typename AffT>
+__global__ void __launch_bounds__(PAR_TX* PAR_TY) par_iter_kernel(const AffT* __restrict__ aff,
+                                                                   const float* __restrict__ in, int in_pitch,
+                                                                   float* __restrict__ out, int out_pitch,
                                                                    const __grid_constant__ ParGeom g,
                                                                    const __grid_constant__ ParChunks ch) {
     const int x = blockIdx.x * PAR_TX + threadIdx.x;
@@ -163,29 +220,287 @@ __global__ void __launch_bounds__(PAR_TX* PAR_TY) par_iter_kernel(const float* _
     const int c = blockIdx.z;
     const int H = g.H, W = g.W;
     if (x >= W || y >= H) return;
-    const int nn = NN > 0 ? NN : g.nn;
+    const int nn = g.nn;
     const int cnt = ch.cnt[c];
-    const size_t hw = (size_t)H * W;
-    const float* a = aff + (size_t)ch.b[c] * nn * hw + (size_t)y * W + x;
-    const float* m = in + (size_t)ch.ch0[c] * hw;
+    const size_t aplane = (size_t)H * g.wp, iplane = (size_t)H * in_pitch, oplane = (size_t)H * out_pitch;
+    const AffT* a = aff + (size_t)ch.b[c] * nn * aplane + (size_t)y * g.wp + x;
+    const float* m = in + (size_t)ch.ch0[c] * iplane;
     float acc[PAR_KC];
 #pragma unroll
     for (int k = 0; k < PAR_KC; ++k) acc[k] = 0.f;
-#pragma unroll
-    for (int n = 0; n < (NN > 0 ? NN : PAR_MAX_NN); ++n) {
-        if (NN == 0 && n >= nn) break;
+    for (int n = 0; n < nn; ++n) {
         const int yy = min(max(y + g.dy[n], 0), H - 1), xx = min(max(x + g.dx[n], 0), W - 1);
-        const float w = ldg_stream(a + (size_t)n * hw);
-        const float* p = m + (size_t)yy * W + xx;
+        const float w = AffIO<AffT>::ld(a + (size_t)n * aplane);
+        const float* p = m + (size_t)yy * in_pitch + xx;
 #pragma unroll
         for (int k = 0; k < PAR_KC; ++k)
-            if (k < cnt) acc[k] = fmaf(w, __ldg(p + (size_t)k * hw), acc[k]);
+            if (k < cnt) acc[k] = fmaf(w, __ldg(p + (size_t)k * iplane), acc[k]);
     }
-    float* o = out + (size_t)ch.ch0[c] * hw + (size_t)y * W + x;
+    float* o = out + (size_t)ch.ch0[c] * oplane + (size_t)y * out_pitch + x;
 #pragma unroll
     for (int k = 0; k < PAR_KC; ++k)
-        if (k < cnt) o[(size_t)k * hw] = acc[k];
+        if (k < cnt) o[(size_t)k * oplane] = acc[k];
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Fast path: the module's dilation set {1,2,4,8,12,24} (PAR.py / model_attn_aff_voc.py:92), shared-memory tiles.
+// ---------------------------------------------------------------------------------------------------
+constexpr int PT_W = 64;                 // tile width in pixels (16 threads x 4 pixels)
+constexpr int PT_HALO = 24;              // largest dilation
+constexpr int PT_SW = PT_W + 2 * PT_HALO;   // 112 floats per shared-memory row (448 B: 16 B aligned)
+constexpr int PT_THREADS = 256;
+
+struct TileArgs {
+    int H, W, wp;            // wp: affinity pitch
+    int in_pitch, out_pitch; // mask plane pitches of this step's source / destination
+    int in_vec, out_vec;     // 128-bit global access allowed (pitch % 4 == 0 and base 16 B aligned)
+};
+
+__host__ __device__ constexpr int std_dil(int d) { return d == 0 ? 1 : d == 1 ? 2 : d == 2 ? 4 : d == 3 ? 8 : d == 4 ? 12 : 24; }
+
+// Fill `planes` shared-memory planes [SH][PT_SW] with the (x0-24.., y0-24..) window of src planes, coordinates clamped
+// to the image (= F.pad(mode='replicate'), PAR.py:44).
+template <int SH, int NT>
+__device__ __forceinline__ void fill_tile(float* tile, const float* __restrict__ src, size_t plane, int pitch, int planes,
+                                          int x0, int y0, int H, int W, int vec) {
+    constexpr int VPR = PT_SW / 4;   // 28 vectors per row
+    const int total = planes * SH * VPR;
+    for (int i = threadIdx.x; i < total; i += NT) {
+        const int v = i % VPR, rk = i / VPR;
+        const int r = rk % SH, k = rk / SH;
+        const int gy = min(max(y0 - PT_HALO + r, 0), H - 1);
+        const int gx = x0 - PT_HALO + 4 * v;
+        const float* rowp = src + (size_t)k * plane + (size_t)gy * pitch;
+        float* dst = tile + ((size_t)k * SH + r) * PT_SW + 4 * v;
+        if (vec && gx >= 0 && gx + 3 < W) {
+            // interior vector: asynchronous 16-byte global->shared copy (no register staging, many in flight)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)),
+                         "l"(rowp + gx) : "memory");
+        } else {
+            float4 val;
+            val.x = __ldg(rowp + min(max(gx, 0), W - 1));
+            val.y = __ldg(rowp + min(max(gx + 1, 0), W - 1));
+            val.z = __ldg(rowp + min(max(gx + 2, 0), W - 1));
+            val.w = __ldg(rowp + min(max(gx + 3, 0), W - 1));
+            *reinterpret_cast<float4*>(dst) = val;
+        }
+    }
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+// acc[k][i] += w * mask(k, row, x+i+shift): the four pixels of this thread against one neighbour
+template <int KC>
+__device__ __forceinline__ void fma4(float (&acc)[KC][4], int k, const float4& w, float a, float b, float c, float d) {
+    acc[k][0] = fmaf(w.x, a, acc[k][0]);
+    acc[k][1] = fmaf(w.y, b, acc[k][1]);
+    acc[k][2] = fmaf(w.z, c, acc[k][2]);
+    acc[k][3] = fmaf(w.w, d, acc[k][3]);
+}
+
+// One dilation DD: 8 neighbours x KC channels for 4 consecutive pixels.  sc -> centre pixel 0 of channel 0 in the tile.
+template <typename AffT, int KC, int SH, int DD>
+__device__ __forceinline__ void accumulate_dilation(float (&acc)[KC][4], const float* sc,
+                                                    const typename AffIO<AffT>::Raw (&wr)[8]) {
+    float4 w[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) w[j] = AffIO<AffT>::unpack(wr[j]);
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+#pragma unroll
+        for (int r = -1; r <= 1; ++r) {
+            const float* rowp = sc + k * (SH * PT_SW) + r * DD * PT_SW;
+            const int jl = (r == -1) ? 0 : (r == 0) ? 3 : 5;      // neighbour index of (r, -1)
+            const int jr = (r == -1) ? 2 : (r == 0) ? 4 : 7;      // neighbour index of (r, +1)
+            if (DD % 4 == 0) {
+                const float4 L = *reinterpret_cast<const float4*>(rowp - DD);
+                const float4 R = *reinterpret_cast<const float4*>(rowp + DD);
+                fma4<KC>(acc, k, w[jl], L.x, L.y, L.z, L.w);
+                fma4<KC>(acc, k, w[jr], R.x, R.y, R.z, R.w);
+                if (r != 0) {
+                    const float4 C = *reinterpret_cast<const float4*>(rowp);
+                    fma4<KC>(acc, k, w[jl + 1], C.x, C.y, C.z, C.w);
+                }
+            } else {
+                const float4 L = *reinterpret_cast<const float4*>(rowp - 4);
+                const float4 C = *reinterpret_cast<const float4*>(rowp);
+                const float4 R = *reinterpret_cast<const float4*>(rowp + 4);
+                if (DD == 1) {
+                    fma4<KC>(acc, k, w[jl], L.w, C.x, C.y, C.z);
+                    fma4<KC>(acc, k, w[jr], C.y, C.z, C.w, R.x);
+                } else {   // DD == 2
+                    fma4<KC>(acc, k, w[jl], L.z, L.w, C.x, C.y);
+                    fma4<KC>(acc, k, w[jr], C.z, C.w, R.x, R.y);
+                }
+                if (r != 0) fma4<KC>(acc, k, w[jl + 1], C.x, C.y, C.z, C.w);
+            }
+        }
+    }
+}
+
+template <typename AffT>
+__device__ __forceinline__ void load_weights(typename AffIO<AffT>::Raw (&w)[8], const AffT* ap, size_t aplane, int d,
+                                             uint64_t pol) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) w[j] = AffIO<AffT>::ld4(ap + (size_t)(d * 8 + j) * aplane, pol);
+}
+
+constexpr int PT_KC = 3;                 // channels per chunk on the tile path: 3 x 35 KB planes -> two CTAs per SM
+constexpr int PT_TH = 32;
+
+template <typename AffT, int KC, int TH>
+__device__ __forceinline__ void par_iter_tile_body(float* par_tile, const AffT* __restrict__ aff, const float* __restrict__ in,
+                                                   float* __restrict__ out, const TileArgs& a, const ParChunks& ch) {
+    constexpr int SH = TH + 2 * PT_HALO;
+    const int c = blockIdx.z;
+    const int x0 = blockIdx.x * PT_W, y0 = blockIdx.y * TH;
+    const int H = a.H, W = a.W;
+    const size_t iplane = (size_t)H * a.in_pitch, oplane = (size_t)H * a.out_pitch, aplane = (size_t)H * a.wp;
+    const int ch0 = ch.ch0[c];
+    fill_tile<SH, PT_THREADS>(par_tile, in + (size_t)ch0 * iplane, iplane, a.in_pitch, KC, x0, y0, H, W, a.in_vec);
+    __syncthreads();
+    const uint64_t pol = l2_evict_first_policy();
+    const int tx4 = threadIdx.x & 15, tyb = threadIdx.x >> 4;
+    const int x = x0 + 4 * tx4;
+    if (x >= W) return;
+    const AffT* abase = aff + (size_t)ch.b[c] * 48 * aplane + x;
+#pragma unroll 1
+    for (int pass = 0; pass < TH / 16; ++pass) {
+        const int ty = tyb + 16 * pass, y = y0 + ty;
+        if (y >= H) break;
+        const AffT* ap = abase + (size_t)y * a.wp;
+        const float* sc = par_tile + (ty + PT_HALO) * PT_SW + PT_HALO + 4 * tx4;
+        float acc[KC][4];
+#pragma unroll
+        for (int k = 0; k < KC; ++k) acc[k][0] = acc[k][1] = acc[k][2] = acc[k][3] = 0.f;
+        typename AffIO<AffT>::Raw wa[8], wb[8];
+        if (AffIO<AffT>::LOOKAHEAD == 2) {
+            typename AffIO<AffT>::Raw wc[8];
+            load_weights<AffT>(wa, ap, aplane, 0, pol);
+            load_weights<AffT>(wb, ap, aplane, 1, pol);
+            load_weights<AffT>(wc, ap, aplane, 2, pol);
+            accumulate_dilation<AffT, KC, SH, 1>(acc, sc, wa);
+            load_weights<AffT>(wa, ap, aplane, 3, pol);
+            accumulate_dilation<AffT, KC, SH, 2>(acc, sc, wb);
+            load_weights<AffT>(wb, ap, aplane, 4, pol);
+            accumulate_dilation<AffT, KC, SH, 4>(acc, sc, wc);
+            load_weights<AffT>(wc, ap, aplane, 5, pol);
+            accumulate_dilation<AffT, KC, SH, 8>(acc, sc, wa);
+            accumulate_dilation<AffT, KC, SH, 12>(acc, sc, wb);
+            accumulate_dilation<AffT, KC, SH, 24>(acc, sc, wc);
+        } else {
+            load_weights<AffT>(wa, ap, aplane, 0, pol);
+            load_weights<AffT>(wb, ap, aplane, 1, pol);
+            accumulate_dilation<AffT, KC, SH, 1>(acc, sc, wa);
+            load_weights<AffT>(wa, ap, aplane, 2, pol);
+            accumulate_dilation<AffT, KC, SH, 2>(acc, sc, wb);
+            load_weights<AffT>(wb, ap, aplane, 3, pol);
+            accumulate_dilation<AffT, KC, SH, 4>(acc, sc, wa);
+            load_weights<AffT>(wa, ap, aplane, 4, pol);
+            accumulate_dilation<AffT, KC, SH, 8>(acc, sc, wb);
+            load_weights<AffT>(wb, ap, aplane, 5, pol);
+            accumulate_dilation<AffT, KC, SH, 12>(acc, sc, wa);
+            accumulate_dilation<AffT, KC, SH, 24>(acc, sc, wb);
+        }
+        float* op = out + (size_t)ch0 * oplane + (size_t)y * a.out_pitch + x;
+#pragma unroll
+        for (int k = 0; k < KC; ++k) {
+            if (a.out_vec && x + 3 < W) {
+                *reinterpret_cast<float4*>(op + (size_t)k * oplane) = make_float4(acc[k][0], acc[k][1], acc[k][2], acc[k][3]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (x + i < W) op[(size_t)k * oplane + i] = acc[k][i];
+            }
+        }
+    }
+}
+
+// One launch per propagation step: blockIdx.z = chunk (image, first channel, 1..PT_KC channels); the channel count is
+// CTA-uniform, each count has its own fully unrolled body.
+template <typename AffT>
+__global__ void __launch_bounds__(PT_THREADS, 2) par_iter_tile_kernel(const AffT* __restrict__ aff,
+                                                                       const float* __restrict__ in,
+                                                                       float* __restrict__ out,
+                                                                       const __grid_constant__ TileArgs a,
+                                                                       const __grid_constant__ ParChunks ch) {
+    extern __shared__ __align__(16) float par_tile[];
+    switch (ch.cnt[blockIdx.z]) {
+        case 1: par_iter_tile_body<AffT, 1, PT_TH>(par_tile, aff, in, out, a, ch); break;
+        case 2: par_iter_tile_body<AffT, 2, PT_TH>(par_tile, aff, in, out, a, ch); break;
+        default: par_iter_tile_body<AffT, 3, PT_TH>(par_tile, aff, in, out, a, ch); break;
+    }
+}
+
+// Affinity build on a 64x24 tile: the 3 image planes + halo live in shared memory (96.8 KB, 2 CTAs per SM); 192 threads
+// (170 registers each: the 48 logits stay in registers), each walks 8 pixels (lanes = consecutive x: conflict-free scalar
+// LDS), 3 passes over the 48 compile-time neighbour offsets.
+constexpr int PA_TH = 24;
+constexpr int PA_THREADS = 192;
+constexpr int PA_SH = PA_TH + 2 * PT_HALO;
+
+template <typename AffT>
+__global__ void __launch_bounds__(PA_THREADS, 2) par_aff_tile_kernel(const float* __restrict__ img, AffT* __restrict__ aff,
+                                                                      int H, int W, int wp, int vec,
+                                                                      const __grid_constant__ ParPos pos) {
+    extern __shared__ __align__(16) float par_tile[];
+    constexpr int PLANE = PA_SH * PT_SW;
+    const int b = blockIdx.z;
+    const int x0 = blockIdx.x * PT_W, y0 = blockIdx.y * PA_TH;
+    const size_t hw = (size_t)H * W;
+    fill_tile<PA_SH, PA_THREADS>(par_tile, img + (size_t)b * 3 * hw, hw, W, 3, x0, y0, H, W, vec);
+    __syncthreads();
+    const size_t aplane = (size_t)H * wp;
+    const int tx = threadIdx.x & 63, ty0 = threadIdx.x >> 6;
+    const int x = x0 + tx;
+    if (x >= W) return;
+    constexpr int by[8] = {-1, -1, -1, 0, 0, 1, 1, 1};
+    constexpr int bx[8] = {-1, 0, 1, -1, 1, -1, 0, 1};
+#pragma unroll 1
+    for (int i = 0; i < PA_TH / 3; ++i) {
+        const int ty = ty0 + 3 * i, y = y0 + ty;
+        if (y >= H) break;
+        const float* sc = par_tile + (ty + PT_HALO) * PT_SW + PT_HALO + tx;
+        const float c0 = sc[0], c1 = sc[PLANE], c2 = sc[2 * PLANE];
+        // pass 1: per-channel mean of the 48 neighbour values
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int n = 0; n < 48; ++n) {
+            const int o = by[n & 7] * std_dil(n >> 3) * PT_SW + bx[n & 7] * std_dil(n >> 3);
+            s0 += sc[o]; s1 += sc[PLANE + o]; s2 += sc[2 * PLANE + o];
+        }
+        const float m0 = s0 * (1.f / 48.f), m1 = s1 * (1.f / 48.f), m2 = s2 * (1.f / 48.f);
+        // pass 2: centred sum of squares -> unbiased std (torch.std, PAR.py:77)
+        float q0 = 0.f, q1 = 0.f, q2 = 0.f;
+#pragma unroll
+        for (int n = 0; n < 48; ++n) {
+            const int o = by[n & 7] * std_dil(n >> 3) * PT_SW + bx[n & 7] * std_dil(n >> 3);
+            const float d0 = sc[o] - m0, d1 = sc[PLANE + o] - m1, d2 = sc[2 * PLANE + o] - m2;
+            q0 = fmaf(d0, d0, q0); q1 = fmaf(d1, d1, q1); q2 = fmaf(d2, d2, q2);
+        }
+        const float e0 = sqrtf(q0 * (1.f / 47.f)) + 1e-8f, e1 = sqrtf(q1 * (1.f / 47.f)) + 1e-8f,
+                    e2 = sqrtf(q2 * (1.f / 47.f)) + 1e-8f;
+        // pass 3: logits = -mean_c((|v-c|/(std+1e-8)/w1)^2) (PAR.py:80-81), kept in registers; the two divisions per
+        // term are one multiplication by r = 1/(std+1e-8)/w1 (1-2 ulp from the reference's order)
+        const float r0 = 1.f / e0 / 0.3f, r1 = 1.f / e1 / 0.3f, r2 = 1.f / e2 / 0.3f;
+        float l[48];
+        float mx = -INFINITY;
+#pragma unroll
+        for (int n = 0; n < 48; ++n) {
+            const int o = by[n & 7] * std_dil(n >> 3) * PT_SW + bx[n & 7] * std_dil(n >> 3);
+            const float t0 = (sc[o] - c0) * r0, t1 = (sc[PLANE + o] - c1) * r1, t2 = (sc[2 * PLANE + o] - c2) * r2;
+            l[n] = (t0 * t0 + t1 * t1 + t2 * t2) * (-1.f / 3.f);
+            mx = fmaxf(mx, l[n]);
+        }
+        float sum = 0.f;
+#pragma unroll
+        for (int n = 0; n < 48; ++n) { l[n] = expf(l[n] - mx); sum += l[n]; }
+        const float inv = 1.f / sum;
+        AffT* ap = aff + (size_t)b * 48 * aplane + (size_t)y * wp + x;
+#pragma unroll
+        for (int n = 0; n < 48; ++n) AffIO<AffT>::st(ap + (size_t)n * aplane, l[n] * inv + pos.v[n]);   // PAR.py:86
+    }
+}
+
 
 // ---------------------------------------------------------------------------------------------------
 __global__ void argmax_lut_kernel(const float* __restrict__ masks, const int64_t* __restrict__ lut,
@@ -202,48 +517,102 @@ __global__ void argmax_lut_kernel(const float* __restrict__ masks, const int64_t
     labels[(size_t)b * hw + i] = lut[ch0 + arg];
 }
 
-static int propagate(const float* aff, const float* masks, float* out, float* scratch, const int* ch_off, int B,
-                     const ParGeom& g, int num_iter, cudaStream_t st) {
+template <typename AffT>
+static int launch_iter_tile(const AffT* aff, const float* src, float* dst, const TileArgs& ta, const ParChunks& chunks,
+                            int n, int max_cnt, cudaStream_t st) {
+    constexpr int PLANE = (PT_TH + 2 * PT_HALO) * PT_SW * (int)sizeof(float);
+    static bool attr_set = false;
+    if (!attr_set) {
+        WC_CUDA(cudaFuncSetAttribute(par_iter_tile_kernel<AffT>, cudaFuncAttributeMaxDynamicSharedMemorySize, PT_KC * PLANE));
+        attr_set = true;
+    }
+    dim3 grid(ceil_div(ta.W, PT_W), ceil_div(ta.H, PT_TH), n);
+    par_iter_tile_kernel<AffT><<<grid, PT_THREADS, max_cnt * PLANE, st>>>(aff, src, dst, ta, chunks);
+    WC_LAUNCH_CHECK();
+    return WC_OK;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// num_iter propagation steps.  masks / out have row pitch W; the ping-pong planes in `scratch` have pitch g.wp.
+template <typename AffT>
+static int propagate(const AffT* aff, const float* masks, float* out, float* scratch, const int* ch_off, int B,
+                     const ParGeom& g, bool fast, int num_iter, cudaStream_t st) {
     const int sum_kc = ch_off[B];
-    const size_t hw = (size_t)g.H * g.W;
+    const size_t hw = (size_t)g.H * g.W, hwp = (size_t)g.H * g.wp;
     if (num_iter == 0) {
         if (out != masks)
             WC_CUDA(cudaMemcpyAsync(out, masks, sizeof(float) * sum_kc * hw, cudaMemcpyDeviceToDevice, st));
         return WC_OK;
     }
-    // chunk table
-    ParChunks chunks;
-    int nchunks_total = 0;
-    for (int b = 0; b < B; ++b) nchunks_total += ceil_div(ch_off[b + 1] - ch_off[b], PAR_KC);
-    float* ping = scratch;
-    float* pong = scratch + (size_t)sum_kc * hw;
-    dim3 block(PAR_TX, PAR_TY);
-    for (int it = 0; it < num_iter; ++it) {
-        const float* src = (it == 0) ? masks : ((it & 1) ? ping : pong);
-        float* dst = (it == num_iter - 1) ? out : ((it & 1) ? pong : ping);
-        int b = 0, k = ch_off[0];
-        int done = 0;
-        while (done < nchunks_total) {
-            int n = 0;
-            while (n < PAR_MAX_CHUNKS && b < B) {
-                if (k >= ch_off[b + 1]) { ++b; if (b < B) k = ch_off[b]; continue; }
-                chunks.b[n] = (short)b; chunks.ch0[n] = (short)k;
-                chunks.cnt[n] = (short)min(PAR_KC, ch_off[b + 1] - k);
-                k += chunks.cnt[n]; ++n;
-            }
-            if (n == 0) break;
-            dim3 grid(ceil_div(g.W, PAR_TX), ceil_div(g.H, PAR_TY), n);
-            {
-                int chs = 0;
-                for (int i = 0; i < n; ++i) chs += chunks.cnt[i];
-                ProfScope prof(PK_PAR_ITER, (double)hw * (4.0 * g.nn * n + 8.0 * chs), st);
-                if (g.nn == 48) par_iter_kernel<48><<<grid, block, 0, st>>>(aff, src, dst, g, chunks);
-                else par_iter_kernel<0><<<grid, block, 0, st>>>(aff, src, dst, g, chunks);
-            }
-            WC_LAUNCH_CHECK();
-            done += n;
+    // chunk list: the channels of one image in groups of <= kc_max (tile path 3, generic path 4); an image with more
+    // channels streams its affinity once per group
+    struct Item { short b, ch0, cnt; };
+    std::vector<Item> items;
+    const int kc_max = fast ? PT_KC : PAR_KC;
+    for (int b = 0; b < B; ++b) {
+        const int kc = ch_off[b + 1] - ch_off[b], groups = ceil_div(kc, kc_max);
+        int k = ch_off[b];
+        for (int gi = 0; gi < groups; ++gi) {          // balanced groups: 4 -> 2+2, 5 -> 3+2, 7 -> 3+2+2
+            const int cnt = kc / groups + (gi < kc % groups ? 1 : 0);
+            items.push_back(Item{(short)b, (short)k, (short)cnt});
+            k += cnt;
         }
     }
+    float* ping = scratch;
+    float* pong = scratch + (size_t)sum_kc * hwp;
+    for (int it = 0; it < num_iter; ++it) {
+        const bool first = it == 0, last = it == num_iter - 1;
+        const float* src = first ? masks : ((it & 1) ? ping : pong);
+        float* dst = last ? out : ((it & 1) ? pong : ping);
+        TileArgs ta;
+        ta.H = g.H; ta.W = g.W; ta.wp = g.wp;
+        ta.in_pitch = first ? g.W : g.wp;
+        ta.out_pitch = last ? g.W : g.wp;
+        ta.in_vec = (ta.in_pitch % 4 == 0) && aligned16(src);
+        ta.out_vec = (ta.out_pitch % 4 == 0) && aligned16(dst);
+        const std::vector<Item>& v = items;
+        for (size_t off = 0; off < v.size(); off += PAR_MAX_CHUNKS) {
+            const int n = (int)min((size_t)PAR_MAX_CHUNKS, v.size() - off);
+            ParChunks chunks;
+            int chs = 0, max_cnt = 1;
+            for (int i = 0; i < n; ++i) {
+                chunks.b[i] = v[off + i].b; chunks.ch0[i] = v[off + i].ch0; chunks.cnt[i] = v[off + i].cnt;
+                chs += v[off + i].cnt;
+                max_cnt = max(max_cnt, (int)v[off + i].cnt);
+            }
+            ProfScope prof(PK_PAR_ITER, (double)hw * ((double)sizeof(AffT) * g.nn * n + 8.0 * chs), st);
+            if (fast) {
+                int rc = launch_iter_tile<AffT>(aff, src, dst, ta, chunks, n, max_cnt, st);
+                if (rc) return rc;
+            } else {
+                dim3 block(PAR_TX, PAR_TY), grid(ceil_div(g.W, PAR_TX), ceil_div(g.H, PAR_TY), n);
+                par_iter_kernel<AffT><<<grid, block, 0, st>>>(aff, src, ta.in_pitch, dst, ta.out_pitch, g, chunks);
+                WC_LAUNCH_CHECK();
+            }
+        }
+    }
+    return WC_OK;
+}
+
+template <typename AffT>
+static int affinity(const float* img, AffT* aff, int B, const ParGeom& g, const ParPos& pos, bool fast, cudaStream_t st) {
+    ProfScope prof(PK_PAR_AFF, (double)B * g.H * g.W * (12.0 + (double)sizeof(AffT) * g.nn), st);
+    if (fast) {
+        constexpr int SMEM = 3 * PA_SH * PT_SW * (int)sizeof(float);
+        static bool attr_set = false;
+        if (!attr_set) {
+            WC_CUDA(cudaFuncSetAttribute(par_aff_tile_kernel<AffT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+            attr_set = true;
+        }
+        dim3 grid(ceil_div(g.W, PT_W), ceil_div(g.H, PA_TH), B);
+        const int vec = (g.W % 4 == 0) && aligned16(img);
+        par_aff_tile_kernel<AffT><<<grid, PA_THREADS, SMEM, st>>>(img, aff, g.H, g.W, g.wp, vec, pos);
+    } else {
+        dim3 block(32, 8), grid(ceil_div(g.W, 32), ceil_div(g.H, 8), B);
+        par_aff_kernel<AffT><<<grid, block, 0, st>>>(img, aff, g, pos);
+    }
+    WC_LAUNCH_CHECK();
     return WC_OK;
 }
 
@@ -258,47 +627,51 @@ static int check_ragged(const int* ch_off, int B) {
 
 using namespace wc;
 
+extern "C" int wc_par_aff_pitch(int W) { return par_pitch(W); }
+
 extern "C" size_t wc_par_workspace_bytes(int B, int sum_kc, int H, int W, int n_dil) {
-    const size_t hw = (size_t)H * W;
-    return sizeof(float) * hw * ((size_t)B * 3 + (size_t)B * 8 * n_dil + 2 * (size_t)sum_kc) + 256;
+    const size_t hw = (size_t)H * W, hwp = (size_t)H * par_pitch(W);
+    return sizeof(float) * (hw * (size_t)B * 3 + hwp * ((size_t)B * 8 * n_dil + 2 * (size_t)sum_kc)) + 1024;
 }
 
-extern "C" int wc_par_affinity(const float* img, float* aff, int B, int H, int W, const int* dil, int n_dil,
+extern "C" int wc_par_affinity(const float* img, void* aff, int aff_f16, int B, int H, int W, const int* dil, int n_dil,
                                void* stream) {
-    WC_CHECK_ARG(img && aff && B > 0 && H > 0 && W > 0 && dil);
+    WC_CHECK_ARG(img && aff && B > 0 && B <= 65535 && H > 0 && W > 0 && dil);
     ParGeom g; ParPos pos;
     WC_CHECK_ARG(make_geom(g, &pos, H, W, dil, n_dil) == 0);
-    dim3 block(32, 8), grid(ceil_div(W, 32), ceil_div(H, 8), B);
-    ProfScope prof(PK_PAR_AFF, (double)B * H * W * (12.0 + 4.0 * g.nn), as_stream(stream));
-    if (g.nn == 48) par_aff_kernel<48><<<grid, block, 0, as_stream(stream)>>>(img, aff, g, pos);
-    else par_aff_kernel<0><<<grid, block, 0, as_stream(stream)>>>(img, aff, g, pos);
-    WC_LAUNCH_CHECK();
-    return WC_OK;
+    const bool fast = is_standard_dilations(dil, n_dil) && aligned16(aff);
+    if (aff_f16) return affinity<__half>(img, reinterpret_cast<__half*>(aff), B, g, pos, fast, as_stream(stream));
+    return affinity<float>(img, reinterpret_cast<float*>(aff), B, g, pos, fast, as_stream(stream));
 }
 
-extern "C" int wc_par_propagate(const float* aff, const float* masks, float* out, float* scratch,
+extern "C" int wc_par_propagate(const void* aff, int aff_f16, const float* masks, float* out, float* scratch,
                                 const int* ch_off, int B, int H, int W, const int* dil, int n_dil, int num_iter,
                                 void* stream) {
     WC_CHECK_ARG(aff && masks && out && scratch && H > 0 && W > 0 && num_iter >= 0);
     WC_CHECK_ARG(check_ragged(ch_off, B) == 0);
     ParGeom g;
     WC_CHECK_ARG(make_geom(g, nullptr, H, W, dil, n_dil) == 0);
-    return propagate(aff, masks, out, scratch, ch_off, B, g, num_iter, as_stream(stream));
+    const bool fast = is_standard_dilations(dil, n_dil) && aligned16(aff) && aligned16(scratch);
+    if (aff_f16)
+        return propagate<__half>(reinterpret_cast<const __half*>(aff), masks, out, scratch, ch_off, B, g, fast, num_iter,
+                                 as_stream(stream));
+    return propagate<float>(reinterpret_cast<const float*>(aff), masks, out, scratch, ch_off, B, g, fast, num_iter,
+                            as_stream(stream));
 }
 
 extern "C" int wc_par_fwd(const float* imgs, int Hi, int Wi, const float* masks, float* out, const int* ch_off,
-                          int B, int H, int W, const int* dil, int n_dil, int num_iter, void* workspace,
+                          int B, int H, int W, const int* dil, int n_dil, int num_iter, int aff_f16, void* workspace,
                           size_t workspace_bytes, void* stream) {
     WC_CHECK_ARG(imgs && masks && out && workspace && Hi > 0 && Wi > 0 && H > 0 && W > 0 && num_iter >= 0);
     WC_CHECK_ARG(check_ragged(ch_off, B) == 0);
     if (workspace_bytes < wc_par_workspace_bytes(B, ch_off[B], H, W, n_dil))
         return fail(WC_ERR_WORKSPACE, "%s: workspace too small (%ld bytes)", __func__, (long)workspace_bytes);
     cudaStream_t st = as_stream(stream);
-    const size_t hw = (size_t)H * W;
+    const size_t hw = (size_t)H * W, hwp = (size_t)H * par_pitch(W);
     float* ws = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~(uintptr_t)255);
     float* img_r = ws;
-    float* aff = img_r + (size_t)B * 3 * hw;
-    float* scratch = aff + (size_t)B * 8 * n_dil * hw;
+    float* scratch = img_r + (((size_t)B * 3 * hw + 63) & ~(size_t)63);
+    void* aff = scratch + 2 * (size_t)ch_off[B] * hwp;
     const float* img = imgs;
     if (Hi != H || Wi != W) {
         dim3 block(32, 8), grid(ceil_div(W, 32), ceil_div(H, 8), B * 3);
@@ -308,11 +681,9 @@ extern "C" int wc_par_fwd(const float* imgs, int Hi, int Wi, const float* masks,
         WC_LAUNCH_CHECK();
         img = img_r;
     }
-    int rc = wc_par_affinity(img, aff, B, H, W, dil, n_dil, stream);
+    int rc = wc_par_affinity(img, aff, aff_f16, B, H, W, dil, n_dil, stream);
     if (rc) return rc;
-    ParGeom g;
-    WC_CHECK_ARG(make_geom(g, nullptr, H, W, dil, n_dil) == 0);
-    return propagate(aff, masks, out, scratch, ch_off, B, g, num_iter, st);
+    return wc_par_propagate(aff, aff_f16, masks, out, scratch, ch_off, B, H, W, dil, n_dil, num_iter, stream);
 }
 
 extern "C" int wc_argmax_lut(const float* masks, const int64_t* lut, int64_t* labels, const int* ch_off, int B,

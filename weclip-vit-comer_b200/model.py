@@ -75,7 +75,7 @@ class WeCLIP(nn.Module):
         self.require_all_fts = True
         self.fg_text_features = fg_text_features
         self.bg_text_features = bg_text_features
-        self.par = PAR(num_iter=20, dilations=[1, 2, 4, 8, 12, 24])
+        self.par = PAR(num_iter=20, dilations=[1, 2, 4, 8, 12, 24], affinity_dtype=torch.float16)
         self.label_reader = LabelReader()
         self.keep_intermediates = False      # debugging / test hook: keep raw CAMs, box masks, refined CAMs in self.last
         self.last: dict = {}

@@ -112,3 +112,21 @@ def confusion_hist(pred: torch.Tensor, gt: torch.Tensor, hist: torch.Tensor) -> 
                                       _lib.ptr(hist), _lib.stream_ptr())
     _lib.check(rc, "wc_confusion_hist")
     return hist
+
+
+def attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, want_avg: bool = True):
+    """Fused attention (head_dim 64).  q, k, v fp16 [N, heads, L, 64] (q already scaled by 1/8).
+    Returns (o fp16 [N, L, heads*64], attn_avg fp32 [N, L, L] | None)."""
+    _lib.require_device()
+    N, heads, L, hd = q.shape
+    assert hd == 64 and q.dtype == torch.float16
+    Lp = (L + 7) // 8 * 8
+    vt = torch.full((N, heads, hd, Lp), float("nan"), dtype=torch.float16, device=q.device)   # pad columns must not matter
+    vt[..., :L] = v.transpose(-1, -2)
+    o = torch.empty(N, L, heads * hd, dtype=torch.float16, device=q.device)
+    lse = torch.empty(N, heads, L, dtype=torch.float32, device=q.device)
+    avg = torch.empty(N, L, L, dtype=torch.float32, device=q.device) if want_avg else None
+    rc = _lib.lib().wc_attention_fwd(_lib.ptr(q.contiguous()), _lib.ptr(k.contiguous()), _lib.ptr(vt), _lib.ptr(o),
+                                     _lib.ptr(lse), _lib.ptr(avg), N, heads, L, Lp, _lib.stream_ptr())
+    _lib.check(rc, "wc_attention_fwd")
+    return o, avg

@@ -20,8 +20,12 @@ def get_kernel() -> torch.Tensor:
 
 
 class PAR(nn.Module):
-    def __init__(self, dilations, num_iter):
+    def __init__(self, dilations, num_iter, affinity_dtype=torch.float32):
+        """``affinity_dtype``: storage type of the materialised affinity (fp32 = exact, within 2e-5 of PAR.py;
+        fp16 = the WeCLIP pipeline's setting, half the bytes per propagation step)."""
         super().__init__()
+        assert affinity_dtype in (torch.float32, torch.float16)
+        self.affinity_dtype = affinity_dtype
         self.dilations = list(dilations)
         self.num_iter = int(num_iter)
         self.register_buffer("kernel", get_kernel())
@@ -49,7 +53,7 @@ class PAR(nn.Module):
         ws = self._workspace(nbytes, imgs.device)
         rc = L.wc_par_fwd(_lib.ptr(imgs), Hi, Wi, _lib.ptr(masks), _lib.ptr(out), _lib.int_array(ch_off), B, H, W,
                           _lib.int_array(self.dilations), len(self.dilations), self.num_iter,
-                          _lib.ptr(ws), _lib.c_size_t(ws.numel()), _lib.stream_ptr())
+                          int(self.affinity_dtype == torch.float16), _lib.ptr(ws), _lib.c_size_t(ws.numel()), _lib.stream_ptr())
         _lib.check(rc, "wc_par_fwd")
         return out
 
