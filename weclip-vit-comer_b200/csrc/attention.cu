@@ -20,7 +20,8 @@ namespace wc {
 
 constexpr int AT_BM = 128, AT_BN = 128, AT_HD = 64;
 constexpr int AT_STAGES = 4;
-constexpr int AT_THREADS = 192;
+constexpr int AT_SM_WARPS = 8;          // softmax warps: two per TMEM lane quarter, each owning 64 of a tile's 128 key columns
+constexpr int AT_THREADS = 64 + 32 * AT_SM_WARPS;
 constexpr int AT_TILE_BYTES = 128 * 64 * 2;          // one [128][64] fp16 operand tile (Q, K, V^T pair, half of P)
 constexpr float AT_LOG2E = 1.4426950408889634f;
 
@@ -43,7 +44,8 @@ struct FwdSmem {
     static constexpr int RING = AT_TILE_BYTES;                               // stage s: K at +s*32K, V^T at +s*32K+16K
     static constexpr int P = RING + AT_STAGES * 2 * AT_TILE_BYTES;           // two P buffers of 32 KB
     static constexpr int BARS = P + 2 * 2 * AT_TILE_BYTES;
-    static constexpr int TOTAL = BARS + 256 + 1024;                          // + alignment slack
+    static constexpr int STATS = BARS + 256;                                 // float2 [2 halves][128 rows]: pass-1 (max, sum)
+    static constexpr int TOTAL = STATS + 2 * 128 * 8 + 1024;                 // + alignment slack
 };
 
 __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap mapQ,
@@ -73,8 +75,8 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
         mbar_init(q_full, 1);
         for (int s = 0; s < AT_STAGES; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
         for (int b = 0; b < 2; ++b) {
-            mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], 4);
-            mbar_init(&p_full[b], 4); mbar_init(&p_empty[b], 1);
+            mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], AT_SM_WARPS);
+            mbar_init(&p_full[b], AT_SM_WARPS); mbar_init(&p_empty[b], 1);
         }
         mbar_init(o_full, 1);
         mbar_fence_init();
@@ -148,103 +150,129 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             umma_commit(o_full);
         }
     } else {
-        const int q = warp & 3;                              // TMEM lane quarter
+        const int q = warp & 3;                              // TMEM lane quarter (hardware: warp id % 4)
+        const int half = (warp - 2) >> 2;                    // which 64 key columns of every tile this warp owns
         const int row = q * 32 + lane, grow = qt * AT_BM + row;
-        const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
+        const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16) + half * 64;
+        float2* stats = reinterpret_cast<float2*>(smem + FwdSmem::STATS);
         uint32_t sc = 0;
-        uint32_t r[32];
-        // ---- pass 1: row max and sum of exp2 in the log2 domain
+        uint32_t r0[32], r1[32];
+        // ---- pass 1: row max and sum of exp2 over this warp's columns, log2 domain
         float m = -INFINITY, l = 0.f;
         for (int j = 0; j < n_kt; ++j, ++sc) {
             const int b = sc & 1;
-            const int nvalid = a.L - j * AT_BN;              // keys of this tile that exist
+            const int nv = a.L - j * AT_BN - half * 64;      // this warp's columns of the tile that exist (may be <= 0)
             mbar_wait(&s_full[b], (sc >> 1) & 1);
             tc_fence_after();
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                if (c * 32 >= nvalid) break;
-                tmem_ld32_issue(tlane + b * AT_BN + c * 32, r);
+            if (nv > 0) {
+                tmem_ld32_issue(tlane + b * AT_BN, r0);
+                tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
                 tmem_ld_wait();
-                float cm = -INFINITY;
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the MMA warp may overwrite it
+            if (nv > 0) {
+                if (nv < 64) {
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    float v = __uint_as_float(r[i]) * AT_LOG2E;
-                    if (c * 32 + i >= nvalid) v = -INFINITY;
-                    r[i] = __float_as_uint(v);
-                    cm = fmaxf(cm, v);
+                    for (int i = 0; i < 32; ++i) {
+                        if (i >= nv) r0[i] = 0xff800000u;            // -inf
+                        if (32 + i >= nv) r1[i] = 0xff800000u;
+                    }
                 }
-                const float mn = fmaxf(m, cm);
-                float acc = 0.f;
+                float c0 = -INFINITY, c1 = -INFINITY, c2 = -INFINITY, c3 = -INFINITY;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) acc += ex2_approx(__uint_as_float(r[i]) - mn);
-                l = l * ex2_approx(m - mn) + acc;
+                for (int i = 0; i < 32; i += 2) {
+                    c0 = fmaxf(c0, __uint_as_float(r0[i])); c1 = fmaxf(c1, __uint_as_float(r0[i + 1]));
+                    c2 = fmaxf(c2, __uint_as_float(r1[i])); c3 = fmaxf(c3, __uint_as_float(r1[i + 1]));
+                }
+                const float mn = fmaxf(m, fmaxf(fmaxf(c0, c1), fmaxf(c2, c3)) * AT_LOG2E);
+                float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) {
+                    a0 += ex2_approx(fmaf(__uint_as_float(r0[i]), AT_LOG2E, -mn));
+                    a1 += ex2_approx(fmaf(__uint_as_float(r0[i + 1]), AT_LOG2E, -mn));
+                    a2 += ex2_approx(fmaf(__uint_as_float(r1[i]), AT_LOG2E, -mn));
+                    a3 += ex2_approx(fmaf(__uint_as_float(r1[i + 1]), AT_LOG2E, -mn));
+                }
+                l = l * ex2_approx(m - mn) + ((a0 + a1) + (a2 + a3));
                 m = mn;
+            }
+        }
+        // combine the two column halves of each row (named barrier over the 256 softmax threads)
+        stats[half * 128 + row] = make_float2(m, l);
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        {
+            const float2 o = stats[(half ^ 1) * 128 + row];
+            const float mn = fmaxf(m, o.x);
+            l = l * ex2_approx(m - mn) + (o.y > 0.f ? o.y * ex2_approx(o.x - mn) : 0.f);
+            m = mn;
+        }
+        const float lse2 = m + __log2f(l);
+        if (half == 0 && a.lse2 && grow < a.L) a.lse2[(size_t)bh * a.L + grow] = lse2;
+        // ---- pass 2: exact probabilities -> fp16 P tile in shared memory (K-major, 128B swizzle); this warp's 64 columns
+        //      are exactly one [128][64] swizzled block
+        uint32_t pc = 0;
+        for (int j = 0; j < n_kt; ++j, ++sc, ++pc) {
+            const int b = sc & 1, pb = pc & 1;
+            const int nv = a.L - j * AT_BN - half * 64;
+            mbar_wait(&s_full[b], (sc >> 1) & 1);
+            tc_fence_after();
+            uint8_t* blk = smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES + half * AT_TILE_BYTES + row * 128;
+            uint32_t pk[32];
+            if (nv > 0) {
+                tmem_ld32_issue(tlane + b * AT_BN, r0);
+                tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
+                tmem_ld_wait();
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&s_empty[b]);
-        }
-        const float lse2 = m + __log2f(l);
-        if (a.lse2 && grow < a.L) a.lse2[(size_t)bh * a.L + grow] = lse2;
-        // ---- pass 2: exact probabilities -> fp16 P tile in shared memory (K-major, 128B swizzle)
-        uint32_t pc = 0;
-        for (int j = 0; j < n_kt; ++j, ++sc, ++pc) {
-            const int b = sc & 1, pb = pc & 1;
-            const int nvalid = a.L - j * AT_BN;
-            mbar_wait(&s_full[b], (sc >> 1) & 1);
             mbar_wait(&p_empty[pb], ((pc >> 1) & 1) ^ 1);
-            tc_fence_after();
-            uint8_t* sp = smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES + row * 128;
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                uint32_t pk[16];
-                if (c * 32 < nvalid) {
-                    tmem_ld32_issue(tlane + b * AT_BN + c * 32, r);
-                    tmem_ld_wait();
+            if (nv > 0) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * i]), AT_LOG2E, -lse2));
-                        float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * i + 1]), AT_LOG2E, -lse2));
-                        if (c * 32 + 2 * i >= nvalid) p0 = 0.f;
-                        if (c * 32 + 2 * i + 1 >= nvalid) p1 = 0.f;
-                        const h16x2 h = __floats2half2_rn(p0, p1);
-                        pk[i] = *reinterpret_cast<const uint32_t*>(&h);
+                for (int i = 0; i < 16; ++i) {
+                    float p0 = ex2_approx(fmaf(__uint_as_float(r0[2 * i]), AT_LOG2E, -lse2));
+                    float p1 = ex2_approx(fmaf(__uint_as_float(r0[2 * i + 1]), AT_LOG2E, -lse2));
+                    float p2 = ex2_approx(fmaf(__uint_as_float(r1[2 * i]), AT_LOG2E, -lse2));
+                    float p3 = ex2_approx(fmaf(__uint_as_float(r1[2 * i + 1]), AT_LOG2E, -lse2));
+                    if (nv < 64) {
+                        if (2 * i >= nv) p0 = 0.f;
+                        if (2 * i + 1 >= nv) p1 = 0.f;
+                        if (32 + 2 * i >= nv) p2 = 0.f;
+                        if (33 + 2 * i >= nv) p3 = 0.f;
                     }
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) pk[i] = 0u;
+                    const h16x2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
+                    pk[i] = *reinterpret_cast<const uint32_t*>(&ha);
+                    pk[16 + i] = *reinterpret_cast<const uint32_t*>(&hb);
                 }
-                uint8_t* blk = sp + (c >> 1) * AT_TILE_BYTES;
+            } else {
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const int cc = (c & 1) * 4 + t;
-                    *reinterpret_cast<uint4*>(blk + ((cc ^ (row & 7)) << 4)) = make_uint4(pk[4 * t], pk[4 * t + 1], pk[4 * t + 2], pk[4 * t + 3]);
-                }
+                for (int i = 0; i < 32; ++i) pk[i] = 0u;
             }
+#pragma unroll
+            for (int cc = 0; cc < 8; ++cc)
+                *reinterpret_cast<uint4*>(blk + ((cc ^ (row & 7)) << 4)) = make_uint4(pk[4 * cc], pk[4 * cc + 1], pk[4 * cc + 2], pk[4 * cc + 3]);
             fence_async_smem();
-            tc_fence_before();
             __syncwarp();
-            if (lane == 0) { mbar_arrive(&s_empty[b]); mbar_arrive(&p_full[pb]); }
+            if (lane == 0) mbar_arrive(&p_full[pb]);
         }
-        // ---- epilogue: O (already normalised) -> fp16, head-interleaved [N*L, heads*64]
+        // ---- epilogue: O (already normalised) -> fp16, head-interleaved [N*L, heads*64]; this warp's 32 of the 64 dims
         mbar_wait(o_full, 0);
         tc_fence_after();
-        h16* orow = a.o + ((size_t)img * a.L + grow) * (size_t)(a.heads * AT_HD) + head * AT_HD;
-#pragma unroll 1
-        for (int c = 0; c < 2; ++c) {
-            tmem_ld32_issue(tlane + 256 + c * 32, r);
-            tmem_ld_wait();
-            if (grow < a.L) {
+        h16* orow = a.o + ((size_t)img * a.L + grow) * (size_t)(a.heads * AT_HD) + head * AT_HD + half * 32;
+        tmem_ld32_issue(tmem_base + ((uint32_t)(q * 32) << 16) + 256 + half * 32, r0);
+        tmem_ld_wait();
+        if (grow < a.L) {
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    uint32_t w[4];
+            for (int t = 0; t < 4; ++t) {
+                uint32_t w[4];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const h16x2 h = __floats2half2_rn(__uint_as_float(r[8 * t + 2 * i]), __uint_as_float(r[8 * t + 2 * i + 1]));
-                        w[i] = *reinterpret_cast<const uint32_t*>(&h);
-                    }
-                    *reinterpret_cast<uint4*>(orow + c * 32 + t * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+                for (int i = 0; i < 4; ++i) {
+                    const h16x2 h = __floats2half2_rn(__uint_as_float(r0[8 * t + 2 * i]), __uint_as_float(r0[8 * t + 2 * i + 1]));
+                    w[i] = *reinterpret_cast<const uint32_t*>(&h);
                 }
+                *reinterpret_cast<uint4*>(orow + t * 8) = make_uint4(w[0], w[1], w[2], w[3]);
             }
         }
         tc_fence_before();
@@ -260,8 +288,8 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
 // ---------------------------------------------------------------------------------------------------
 struct MeanSmem {
     static constexpr int RING = 0;                                           // stage s: Q_h at +s*32K, K_h at +s*32K+16K
-    static constexpr int STG = AT_STAGES * 2 * AT_TILE_BYTES;                // 4 warps x 4 KB transposition blocks
-    static constexpr int BARS = STG + 4 * 32 * 32 * 4;
+    static constexpr int STG = AT_STAGES * 2 * AT_TILE_BYTES;                // 8 warps x 4 KB transposition blocks
+    static constexpr int BARS = STG + AT_SM_WARPS * 32 * 32 * 4;
     static constexpr int TOTAL = BARS + 256 + 1024;
 };
 struct MeanArgs {
@@ -288,7 +316,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __gr
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&mapQ); prefetch_tmap(&mapK);
         for (int s = 0; s < AT_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], 4); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], AT_SM_WARPS); }
         mbar_fence_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, 256);
@@ -325,36 +353,40 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __gr
             }
         }
     } else {
-        const int q = warp & 3;
+        const int q = warp & 3;                              // TMEM lane quarter
+        const int half = (warp - 2) >> 2;                    // which 64 key columns this warp accumulates
         const int row = q * 32 + lane, grow = qt * AT_BM + row;
-        const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
+        const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16) + half * 64;
         float* stg = reinterpret_cast<float*>(smem + MeanSmem::STG) + (warp - 2) * 32 * 32;
-        float acc[AT_BN];
+        float acc[64];
 #pragma unroll
-        for (int i = 0; i < AT_BN; ++i) acc[i] = 0.f;
-        uint32_t r[32];
+        for (int i = 0; i < 64; ++i) acc[i] = 0.f;
+        uint32_t r0[32], r1[32];
+        float lse = (grow < a.L) ? __ldg(a.lse2 + (size_t)(img * a.heads) * a.L + grow) : 0.f;
         for (int h = 0; h < a.heads; ++h) {
             const int b = h & 1;
-            const float lse = (grow < a.L) ? __ldg(a.lse2 + (size_t)(img * a.heads + h) * a.L + grow) : 0.f;
+            const float lse_next = (grow < a.L && h + 1 < a.heads) ? __ldg(a.lse2 + (size_t)(img * a.heads + h + 1) * a.L + grow) : 0.f;
             mbar_wait(&s_full[b], (h >> 1) & 1);
             tc_fence_after();
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                tmem_ld32_issue(tlane + b * AT_BN + c * 32, r);
-                tmem_ld_wait();
-#pragma unroll
-                for (int i = 0; i < 32; ++i) acc[c * 32 + i] += ex2_approx(fmaf(__uint_as_float(r[i]), AT_LOG2E, -lse));
-            }
+            tmem_ld32_issue(tlane + b * AT_BN, r0);
+            tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
+            tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&s_empty[b]);
+            if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the next head's MMA may overwrite it
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                acc[i] += ex2_approx(fmaf(__uint_as_float(r0[i]), AT_LOG2E, -lse));
+                acc[32 + i] += ex2_approx(fmaf(__uint_as_float(r1[i]), AT_LOG2E, -lse));
+            }
+            lse = lse_next;
         }
         // mean over heads, transposed through the warp's swizzled 32x32 block so that each store is one row x 32 keys
         const float inv_h = 1.f / (float)a.heads;
         const int row0 = qt * AT_BM + q * 32;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const int key = kt * AT_BN + c * 32 + lane;
+        for (int c = 0; c < 2; ++c) {
+            const int key = kt * AT_BN + half * 64 + c * 32 + lane;
 #pragma unroll
             for (int j = 0; j < 8; ++j)
                 *reinterpret_cast<float4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) =
