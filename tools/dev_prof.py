@@ -27,6 +27,14 @@ def main():
         if kind[i] == 0:
             key = tuple(tags[4 * i:4 * i + 4])
             g = groups[key]; g[0] += 1; g[1] += ms[i]; g[2] += work[i]
+    other = collections.defaultdict(lambda: [0, 0.0])
+    names = {10: "attention", 2: "softmax/headmean", 4: "par_iter", 3: "par_aff"}
+    for i in range(n):
+        if kind[i] in names:
+            key = (names[kind[i]],) + tuple(tags[4 * i:4 * i + 4])
+            other[key][0] += 1; other[key][1] += ms[i]
+    for key, (c, m) in sorted(other.items(), key=lambda kv: -kv[1][1]):
+        print(f"  {str(key):48s} x{c:4d} {m:9.3f} ms  {1e3 * m / c:9.1f} us each")
     print("GEMM shapes (M,N,K,batch): count, total ms, TFLOP/s")
     for key, (c, m, w) in sorted(groups.items(), key=lambda kv: -kv[1][1]):
         print(f"  {str(key):32s} x{c:4d} {m:9.3f} ms {w / (m * 1e-3) / 1e12:8.1f} TF/s")

@@ -1,12 +1,14 @@
 // Fused multi-head attention forward (head_dim 64) for sm_100a.  See attention.cuh for the contract.
 //
-// attn_fwd_kernel — one CTA per (128-query tile, head, image), 192 threads, TWO passes over the key tiles:
+// attn_fwd_kernel — one CTA per (128-query tile, head, image), 320 threads, TWO passes over the key tiles:
 //   pass 1  S = Q K^T per 128-key tile (tcgen05.mma, fp32 in TMEM) -> running row max / sum of exp2 (registers)
 //   pass 2  S again, P = exp2(S*log2e - lse2) is the EXACT softmax probability (no rescaling of the output accumulator),
 //           rounded to fp16 into a 128B-swizzled shared-memory tile, O += P V (tcgen05.mma, O stays in TMEM)
 //   warp 0     TMA producer: Q once, then a 4-stage ring of K (pass 1) / K + V^T (pass 2) tiles, OOB rows zero-filled
 //   warp 1     MMA issuer (one lane): S double-buffered in TMEM so QK^T of tile j+1 overlaps the softmax of tile j
-//   warps 2-5  softmax: thread = query row (TMEM lane), tcgen05.ld 32 columns at a time, ex2.approx
+//   warps 2-9  softmax: thread = query row (TMEM lane), two warps per lane quarter (64 key columns each);
+//              tcgen05.ld 32 columns at a time, software-pipelined against the ex2.approx work (MUFU is the bound:
+//              16 exp2/clk/SM measured, tools/micro/mufu_bench.cu)
 // The score matrix never leaves the SM: HBM traffic is q, k, v once per query tile (L2-resident) + o.
 //
 // attn_headmean_kernel — the head-averaged probability map the CAM refinement consumes (myAtt.py:323-326): one CTA per
@@ -157,47 +159,56 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
         float2* stats = reinterpret_cast<float2*>(smem + FwdSmem::STATS);
         uint32_t sc = 0;
         uint32_t r0[32], r1[32];
-        // ---- pass 1: row max and sum of exp2 over this warp's columns, log2 domain
+        // ---- pass 1: row max and sum of exp2 over this warp's columns, log2 domain.  The two 32-column TMEM loads of a
+        //      tile are software-pipelined against the exp2 work (LDTM of chunk B / of the next tile's chunk A is in flight
+        //      while the MUFU works on the previous chunk).
         float m = -INFINITY, l = 0.f;
+        auto online_chunk = [&](const uint32_t (&r)[32], int nvc) {   // nvc: columns of this chunk that exist (>= 1)
+            float c0 = -INFINITY, c1 = -INFINITY;
+            if (nvc >= 32) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) { c0 = fmaxf(c0, __uint_as_float(r[i])); c1 = fmaxf(c1, __uint_as_float(r[i + 1])); }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) if (i < nvc) c0 = fmaxf(c0, __uint_as_float(r[i]));
+            }
+            const float mn = fmaxf(m, fmaxf(c0, c1) * AT_LOG2E);
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+            if (nvc >= 32) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                    a0 += ex2_approx(fmaf(__uint_as_float(r[i]), AT_LOG2E, -mn));
+                    a1 += ex2_approx(fmaf(__uint_as_float(r[i + 1]), AT_LOG2E, -mn));
+                    a2 += ex2_approx(fmaf(__uint_as_float(r[i + 2]), AT_LOG2E, -mn));
+                    a3 += ex2_approx(fmaf(__uint_as_float(r[i + 3]), AT_LOG2E, -mn));
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) if (i < nvc) a0 += ex2_approx(fmaf(__uint_as_float(r[i]), AT_LOG2E, -mn));
+            }
+            l = l * ex2_approx(m - mn) + ((a0 + a1) + (a2 + a3));
+            m = mn;
+        };
+        mbar_wait(&s_full[0], 0);
+        tc_fence_after();
+        tmem_ld32_issue(tlane, r0);
         for (int j = 0; j < n_kt; ++j, ++sc) {
             const int b = sc & 1;
             const int nv = a.L - j * AT_BN - half * 64;      // this warp's columns of the tile that exist (may be <= 0)
-            mbar_wait(&s_full[b], (sc >> 1) & 1);
-            tc_fence_after();
-            if (nv > 0) {
-                tmem_ld32_issue(tlane + b * AT_BN, r0);
-                tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
-                tmem_ld_wait();
-            }
+            tmem_ld_wait();
+            tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
+            if (nv > 0) online_chunk(r0, nv);
+            tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the MMA warp may overwrite it
-            if (nv > 0) {
-                if (nv < 64) {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        if (i >= nv) r0[i] = 0xff800000u;            // -inf
-                        if (32 + i >= nv) r1[i] = 0xff800000u;
-                    }
-                }
-                float c0 = -INFINITY, c1 = -INFINITY, c2 = -INFINITY, c3 = -INFINITY;
-#pragma unroll
-                for (int i = 0; i < 32; i += 2) {
-                    c0 = fmaxf(c0, __uint_as_float(r0[i])); c1 = fmaxf(c1, __uint_as_float(r0[i + 1]));
-                    c2 = fmaxf(c2, __uint_as_float(r1[i])); c3 = fmaxf(c3, __uint_as_float(r1[i + 1]));
-                }
-                const float mn = fmaxf(m, fmaxf(fmaxf(c0, c1), fmaxf(c2, c3)) * AT_LOG2E);
-                float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll
-                for (int i = 0; i < 32; i += 2) {
-                    a0 += ex2_approx(fmaf(__uint_as_float(r0[i]), AT_LOG2E, -mn));
-                    a1 += ex2_approx(fmaf(__uint_as_float(r0[i + 1]), AT_LOG2E, -mn));
-                    a2 += ex2_approx(fmaf(__uint_as_float(r1[i]), AT_LOG2E, -mn));
-                    a3 += ex2_approx(fmaf(__uint_as_float(r1[i + 1]), AT_LOG2E, -mn));
-                }
-                l = l * ex2_approx(m - mn) + ((a0 + a1) + (a2 + a3));
-                m = mn;
+            {   // next tile (pass 2 re-reads tile 0 right after the last tile of pass 1)
+                const uint32_t sn = sc + 1;
+                mbar_wait(&s_full[sn & 1], (sn >> 1) & 1);
+                tc_fence_after();
+                tmem_ld32_issue(tlane + (sn & 1) * AT_BN, r0);
             }
+            if (nv > 32) online_chunk(r1, nv - 32);
         }
         // combine the two column halves of each row (named barrier over the 256 softmax threads)
         stats[half * 128 + row] = make_float2(m, l);
@@ -211,48 +222,45 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
         const float lse2 = m + __log2f(l);
         if (half == 0 && a.lse2 && grow < a.L) a.lse2[(size_t)bh * a.L + grow] = lse2;
         // ---- pass 2: exact probabilities -> fp16 P tile in shared memory (K-major, 128B swizzle); this warp's 64 columns
-        //      are exactly one [128][64] swizzled block
+        //      are exactly one [128][64] swizzled block.  Same load / exp2 pipelining as pass 1 (chunk A of tile 0 is
+        //      already in flight).
+        auto prob_chunk = [&](const uint32_t (&r)[32], int nvc, uint8_t* blk, int cc0) {
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * i]), AT_LOG2E, -lse2));
+                float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * i + 1]), AT_LOG2E, -lse2));
+                if (nvc < 32) {
+                    if (2 * i >= nvc) p0 = 0.f;
+                    if (2 * i + 1 >= nvc) p1 = 0.f;
+                }
+                const h16x2 h = __floats2half2_rn(p0, p1);
+                pk[i] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                *reinterpret_cast<uint4*>(blk + (((cc0 + t) ^ (row & 7)) << 4)) = make_uint4(pk[4 * t], pk[4 * t + 1], pk[4 * t + 2], pk[4 * t + 3]);
+        };
         uint32_t pc = 0;
         for (int j = 0; j < n_kt; ++j, ++sc, ++pc) {
             const int b = sc & 1, pb = pc & 1;
             const int nv = a.L - j * AT_BN - half * 64;
-            mbar_wait(&s_full[b], (sc >> 1) & 1);
-            tc_fence_after();
             uint8_t* blk = smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES + half * AT_TILE_BYTES + row * 128;
-            uint32_t pk[32];
-            if (nv > 0) {
-                tmem_ld32_issue(tlane + b * AT_BN, r0);
-                tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
-                tmem_ld_wait();
-            }
+            tmem_ld_wait();
+            tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
+            mbar_wait(&p_empty[pb], ((pc >> 1) & 1) ^ 1);
+            prob_chunk(r0, nv, blk, 0);
+            tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&s_empty[b]);
-            mbar_wait(&p_empty[pb], ((pc >> 1) & 1) ^ 1);
-            if (nv > 0) {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    float p0 = ex2_approx(fmaf(__uint_as_float(r0[2 * i]), AT_LOG2E, -lse2));
-                    float p1 = ex2_approx(fmaf(__uint_as_float(r0[2 * i + 1]), AT_LOG2E, -lse2));
-                    float p2 = ex2_approx(fmaf(__uint_as_float(r1[2 * i]), AT_LOG2E, -lse2));
-                    float p3 = ex2_approx(fmaf(__uint_as_float(r1[2 * i + 1]), AT_LOG2E, -lse2));
-                    if (nv < 64) {
-                        if (2 * i >= nv) p0 = 0.f;
-                        if (2 * i + 1 >= nv) p1 = 0.f;
-                        if (32 + 2 * i >= nv) p2 = 0.f;
-                        if (33 + 2 * i >= nv) p3 = 0.f;
-                    }
-                    const h16x2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
-                    pk[i] = *reinterpret_cast<const uint32_t*>(&ha);
-                    pk[16 + i] = *reinterpret_cast<const uint32_t*>(&hb);
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) pk[i] = 0u;
+            if (j + 1 < n_kt) {
+                const uint32_t sn = sc + 1;
+                mbar_wait(&s_full[sn & 1], (sn >> 1) & 1);
+                tc_fence_after();
+                tmem_ld32_issue(tlane + (sn & 1) * AT_BN, r0);
             }
-#pragma unroll
-            for (int cc = 0; cc < 8; ++cc)
-                *reinterpret_cast<uint4*>(blk + ((cc ^ (row & 7)) << 4)) = make_uint4(pk[4 * cc], pk[4 * cc + 1], pk[4 * cc + 2], pk[4 * cc + 3]);
+            prob_chunk(r1, nv - 32, blk, 4);
             fence_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(&p_full[pb]);
@@ -363,24 +371,31 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __gr
         for (int i = 0; i < 64; ++i) acc[i] = 0.f;
         uint32_t r0[32], r1[32];
         float lse = (grow < a.L) ? __ldg(a.lse2 + (size_t)(img * a.heads) * a.L + grow) : 0.f;
+        mbar_wait(&s_full[0], 0);
+        tc_fence_after();
+        tmem_ld32_issue(tlane, r0);
         for (int h = 0; h < a.heads; ++h) {
             const int b = h & 1;
             const float lse_next = (grow < a.L && h + 1 < a.heads) ? __ldg(a.lse2 + (size_t)(img * a.heads + h + 1) * a.L + grow) : 0.f;
-            mbar_wait(&s_full[b], (h >> 1) & 1);
-            tc_fence_after();
-            tmem_ld32_issue(tlane + b * AT_BN, r0);
+            // the TMEM load of the second 32 columns / of the next head's first 32 runs under the exp2 work
+            tmem_ld_wait();
             tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[i] += ex2_approx(fmaf(__uint_as_float(r0[i]), AT_LOG2E, -lse));
             tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the next head's MMA may overwrite it
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                acc[i] += ex2_approx(fmaf(__uint_as_float(r0[i]), AT_LOG2E, -lse));
-                acc[32 + i] += ex2_approx(fmaf(__uint_as_float(r1[i]), AT_LOG2E, -lse));
+            if (h + 1 < a.heads) {
+                mbar_wait(&s_full[b ^ 1], ((h + 1) >> 1) & 1);
+                tc_fence_after();
+                tmem_ld32_issue(tlane + (b ^ 1) * AT_BN, r0);
             }
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[32 + i] += ex2_approx(fmaf(__uint_as_float(r1[i]), AT_LOG2E, -lse));
             lse = lse_next;
         }
+        tmem_ld_wait();
         // mean over heads, transposed through the warp's swizzled 32x32 block so that each store is one row x 32 keys
         const float inv_h = 1.f / (float)a.heads;
         const int row0 = qt * AT_BM + q * 32;
@@ -443,6 +458,7 @@ int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, floa
     AttnArgs a{L, heads, ceil_div(L, AT_BN), o, lse2};
     dim3 grid(ceil_div(L, AT_BM), heads, n_img);
     ProfScope prof(PK_ATTENTION, 4.0 * L * L * AT_HD * heads * n_img, st);
+    if (g_prof_on) prof_tag(L, n_img, heads, 0);
     attn_fwd_kernel<<<grid, AT_THREADS, FwdSmem::TOTAL, st>>>(mq, mk, mv, a);
     WC_LAUNCH_CHECK();
     return WC_OK;
@@ -462,6 +478,7 @@ int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* a
     MeanArgs a{L, heads, lse2, avg};
     dim3 grid(ceil_div(L, AT_BN), ceil_div(L, AT_BM), n_img);
     ProfScope prof(PK_SOFTMAX, 4.0 * n_img * (double)L * L, st);
+    if (g_prof_on) prof_tag(L, n_img, heads, 1);
     attn_headmean_kernel<<<grid, AT_THREADS, MeanSmem::TOTAL, st>>>(mq, mk, a);
     WC_LAUNCH_CHECK();
     return WC_OK;

@@ -356,18 +356,6 @@ __device__ __forceinline__ void par_iter_tile_body(float* par_tile, const AffT* 
     const int H = a.H, W = a.W;
     const size_t iplane = (size_t)H * a.in_pitch, oplane = (size_t)H * a.out_pitch, aplane = (size_t)H * a.wp;
     const int ch0 = ch.ch0[c];
-    {
-        // L2 prefetch of this tile's affinity rows (48 planes x TH rows x 64 pixels) while the mask tile is being filled:
-        // the streaming loads below then hit L2 instead of paying the HBM latency under load
-        const int rows = min(TH, H - y0);
-        const int seg = min(PT_W, a.wp - x0) * (int)sizeof(AffT);          // bytes per row segment (multiple of 16)
-        const AffT* pbase = aff + (size_t)ch.b[c] * 48 * aplane + (size_t)y0 * a.wp + x0;
-        for (int i = threadIdx.x; i < 48 * rows; i += PT_THREADS) {
-            const int n = i / rows, r = i - n * rows;
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pbase + (size_t)n * aplane + (size_t)r * a.wp), "r"(seg)
-                         : "memory");
-        }
-    }
     fill_tile<SH, PT_THREADS>(par_tile, in + (size_t)ch0 * iplane, iplane, a.in_pitch, KC, x0, y0, H, W, a.in_vec);
     __syncthreads();
     const uint64_t pol = l2_evict_first_policy();
