@@ -162,13 +162,14 @@ int wc_decoder_fwd(const wc_decoder_weights* w, const void* taps, int N, int h, 
 int wc_layernorm(const float* x, const float* w, const float* b, void* out_f16, float* out_f32, long rows, int E,
                  void* stream);
 int wc_softmax_headmean(const float* S, void* P_f16, float* avg, int n_img, int heads, int L, int Lp, void* stream);
-/* Fused attention of the encoder blocks (head_dim 64): softmax(q k^T) v without materialising the scores
- * (clip/myAtt.py:53-64), output head-interleaved (myAtt.py:320), plus the head-mean probability map (myAtt.py:323-326).
- *   q, k fp16 [N*heads, L, 64] (q pre-scaled by 1/8); vt fp16 [N*heads, 64, Lp] (V transposed, Lp = round_up(L,8));
- *   o fp16 [N*L, heads*64]; lse2 fp32 [N*heads, L] or NULL (log2-domain row log-sum-exp);
- *   attn_avg fp32 [N, L, L] or NULL (needs lse2). */
+/* Fused attention of the encoder (head_dim 64) and decoder (head_dim 32) blocks: softmax(q k^T) v without materialising
+ * the scores (clip/myAtt.py:53-64), output head-interleaved (myAtt.py:320), plus the head-mean probability map
+ * (myAtt.py:323-326, head_dim 64 only).
+ *   q, k fp16 [N*heads, L, hd] (q pre-scaled by 1/sqrt(hd)); vt fp16 [N*heads, hd, Lp] (V transposed, Lp = round_up(L,8));
+ *   o fp16 [N*L, heads*hd]; lse2 fp32 [N*heads, L] or NULL (log2-domain row log-sum-exp);
+ *   attn_avg fp32 [N, L, L] or NULL (needs lse2 and head_dim 64). */
 int wc_attention_fwd(const void* q, const void* k, const void* vt, void* o, float* lse2, float* attn_avg,
-                     int n_img, int heads, int L, int Lp, void* stream);
+                     int n_img, int heads, int L, int Lp, int head_dim, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Grad-CAM head.  Replaces CLIP.forward_last_layer (clip/model.py:407-429) + GradCAM.__call__

@@ -30,6 +30,19 @@ def test_attention_matches_torch(N, heads, L):
     assert (avg.sum(-1) - 1).abs().max().item() < 1e-4
 
 
+@pytest.mark.parametrize("N,heads,L", [(1, 1, 64), (2, 8, 400), (1, 8, 576), (1, 3, 1024), (2, 8, 1600), (1, 2, 37)])
+def test_attention_head_dim_32_matches_torch(N, heads, L):
+    """Decoder blocks (TransDecoder.py:104-125: width 256, 8 heads x 32): same kernel, HD = 32 instantiation."""
+    g = torch.Generator(device="cuda").manual_seed(3 * L + heads)
+    q = (torch.randn(N, heads, L, 32, device="cuda", generator=g) * 0.35).half()
+    k = (torch.randn(N, heads, L, 32, device="cuda", generator=g) * 1.5).half()
+    v = torch.randn(N, heads, L, 32, device="cuda", generator=g).half()
+    o, _ = ops.attention_fwd(q, k, v, want_avg=False)
+    o_ref, _ = _ref(q, k, v)
+    assert torch.isfinite(o.float()).all()
+    assert (o.float() - o_ref).abs().max().item() < 4e-3
+
+
 def test_attention_peaked_rows_and_large_scores():
     """Rows dominated by one key (scores ~ +-60): the two-pass log-sum-exp must not overflow or lose the small terms."""
     torch.manual_seed(0)

@@ -46,14 +46,18 @@ struct FwdSmem {
     static constexpr int RING = AT_TILE_BYTES;                               // stage s: K at +s*32K, V^T at +s*32K+16K
     static constexpr int P = RING + AT_STAGES * 2 * AT_TILE_BYTES;           // two P buffers of 32 KB
     static constexpr int BARS = P + 2 * 2 * AT_TILE_BYTES;
-    static constexpr int STATS = BARS + 256;                                 // float2 [2 halves][128 rows]: pass-1 (max, sum)
+    static constexpr int STATS = BARS + 256;                                 // float [2 halves][128 rows] x {max, sum}
     static constexpr int TOTAL = STATS + 2 * 128 * 8 + 1024;                 // + alignment slack
 };
 
+// HD = head dim (64: CLIP blocks, 32: decoder blocks).  Q / K tiles are always [128][64] fp16 in shared memory: for HD = 32
+// the TMA box runs past the tensor's 32-element rows and the tail is zero-filled, and only HD/16 MMA k-steps are issued.
+template <int HD>
 __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap mapQ,
                                                                   const __grid_constant__ CUtensorMap mapK,
                                                                   const __grid_constant__ CUtensorMap mapV,
                                                                   const __grid_constant__ AttnArgs a) {
+    constexpr int V_BLK = HD * 128;                // one K-major [HD dims][64 keys] block of V^T
     extern __shared__ uint8_t at_smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~(uintptr_t)1023);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FwdSmem::BARS);
@@ -100,19 +104,19 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                     const int s = it % AT_STAGES;
                     mbar_wait(&kv_empty[s], ((it / AT_STAGES) & 1) ^ 1);
                     uint8_t* sk = smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES;
-                    mbar_expect_tx(&kv_full[s], pass == 0 ? AT_TILE_BYTES : 2 * AT_TILE_BYTES);
+                    mbar_expect_tx(&kv_full[s], pass == 0 ? AT_TILE_BYTES : AT_TILE_BYTES + 2 * V_BLK);
                     tma_load_4d(sk, &mapK, &kv_full[s], 0, j * AT_BN, bh, 0);
                     if (pass == 1) {
-                        // V^T [64 dims][128 keys] as two K-major [64][64] blocks (box = 64 keys x 64 dims)
+                        // V^T [HD dims][128 keys] as two K-major [HD][64] blocks (box = 64 keys x HD dims)
                         tma_load_4d(sk + AT_TILE_BYTES, &mapV, &kv_full[s], j * AT_BN, 0, bh, 0);
-                        tma_load_4d(sk + AT_TILE_BYTES + AT_TILE_BYTES / 2, &mapV, &kv_full[s], j * AT_BN + 64, 0, bh, 0);
+                        tma_load_4d(sk + AT_TILE_BYTES + V_BLK, &mapV, &kv_full[s], j * AT_BN + 64, 0, bh, 0);
                     }
                 }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc_s = make_idesc(AT_BM, AT_BN), idesc_o = make_idesc(AT_BM, AT_HD);
+            constexpr uint32_t idesc_s = make_idesc(AT_BM, AT_BN), idesc_o = make_idesc(AT_BM, HD);
             const uint64_t dq = make_smem_desc(smem_u32(smem + FwdSmem::Q));
             mbar_wait(q_full, 0);
             uint32_t it = 0, sc = 0;
@@ -123,7 +127,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                 tc_fence_after();
                 const uint64_t dk = make_smem_desc(smem_u32(smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES));
 #pragma unroll
-                for (int k = 0; k < AT_HD / 16; ++k) umma_f16(tmem_base + b * AT_BN, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+                for (int k = 0; k < HD / 16; ++k) umma_f16(tmem_base + b * AT_BN, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
                 umma_commit(&s_full[b]);
                 ++sc;
             };
@@ -142,7 +146,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                 const uint32_t sv = smem_u32(smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES + AT_TILE_BYTES);
 #pragma unroll
                 for (int kb = 0; kb < 2; ++kb) {
-                    const uint64_t dp = make_smem_desc(sp + kb * AT_TILE_BYTES), dv = make_smem_desc(sv + kb * (AT_TILE_BYTES / 2));
+                    const uint64_t dp = make_smem_desc(sp + kb * AT_TILE_BYTES), dv = make_smem_desc(sv + kb * V_BLK);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) umma_f16(tmem_o, dp + 2 * k, dv + 2 * k, idesc_o, (j | kb | k) != 0);
                 }
@@ -156,38 +160,26 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
         const int half = (warp - 2) >> 2;                    // which 64 key columns of every tile this warp owns
         const int row = q * 32 + lane, grow = qt * AT_BM + row;
         const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16) + half * 64;
-        float2* stats = reinterpret_cast<float2*>(smem + FwdSmem::STATS);
+        float* stat_m = reinterpret_cast<float*>(smem + FwdSmem::STATS);
+        float* stat_l = stat_m + 256;
         uint32_t sc = 0;
         uint32_t r0[32], r1[32];
-        // ---- pass 1: row max and sum of exp2 over this warp's columns, log2 domain.  The two 32-column TMEM loads of a
-        //      tile are software-pipelined against the exp2 work (LDTM of chunk B / of the next tile's chunk A is in flight
-        //      while the MUFU works on the previous chunk).
-        float m = -INFINITY, l = 0.f;
-        auto online_chunk = [&](const uint32_t (&r)[32], int nvc) {   // nvc: columns of this chunk that exist (>= 1)
-            float c0 = -INFINITY, c1 = -INFINITY;
+        // ---- pass 1: row max only (no MUFU work).  The two 32-column TMEM loads of a tile are software-pipelined against
+        //      the FMNMX work.
+        float m = -INFINITY;
+        auto max_chunk = [&](const uint32_t (&r)[32], int nvc) {   // nvc: columns of this chunk that exist (>= 1)
+            float c0 = -INFINITY, c1 = -INFINITY, c2 = -INFINITY, c3 = -INFINITY;
             if (nvc >= 32) {
 #pragma unroll
-                for (int i = 0; i < 32; i += 2) { c0 = fmaxf(c0, __uint_as_float(r[i])); c1 = fmaxf(c1, __uint_as_float(r[i + 1])); }
+                for (int i = 0; i < 32; i += 4) {
+                    c0 = fmaxf(c0, __uint_as_float(r[i])); c1 = fmaxf(c1, __uint_as_float(r[i + 1]));
+                    c2 = fmaxf(c2, __uint_as_float(r[i + 2])); c3 = fmaxf(c3, __uint_as_float(r[i + 3]));
+                }
             } else {
 #pragma unroll
                 for (int i = 0; i < 32; ++i) if (i < nvc) c0 = fmaxf(c0, __uint_as_float(r[i]));
             }
-            const float mn = fmaxf(m, fmaxf(c0, c1) * AT_LOG2E);
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-            if (nvc >= 32) {
-#pragma unroll
-                for (int i = 0; i < 32; i += 4) {
-                    a0 += ex2_approx(fmaf(__uint_as_float(r[i]), AT_LOG2E, -mn));
-                    a1 += ex2_approx(fmaf(__uint_as_float(r[i + 1]), AT_LOG2E, -mn));
-                    a2 += ex2_approx(fmaf(__uint_as_float(r[i + 2]), AT_LOG2E, -mn));
-                    a3 += ex2_approx(fmaf(__uint_as_float(r[i + 3]), AT_LOG2E, -mn));
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) if (i < nvc) a0 += ex2_approx(fmaf(__uint_as_float(r[i]), AT_LOG2E, -mn));
-            }
-            l = l * ex2_approx(m - mn) + ((a0 + a1) + (a2 + a3));
-            m = mn;
+            m = fmaxf(m, fmaxf(fmaxf(c0, c1), fmaxf(c2, c3)));
         };
         mbar_wait(&s_full[0], 0);
         tc_fence_after();
@@ -197,7 +189,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             const int nv = a.L - j * AT_BN - half * 64;      // this warp's columns of the tile that exist (may be <= 0)
             tmem_ld_wait();
             tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
-            if (nv > 0) online_chunk(r0, nv);
+            if (nv > 0) max_chunk(r0, nv);
             tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
@@ -208,32 +200,28 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                 tc_fence_after();
                 tmem_ld32_issue(tlane + (sn & 1) * AT_BN, r0);
             }
-            if (nv > 32) online_chunk(r1, nv - 32);
+            if (nv > 32) max_chunk(r1, nv - 32);
         }
         // combine the two column halves of each row (named barrier over the 256 softmax threads)
-        stats[half * 128 + row] = make_float2(m, l);
+        stat_m[half * 128 + row] = m;
         asm volatile("bar.sync 1, 256;" ::: "memory");
-        {
-            const float2 o = stats[(half ^ 1) * 128 + row];
-            const float mn = fmaxf(m, o.x);
-            l = l * ex2_approx(m - mn) + (o.y > 0.f ? o.y * ex2_approx(o.x - mn) : 0.f);
-            m = mn;
-        }
-        const float lse2 = m + __log2f(l);
-        if (half == 0 && a.lse2 && grow < a.L) a.lse2[(size_t)bh * a.L + grow] = lse2;
-        // ---- pass 2: exact probabilities -> fp16 P tile in shared memory (K-major, 128B swizzle); this warp's 64 columns
-        //      are exactly one [128][64] swizzled block.  Same load / exp2 pipelining as pass 1 (chunk A of tile 0 is
-        //      already in flight).
+        m = fmaxf(m, stat_m[(half ^ 1) * 128 + row]);
+        const float m2 = m * AT_LOG2E;                       // log2 domain; key 0 always exists, so m is finite
+        // ---- pass 2: P = exp2(S*log2e - m2) in (0, 1], UN-normalised (one exp per score in the whole kernel), rounded to
+        //      fp16 into the K-major 128B-swizzled P tile; the row sum is accumulated in fp32 and divides O in the epilogue.
+        //      This warp's 64 columns are exactly one [128][64] swizzled block.  Chunk A of tile 0 is already in flight.
+        float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
         auto prob_chunk = [&](const uint32_t (&r)[32], int nvc, uint8_t* blk, int cc0) {
             uint32_t pk[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-                float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * i]), AT_LOG2E, -lse2));
-                float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * i + 1]), AT_LOG2E, -lse2));
+                float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * i]), AT_LOG2E, -m2));
+                float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * i + 1]), AT_LOG2E, -m2));
                 if (nvc < 32) {
                     if (2 * i >= nvc) p0 = 0.f;
                     if (2 * i + 1 >= nvc) p1 = 0.f;
                 }
+                if (i & 1) { l2 += p0; l3 += p1; } else { l0 += p0; l1 += p1; }
                 const h16x2 h = __floats2half2_rn(p0, p1);
                 pk[i] = *reinterpret_cast<const uint32_t*>(&h);
             }
@@ -265,22 +253,33 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             __syncwarp();
             if (lane == 0) mbar_arrive(&p_full[pb]);
         }
-        // ---- epilogue: O (already normalised) -> fp16, head-interleaved [N*L, heads*64]; this warp's 32 of the 64 dims
+        // row sums of the two column halves -> 1 / l and the log2-domain log-sum-exp
+        float l = (l0 + l1) + (l2 + l3);
+        stat_l[half * 128 + row] = l;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        l += stat_l[(half ^ 1) * 128 + row];
+        const float inv_l = 1.f / l;
+        if (half == 0 && a.lse2 && grow < a.L) a.lse2[(size_t)bh * a.L + grow] = m2 + __log2f(l);
+        // ---- epilogue: O / l -> fp16, head-interleaved [N*L, heads*HD]; HD = 64: this warp's 32 of the 64 dims,
+        //      HD = 32: the half-0 warps store the whole row
         mbar_wait(o_full, 0);
         tc_fence_after();
-        h16* orow = a.o + ((size_t)img * a.L + grow) * (size_t)(a.heads * AT_HD) + head * AT_HD + half * 32;
-        tmem_ld32_issue(tmem_base + ((uint32_t)(q * 32) << 16) + 256 + half * 32, r0);
-        tmem_ld_wait();
-        if (grow < a.L) {
+        if (HD == 64 || half == 0) {
+            h16* orow = a.o + ((size_t)img * a.L + grow) * (size_t)(a.heads * HD) + head * HD + (HD == 64 ? half * 32 : 0);
+            tmem_ld32_issue(tmem_base + ((uint32_t)(q * 32) << 16) + 256 + (HD == 64 ? half * 32 : 0), r0);
+            tmem_ld_wait();
+            if (grow < a.L) {
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-                uint32_t w[4];
+                for (int t = 0; t < 4; ++t) {
+                    uint32_t w[4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const h16x2 h = __floats2half2_rn(__uint_as_float(r0[8 * t + 2 * i]), __uint_as_float(r0[8 * t + 2 * i + 1]));
-                    w[i] = *reinterpret_cast<const uint32_t*>(&h);
+                    for (int i = 0; i < 4; ++i) {
+                        const h16x2 h = __floats2half2_rn(__uint_as_float(r0[8 * t + 2 * i]) * inv_l,
+                                                          __uint_as_float(r0[8 * t + 2 * i + 1]) * inv_l);
+                        w[i] = *reinterpret_cast<const uint32_t*>(&h);
+                    }
+                    *reinterpret_cast<uint4*>(orow + t * 8) = make_uint4(w[0], w[1], w[2], w[3]);
                 }
-                *reinterpret_cast<uint4*>(orow + t * 8) = make_uint4(w[0], w[1], w[2], w[3]);
             }
         }
         tc_fence_before();
@@ -428,40 +427,47 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __gr
 }
 
 // ---------------------------------------------------------------------------------------------------
-static int attn_maps(const h16* q, const h16* k, const h16* vt, int nh, int L, int Lp, CUtensorMap* mq, CUtensorMap* mk,
+static int attn_maps(const h16* q, const h16* k, const h16* vt, int nh, int L, int Lp, int hd, CUtensorMap* mq, CUtensorMap* mk,
                      CUtensorMap* mv) {
     int u0, u1, rc;
-    GemmOperand oq{q, L, AT_HD, (long)L * AT_HD, 0}, ok{k, L, AT_HD, (long)L * AT_HD, 0};
-    if ((rc = make_tma_map(mq, oq, AT_HD, nh, 1, AT_BM, &u0, &u1))) return rc;
-    if ((rc = make_tma_map(mk, ok, AT_HD, nh, 1, AT_BN, &u0, &u1))) return rc;
+    GemmOperand oq{q, L, hd, (long)L * hd, 0}, ok{k, L, hd, (long)L * hd, 0};
+    if ((rc = make_tma_map(mq, oq, hd, nh, 1, AT_BM, &u0, &u1))) return rc;
+    if ((rc = make_tma_map(mk, ok, hd, nh, 1, AT_BN, &u0, &u1))) return rc;
     if (vt && mv) {
         // V^T rows = head dims, K extent = L keys (NOT Lp): columns L..Lp-1 are never written and must read as zero
-        GemmOperand ov{vt, AT_HD, Lp, (long)AT_HD * Lp, 0};
-        if ((rc = make_tma_map(mv, ov, L, nh, 1, AT_HD, &u0, &u1))) return rc;
+        GemmOperand ov{vt, hd, Lp, (long)hd * Lp, 0};
+        if ((rc = make_tma_map(mv, ov, L, nh, 1, hd, &u0, &u1))) return rc;
     }
     return WC_OK;
 }
 
-int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, float* lse2, int n_img, int heads, int L, int Lp,
+template <int HD>
+static int launch_fwd_hd(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const AttnArgs& a, dim3 grid,
                          cudaStream_t st) {
-    WC_CHECK_ARG(q && k && vt && o && n_img > 0 && heads > 0 && L > 0 && Lp >= L && (Lp & 7) == 0);
-    WC_CHECK_ARG(heads <= 65535 && n_img <= 65535);
     static bool attr_set = false;
     if (!attr_set) {
-        WC_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::TOTAL));
+        WC_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::TOTAL));
         attr_set = true;
     }
+    attn_fwd_kernel<HD><<<grid, AT_THREADS, FwdSmem::TOTAL, st>>>(mq, mk, mv, a);
+    WC_LAUNCH_CHECK();
+    return WC_OK;
+}
+
+int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, float* lse2, int n_img, int heads, int L, int Lp,
+                         int hd, cudaStream_t st) {
+    WC_CHECK_ARG(q && k && vt && o && n_img > 0 && heads > 0 && L > 0 && Lp >= L && (Lp & 7) == 0);
+    WC_CHECK_ARG(heads <= 65535 && n_img <= 65535);
+    if (hd != 64 && hd != 32) return fail(WC_ERR_UNSUPPORTED, "%s: head_dim %d (64 and 32 are built)", __func__, hd);
     CUtensorMap mq, mk, mv;
-    int rc = attn_maps(q, k, vt, n_img * heads, L, Lp, &mq, &mk, &mv);
+    int rc = attn_maps(q, k, vt, n_img * heads, L, Lp, hd, &mq, &mk, &mv);
     if (rc) return rc;
     // a batch of 1 collapses the map's batch dimension; the kernel's batch coordinate is then 0 anyway
     AttnArgs a{L, heads, ceil_div(L, AT_BN), o, lse2};
     dim3 grid(ceil_div(L, AT_BM), heads, n_img);
-    ProfScope prof(PK_ATTENTION, 4.0 * L * L * AT_HD * heads * n_img, st);
-    if (g_prof_on) prof_tag(L, n_img, heads, 0);
-    attn_fwd_kernel<<<grid, AT_THREADS, FwdSmem::TOTAL, st>>>(mq, mk, mv, a);
-    WC_LAUNCH_CHECK();
-    return WC_OK;
+    ProfScope prof(PK_ATTENTION, 4.0 * L * L * hd * heads * n_img, st);
+    if (g_prof_on) prof_tag(L, n_img, heads, hd);
+    return hd == 64 ? launch_fwd_hd<64>(mq, mk, mv, a, grid, st) : launch_fwd_hd<32>(mq, mk, mv, a, grid, st);
 }
 
 int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* avg, int n_img, int heads, int L,
@@ -473,7 +479,7 @@ int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* a
         attr_set = true;
     }
     CUtensorMap mq, mk;
-    int rc = attn_maps(q, k, nullptr, n_img * heads, L, 0, &mq, &mk, nullptr);
+    int rc = attn_maps(q, k, nullptr, n_img * heads, L, 0, AT_HD, &mq, &mk, nullptr);
     if (rc) return rc;
     MeanArgs a{L, heads, lse2, avg};
     dim3 grid(ceil_div(L, AT_BN), ceil_div(L, AT_BM), n_img);
@@ -490,11 +496,12 @@ using namespace wc;
 
 // Test / micro-bench entry for the fused attention pair (see include/weclip_b200.h).
 extern "C" int wc_attention_fwd(const void* q, const void* k, const void* vt, void* o, float* lse2, float* attn_avg,
-                                int n_img, int heads, int L, int Lp, void* stream) {
+                                int n_img, int heads, int L, int Lp, int head_dim, void* stream) {
     WC_CHECK_ARG(lse2 || !attn_avg);
+    WC_CHECK_ARG(head_dim == 64 || !attn_avg);
     int rc = launch_attention_fwd(reinterpret_cast<const h16*>(q), reinterpret_cast<const h16*>(k),
                                   reinterpret_cast<const h16*>(vt), reinterpret_cast<h16*>(o), lse2, n_img, heads, L, Lp,
-                                  as_stream(stream));
+                                  head_dim, as_stream(stream));
     if (rc || !attn_avg) return rc;
     return launch_attn_headmean(reinterpret_cast<const h16*>(q), reinterpret_cast<const h16*>(k), lse2, attn_avg, n_img,
                                 heads, L, as_stream(stream));

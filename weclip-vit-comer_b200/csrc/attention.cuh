@@ -1,15 +1,15 @@
-// Fused multi-head attention forward for sm_100a (tcgen05 + TMEM + TMA), head_dim 64.
-// Replaces the materialised [N*heads, L, L] score tensor of clip/myAtt.py:53-64 on the encoder blocks.
+// Fused multi-head attention forward for sm_100a (tcgen05 + TMEM + TMA), head_dim 64 (CLIP blocks) or 32 (decoder blocks).
+// Replaces the materialised [N*heads, L, L] score tensor of clip/myAtt.py:53-64.
 #pragma once
 #include "common.cuh"
 
 namespace wc {
 
-// q, k: [N*heads, L, 64] fp16 (q pre-scaled by 1/sqrt(64), myAtt.py:54); vt: [N*heads, 64, Lp] fp16 (V transposed).
-// o: [N*L, heads*64] fp16, head-interleaved (myAtt.py:320).  lse2 (optional): [N*heads, L] fp32, log2-domain
-// log-sum-exp of each score row (input of launch_attn_headmean).
+// q, k: [N*heads, L, hd] fp16 (q pre-scaled by 1/sqrt(hd), myAtt.py:54); vt: [N*heads, hd, Lp] fp16 (V transposed).
+// o: [N*L, heads*hd] fp16, head-interleaved (myAtt.py:320).  lse2 (optional): [N*heads, L] fp32, log2-domain
+// log-sum-exp of each score row (input of launch_attn_headmean).  hd in {64, 32}.
 int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, float* lse2, int n_img, int heads, int L, int Lp,
-                         cudaStream_t st);
+                         int hd, cudaStream_t st);
 
 // avg[n, i, j] = mean over heads of softmax(q k^T)[n, h, i, j] (myAtt.py:323-326), fp32 [N, L, L], each element written
 // once.  Needs lse2 from launch_attention_fwd.

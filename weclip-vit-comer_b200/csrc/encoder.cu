@@ -25,8 +25,9 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
     if (!b.S) {
         // fused path: scores and probabilities never leave the SM (attention.cu); softmax(q k^T) v written
         // head-interleaved into [M,E] (myAtt.py:53-64,320), then the head-mean map from the row log-sum-exps (:323-326)
-        if (hd != 64 || !b.lse) return fail(WC_ERR_UNSUPPORTED, "%s: fused attention needs head_dim 64 and an lse buffer", __func__);
-        if ((rc = launch_attention_fwd(b.q, b.k, b.vt, b.o, b.lse, n_img, heads, L, (int)Lp, st))) return rc;
+        if (b.attn_avg && (hd != 64 || !b.lse))
+            return fail(WC_ERR_UNSUPPORTED, "%s: the head-mean map needs head_dim 64 and an lse buffer", __func__);
+        if ((rc = launch_attention_fwd(b.q, b.k, b.vt, b.o, b.lse, n_img, heads, L, (int)Lp, hd, st))) return rc;
         if (b.attn_avg && (rc = launch_attn_headmean(b.q, b.k, b.lse, b.attn_avg, n_img, heads, L, st))) return rc;
     } else {
         // S = q k^T (myAtt.py:56), fp32 [N*heads, L, Lp]
@@ -107,7 +108,7 @@ static size_t decoder_layout(Arena& ar, int N, int P, int C, h16** z1, h16** cat
     *cat = ar.get<h16>((long)N * P * 11 * D);
     *x = ar.get<float>((long)N * P * D);
     *x_bf = ar.get<h16>((long)N * P * D);
-    *s = carve_block(ar, N, P, D, 8, false);
+    *s = carve_block(ar, N, P, D, 8, true);     // fused attention (head_dim 32); the three maps are unused downstream
     return ar.off;
 }
 

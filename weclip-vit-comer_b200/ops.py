@@ -115,11 +115,11 @@ def confusion_hist(pred: torch.Tensor, gt: torch.Tensor, hist: torch.Tensor) -> 
 
 
 def attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, want_avg: bool = True):
-    """Fused attention (head_dim 64).  q, k, v fp16 [N, heads, L, 64] (q already scaled by 1/8).
-    Returns (o fp16 [N, L, heads*64], attn_avg fp32 [N, L, L] | None)."""
+    """Fused attention (head_dim 64 or 32).  q, k, v fp16 [N, heads, L, hd] (q already scaled by 1/sqrt(hd)).
+    Returns (o fp16 [N, L, heads*hd], attn_avg fp32 [N, L, L] | None; the map needs head_dim 64)."""
     _lib.require_device()
     N, heads, L, hd = q.shape
-    assert hd == 64 and q.dtype == torch.float16
+    assert hd in (64, 32) and q.dtype == torch.float16
     Lp = (L + 7) // 8 * 8
     vt = torch.full((N, heads, hd, Lp), float("nan"), dtype=torch.float16, device=q.device)   # pad columns must not matter
     vt[..., :L] = v.transpose(-1, -2)
@@ -127,6 +127,6 @@ def attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, want_avg: b
     lse = torch.empty(N, heads, L, dtype=torch.float32, device=q.device)
     avg = torch.empty(N, L, L, dtype=torch.float32, device=q.device) if want_avg else None
     rc = _lib.lib().wc_attention_fwd(_lib.ptr(q.contiguous()), _lib.ptr(k.contiguous()), _lib.ptr(vt), _lib.ptr(o),
-                                     _lib.ptr(lse), _lib.ptr(avg), N, heads, L, Lp, _lib.stream_ptr())
+                                     _lib.ptr(lse), _lib.ptr(avg), N, heads, L, Lp, hd, _lib.stream_ptr())
     _lib.check(rc, "wc_attention_fwd")
     return o, avg
