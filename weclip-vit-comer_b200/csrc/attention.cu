@@ -427,6 +427,219 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __gr
 }
 
 // ---------------------------------------------------------------------------------------------------
+// attn_bwd_colsum_kernel — the only L x L work of the Grad-CAM backward (gradcam.cu header):
+//     colsum[j] = sum_{i>=1} dS_ij,   dS = P * (dP - delta),  dP = dO V^T,  delta_i = dO_i . O_i
+//               = V'_j . W'_j         with  W' = P~^T dO'   (P~ = P without the class-token query row,
+//                                            dO' = [dO | -delta_hi | -delta_lo | 0...],  V' = [V | 1 | 1 | 0...])
+// so neither P nor dP is ever materialised.  One CTA per (128-key tile, head, instance) walks the query tiles ONCE:
+//   S^T = K Q^T (tcgen05, keys on the TMEM lanes)  ->  P^T = exp2(S^T log2e - lse2_i) (the exact probabilities, from the forward's
+//   row log-sum-exps; masked queries carry lse = +inf)  ->  fp16 tile in shared memory  ->  W' += P^T dO' (tcgen05, N = 80)
+// and the epilogue contracts W'_j with V'_j.  Same warp roles and barriers as attn_fwd_kernel's second pass.
+constexpr int BW_ND = 80;                          // 64 head dims + delta hi / lo + padding to a legal MMA N
+constexpr int BW_STAGES = 3;
+constexpr int BW_DBLK = BW_ND * 128;               // one K-major [80][64 queries] block of dO'^T (10 KB)
+constexpr int BW_STAGE_BYTES = AT_TILE_BYTES + 2 * BW_DBLK + 3072;     // 40 KB: keeps every stage 1024-byte aligned
+constexpr int BW_MAX_L = 2048;
+struct BwdSmem {
+    static constexpr int KT = 0;
+    static constexpr int RING = AT_TILE_BYTES;
+    static constexpr int P = RING + BW_STAGES * BW_STAGE_BYTES;
+    static constexpr int LSE = P + 2 * 2 * AT_TILE_BYTES;
+    static constexpr int BARS = LSE + BW_MAX_L * 4;
+    static constexpr int TOTAL = BARS + 256 + 1024;
+};
+struct BwdArgs {
+    int L, heads, n_qt;
+    const float* lse2;       // [N*heads, L]
+    const h16* v;            // [N*heads, L, 64]
+    float* colsum;           // [n_inst*heads, L]
+    BwdInstTable tab;
+};
+
+__global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __grid_constant__ CUtensorMap mapK,
+                                                                         const __grid_constant__ CUtensorMap mapQ,
+                                                                         const __grid_constant__ CUtensorMap mapD,
+                                                                         const __grid_constant__ BwdArgs a) {
+    extern __shared__ uint8_t at_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BwdSmem::BARS);
+    uint64_t* k_full = bars;                       // [1]
+    uint64_t* qd_full = bars + 1;                  // [STAGES]
+    uint64_t* qd_empty = qd_full + BW_STAGES;      // [STAGES]
+    uint64_t* s_full = qd_empty + BW_STAGES;       // [2]
+    uint64_t* s_empty = s_full + 2;                // [2]
+    uint64_t* p_full = s_empty + 2;                // [2]
+    uint64_t* p_empty = p_full + 2;                // [2]
+    uint64_t* w_full = p_empty + 2;                // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 1);
+    float* lse_s = reinterpret_cast<float*>(smem + BwdSmem::LSE);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int jt = blockIdx.x, head = blockIdx.y, inst = blockIdx.z;
+    const int img = a.tab.img[inst];
+    const int bh = img * a.heads + head, ih = inst * a.heads + head;
+    const int n_qt = a.n_qt;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&mapK); prefetch_tmap(&mapQ); prefetch_tmap(&mapD);
+        mbar_init(k_full, 1);
+        for (int s = 0; s < BW_STAGES; ++s) { mbar_init(&qd_full[s], 1); mbar_init(&qd_empty[s], 1); }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], AT_SM_WARPS);
+            mbar_init(&p_full[b], AT_SM_WARPS); mbar_init(&p_empty[b], 1);
+        }
+        mbar_init(w_full, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    // row log-sum-exps of this (image, head); the class-token query (i = 0, excluded from the Grad-CAM mean) and the padding
+    // queries get +inf so that their probabilities come out as exactly 0
+    for (int i = threadIdx.x; i < n_qt * AT_BN; i += AT_THREADS)
+        lse_s[i] = (i >= 1 && i < a.L) ? __ldg(a.lse2 + (size_t)bh * a.L + i) : INFINITY;
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_w = tmem_base + 256;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(k_full, AT_TILE_BYTES);
+            tma_load_4d(smem + BwdSmem::KT, &mapK, k_full, 0, jt * AT_BM, bh, 0);
+            for (int it = 0; it < n_qt; ++it) {
+                const int s = it % BW_STAGES;
+                mbar_wait(&qd_empty[s], ((it / BW_STAGES) & 1) ^ 1);
+                uint8_t* sq = smem + BwdSmem::RING + s * BW_STAGE_BYTES;
+                mbar_expect_tx(&qd_full[s], AT_TILE_BYTES + 2 * BW_DBLK);
+                tma_load_4d(sq, &mapQ, &qd_full[s], 0, it * AT_BN, bh, 0);
+                tma_load_4d(sq + AT_TILE_BYTES, &mapD, &qd_full[s], it * AT_BN, 0, ih, 0);
+                tma_load_4d(sq + AT_TILE_BYTES + BW_DBLK, &mapD, &qd_full[s], it * AT_BN + 64, 0, ih, 0);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_s = make_idesc(AT_BM, AT_BN), idesc_w = make_idesc(AT_BM, BW_ND);
+            const uint64_t dk = make_smem_desc(smem_u32(smem + BwdSmem::KT));
+            mbar_wait(k_full, 0);
+            uint32_t sc = 0;
+            auto issue_s = [&](int it_) {          // S^T[sc & 1] = K Q^T for ring slot it_
+                const int s = it_ % BW_STAGES, b = sc & 1;
+                mbar_wait(&qd_full[s], (it_ / BW_STAGES) & 1);
+                mbar_wait(&s_empty[b], ((sc >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint64_t dq = make_smem_desc(smem_u32(smem + BwdSmem::RING + s * BW_STAGE_BYTES));
+#pragma unroll
+                for (int k = 0; k < AT_HD / 16; ++k) umma_f16(tmem_base + b * AT_BN, dk + 2 * k, dq + 2 * k, idesc_s, k != 0);
+                umma_commit(&s_full[b]);
+                ++sc;
+            };
+            issue_s(0);
+            for (int it = 0; it < n_qt; ++it) {
+                if (it + 1 < n_qt) issue_s(it + 1);
+                const int s = it % BW_STAGES, pb = it & 1;
+                mbar_wait(&p_full[pb], (it >> 1) & 1);
+                tc_fence_after();
+                const uint32_t sp = smem_u32(smem + BwdSmem::P + pb * 2 * AT_TILE_BYTES);
+                const uint32_t sd = smem_u32(smem + BwdSmem::RING + s * BW_STAGE_BYTES + AT_TILE_BYTES);
+#pragma unroll
+                for (int kb = 0; kb < 2; ++kb) {
+                    const uint64_t dp = make_smem_desc(sp + kb * AT_TILE_BYTES), dd = make_smem_desc(sd + kb * BW_DBLK);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_f16(tmem_w, dp + 2 * k, dd + 2 * k, idesc_w, (it | kb | k) != 0);
+                }
+                umma_commit(&p_empty[pb]);
+                umma_commit(&qd_empty[s]);
+            }
+            umma_commit(w_full);
+        }
+    } else {
+        const int q = warp & 3;                              // TMEM lane quarter
+        const int half = (warp - 2) >> 2;                    // which 64 query columns of every tile this warp owns
+        const int row = q * 32 + lane, gkey = jt * AT_BM + row;
+        const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16) + half * 64;
+        uint32_t r0[32], r1[32];
+        auto prob_chunk = [&](const uint32_t (&r)[32], const float* lse, uint8_t* blk, int cc0) {
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float4 ls = *reinterpret_cast<const float4*>(lse + 4 * i);      // broadcast: same queries for every lane
+                const float p0 = ex2_approx(fmaf(__uint_as_float(r[4 * i]), AT_LOG2E, -ls.x));
+                const float p1 = ex2_approx(fmaf(__uint_as_float(r[4 * i + 1]), AT_LOG2E, -ls.y));
+                const float p2 = ex2_approx(fmaf(__uint_as_float(r[4 * i + 2]), AT_LOG2E, -ls.z));
+                const float p3 = ex2_approx(fmaf(__uint_as_float(r[4 * i + 3]), AT_LOG2E, -ls.w));
+                const h16x2 h0 = __floats2half2_rn(p0, p1), h1 = __floats2half2_rn(p2, p3);
+                pk[2 * i] = *reinterpret_cast<const uint32_t*>(&h0);
+                pk[2 * i + 1] = *reinterpret_cast<const uint32_t*>(&h1);
+            }
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                *reinterpret_cast<uint4*>(blk + (((cc0 + t) ^ (row & 7)) << 4)) = make_uint4(pk[4 * t], pk[4 * t + 1], pk[4 * t + 2], pk[4 * t + 3]);
+        };
+        mbar_wait(&s_full[0], 0);
+        tc_fence_after();
+        tmem_ld32_issue(tlane, r0);
+        for (int it = 0; it < n_qt; ++it) {
+            const int b = it & 1, pb = it & 1;
+            const float* lse = lse_s + it * AT_BN + half * 64;
+            uint8_t* blk = smem + BwdSmem::P + pb * 2 * AT_TILE_BYTES + half * AT_TILE_BYTES + row * 128;
+            tmem_ld_wait();
+            tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
+            mbar_wait(&p_empty[pb], ((it >> 1) & 1) ^ 1);
+            prob_chunk(r0, lse, blk, 0);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_empty[b]);
+            if (it + 1 < n_qt) {
+                mbar_wait(&s_full[b ^ 1], ((it + 1) >> 1) & 1);
+                tc_fence_after();
+                tmem_ld32_issue(tlane + (b ^ 1) * AT_BN, r0);
+            }
+            prob_chunk(r1, lse + 32, blk, 4);
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[pb]);
+        }
+        // ---- epilogue: colsum[key] = V'_key . W'_key (the half-0 warps hold the whole row: 3 x 32 TMEM columns)
+        mbar_wait(w_full, 0);
+        tc_fence_after();
+        if (half == 0) {
+            const uint32_t wl = tmem_w + ((uint32_t)(q * 32) << 16);
+            const int key = gkey < a.L ? gkey : a.L - 1;            // clamped read; out-of-range rows are not stored
+            const uint4* vr = reinterpret_cast<const uint4*>(a.v + ((size_t)bh * a.L + key) * AT_HD);
+            float acc = 0.f;
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                tmem_ld32_issue(wl + c * 32, r0);
+                tmem_ld_wait();
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const uint4 pk = __ldg(vr + c * 4 + t);
+                    const uint32_t w4[4] = {pk.x, pk.y, pk.z, pk.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float2 vf = __half22float2(*reinterpret_cast<const h16x2*>(&w4[e]));
+                        acc = fmaf(vf.x, __uint_as_float(r0[8 * t + 2 * e]), acc);
+                        acc = fmaf(vf.y, __uint_as_float(r0[8 * t + 2 * e + 1]), acc);
+                    }
+                }
+            }
+            tmem_ld32_issue(wl + 64, r0);
+            tmem_ld_wait();
+            acc += __uint_as_float(r0[0]) + __uint_as_float(r0[1]);
+            if (gkey < a.L) a.colsum[(size_t)ih * a.L + gkey] = acc;
+        }
+        tc_fence_before();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
 static int attn_maps(const h16* q, const h16* k, const h16* vt, int nh, int L, int Lp, int hd, CUtensorMap* mq, CUtensorMap* mk,
                      CUtensorMap* mv) {
     int u0, u1, rc;
@@ -486,6 +699,31 @@ int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* a
     ProfScope prof(PK_SOFTMAX, 4.0 * n_img * (double)L * L, st);
     if (g_prof_on) prof_tag(L, n_img, heads, 1);
     attn_headmean_kernel<<<grid, AT_THREADS, MeanSmem::TOTAL, st>>>(mq, mk, a);
+    WC_LAUNCH_CHECK();
+    return WC_OK;
+}
+
+int launch_attn_bwd_colsum(const h16* q, const h16* k, const h16* v, const h16* dOT, const float* lse2, float* colsum,
+                           const BwdInstTable& tab, int n_inst, int n_img, int heads, int L, int Lp, cudaStream_t st) {
+    WC_CHECK_ARG(q && k && v && dOT && lse2 && colsum && n_inst > 0 && n_inst <= BWD_MAX_INST && n_img > 0 && heads > 0);
+    WC_CHECK_ARG(L > 1 && Lp >= L && (Lp & 7) == 0 && ceil_div(L, AT_BN) * AT_BN <= BW_MAX_L && heads <= 65535);
+    static bool attr_set = false;
+    if (!attr_set) {
+        WC_CUDA(cudaFuncSetAttribute(attn_bwd_colsum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::TOTAL));
+        attr_set = true;
+    }
+    CUtensorMap mq, mk, md;
+    int rc = attn_maps(q, k, nullptr, n_img * heads, L, 0, AT_HD, &mq, &mk, nullptr);
+    if (rc) return rc;
+    int u0, u1;
+    // dO'^T rows = 80 (dims, -delta hi/lo, zero padding), K extent = L queries: columns L..Lp-1 read as zero
+    GemmOperand od{dOT, BW_ND, Lp, (long)BW_ND * Lp, 0};
+    if ((rc = make_tma_map(&md, od, L, n_inst * heads, 1, BW_ND, &u0, &u1))) return rc;
+    BwdArgs a{L, heads, ceil_div(L, AT_BN), lse2, v, colsum, tab};
+    dim3 grid(ceil_div(L, AT_BM), heads, n_inst);
+    ProfScope prof(PK_ATTENTION, 2.0 * L * L * (AT_HD + BW_ND) * heads * n_inst, st);
+    if (g_prof_on) prof_tag(L, n_inst, heads, 2);
+    attn_bwd_colsum_kernel<<<grid, AT_THREADS, BwdSmem::TOTAL, st>>>(mk, mq, md, a);
     WC_LAUNCH_CHECK();
     return WC_OK;
 }

@@ -16,4 +16,12 @@ int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, floa
 int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* avg, int n_img, int heads, int L,
                          cudaStream_t st);
 
+// Grad-CAM attention backward reduced to column sums (see attention.cu / gradcam.cu headers).
+//   dOT: fp16 [n_inst*heads, 80, Lp] = rows 0..63 dO^T of the head, row 64 / 65 = -delta (hi / lo fp16 split), rest zero.
+//   colsum: fp32 [n_inst*heads, L] = sum over the patch query rows of dS.  tab.img[inst] = image of each instance.
+constexpr int BWD_MAX_INST = 64;
+struct BwdInstTable { short img[BWD_MAX_INST]; };
+int launch_attn_bwd_colsum(const h16* q, const h16* k, const h16* v, const h16* dOT, const float* lse2, float* colsum,
+                           const BwdInstTable& tab, int n_inst, int n_img, int heads, int L, int Lp, cudaStream_t st);
+
 }  // namespace wc

@@ -108,12 +108,29 @@ __global__ void __launch_bounds__(256) upsample_argmax_hist_kernel(const float* 
 
 // hist[C*gt+pred] += 1 over flat arrays (the cam-label histogram, test_msc_flip_voc.py:107)
 __global__ void __launch_bounds__(256) confusion_hist_kernel(const int64_t* __restrict__ pred, const int16_t* __restrict__ gt,
-                                                             long n, int C, unsigned long long* __restrict__ hist) {
+                                                             long n, int C, unsigned long long* __restrict__ hist, int smem_hist) {
+    if (!smem_hist) {   // C*C bins do not fit the static shared-memory window: global atomics
+        for (long i = (long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long)gridDim.x * 256) {
+            const int g = gt[i];
+            const long p = pred[i];
+            if (g >= 0 && g < C && p >= 0 && p < C) atomicAdd(hist + (size_t)g * C + p, 1ULL);
+        }
+        return;
+    }
+    // CTA-private histogram in shared memory (C*C <= 81*81 bins), flushed once: a few bins take almost every pixel, so
+    // global atomics would serialise in L2
+    extern __shared__ unsigned int bins[];
+    const int nb = C * C;
+    for (int b = threadIdx.x; b < nb; b += 256) bins[b] = 0u;
+    __syncthreads();
     for (long i = (long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long)gridDim.x * 256) {
         const int g = gt[i];
         const long p = pred[i];
-        if (g >= 0 && g < C && p >= 0 && p < C) atomicAdd(hist + (size_t)g * C + p, 1ULL);
+        if (g >= 0 && g < C && p >= 0 && p < C) atomicAdd(bins + g * C + (int)p, 1u);
     }
+    __syncthreads();
+    for (int b = threadIdx.x; b < nb; b += 256)
+        if (bins[b]) atomicAdd(hist + b, (unsigned long long)bins[b]);
 }
 
 static inline float torch_scale(int in_size, int out_size, float scale_factor) {
@@ -173,9 +190,11 @@ extern "C" int wc_upsample_argmax_hist(const float* logits, int B, int C, int h,
 
 extern "C" int wc_confusion_hist(const int64_t* pred, const int16_t* gt, long n, int C, int64_t* hist, void* stream) {
     WC_CHECK_ARG(pred && gt && hist && n > 0 && C > 0);
+    const int smem_hist = ((size_t)C * C * 4 <= 40 * 1024) ? 1 : 0;
     ProfScope prof(PK_EVAL, 0.0, as_stream(stream));
-    const unsigned grid = (unsigned)min((long)148 * 8, ceil_div(n, 256L));
-    confusion_hist_kernel<<<grid, 256, 0, as_stream(stream)>>>(pred, gt, n, C, reinterpret_cast<unsigned long long*>(hist));
+    const unsigned grid = (unsigned)min((long)148 * 4, ceil_div(n, 1024L));
+    confusion_hist_kernel<<<grid, 256, smem_hist ? (size_t)C * C * 4 : 0, as_stream(stream)>>>(
+        pred, gt, n, C, reinterpret_cast<unsigned long long*>(hist), smem_hist);
     WC_LAUNCH_CHECK();
     return WC_OK;
 }

@@ -30,10 +30,18 @@ constexpr int GEMM_THREADS = 64 + 32 * EPI_WARPS;
 __device__ __forceinline__ int stg_off(int row, int vec) { return row * 32 + ((vec ^ (row & 7)) << 2); }
 constexpr int RING_BYTES = 192 * 1024;
 
+__device__ __forceinline__ float tanh_approx(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ float apply_act(float x, int act) {
     switch (act) {
         case ACT_RELU: return fmaxf(x, 0.f);
-        case ACT_QUICKGELU: return __fdividef(x, 1.f + __expf(-1.702f * x));     // 2 MUFU (ex2, rcp) + 3 FP32 ops
+        // x * sigmoid(1.702 x) = 0.5 x (1 + tanh(0.851 x)): ONE MUFU op per element instead of ex2 + rcp (the c_fc epilogue is
+        // MUFU-paced: 128 x 256 outputs per tile at 16 MUFU/clk/SM).  tanh.approx.f32 is accurate to 2^-11 relative, the
+        // same as the fp16 rounding of the result.
+        case ACT_QUICKGELU: { const float h = 0.5f * x; return fmaf(h, tanh_approx(0.851f * x), h); }
         case ACT_SIGMOID: return __fdividef(1.f, 1.f + __expf(-x));
         default: return x;
     }

@@ -13,7 +13,10 @@
 //     sum_{i>=1} dQs_i = sum_j (sum_{i>=1} dS_ij) K_j          (column sums of dS over patch rows)
 //     sum_{j>=1} dK_j  = sum_i (-dS_i0) Qs_i                   (rows of dS sum to zero)
 //     sum_{j>=1} dV_j  = sum_i (1 - P_i0) dO_i
-// so the only L x L work per (instance, head) is the dP GEMM (tcgen05) and one fused reduction pass.
+// The column sums themselves never touch an L x L tensor in memory (attention.cu, attn_bwd_colsum_kernel):
+//     delta_i = dO_i . O_i,   colsum_j = V_j . (sum_{i>=1} P_ij dO_i) - sum_{i>=1} P_ij delta_i
+// with P recomputed tile by tile from q, k and the forward's row log-sum-exps; dS_i0 and P_i0 are per-row dot products.
+#include "attention.cuh"
 #include "encoder.cuh"
 
 #include <math.h>
@@ -229,34 +232,79 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
 }
 
 // ---------------------------------------------------------------------------------------------------
-// Fused softmax-backward reduction.  For (instance, head, 32-row chunk):  delta_i, dS = P*(dP-delta),
-//   colsum[j] += sum_{i>=1 in chunk} dS_ij ;  ds0[i] = dS_i0.
-// dP fp32 [n_inst*12, L, Lp] (chunk-local instances), P h16 [N*12, L, Lp] (per image).
+// Operand preparation for attn_bwd_colsum_kernel + the per-row terms.  For (64-query chunk, head, instance):
+//   delta_i = dO_i . O_i ;  dOT[inst,h] = [dO^T ; -delta (hi, lo fp16 split) ; 0]  as [80][Lp] fp16 ;
+//   P_i0 = exp2(Qs_i . K_0 log2e - lse2_i) ;  dS_i0 = P_i0 (dO_i . V_0 - delta_i).
+// dO fp16 [n_inst*L, 768] (chunk-local instances), O fp16 [N*L, 768] (block-12 attention output, head-interleaved).
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) attn_bwd_reduce_kernel(const float* __restrict__ dP, const h16* __restrict__ Pm,
-                                                              float* __restrict__ colsum, float* __restrict__ ds0,
-                                                              const __grid_constant__ InstTable it, int L, int Lp) {
-    extern __shared__ float colacc[];   // [L]
-    __shared__ float red[32];
-    const int inst = blockIdx.z, h = blockIdx.y, tid = threadIdx.x;
+__device__ __forceinline__ void load16h(const h16* p, float* out) {
+    const uint4 a = *reinterpret_cast<const uint4*>(p), b = *reinterpret_cast<const uint4*>(p + 8);
+    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        const float2 f = __half22float2(*reinterpret_cast<const h16x2*>(&w[e]));
+        out[2 * e] = f.x; out[2 * e + 1] = f.y;
+    }
+}
+
+__global__ void __launch_bounds__(256) do_prep_kernel(const h16* __restrict__ dO, const h16* __restrict__ O,
+                                                      const h16* __restrict__ q, const h16* __restrict__ k,
+                                                      const h16* __restrict__ v, const float* __restrict__ lse2,
+                                                      h16* __restrict__ dOT, float* __restrict__ ds0, float* __restrict__ p0,
+                                                      const __grid_constant__ InstTable it, int L, int Lp) {
+    __shared__ h16x2 tile[64][33];       // [query][dim pair], padded: the transposed read is 2-way conflicted at worst
+    __shared__ h16 dl[2][64];
+    const int i0 = blockIdx.x * 64, h = blockIdx.y, inst = blockIdx.z, tid = threadIdx.x;
     const int img = it.img[inst];
-    for (int c = tid; c < L; c += 256) colacc[c] = 0.f;
-    const int r0 = blockIdx.x * 32, r1 = min(r0 + 32, L);
-    for (int i = r0; i < r1; ++i) {
-        const float* dp = dP + ((size_t)(inst * GC_HEADS + h) * L + i) * Lp;
-        const h16* p = Pm + ((size_t)(img * GC_HEADS + h) * L + i) * Lp;
-        float d = 0.f;
-        for (int c = tid; c < L; c += 256) d = fmaf(dp[c], __half2float(p[c]), d);
-        d = block_sum(d, red);
-        for (int c = tid; c < L; c += 256) {
-            const float ds = __half2float(p[c]) * (dp[c] - d);
-            if (i >= 1) colacc[c] += ds;
-            if (c == 0) ds0[(size_t)(inst * GC_HEADS + h) * L + i] = ds;
+    const size_t hb = (size_t)img * GC_HEADS + h, ih = (size_t)inst * GC_HEADS + h;
+    const int r = tid >> 2, qd = tid & 3, i = i0 + r;
+    float dlt = 0.f, dp0 = 0.f, s0 = 0.f;
+    float g[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) g[e] = 0.f;
+    if (i < L) {
+        float o[16], qq[16], k0[16], v0[16];
+        load16h(dO + ((size_t)inst * L + i) * GC_E + h * GC_HD + qd * 16, g);
+        load16h(O + ((size_t)img * L + i) * GC_E + h * GC_HD + qd * 16, o);
+        load16h(q + (hb * L + i) * GC_HD + qd * 16, qq);
+        load16h(k + (hb * L) * GC_HD + qd * 16, k0);
+        load16h(v + (hb * L) * GC_HD + qd * 16, v0);
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            dlt = fmaf(g[e], o[e], dlt);
+            dp0 = fmaf(g[e], v0[e], dp0);
+            s0 = fmaf(qq[e], k0[e], s0);
         }
     }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) tile[r][qd * 8 + e] = __floats2half2_rn(g[2 * e], g[2 * e + 1]);
+#pragma unroll
+    for (int m = 1; m <= 2; m <<= 1) {
+        dlt += __shfl_xor_sync(0xffffffffu, dlt, m);
+        dp0 += __shfl_xor_sync(0xffffffffu, dp0, m);
+        s0 += __shfl_xor_sync(0xffffffffu, s0, m);
+    }
+    if (qd == 0) {
+        if (i < L) {
+            const float p = exp2f(s0 * 1.4426950408889634f - __ldg(lse2 + hb * L + i));
+            p0[ih * L + i] = p;
+            ds0[ih * L + i] = p * (dp0 - dlt);
+        }
+        const h16 hi = __float2half_rn(-dlt);
+        dl[0][r] = hi;
+        dl[1][r] = __float2half_rn(-dlt - __half2float(hi));
+    }
     __syncthreads();
-    float* cs = colsum + (size_t)(inst * GC_HEADS + h) * L;
-    for (int c = tid; c < L; c += 256) atomicAdd(cs + c, colacc[c]);
+    const h16* th = reinterpret_cast<const h16*>(&tile[0][0]);
+    for (int idx = tid; idx < 80 * 8; idx += 256) {
+        const int d = idx >> 3, c8 = (idx & 7) * 8, col = i0 + c8;
+        if (col >= Lp) continue;
+        __align__(16) h16 vals[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+            vals[e] = d < 64 ? th[(c8 + e) * 66 + d] : d == 64 ? dl[0][c8 + e] : d == 65 ? dl[1][c8 + e] : __float2half_rn(0.f);
+        *reinterpret_cast<uint4*>(dOT + (ih * 80 + d) * (size_t)Lp + col) = *reinterpret_cast<const uint4*>(vals);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -264,7 +312,7 @@ __global__ void __launch_bounds__(256) attn_bwd_reduce_kernel(const float* __res
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) qkv_grad_sum_kernel(const float* __restrict__ colsum, const float* __restrict__ ds0,
                                                            const h16* __restrict__ q, const h16* __restrict__ k,
-                                                           const h16* __restrict__ Pm, const h16* __restrict__ dO,
+                                                           const float* __restrict__ p0, const h16* __restrict__ dO,
                                                            float* __restrict__ dqkv, const __grid_constant__ InstTable it,
                                                            int L, int Lp, float qscale) {
     __shared__ float part[3][4][GC_HD];
@@ -277,7 +325,7 @@ __global__ void __launch_bounds__(256) qkv_grad_sum_kernel(const float* __restri
     for (int i = grp; i < L; i += 4) {
         gq = fmaf(cs[i], __half2float(k[(hb * L + i) * GC_HD + d]), gq);
         gk = fmaf(-d0[i], __half2float(q[(hb * L + i) * GC_HD + d]), gk);
-        const float pi0 = __half2float(Pm[(hb * L + i) * Lp]);
+        const float pi0 = p0[(size_t)(inst * GC_HEADS + h) * L + i];
         gv = fmaf(1.f - pi0, __half2float(dO[((size_t)inst * L + i) * GC_E + h * GC_HD + d]), gv);
     }
     part[0][grp][d] = gq; part[1][grp][d] = gk; part[2][grp][d] = gv;
@@ -289,35 +337,59 @@ __global__ void __launch_bounds__(256) qkv_grad_sum_kernel(const float* __restri
 }
 
 // w[inst][c] = (1/P) * sum_r dqkv[inst][r] * W_in[r][c]   (mean over patch tokens of the hooked gradient, grad_cam.py:23)
-__global__ void __launch_bounds__(128) cam_weight_kernel(const float* __restrict__ dqkv, const float* __restrict__ w_in,
+// 64 columns x 4 row groups per CTA (the row groups are reduced through shared memory).
+__global__ void __launch_bounds__(256) cam_weight_kernel(const float* __restrict__ dqkv, const float* __restrict__ w_in,
                                                          float* __restrict__ wvec, const float* __restrict__ gscale, int P) {
     __shared__ float dq[3 * GC_E];
-    const int inst = blockIdx.y, c = blockIdx.x * 128 + threadIdx.x;
-    for (int r = threadIdx.x; r < 3 * GC_E; r += 128) dq[r] = dqkv[(size_t)inst * 3 * GC_E + r];
+    __shared__ float part[4][64];
+    const int inst = blockIdx.y, cl = threadIdx.x & 63, grp = threadIdx.x >> 6, c = blockIdx.x * 64 + cl;
+    for (int r = threadIdx.x; r < 3 * GC_E; r += 256) dq[r] = dqkv[(size_t)inst * 3 * GC_E + r];
     __syncthreads();
-    float s = 0.f;
+    float s0 = 0.f, s1 = 0.f;
+    const int r0 = grp * (3 * GC_E / 4);
 #pragma unroll 8
-    for (int r = 0; r < 3 * GC_E; ++r) s = fmaf(dq[r], __ldg(w_in + (size_t)r * GC_E + c), s);
-    wvec[(size_t)inst * GC_E + c] = s / (float)P / gscale[inst];
+    for (int r = r0; r < r0 + 3 * GC_E / 4; r += 2) {
+        s0 = fmaf(dq[r], __ldg(w_in + (size_t)r * GC_E + c), s0);
+        s1 = fmaf(dq[r + 1], __ldg(w_in + (size_t)(r + 1) * GC_E + c), s1);
+    }
+    part[grp][cl] = s0 + s1;
+    __syncthreads();
+    if (grp == 0) wvec[(size_t)inst * GC_E + c] = (part[0][cl] + part[1][cl] + part[2][cl] + part[3][cl]) / (float)P / gscale[inst];
 }
 
-// cam = relu(sum_c w_c A_c) over the patch tokens, then scale_cam_image twice (base_cam.py:55-59,144-145,150-154).
-__global__ void __launch_bounds__(256) cam_kernel(const float* __restrict__ A32, const float* __restrict__ wvec,
-                                                  float* __restrict__ cams, const __grid_constant__ InstTable it, int L) {
-    extern __shared__ float cam[];   // [P]
-    __shared__ float wv[GC_E];
-    __shared__ float red[32];
-    const int inst = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+// cam = relu(sum_c w_c A_c) over the patch tokens (base_cam.py:55-59,144-145): one warp per (patch, instance), the grid
+// covers every patch of every instance so the A32 stream runs at memory speed (the K classes of an image re-read it from L2).
+__global__ void __launch_bounds__(256) cam_dot_kernel(const float* __restrict__ A32, const float* __restrict__ wvec,
+                                                      float* __restrict__ cams, const __grid_constant__ InstTable it, int L) {
+    __shared__ float4 wv[GC_E / 4];
+    const int inst = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int P = L - 1, img = it.img[inst];
-    for (int c = tid; c < GC_E; c += 256) wv[c] = wvec[(size_t)(it.inst0 + inst) * GC_E + c];
+    if (tid < GC_E / 4) wv[tid] = reinterpret_cast<const float4*>(wvec + (size_t)(it.inst0 + inst) * GC_E)[tid];
     __syncthreads();
-    for (int p = warp; p < P; p += 8) {
-        const float* a = A32 + ((size_t)img * L + 1 + p) * GC_E;
+    float* o = cams + (size_t)(it.inst0 + inst) * P;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const int p = (blockIdx.x * 8 + warp) * 4 + r;
+        if (p >= P) break;
+        const float4* a = reinterpret_cast<const float4*>(A32 + ((size_t)img * L + 1 + p) * GC_E);
         float s = 0.f;
-        for (int c = lane; c < GC_E; c += 32) s = fmaf(wv[c], a[c], s);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            const float4 x = a[lane + 32 * i], w = wv[lane + 32 * i];
+            s += x.x * w.x + x.y * w.y + x.z * w.z + x.w * w.w;
+        }
         s = warp_sum(s);
-        if (lane == 0) cam[p] = fmaxf(s, 0.f);
+        if (lane == 0) o[p] = fmaxf(s, 0.f);
     }
+}
+
+// scale_cam_image twice (utils/image.py:51-61, base_cam.py:150-154), in place, one CTA per instance.
+__global__ void __launch_bounds__(256) cam_norm_kernel(float* __restrict__ cams, int inst0, int P) {
+    extern __shared__ float cam[];   // [P]
+    __shared__ float red[32];
+    const int tid = threadIdx.x;
+    float* o = cams + (size_t)(inst0 + blockIdx.x) * P;
+    for (int p = tid; p < P; p += 256) cam[p] = o[p];
     __syncthreads();
     for (int rep = 0; rep < 2; ++rep) {
         float mn = INFINITY;
@@ -330,36 +402,35 @@ __global__ void __launch_bounds__(256) cam_kernel(const float* __restrict__ A32,
         for (int p = tid; p < P; p += 256) cam[p] = (cam[p] - mn) / den;
         __syncthreads();
     }
-    float* o = cams + (size_t)(it.inst0 + inst) * P;
     for (int p = tid; p < P; p += 256) o[p] = cam[p];
 }
 
 // ---------------------------------------------------------------------------------------------------
 struct GcLayout {
     // forward (per call)
-    float *a32, *x1, *x2, *S, *msum, *dm, *dqkv, *wvec, *gscale;
-    h16 *a, *q, *k, *v, *vt, *P, *o, *u, *upre;
+    float *a32, *x1, *x2, *lse, *msum, *dm, *dqkv, *wvec, *gscale;
+    h16 *a, *q, *k, *v, *vt, *o, *u, *upre;
     // backward (per chunk of <= chunk instances)
-    float *dx2, *da2, *dP, *colsum, *ds0;
-    h16 *dx2b, *dh, *dx1b, *dO;
+    float *dx2, *da2, *colsum, *ds0, *p0;
+    h16 *dx2b, *dh, *dx1b, *dO, *dOT;
 };
 
 static void gc_layout(Arena& ar, GcLayout& g, int N, int L, int total_inst, int chunk) {
     const long M = (long)N * L, Lp = round8(L), E = GC_E;
     g.a32 = ar.get<float>(M * E); g.x1 = ar.get<float>(M * E); g.x2 = ar.get<float>(M * E);
-    g.S = ar.get<float>((long)N * GC_HEADS * L * Lp);
+    g.lse = ar.get<float>((long)N * GC_HEADS * L);
     g.msum = ar.get<float>((long)N * E); g.dm = ar.get<float>((long)total_inst * E);
     g.dqkv = ar.get<float>((long)total_inst * 3 * E); g.wvec = ar.get<float>((long)total_inst * E);
     g.gscale = ar.get<float>((long)total_inst);
     g.a = ar.get<h16>(M * E); g.q = ar.get<h16>(M * E); g.k = ar.get<h16>(M * E); g.v = ar.get<h16>(M * E);
     g.vt = ar.get<h16>((long)N * GC_HEADS * GC_HD * Lp);
-    g.P = ar.get<h16>((long)N * GC_HEADS * L * Lp);
     g.o = ar.get<h16>(M * E); g.u = ar.get<h16>(M * 4 * E); g.upre = ar.get<h16>(M * 4 * E);
     const long R = (long)chunk * L;
     g.dx2 = ar.get<float>(R * E); g.da2 = ar.get<float>(R * E);
-    g.dP = ar.get<float>((long)chunk * GC_HEADS * L * Lp);
     g.colsum = ar.get<float>((long)chunk * GC_HEADS * L); g.ds0 = ar.get<float>((long)chunk * GC_HEADS * L);
+    g.p0 = ar.get<float>((long)chunk * GC_HEADS * L);
     g.dx2b = ar.get<h16>(R * E); g.dh = ar.get<h16>(R * 4 * E); g.dx1b = ar.get<h16>(R * E); g.dO = ar.get<h16>(R * E);
+    g.dOT = ar.get<h16>((long)chunk * GC_HEADS * 80 * Lp);
 }
 
 // instances per backward chunk: 16 (bounds the dP scratch), but never less than the largest image's class count
@@ -399,7 +470,7 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
     }
     const int chunk = chunk_size(total, max_k);
     WC_CHECK_ARG(chunk <= GC_MAX_INST);
-    WC_CHECK_ARG(L * (int)sizeof(float) <= 48 * 1024);
+    WC_CHECK_ARG(L <= 2048 && chunk <= BWD_MAX_INST);
     Arena ar(workspace, workspace_bytes);
     GcLayout g;
     gc_layout(ar, g, N, L, total, chunk);
@@ -409,7 +480,7 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
     {
         BlockBuffers b{};
         b.x_in = x11; b.x_mid = g.x1; b.x_out = g.x2;
-        b.a = g.a; b.a_f32 = g.a32; b.q = g.q; b.k = g.k; b.v = g.v; b.vt = g.vt; b.S = g.S; b.P = g.P; b.o = g.o;
+        b.a = g.a; b.a_f32 = g.a32; b.q = g.q; b.k = g.k; b.v = g.v; b.vt = g.vt; b.lse = g.lse; b.o = g.o;   // fused attention
         b.u = g.u; b.u_pre = g.upre; b.attn_avg = attn_last;
         if ((rc = run_block(w->blocks[11], b, N, L, E, GC_HEADS, st))) return rc;
     }
@@ -465,27 +536,24 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
             p.epi.out = g.dO; p.epi.out_f16 = 1; p.epi.ldo = E;
             if ((rc = launch_gemm(p, st))) return rc;
         }
-        // dP = dO V^T per head; V is shared by the classes of an image
-        for (int i = img0; i < img1; ++i) {
-            const int li = k_off_host[i] - it.inst0, K = k_off_host[i + 1] - k_off_host[i];
-            GemmProblem p; p.M = L; p.N = L; p.K = GC_HD; p.nb0 = GC_HEADS; p.nb1 = K;
-            p.A = GemmOperand{g.dO + (long)li * L * E, L, E, GC_HD, (long)L * E};
-            p.B = GemmOperand{g.v + (long)i * GC_HEADS * L * GC_HD, L, GC_HD, (long)L * GC_HD, 0};
-            p.epi.out = g.dP + (long)li * GC_HEADS * L * Lp; p.epi.ldo = Lp; p.epi.out_bs0 = (long)L * Lp;
-            p.epi.out_bs1 = (long)GC_HEADS * L * Lp;
-            if ((rc = launch_gemm(p, st))) return rc;
-        }
-        WC_CUDA(cudaMemsetAsync(g.colsum, 0, sizeof(float) * n_inst * GC_HEADS * L, st));
-        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, attn_bwd_reduce_kernel<<<dim3(ceil_div(L, 32), GC_HEADS, n_inst), 256, sizeof(float) * L, st>>>(
-            g.dP, g.P, g.colsum, g.ds0, it, L, (int)Lp));
+        // delta, dO'^T, dS_i0, P_i0; then the column sums of dS without materialising P or dP (attention.cu)
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, do_prep_kernel<<<dim3(ceil_div(L, 64), GC_HEADS, n_inst), 256, 0, st>>>(
+            g.dO, g.o, g.q, g.k, g.v, g.lse, g.dOT, g.ds0, g.p0, it, L, (int)Lp));
         WC_LAUNCH_CHECK();
-        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, qkv_grad_sum_kernel<<<dim3(GC_HEADS, n_inst), 256, 0, st>>>(g.colsum, g.ds0, g.q, g.k, g.P, g.dO,
+        {
+            BwdInstTable bt;
+            for (int c = 0; c < n_inst; ++c) bt.img[c] = it.img[c];
+            if ((rc = launch_attn_bwd_colsum(g.q, g.k, g.v, g.dOT, g.lse, g.colsum, bt, n_inst, N, GC_HEADS, L, (int)Lp, st))) return rc;
+        }
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, qkv_grad_sum_kernel<<<dim3(GC_HEADS, n_inst), 256, 0, st>>>(g.colsum, g.ds0, g.q, g.k, g.p0, g.dO,
                                                                     g.dqkv + (long)it.inst0 * 3 * E, it, L, (int)Lp, qscale));
         WC_LAUNCH_CHECK();
-        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, cam_weight_kernel<<<dim3(E / 128, n_inst), 128, 0, st>>>(g.dqkv + (long)it.inst0 * 3 * E, w->w_in_f32,
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, cam_weight_kernel<<<dim3(E / 64, n_inst), 256, 0, st>>>(g.dqkv + (long)it.inst0 * 3 * E, w->w_in_f32,
                                                                  g.wvec + (long)it.inst0 * E, g.gscale + it.inst0, P));
         WC_LAUNCH_CHECK();
-        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, cam_kernel<<<n_inst, 256, sizeof(float) * P, st>>>(g.a32, g.wvec, cams, it, L));
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, cam_dot_kernel<<<dim3(ceil_div(P, 32), n_inst), 256, 0, st>>>(g.a32, g.wvec, cams, it, L));
+        WC_LAUNCH_CHECK();
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, cam_norm_kernel<<<n_inst, 256, sizeof(float) * P, st>>>(cams, it.inst0, P));
         WC_LAUNCH_CHECK();
         img0 = img1;
     }
