@@ -22,6 +22,7 @@ namespace wc {
 
 constexpr int AT_BM = 128, AT_BN = 128, AT_HD = 64;
 constexpr int AT_STAGES = 4;
+constexpr int AT_SBUF = 3;             // score tiles buffered in tensor memory (3 x 128 columns + the output accumulator <= 512)
 constexpr int AT_SM_WARPS = 8;          // softmax warps: two per TMEM lane quarter, each owning 64 of a tile's 128 key columns
 constexpr int AT_THREADS = 64 + 32 * AT_SM_WARPS;
 constexpr int AT_TILE_BYTES = 128 * 64 * 2;          // one [128][64] fp16 operand tile (Q, K, V^T pair, half of P)
@@ -64,9 +65,9 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
     uint64_t* q_full = bars;                       // [1]
     uint64_t* kv_full = bars + 1;                  // [STAGES]
     uint64_t* kv_empty = kv_full + AT_STAGES;      // [STAGES]
-    uint64_t* s_full = kv_empty + AT_STAGES;       // [2]  S[b] computed            (MMA -> softmax)
-    uint64_t* s_empty = s_full + 2;                // [2]  S[b] read into registers (softmax -> MMA)
-    uint64_t* p_full = s_empty + 2;                // [2]  P[b] written             (softmax -> MMA)
+    uint64_t* s_full = kv_empty + AT_STAGES;       // [3]  S[b] computed            (MMA -> softmax)
+    uint64_t* s_empty = s_full + AT_SBUF;          // [3]  S[b] read into registers (softmax -> MMA)
+    uint64_t* p_full = s_empty + AT_SBUF;          // [2]  P[b] written             (softmax -> MMA)
     uint64_t* p_empty = p_full + 2;                // [2]  P[b] consumed by P V     (MMA -> softmax)
     uint64_t* o_full = p_empty + 2;                // [1]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
@@ -80,10 +81,8 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
         prefetch_tmap(&mapQ); prefetch_tmap(&mapK); prefetch_tmap(&mapV);
         mbar_init(q_full, 1);
         for (int s = 0; s < AT_STAGES; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
-        for (int b = 0; b < 2; ++b) {
-            mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], AT_SM_WARPS);
-            mbar_init(&p_full[b], AT_SM_WARPS); mbar_init(&p_empty[b], 1);
-        }
+        for (int b = 0; b < AT_SBUF; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], AT_SM_WARPS); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&p_full[b], AT_SM_WARPS); mbar_init(&p_empty[b], 1); }
         mbar_init(o_full, 1);
         mbar_fence_init();
     }
@@ -92,7 +91,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t tmem_o = tmem_base + 256;
+    const uint32_t tmem_o = tmem_base + AT_SBUF * AT_BN;
 
     if (warp == 0) {
         if (lane == 0) {
@@ -120,10 +119,10 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             const uint64_t dq = make_smem_desc(smem_u32(smem + FwdSmem::Q));
             mbar_wait(q_full, 0);
             uint32_t it = 0, sc = 0;
-            auto issue_s = [&](uint32_t it_) {     // S[sc & 1] = Q K^T for ring slot it_
-                const int s = it_ % AT_STAGES, b = sc & 1;
+            auto issue_s = [&](uint32_t it_) {     // S[sc % 3] = Q K^T for ring slot it_
+                const int s = it_ % AT_STAGES, b = sc % AT_SBUF;
                 mbar_wait(&kv_full[s], (it_ / AT_STAGES) & 1);
-                mbar_wait(&s_empty[b], ((sc >> 1) & 1) ^ 1);
+                mbar_wait(&s_empty[b], ((sc / AT_SBUF) & 1) ^ 1);
                 tc_fence_after();
                 const uint64_t dk = make_smem_desc(smem_u32(smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES));
 #pragma unroll
@@ -135,10 +134,13 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                 issue_s(it);
                 umma_commit(&kv_empty[it % AT_STAGES]);
             }
+            // pass 2: the scores run TWO tiles ahead of the P V product (three S buffers in tensor memory), so a score tile is
+            // complete long before the softmax warps ask for it half a tile early
             uint32_t pc = 0;
-            issue_s(it);                                     // pass 2, software-pipelined by one tile
+            issue_s(it);
+            if (n_kt > 1) issue_s(it + 1);
             for (int j = 0; j < n_kt; ++j, ++it, ++pc) {
-                if (j + 1 < n_kt) issue_s(it + 1);
+                if (j + 2 < n_kt) issue_s(it + 2);
                 const int s = it % AT_STAGES, pb = pc & 1;
                 mbar_wait(&p_full[pb], (pc >> 1) & 1);
                 tc_fence_after();
@@ -185,7 +187,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
         tc_fence_after();
         tmem_ld32_issue(tlane, r0);
         for (int j = 0; j < n_kt; ++j, ++sc) {
-            const int b = sc & 1;
+            const int b = sc % AT_SBUF;
             const int nv = a.L - j * AT_BN - half * 64;      // this warp's columns of the tile that exist (may be <= 0)
             tmem_ld_wait();
             tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
@@ -196,9 +198,9 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the MMA warp may overwrite it
             {   // next tile (pass 2 re-reads tile 0 right after the last tile of pass 1)
                 const uint32_t sn = sc + 1;
-                mbar_wait(&s_full[sn & 1], (sn >> 1) & 1);
+                mbar_wait(&s_full[sn % AT_SBUF], (sn / AT_SBUF) & 1);
                 tc_fence_after();
-                tmem_ld32_issue(tlane + (sn & 1) * AT_BN, r0);
+                tmem_ld32_issue(tlane + (sn % AT_SBUF) * AT_BN, r0);
             }
             if (nv > 32) max_chunk(r1, nv - 32);
         }
@@ -231,7 +233,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
         };
         uint32_t pc = 0;
         for (int j = 0; j < n_kt; ++j, ++sc, ++pc) {
-            const int b = sc & 1, pb = pc & 1;
+            const int b = sc % AT_SBUF, pb = pc & 1;
             const int nv = a.L - j * AT_BN - half * 64;
             uint8_t* blk = smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES + half * AT_TILE_BYTES + row * 128;
             tmem_ld_wait();
@@ -244,9 +246,9 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             if (lane == 0) mbar_arrive(&s_empty[b]);
             if (j + 1 < n_kt) {
                 const uint32_t sn = sc + 1;
-                mbar_wait(&s_full[sn & 1], (sn >> 1) & 1);
+                mbar_wait(&s_full[sn % AT_SBUF], (sn / AT_SBUF) & 1);
                 tc_fence_after();
-                tmem_ld32_issue(tlane + (sn & 1) * AT_BN, r0);
+                tmem_ld32_issue(tlane + (sn % AT_SBUF) * AT_BN, r0);
             }
             prob_chunk(r1, nv - 32, blk, 4);
             fence_async_smem();
@@ -266,7 +268,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
         tc_fence_after();
         if (HD == 64 || half == 0) {
             h16* orow = a.o + ((size_t)img * a.L + grow) * (size_t)(a.heads * HD) + head * HD + (HD == 64 ? half * 32 : 0);
-            tmem_ld32_issue(tmem_base + ((uint32_t)(q * 32) << 16) + 256 + (HD == 64 ? half * 32 : 0), r0);
+            tmem_ld32_issue(tmem_o + ((uint32_t)(q * 32) << 16) + (HD == 64 ? half * 32 : 0), r0);
             tmem_ld_wait();
             if (grow < a.L) {
 #pragma unroll
@@ -466,9 +468,9 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
     uint64_t* k_full = bars;                       // [1]
     uint64_t* qd_full = bars + 1;                  // [STAGES]
     uint64_t* qd_empty = qd_full + BW_STAGES;      // [STAGES]
-    uint64_t* s_full = qd_empty + BW_STAGES;       // [2]
-    uint64_t* s_empty = s_full + 2;                // [2]
-    uint64_t* p_full = s_empty + 2;                // [2]
+    uint64_t* s_full = qd_empty + BW_STAGES;       // [3]
+    uint64_t* s_empty = s_full + AT_SBUF;          // [3]
+    uint64_t* p_full = s_empty + AT_SBUF;          // [2]
     uint64_t* p_empty = p_full + 2;                // [2]
     uint64_t* w_full = p_empty + 2;                // [1]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 1);
@@ -484,10 +486,8 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
         prefetch_tmap(&mapK); prefetch_tmap(&mapQ); prefetch_tmap(&mapD);
         mbar_init(k_full, 1);
         for (int s = 0; s < BW_STAGES; ++s) { mbar_init(&qd_full[s], 1); mbar_init(&qd_empty[s], 1); }
-        for (int b = 0; b < 2; ++b) {
-            mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], AT_SM_WARPS);
-            mbar_init(&p_full[b], AT_SM_WARPS); mbar_init(&p_empty[b], 1);
-        }
+        for (int b = 0; b < AT_SBUF; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], AT_SM_WARPS); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&p_full[b], AT_SM_WARPS); mbar_init(&p_empty[b], 1); }
         mbar_init(w_full, 1);
         mbar_fence_init();
     }
@@ -500,7 +500,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t tmem_w = tmem_base + 256;
+    const uint32_t tmem_w = tmem_base + AT_SBUF * AT_BN;
 
     if (warp == 0) {
         if (lane == 0) {
@@ -522,10 +522,10 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
             const uint64_t dk = make_smem_desc(smem_u32(smem + BwdSmem::KT));
             mbar_wait(k_full, 0);
             uint32_t sc = 0;
-            auto issue_s = [&](int it_) {          // S^T[sc & 1] = K Q^T for ring slot it_
-                const int s = it_ % BW_STAGES, b = sc & 1;
+            auto issue_s = [&](int it_) {          // S^T[sc % 3] = K Q^T for ring slot it_
+                const int s = it_ % BW_STAGES, b = sc % AT_SBUF;
                 mbar_wait(&qd_full[s], (it_ / BW_STAGES) & 1);
-                mbar_wait(&s_empty[b], ((sc >> 1) & 1) ^ 1);
+                mbar_wait(&s_empty[b], ((sc / AT_SBUF) & 1) ^ 1);
                 tc_fence_after();
                 const uint64_t dq = make_smem_desc(smem_u32(smem + BwdSmem::RING + s * BW_STAGE_BYTES));
 #pragma unroll
@@ -533,9 +533,10 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
                 umma_commit(&s_full[b]);
                 ++sc;
             };
-            issue_s(0);
+            issue_s(0);                             // scores run two tiles ahead of the P^T dO' product
+            if (n_qt > 1) issue_s(1);
             for (int it = 0; it < n_qt; ++it) {
-                if (it + 1 < n_qt) issue_s(it + 1);
+                if (it + 2 < n_qt) issue_s(it + 2);
                 const int s = it % BW_STAGES, pb = it & 1;
                 mbar_wait(&p_full[pb], (it >> 1) & 1);
                 tc_fence_after();
@@ -579,7 +580,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
         tc_fence_after();
         tmem_ld32_issue(tlane, r0);
         for (int it = 0; it < n_qt; ++it) {
-            const int b = it & 1, pb = it & 1;
+            const int b = it % AT_SBUF, pb = it & 1;
             const float* lse = lse_s + it * AT_BN + half * 64;
             uint8_t* blk = smem + BwdSmem::P + pb * 2 * AT_TILE_BYTES + half * AT_TILE_BYTES + row * 128;
             tmem_ld_wait();
@@ -591,9 +592,10 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
             __syncwarp();
             if (lane == 0) mbar_arrive(&s_empty[b]);
             if (it + 1 < n_qt) {
-                mbar_wait(&s_full[b ^ 1], ((it + 1) >> 1) & 1);
+                const int bn = (it + 1) % AT_SBUF;
+                mbar_wait(&s_full[bn], ((it + 1) / AT_SBUF) & 1);
                 tc_fence_after();
-                tmem_ld32_issue(tlane + (b ^ 1) * AT_BN, r0);
+                tmem_ld32_issue(tlane + bn * AT_BN, r0);
             }
             prob_chunk(r1, lse + 32, blk, 4);
             fence_async_smem();

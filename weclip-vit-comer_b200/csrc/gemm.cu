@@ -148,6 +148,38 @@ __device__ __forceinline__ void fast_qkv(const KernelArgs& a, const float* stg, 
     }
 }
 
+// GM_MUL_QGELU_GRAD fast path: out = acc * alpha * quickgelu'(u), u = saved pre-activation (fp16).  The 8 aux loads are issued
+// back to back before any use; sigmoid(1.702 u) = 0.5 + 0.5 tanh(0.851 u) costs one MUFU op.
+__device__ __forceinline__ void fast_qgelu_grad(const KernelArgs& a, const float* stg, int lane, int row0, int col0, int b0, int b1,
+                                                int bz) {
+    const GemmEpilogue& e = a.e;
+    const int cc = (lane & 7) * 4, rsub = lane >> 3, col = col0 + cc, r_first = row0 + rsub;
+    const int ab = e.aux_map ? e.aux_map[bz] : bz;
+    const h16* u = e.aux + (long)ab * e.aux_bs + (long)r_first * e.ldaux + col;
+    h16* o = reinterpret_cast<h16*>(e.out) + b0 * e.out_bs0 + b1 * e.out_bs1 + (long)r_first * e.ldo + col;
+    uint2 uu[8];
+    float4 x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        uu[i] = (r_first + 4 * i < a.M) ? *reinterpret_cast<const uint2*>(u + (long)(4 * i) * e.ldaux) : make_uint2(0u, 0u);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = *reinterpret_cast<const float4*>(stg + stg_off(i * 4 + rsub, lane & 7));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        if (r_first + 4 * i >= a.M) break;
+        const float2 f0 = __half22float2(*reinterpret_cast<const h16x2*>(&uu[i].x));
+        const float2 f1 = __half22float2(*reinterpret_cast<const h16x2*>(&uu[i].y));
+        const float uv[4] = {f0.x, f0.y, f1.x, f1.y};
+        float v[4] = {x[i].x, x[i].y, x[i].z, x[i].w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const float sg = fmaf(0.5f, tanh_approx(0.851f * uv[t]), 0.5f);
+            v[t] = v[t] * e.alpha * (sg * fmaf(1.702f * uv[t], 1.f - sg, 1.f));
+        }
+        store_h4(o + (long)(4 * i) * e.ldo, v);
+    }
+}
+
 // One 32-row x 32-column block of the accumulator owned by this warp (thread `lane` holds row row0+lane, r[j] = column
 // col0+j).  `stg` is the warp's private swizzled 32x32 fp32 staging block (stg_off).
 __device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, const uint32_t* r, float* stg, int lane, int row0,
@@ -207,6 +239,7 @@ __device__ __forceinline__ void epilogue_chunk(const KernelArgs& a, const uint32
     if (ncol == 32) {
         if (e.mode == GM_STORE && a.vec_ok && fast_store_dispatch(a, stg, lane, row0, col0, b0, b1)) { __syncwarp(); return; }
         if (e.mode == GM_QKV && e.L >= 4) { fast_qkv(a, stg, lane, row0, col0, which, head, d0); __syncwarp(); return; }
+        if (e.mode == GM_MUL_QGELU_GRAD && a.vec_ok) { fast_qgelu_grad(a, stg, lane, row0, col0, b0, b1, bz); __syncwarp(); return; }
     }
     const int cc = (lane & 7) * 4, rsub = lane >> 3;
     const int nv = min(4, ncol - cc);           // valid columns of this lane's group (<= 0: nothing)
@@ -337,12 +370,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        if (lane == 0) {
-            uint32_t it = 0;     // running k-block counter across tiles
-            for (int t = blockIdx.x; t < args.total_tiles; t += gridDim.x) {
-                const int mb = t % args.tiles_m, rest = t / args.tiles_m;
-                const int nb = rest % args.tiles_n, bz = rest / args.tiles_n;
-                const int b0 = bz % args.nb0, b1 = bz / args.nb0;
+        uint32_t it = 0;     // running k-block counter across tiles
+        for (int t = blockIdx.x; t < args.total_tiles; t += gridDim.x) {
+            const int mb = t % args.tiles_m, rest = t / args.tiles_m;
+            const int nb = rest % args.tiles_n, bz = rest / args.tiles_n;
+            const int b0 = bz % args.nb0, b1 = bz / args.nb0;
+            if (lane == 0) {
                 for (int kb = 0; kb < num_kb; ++kb, ++it) {
                     const int s = it % STAGES;
                     const uint32_t ph = (it / STAGES) & 1;

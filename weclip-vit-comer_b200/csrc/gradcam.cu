@@ -39,6 +39,11 @@ struct InstTable {
     short img[GC_MAX_INST];  // image of each instance
 };
 
+// image index of each instance of the chunk, as a device array (batch -> aux index of the GEMM epilogue)
+__global__ void inst_map_kernel(const __grid_constant__ InstTable it, int* __restrict__ map) {
+    if ((int)threadIdx.x < it.n) map[threadIdx.x] = it.img[threadIdx.x];
+}
+
 // ---------------------------------------------------------------------------------------------------
 // ln_post + column sums over the patch rows (clip/model.py:411-412).  msum[img][c] += sum_rows LN(x2)[row][c]
 // ---------------------------------------------------------------------------------------------------
@@ -413,6 +418,7 @@ struct GcLayout {
     // backward (per chunk of <= chunk instances)
     float *dx2, *da2, *colsum, *ds0, *p0;
     h16 *dx2b, *dh, *dx1b, *dO, *dOT;
+    int* inst_map;
 };
 
 static void gc_layout(Arena& ar, GcLayout& g, int N, int L, int total_inst, int chunk) {
@@ -431,6 +437,7 @@ static void gc_layout(Arena& ar, GcLayout& g, int N, int L, int total_inst, int 
     g.p0 = ar.get<float>((long)chunk * GC_HEADS * L);
     g.dx2b = ar.get<h16>(R * E); g.dh = ar.get<h16>(R * 4 * E); g.dx1b = ar.get<h16>(R * E); g.dO = ar.get<h16>(R * E);
     g.dOT = ar.get<h16>((long)chunk * GC_HEADS * 80 * Lp);
+    g.inst_map = ar.get<int>(GC_MAX_INST);
 }
 
 // instances per backward chunk: 16 (bounds the dP scratch), but never less than the largest image's class count
@@ -508,15 +515,16 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
         // ln_post backward (dy = dm broadcast over patch rows, class row zero)
         WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x2, w->ln_post_w, nullptr, g.dm, nullptr, g.dx2, g.dx2b, it, L, g.gscale));
         WC_LAUNCH_CHECK();
-        // c_proj^T and the QuickGELU derivative (model.py:198-203); per image because the saved pre-activation
-        // u_pre belongs to the image, shared by its classes
-        for (int i = img0; i < img1; ++i) {
-            const int li = k_off_host[i] - it.inst0, K = k_off_host[i + 1] - k_off_host[i];
-            GemmProblem p; p.M = L; p.N = 4 * E; p.K = E; p.nb0 = K;
-            p.A = GemmOperand{g.dx2b + (long)li * L * E, L, E, (long)L * E, 0};
+        // c_proj^T and the QuickGELU derivative (model.py:198-203): ONE launch batched over the chunk's instances; the saved
+        // pre-activation u_pre belongs to the image, so the epilogue maps instance -> image through inst_map
+        inst_map_kernel<<<1, GC_MAX_INST, 0, st>>>(it, g.inst_map);
+        WC_LAUNCH_CHECK();
+        {
+            GemmProblem p; p.M = L; p.N = 4 * E; p.K = E; p.nb0 = n_inst;
+            p.A = GemmOperand{g.dx2b, L, E, (long)L * E, 0};
             p.B = GemmOperand{reinterpret_cast<const h16*>(w->w_proj_t), 4 * E, E, 0, 0};
-            p.epi.mode = GM_MUL_QGELU_GRAD; p.epi.out = g.dh + (long)li * L * 4 * E; p.epi.ldo = 4 * E;
-            p.epi.out_bs0 = (long)L * 4 * E; p.epi.aux = g.upre + (long)i * L * 4 * E; p.epi.ldaux = 4 * E; p.epi.aux_bs = 0;
+            p.epi.mode = GM_MUL_QGELU_GRAD; p.epi.out = g.dh; p.epi.ldo = 4 * E; p.epi.out_bs0 = (long)L * 4 * E;
+            p.epi.aux = g.upre; p.epi.ldaux = 4 * E; p.epi.aux_bs = (long)L * 4 * E; p.epi.aux_map = g.inst_map;
             if ((rc = launch_gemm(p, st))) return rc;
         }
         {   // c_fc^T
