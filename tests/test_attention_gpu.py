@@ -56,3 +56,22 @@ def test_attention_peaked_rows_and_large_scores():
     assert torch.isfinite(o.float()).all() and torch.isfinite(avg).all()
     assert (o.float() - o_ref).abs().max().item() < 8e-3
     assert (avg - avg_ref).abs().max().item() < 5e-5
+
+
+@pytest.mark.parametrize("hd", [64, 32])
+def test_attention_growing_maximum_forces_accumulator_rescale(hd):
+    """The running maximum jumps by far more than 2^8 in later key tiles (and differently in the two 64-key halves of a
+    tile): the lazily rescaled accumulators must still give the exact softmax."""
+    torch.manual_seed(1)
+    N, heads, L = 1, 2, 700
+    q = torch.randn(N, heads, L, hd, device="cuda").half()
+    k = (torch.randn(N, heads, L, hd, device="cuda") * 0.5).half()
+    for pos, gain in ((130, 3.0), (200, 5.0), (333, 8.0), (480, 12.0), (650, 16.0)):
+        k[:, :, pos] *= gain
+    v = torch.randn(N, heads, L, hd, device="cuda").half()
+    o, avg = ops.attention_fwd(q, k, v, want_avg=(hd == 64))
+    o_ref, avg_ref = _ref(q, k, v)
+    assert torch.isfinite(o.float()).all()
+    assert (o.float() - o_ref).abs().max().item() < 8e-3
+    if avg is not None:
+        assert (avg - avg_ref).abs().max().item() < 5e-5

@@ -53,12 +53,20 @@ struct FwdSmem {
 
 // HD = head dim (64: CLIP blocks, 32: decoder blocks).  Q / K tiles are always [128][64] fp16 in shared memory: for HD = 32
 // the TMA box runs past the tensor's 32-element rows and the tail is zero-filled, and only HD/16 MMA k-steps are issued.
+//
+// ONE pass over the key tiles (online softmax).  Each softmax warp owns 32 query rows x one 64-key half of every tile and
+// keeps its OWN running maximum m (log2 domain) and row sum l; the two halves accumulate into two separate output
+// accumulators in tensor memory (O_A += P_A V_A, O_B += P_B V_B), so no per-tile exchange between warps is needed.  The
+// maximum is updated lazily: only when a tile's maximum exceeds the one in use by more than 2^8 does the warp rescale its own
+// rows of its accumulator (tcgen05.ld / st) — after the first tile this is rare — so P = exp2(S log2e - m) stays below 256 in
+// fp16.  The epilogue merges the halves: O = (c_A O_A + c_B O_B) / (c_A l_A + c_B l_B), c_h = 2^(m_h - max(m_A, m_B)).
 template <int HD>
 __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap mapQ,
                                                                   const __grid_constant__ CUtensorMap mapK,
                                                                   const __grid_constant__ CUtensorMap mapV,
                                                                   const __grid_constant__ AttnArgs a) {
     constexpr int V_BLK = HD * 128;                // one K-major [HD dims][64 keys] block of V^T
+    constexpr float RESCALE_THR = 8.f;             // log2 units
     extern __shared__ uint8_t at_smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~(uintptr_t)1023);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FwdSmem::BARS);
@@ -91,26 +99,21 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t tmem_o = tmem_base + AT_SBUF * AT_BN;
+    const uint32_t tmem_o = tmem_base + AT_SBUF * AT_BN;     // O_A at +0, O_B at +HD
 
     if (warp == 0) {
         if (lane == 0) {
             mbar_expect_tx(q_full, AT_TILE_BYTES);
             tma_load_4d(smem + FwdSmem::Q, &mapQ, q_full, 0, qt * AT_BM, bh, 0);
-            uint32_t it = 0;
-            for (int pass = 0; pass < 2; ++pass) {
-                for (int j = 0; j < n_kt; ++j, ++it) {
-                    const int s = it % AT_STAGES;
-                    mbar_wait(&kv_empty[s], ((it / AT_STAGES) & 1) ^ 1);
-                    uint8_t* sk = smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES;
-                    mbar_expect_tx(&kv_full[s], pass == 0 ? AT_TILE_BYTES : AT_TILE_BYTES + 2 * V_BLK);
-                    tma_load_4d(sk, &mapK, &kv_full[s], 0, j * AT_BN, bh, 0);
-                    if (pass == 1) {
-                        // V^T [HD dims][128 keys] as two K-major [HD][64] blocks (box = 64 keys x HD dims)
-                        tma_load_4d(sk + AT_TILE_BYTES, &mapV, &kv_full[s], j * AT_BN, 0, bh, 0);
-                        tma_load_4d(sk + AT_TILE_BYTES + V_BLK, &mapV, &kv_full[s], j * AT_BN + 64, 0, bh, 0);
-                    }
-                }
+            for (int j = 0; j < n_kt; ++j) {
+                const int s = j % AT_STAGES;
+                mbar_wait(&kv_empty[s], ((j / AT_STAGES) & 1) ^ 1);
+                uint8_t* sk = smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES;
+                mbar_expect_tx(&kv_full[s], AT_TILE_BYTES + 2 * V_BLK);
+                tma_load_4d(sk, &mapK, &kv_full[s], 0, j * AT_BN, bh, 0);
+                // V^T [HD dims][128 keys] as two K-major [HD][64] blocks (box = 64 keys x HD dims)
+                tma_load_4d(sk + AT_TILE_BYTES, &mapV, &kv_full[s], j * AT_BN, 0, bh, 0);
+                tma_load_4d(sk + AT_TILE_BYTES + V_BLK, &mapV, &kv_full[s], j * AT_BN + 64, 0, bh, 0);
             }
         }
     } else if (warp == 1) {
@@ -118,39 +121,31 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             constexpr uint32_t idesc_s = make_idesc(AT_BM, AT_BN), idesc_o = make_idesc(AT_BM, HD);
             const uint64_t dq = make_smem_desc(smem_u32(smem + FwdSmem::Q));
             mbar_wait(q_full, 0);
-            uint32_t it = 0, sc = 0;
-            auto issue_s = [&](uint32_t it_) {     // S[sc % 3] = Q K^T for ring slot it_
-                const int s = it_ % AT_STAGES, b = sc % AT_SBUF;
-                mbar_wait(&kv_full[s], (it_ / AT_STAGES) & 1);
-                mbar_wait(&s_empty[b], ((sc / AT_SBUF) & 1) ^ 1);
+            auto issue_s = [&](int j_) {           // S[j_ % 3] = Q K_j^T
+                const int s = j_ % AT_STAGES, b = j_ % AT_SBUF;
+                mbar_wait(&kv_full[s], (j_ / AT_STAGES) & 1);
+                mbar_wait(&s_empty[b], ((j_ / AT_SBUF) & 1) ^ 1);
                 tc_fence_after();
                 const uint64_t dk = make_smem_desc(smem_u32(smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES));
 #pragma unroll
                 for (int k = 0; k < HD / 16; ++k) umma_f16(tmem_base + b * AT_BN, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
                 umma_commit(&s_full[b]);
-                ++sc;
             };
-            for (int j = 0; j < n_kt; ++j, ++it) {          // pass 1: scores only
-                issue_s(it);
-                umma_commit(&kv_empty[it % AT_STAGES]);
-            }
-            // pass 2: the scores run TWO tiles ahead of the P V product (three S buffers in tensor memory), so a score tile is
-            // complete long before the softmax warps ask for it half a tile early
-            uint32_t pc = 0;
-            issue_s(it);
-            if (n_kt > 1) issue_s(it + 1);
-            for (int j = 0; j < n_kt; ++j, ++it, ++pc) {
-                if (j + 2 < n_kt) issue_s(it + 2);
-                const int s = it % AT_STAGES, pb = pc & 1;
-                mbar_wait(&p_full[pb], (pc >> 1) & 1);
+            // the scores run two tiles ahead of the P V products (three S buffers in tensor memory)
+            issue_s(0);
+            if (n_kt > 1) issue_s(1);
+            for (int j = 0; j < n_kt; ++j) {
+                if (j + 2 < n_kt) issue_s(j + 2);
+                const int s = j % AT_STAGES, pb = j & 1;
+                mbar_wait(&p_full[pb], (j >> 1) & 1);
                 tc_fence_after();
                 const uint32_t sp = smem_u32(smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES);
                 const uint32_t sv = smem_u32(smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES + AT_TILE_BYTES);
 #pragma unroll
-                for (int kb = 0; kb < 2; ++kb) {
+                for (int kb = 0; kb < 2; ++kb) {   // key half kb -> accumulator kb
                     const uint64_t dp = make_smem_desc(sp + kb * AT_TILE_BYTES), dv = make_smem_desc(sv + kb * V_BLK);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) umma_f16(tmem_o, dp + 2 * k, dv + 2 * k, idesc_o, (j | kb | k) != 0);
+                    for (int k = 0; k < 4; ++k) umma_f16(tmem_o + kb * HD, dp + 2 * k, dv + 2 * k, idesc_o, (j | k) != 0);
                 }
                 umma_commit(&p_empty[pb]);
                 umma_commit(&kv_empty[s]);
@@ -161,14 +156,14 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
         const int q = warp & 3;                              // TMEM lane quarter (hardware: warp id % 4)
         const int half = (warp - 2) >> 2;                    // which 64 key columns of every tile this warp owns
         const int row = q * 32 + lane, grow = qt * AT_BM + row;
-        const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16) + half * 64;
+        const uint32_t lanes = (uint32_t)(q * 32) << 16;
+        const uint32_t tlane = tmem_base + lanes + half * 64;
+        const uint32_t to = tmem_o + lanes + half * HD;      // this warp's rows of its own accumulator
         float* stat_m = reinterpret_cast<float*>(smem + FwdSmem::STATS);
         float* stat_l = stat_m + 256;
-        uint32_t sc = 0;
         uint32_t r0[32], r1[32];
-        // ---- pass 1: row max only (no MUFU work).  The two 32-column TMEM loads of a tile are software-pipelined against
-        //      the FMNMX work.
-        float m = -INFINITY;
+        float m_used = -INFINITY;                            // maximum in use, log2 domain
+        float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;        // row sum of P (relative to m_used)
         auto max_chunk = [&](const uint32_t (&r)[32], int nvc) {   // nvc: columns of this chunk that exist (>= 1)
             float c0 = -INFINITY, c1 = -INFINITY, c2 = -INFINITY, c3 = -INFINITY;
             if (nvc >= 32) {
@@ -181,44 +176,14 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
 #pragma unroll
                 for (int i = 0; i < 32; ++i) if (i < nvc) c0 = fmaxf(c0, __uint_as_float(r[i]));
             }
-            m = fmaxf(m, fmaxf(fmaxf(c0, c1), fmaxf(c2, c3)));
+            return fmaxf(fmaxf(c0, c1), fmaxf(c2, c3));
         };
-        mbar_wait(&s_full[0], 0);
-        tc_fence_after();
-        tmem_ld32_issue(tlane, r0);
-        for (int j = 0; j < n_kt; ++j, ++sc) {
-            const int b = sc % AT_SBUF;
-            const int nv = a.L - j * AT_BN - half * 64;      // this warp's columns of the tile that exist (may be <= 0)
-            tmem_ld_wait();
-            tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
-            if (nv > 0) max_chunk(r0, nv);
-            tmem_ld_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the MMA warp may overwrite it
-            {   // next tile (pass 2 re-reads tile 0 right after the last tile of pass 1)
-                const uint32_t sn = sc + 1;
-                mbar_wait(&s_full[sn % AT_SBUF], (sn / AT_SBUF) & 1);
-                tc_fence_after();
-                tmem_ld32_issue(tlane + (sn % AT_SBUF) * AT_BN, r0);
-            }
-            if (nv > 32) max_chunk(r1, nv - 32);
-        }
-        // combine the two column halves of each row (named barrier over the 256 softmax threads)
-        stat_m[half * 128 + row] = m;
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        m = fmaxf(m, stat_m[(half ^ 1) * 128 + row]);
-        const float m2 = m * AT_LOG2E;                       // log2 domain; key 0 always exists, so m is finite
-        // ---- pass 2: P = exp2(S*log2e - m2) in (0, 1], UN-normalised (one exp per score in the whole kernel), rounded to
-        //      fp16 into the K-major 128B-swizzled P tile; the row sum is accumulated in fp32 and divides O in the epilogue.
-        //      This warp's 64 columns are exactly one [128][64] swizzled block.  Chunk A of tile 0 is already in flight.
-        float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
         auto prob_chunk = [&](const uint32_t (&r)[32], int nvc, uint8_t* blk, int cc0) {
             uint32_t pk[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-                float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * i]), AT_LOG2E, -m2));
-                float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * i + 1]), AT_LOG2E, -m2));
+                float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * i]), AT_LOG2E, -m_used));
+                float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * i + 1]), AT_LOG2E, -m_used));
                 if (nvc < 32) {
                     if (2 * i >= nvc) p0 = 0.f;
                     if (2 * i + 1 >= nvc) p1 = 0.f;
@@ -231,53 +196,88 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             for (int t = 0; t < 4; ++t)
                 *reinterpret_cast<uint4*>(blk + (((cc0 + t) ^ (row & 7)) << 4)) = make_uint4(pk[4 * t], pk[4 * t + 1], pk[4 * t + 2], pk[4 * t + 3]);
         };
-        uint32_t pc = 0;
-        for (int j = 0; j < n_kt; ++j, ++sc, ++pc) {
-            const int b = sc % AT_SBUF, pb = pc & 1;
-            const int nv = a.L - j * AT_BN - half * 64;
+        mbar_wait(&s_full[0], 0);
+        tc_fence_after();
+        tmem_ld32_issue(tlane, r0);
+        for (int j = 0; j < n_kt; ++j) {
+            const int b = j % AT_SBUF, pb = j & 1;
+            const int nv = a.L - j * AT_BN - half * 64;      // this warp's columns of the tile that exist (may be <= 0)
             uint8_t* blk = smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES + half * AT_TILE_BYTES + row * 128;
             tmem_ld_wait();
             tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
-            mbar_wait(&p_empty[pb], ((pc >> 1) & 1) ^ 1);
-            prob_chunk(r0, nv, blk, 0);
+            float mx = nv > 0 ? max_chunk(r0, nv) : -INFINITY;
             tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&s_empty[b]);
+            if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the MMA warp may overwrite it
+            if (nv > 32) mx = fmaxf(mx, max_chunk(r1, nv - 32));
+            const float m_new = mx * AT_LOG2E;
+            const bool need = m_new > m_used + RESCALE_THR;   // first tile: m_used = -inf
+            if (__any_sync(0xffffffffu, need)) {
+                if (j > 0) {
+                    // rescale this warp's rows of its accumulator and its row sums: every P V product issued so far must have
+                    // finished (p_empty of tile j-1), and P V of tile j cannot start before this warp arrives on p_full
+                    const float f = need ? ex2_approx(m_used - m_new) : 1.f;
+                    mbar_wait(&p_empty[(j - 1) & 1], ((j - 1) >> 1) & 1);
+                    tc_fence_after();
+                    uint32_t t[32];
+#pragma unroll
+                    for (int c = 0; c < HD / 32; ++c) {
+                        tmem_ld32_issue(to + c * 32, t);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) t[i] = __float_as_uint(__uint_as_float(t[i]) * f);
+                        tmem_st32(to + c * 32, t);
+                    }
+                    tmem_st_wait();
+                    l0 *= f; l1 *= f; l2 *= f; l3 *= f;
+                }
+                if (need) m_used = m_new;
+            }
+            mbar_wait(&p_empty[pb], ((j >> 1) & 1) ^ 1);
+            prob_chunk(r0, nv, blk, 0);
             if (j + 1 < n_kt) {
-                const uint32_t sn = sc + 1;
-                mbar_wait(&s_full[sn % AT_SBUF], (sn / AT_SBUF) & 1);
+                const int bn = (j + 1) % AT_SBUF;
+                mbar_wait(&s_full[bn], ((j + 1) / AT_SBUF) & 1);
                 tc_fence_after();
-                tmem_ld32_issue(tlane + (sn % AT_SBUF) * AT_BN, r0);
+                tmem_ld32_issue(tlane + bn * AT_BN, r0);
             }
             prob_chunk(r1, nv - 32, blk, 4);
             fence_async_smem();
+            tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&p_full[pb]);
         }
-        // row sums of the two column halves -> 1 / l and the log2-domain log-sum-exp
-        float l = (l0 + l1) + (l2 + l3);
-        stat_l[half * 128 + row] = l;
+        // ---- merge the two key halves of each row (named barrier over the 256 softmax threads)
+        stat_m[half * 128 + row] = m_used;
+        stat_l[half * 128 + row] = (l0 + l1) + (l2 + l3);
         asm volatile("bar.sync 1, 256;" ::: "memory");
-        l += stat_l[(half ^ 1) * 128 + row];
+        const float mA = stat_m[row], mB = stat_m[128 + row];
+        const float m = fmaxf(mA, mB);                       // key 0 always exists: finite
+        const float cA = ex2_approx(mA - m), cB = ex2_approx(mB - m);
+        const float l = stat_l[row] * cA + stat_l[128 + row] * cB;
         const float inv_l = 1.f / l;
-        if (half == 0 && a.lse2 && grow < a.L) a.lse2[(size_t)bh * a.L + grow] = m2 + __log2f(l);
-        // ---- epilogue: O / l -> fp16, head-interleaved [N*L, heads*HD]; HD = 64: this warp's 32 of the 64 dims,
+        if (half == 0 && a.lse2 && grow < a.L) a.lse2[(size_t)bh * a.L + grow] = m + __log2f(l);
+        // ---- epilogue: (cA O_A + cB O_B) / l -> fp16, head-interleaved [N*L, heads*HD]; HD = 64: this warp's 32 of the 64 dims,
         //      HD = 32: the half-0 warps store the whole row
         mbar_wait(o_full, 0);
         tc_fence_after();
         if (HD == 64 || half == 0) {
-            h16* orow = a.o + ((size_t)img * a.L + grow) * (size_t)(a.heads * HD) + head * HD + (HD == 64 ? half * 32 : 0);
-            tmem_ld32_issue(tmem_o + ((uint32_t)(q * 32) << 16) + (HD == 64 ? half * 32 : 0), r0);
+            const int doff = (HD == 64) ? half * 32 : 0;
+            h16* orow = a.o + ((size_t)img * a.L + grow) * (size_t)(a.heads * HD) + head * HD + doff;
+            tmem_ld32_issue(tmem_o + lanes + doff, r0);
+            tmem_ld32_issue(tmem_o + HD + lanes + doff, r1);
             tmem_ld_wait();
+            const float fa = cA * inv_l, fb = cB * inv_l;
             if (grow < a.L) {
 #pragma unroll
                 for (int t = 0; t < 4; ++t) {
                     uint32_t w[4];
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        const h16x2 h = __floats2half2_rn(__uint_as_float(r0[8 * t + 2 * i]) * inv_l,
-                                                          __uint_as_float(r0[8 * t + 2 * i + 1]) * inv_l);
+                        const int e = 8 * t + 2 * i;
+                        const h16x2 h = __floats2half2_rn(fmaf(__uint_as_float(r0[e]), fa, __uint_as_float(r1[e]) * fb),
+                                                          fmaf(__uint_as_float(r0[e + 1]), fa, __uint_as_float(r1[e + 1]) * fb));
                         w[i] = *reinterpret_cast<const uint32_t*>(&h);
                     }
                     *reinterpret_cast<uint4*>(orow + t * 8) = make_uint4(w[0], w[1], w[2], w[3]);
