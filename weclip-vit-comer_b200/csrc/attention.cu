@@ -37,18 +37,21 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 
 struct AttnArgs {
     int L, heads, n_kt;
+    int n_qt, n_items;       // work items = (query tile, head, image), walked persistently: item w -> qt = w % n_qt, bh = w / n_qt
     h16* o;
     float* lse2;
 };
 
 // ---------------------------------------------------------------------------------------------------
 struct FwdSmem {
-    static constexpr int Q = 0;
-    static constexpr int RING = AT_TILE_BYTES;                               // stage s: K at +s*32K, V^T at +s*32K+16K
-    static constexpr int P = RING + AT_STAGES * 2 * AT_TILE_BYTES;           // two P buffers of 32 KB
+    static constexpr int V_STAGES = 3;
+    static constexpr int Q = 0;                                              // two Q tiles (this item / next item)
+    static constexpr int KRING = 2 * AT_TILE_BYTES;                          // AT_STAGES K tiles
+    static constexpr int VRING = KRING + AT_STAGES * AT_TILE_BYTES;          // V_STAGES V^T tiles
+    static constexpr int P = VRING + V_STAGES * AT_TILE_BYTES;               // two P buffers of 32 KB
     static constexpr int BARS = P + 2 * 2 * AT_TILE_BYTES;
-    static constexpr int STATS = BARS + 256;                                 // float [2 halves][128 rows] x {max, sum}
-    static constexpr int TOTAL = STATS + 2 * 128 * 8 + 1024;                 // + alignment slack
+    static constexpr int STATS = BARS + 512;                                 // [item parity][max | sum][2 halves][128 rows] floats
+    static constexpr int TOTAL = STATS + 2 * 2 * 256 * 4 + 1024;             // + alignment slack
 };
 
 // HD = head dim (64: CLIP blocks, 32: decoder blocks).  Q / K tiles are always [128][64] fp16 in shared memory: for HD = 32
@@ -66,32 +69,37 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                                                                   const __grid_constant__ CUtensorMap mapV,
                                                                   const __grid_constant__ AttnArgs a) {
     constexpr int V_BLK = HD * 128;                // one K-major [HD dims][64 keys] block of V^T
+    constexpr int VST = FwdSmem::V_STAGES;
     constexpr float RESCALE_THR = 8.f;             // log2 units
     extern __shared__ uint8_t at_smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~(uintptr_t)1023);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FwdSmem::BARS);
-    uint64_t* q_full = bars;                       // [1]
-    uint64_t* kv_full = bars + 1;                  // [STAGES]
-    uint64_t* kv_empty = kv_full + AT_STAGES;      // [STAGES]
-    uint64_t* s_full = kv_empty + AT_STAGES;       // [3]  S[b] computed            (MMA -> softmax)
+    uint64_t* q_full = bars;                       // [2]  Q of item i in buffer i & 1
+    uint64_t* q_empty = q_full + 2;                // [2]  every Q K^T of the item has run
+    uint64_t* k_full = q_empty + 2;                // [STAGES]  K ring: a slot is free again once its Q K^T has run
+    uint64_t* k_empty = k_full + AT_STAGES;        // [STAGES]
+    uint64_t* v_full = k_empty + AT_STAGES;        // [VST]     V ring: a slot is free again once its P V has run
+    uint64_t* v_empty = v_full + VST;              // [VST]
+    uint64_t* s_full = v_empty + VST;              // [3]  S[b] computed            (MMA -> softmax)
     uint64_t* s_empty = s_full + AT_SBUF;          // [3]  S[b] read into registers (softmax -> MMA)
     uint64_t* p_full = s_empty + AT_SBUF;          // [2]  P[b] written             (softmax -> MMA)
     uint64_t* p_empty = p_full + 2;                // [2]  P[b] consumed by P V     (MMA -> softmax)
-    uint64_t* o_full = p_empty + 2;                // [1]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+    uint64_t* o_full = p_empty + 2;                // [1]  the item's accumulators are complete (MMA -> softmax)
+    uint64_t* o_empty = o_full + 1;                // [1]  ... and have been read out             (softmax -> MMA)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int qt = blockIdx.x, head = blockIdx.y, img = blockIdx.z;
-    const int bh = img * a.heads + head;
     const int n_kt = a.n_kt;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&mapQ); prefetch_tmap(&mapK); prefetch_tmap(&mapV);
-        mbar_init(q_full, 1);
-        for (int s = 0; s < AT_STAGES; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&q_full[b], 1); mbar_init(&q_empty[b], 1); }
+        for (int s = 0; s < AT_STAGES; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); }
+        for (int s = 0; s < VST; ++s) { mbar_init(&v_full[s], 1); mbar_init(&v_empty[s], 1); }
         for (int b = 0; b < AT_SBUF; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], AT_SM_WARPS); }
         for (int b = 0; b < 2; ++b) { mbar_init(&p_full[b], AT_SM_WARPS); mbar_init(&p_empty[b], 1); }
         mbar_init(o_full, 1);
+        mbar_init(o_empty, AT_SM_WARPS);
         mbar_fence_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -101,69 +109,92 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t tmem_o = tmem_base + AT_SBUF * AT_BN;     // O_A at +0, O_B at +HD
 
+    // Persistent CTA: item i of this CTA is work item w = blockIdx.x + i * gridDim.x; consecutive w share (image, head), so the
+    // CTAs running at the same time read the same K / V from L2.  All ring / barrier indices run on the GLOBAL tile counter
+    // g = i * n_kt + j, so the loads, the score MMAs and the softmax of item i+1 start while item i drains (epilogue, output
+    // stores): the Q / K load latency, the TMEM allocation and the launch gap are paid once per CTA, not once per item.
     if (warp == 0) {
         if (lane == 0) {
-            mbar_expect_tx(q_full, AT_TILE_BYTES);
-            tma_load_4d(smem + FwdSmem::Q, &mapQ, q_full, 0, qt * AT_BM, bh, 0);
-            for (int j = 0; j < n_kt; ++j) {
-                const int s = j % AT_STAGES;
-                mbar_wait(&kv_empty[s], ((j / AT_STAGES) & 1) ^ 1);
-                uint8_t* sk = smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES;
-                mbar_expect_tx(&kv_full[s], AT_TILE_BYTES + 2 * V_BLK);
-                tma_load_4d(sk, &mapK, &kv_full[s], 0, j * AT_BN, bh, 0);
-                // V^T [HD dims][128 keys] as two K-major [HD][64] blocks (box = 64 keys x HD dims)
-                tma_load_4d(sk + AT_TILE_BYTES, &mapV, &kv_full[s], j * AT_BN, 0, bh, 0);
-                tma_load_4d(sk + AT_TILE_BYTES + V_BLK, &mapV, &kv_full[s], j * AT_BN + 64, 0, bh, 0);
+            int i = 0;
+            for (int w = blockIdx.x; w < a.n_items; w += gridDim.x, ++i) {
+                const int qt = w % a.n_qt, bh = w / a.n_qt, g0 = i * n_kt, qb = i & 1;
+                mbar_wait(&q_empty[qb], ((i >> 1) & 1) ^ 1);
+                mbar_expect_tx(&q_full[qb], AT_TILE_BYTES);
+                tma_load_4d(smem + FwdSmem::Q + qb * AT_TILE_BYTES, &mapQ, &q_full[qb], 0, qt * AT_BM, bh, 0);
+                // K and V^T travel in separate rings: a K slot is released by the score MMA (which runs two tiles ahead), a V
+                // slot by the P V MMA, so both kinds of load are requested three to four tiles before their use
+                auto load_v = [&](int j) {
+                    const int g = g0 + j, s = g % VST;
+                    mbar_wait(&v_empty[s], ((g / VST) & 1) ^ 1);
+                    uint8_t* sv = smem + FwdSmem::VRING + s * AT_TILE_BYTES;
+                    mbar_expect_tx(&v_full[s], 2 * V_BLK);
+                    // V^T [HD dims][128 keys] as two K-major [HD][64] blocks (box = 64 keys x HD dims)
+                    tma_load_4d(sv, &mapV, &v_full[s], j * AT_BN, 0, bh, 0);
+                    tma_load_4d(sv + V_BLK, &mapV, &v_full[s], j * AT_BN + 64, 0, bh, 0);
+                };
+                for (int j = 0; j < n_kt; ++j) {
+                    const int g = g0 + j, s = g % AT_STAGES;
+                    mbar_wait(&k_empty[s], ((g / AT_STAGES) & 1) ^ 1);
+                    mbar_expect_tx(&k_full[s], AT_TILE_BYTES);
+                    tma_load_4d(smem + FwdSmem::KRING + s * AT_TILE_BYTES, &mapK, &k_full[s], 0, j * AT_BN, bh, 0);
+                    if (j >= 2) load_v(j - 2);
+                }
+                for (int j = (n_kt >= 2 ? n_kt - 2 : 0); j < n_kt; ++j) load_v(j);
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc_s = make_idesc(AT_BM, AT_BN), idesc_o = make_idesc(AT_BM, HD);
-            const uint64_t dq = make_smem_desc(smem_u32(smem + FwdSmem::Q));
-            mbar_wait(q_full, 0);
-            auto issue_s = [&](int j_) {           // S[j_ % 3] = Q K_j^T
-                const int s = j_ % AT_STAGES, b = j_ % AT_SBUF;
-                mbar_wait(&kv_full[s], (j_ / AT_STAGES) & 1);
-                mbar_wait(&s_empty[b], ((j_ / AT_SBUF) & 1) ^ 1);
-                tc_fence_after();
-                const uint64_t dk = make_smem_desc(smem_u32(smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES));
+            int i = 0;
+            for (int w = blockIdx.x; w < a.n_items; w += gridDim.x, ++i) {
+                const int g0 = i * n_kt, qb = i & 1;
+                const uint64_t dq = make_smem_desc(smem_u32(smem + FwdSmem::Q + qb * AT_TILE_BYTES));
+                mbar_wait(&q_full[qb], (i >> 1) & 1);
+                auto issue_s = [&](int j_) {           // S[g % 3] = Q K_j^T
+                    const int g = g0 + j_, s = g % AT_STAGES, b = g % AT_SBUF;
+                    mbar_wait(&k_full[s], (g / AT_STAGES) & 1);
+                    mbar_wait(&s_empty[b], ((g / AT_SBUF) & 1) ^ 1);
+                    tc_fence_after();
+                    const uint64_t dk = make_smem_desc(smem_u32(smem + FwdSmem::KRING + s * AT_TILE_BYTES));
 #pragma unroll
-                for (int k = 0; k < HD / 16; ++k) umma_f16(tmem_base + b * AT_BN, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
-                umma_commit(&s_full[b]);
-            };
-            // the scores run two tiles ahead of the P V products (three S buffers in tensor memory)
-            issue_s(0);
-            if (n_kt > 1) issue_s(1);
-            for (int j = 0; j < n_kt; ++j) {
-                if (j + 2 < n_kt) issue_s(j + 2);
-                const int s = j % AT_STAGES, pb = j & 1;
-                mbar_wait(&p_full[pb], (j >> 1) & 1);
-                tc_fence_after();
-                const uint32_t sp = smem_u32(smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES);
-                const uint32_t sv = smem_u32(smem + FwdSmem::RING + s * 2 * AT_TILE_BYTES + AT_TILE_BYTES);
+                    for (int k = 0; k < HD / 16; ++k) umma_f16(tmem_base + b * AT_BN, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+                    umma_commit(&s_full[b]);
+                    umma_commit(&k_empty[s]);
+                    if (j_ == n_kt - 1) umma_commit(&q_empty[qb]);
+                };
+                // the scores run two tiles ahead of the P V products (three S buffers in tensor memory)
+                issue_s(0);
+                if (n_kt > 1) issue_s(1);
+                mbar_wait(o_empty, (i & 1) ^ 1);        // the previous item's accumulators have been read out
+                for (int j = 0; j < n_kt; ++j) {
+                    if (j + 2 < n_kt) issue_s(j + 2);
+                    const int g = g0 + j, s = g % VST, pb = g & 1;
+                    mbar_wait(&v_full[s], (g / VST) & 1);
+                    mbar_wait(&p_full[pb], (g >> 1) & 1);
+                    tc_fence_after();
+                    const uint32_t sp = smem_u32(smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES);
+                    const uint32_t sv = smem_u32(smem + FwdSmem::VRING + s * AT_TILE_BYTES);
 #pragma unroll
-                for (int kb = 0; kb < 2; ++kb) {   // key half kb -> accumulator kb
-                    const uint64_t dp = make_smem_desc(sp + kb * AT_TILE_BYTES), dv = make_smem_desc(sv + kb * V_BLK);
+                    for (int kb = 0; kb < 2; ++kb) {   // key half kb -> accumulator kb
+                        const uint64_t dp = make_smem_desc(sp + kb * AT_TILE_BYTES), dv = make_smem_desc(sv + kb * V_BLK);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) umma_f16(tmem_o + kb * HD, dp + 2 * k, dv + 2 * k, idesc_o, (j | k) != 0);
+                        for (int k = 0; k < 4; ++k) umma_f16(tmem_o + kb * HD, dp + 2 * k, dv + 2 * k, idesc_o, (j | k) != 0);
+                    }
+                    umma_commit(&p_empty[pb]);
+                    umma_commit(&v_empty[s]);
                 }
-                umma_commit(&p_empty[pb]);
-                umma_commit(&kv_empty[s]);
+                umma_commit(o_full);
             }
-            umma_commit(o_full);
         }
     } else {
         const int q = warp & 3;                              // TMEM lane quarter (hardware: warp id % 4)
         const int half = (warp - 2) >> 2;                    // which 64 key columns of every tile this warp owns
-        const int row = q * 32 + lane, grow = qt * AT_BM + row;
+        const int row = q * 32 + lane;
         const uint32_t lanes = (uint32_t)(q * 32) << 16;
         const uint32_t tlane = tmem_base + lanes + half * 64;
         const uint32_t to = tmem_o + lanes + half * HD;      // this warp's rows of its own accumulator
-        float* stat_m = reinterpret_cast<float*>(smem + FwdSmem::STATS);
-        float* stat_l = stat_m + 256;
         uint32_t r0[32], r1[32];
-        float m_used = -INFINITY;                            // maximum in use, log2 domain
-        float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;        // row sum of P (relative to m_used)
+        float m_used, l0, l1, l2, l3;                        // maximum in use (log2 domain), row sum of P relative to it
         auto max_chunk = [&](const uint32_t (&r)[32], int nvc) {   // nvc: columns of this chunk that exist (>= 1)
             float c0 = -INFINITY, c1 = -INFINITY, c2 = -INFINITY, c3 = -INFINITY;
             if (nvc >= 32) {
@@ -196,91 +227,113 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             for (int t = 0; t < 4; ++t)
                 *reinterpret_cast<uint4*>(blk + (((cc0 + t) ^ (row & 7)) << 4)) = make_uint4(pk[4 * t], pk[4 * t + 1], pk[4 * t + 2], pk[4 * t + 3]);
         };
-        mbar_wait(&s_full[0], 0);
-        tc_fence_after();
-        tmem_ld32_issue(tlane, r0);
-        for (int j = 0; j < n_kt; ++j) {
-            const int b = j % AT_SBUF, pb = j & 1;
-            const int nv = a.L - j * AT_BN - half * 64;      // this warp's columns of the tile that exist (may be <= 0)
-            uint8_t* blk = smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES + half * AT_TILE_BYTES + row * 128;
-            tmem_ld_wait();
-            tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
-            float mx = nv > 0 ? max_chunk(r0, nv) : -INFINITY;
-            tmem_ld_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the MMA warp may overwrite it
-            if (nv > 32) mx = fmaxf(mx, max_chunk(r1, nv - 32));
-            const float m_new = mx * AT_LOG2E;
-            const bool need = m_new > m_used + RESCALE_THR;   // first tile: m_used = -inf
-            if (__any_sync(0xffffffffu, need)) {
-                if (j > 0) {
-                    // rescale this warp's rows of its accumulator and its row sums: every P V product issued so far must have
-                    // finished (p_empty of tile j-1), and P V of tile j cannot start before this warp arrives on p_full
-                    const float f = need ? ex2_approx(m_used - m_new) : 1.f;
-                    mbar_wait(&p_empty[(j - 1) & 1], ((j - 1) >> 1) & 1);
-                    tc_fence_after();
-                    uint32_t t[32];
+        int it = 0;
+        for (int w = blockIdx.x; w < a.n_items; w += gridDim.x, ++it) {
+            const int qt = w % a.n_qt, bh = w / a.n_qt, head = bh % a.heads, img = bh / a.heads;
+            const int g0 = it * n_kt, grow = qt * AT_BM + row;
+            float* stat_m = reinterpret_cast<float*>(smem + FwdSmem::STATS) + (it & 1) * 512;
+            float* stat_l = stat_m + 256;
+            m_used = -INFINITY; l0 = l1 = l2 = l3 = 0.f;
+            mbar_wait(&s_full[g0 % AT_SBUF], (g0 / AT_SBUF) & 1);
+            tc_fence_after();
+            tmem_ld32_issue(tlane + (g0 % AT_SBUF) * AT_BN, r0);
+            tmem_ld32_issue(tlane + (g0 % AT_SBUF) * AT_BN + 32, r1);
+            for (int j = 0; j < n_kt; ++j) {
+                const int g = g0 + j, b = g % AT_SBUF, pb = g & 1;
+                const int nv = a.L - j * AT_BN - half * 64;      // this warp's columns of the tile that exist (may be <= 0)
+                uint8_t* blk = smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES + half * AT_TILE_BYTES + row * 128;
+                tmem_ld_wait();                                  // both halves were requested during the previous tile's exp work
+                const bool full = nv >= 64;                      // every tile but the last: no column masking (compile-time paths)
+                float mx = full ? max_chunk(r0, 32) : nv > 0 ? max_chunk(r0, nv) : -INFINITY;
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the MMA warp may overwrite it
+                if (full) mx = fmaxf(mx, max_chunk(r1, 32));
+                else if (nv > 32) mx = fmaxf(mx, max_chunk(r1, nv - 32));
+                const float m_new = mx * AT_LOG2E;
+                const bool need = m_new > m_used + RESCALE_THR;   // first tile: m_used = -inf
+                if (__any_sync(0xffffffffu, need)) {
+                    if (j > 0) {
+                        // rescale this warp's rows of its accumulator and its row sums: every P V product issued so far must
+                        // have finished (p_empty of tile g-1), and P V of tile g cannot start before this warp arrives on p_full
+                        const float f = need ? ex2_approx(m_used - m_new) : 1.f;
+                        mbar_wait(&p_empty[(g - 1) & 1], ((g - 1) >> 1) & 1);
+                        tc_fence_after();
+                        uint32_t t[32];
 #pragma unroll
-                    for (int c = 0; c < HD / 32; ++c) {
-                        tmem_ld32_issue(to + c * 32, t);
-                        tmem_ld_wait();
+                        for (int c = 0; c < HD / 32; ++c) {
+                            tmem_ld32_issue(to + c * 32, t);
+                            tmem_ld_wait();
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) t[i] = __float_as_uint(__uint_as_float(t[i]) * f);
-                        tmem_st32(to + c * 32, t);
+                            for (int e = 0; e < 32; ++e) t[e] = __float_as_uint(__uint_as_float(t[e]) * f);
+                            tmem_st32(to + c * 32, t);
+                        }
+                        tmem_st_wait();
+                        l0 *= f; l1 *= f; l2 *= f; l3 *= f;
                     }
-                    tmem_st_wait();
-                    l0 *= f; l1 *= f; l2 *= f; l3 *= f;
+                    if (need) m_used = m_new;
                 }
-                if (need) m_used = m_new;
-            }
-            mbar_wait(&p_empty[pb], ((j >> 1) & 1) ^ 1);
-            prob_chunk(r0, nv, blk, 0);
-            if (j + 1 < n_kt) {
-                const int bn = (j + 1) % AT_SBUF;
-                mbar_wait(&s_full[bn], ((j + 1) / AT_SBUF) & 1);
+                // both waits come before the exp work; the next tile's TMEM loads are issued as soon as r0 / r1 have been consumed
+                mbar_wait(&p_empty[pb], ((g >> 1) & 1) ^ 1);
+                const bool more = j + 1 < n_kt;
+                const int bn = (g + 1) % AT_SBUF;
+                if (more) mbar_wait(&s_full[bn], ((g + 1) / AT_SBUF) & 1);
                 tc_fence_after();
-                tmem_ld32_issue(tlane + bn * AT_BN, r0);
+                if (full) {
+                    prob_chunk(r0, 32, blk, 0);
+                    if (more) tmem_ld32_issue(tlane + bn * AT_BN, r0);
+                    prob_chunk(r1, 32, blk, 4);
+                } else {
+                    prob_chunk(r0, nv, blk, 0);
+                    if (more) tmem_ld32_issue(tlane + bn * AT_BN, r0);
+                    prob_chunk(r1, nv - 32, blk, 4);
+                }
+                if (more) tmem_ld32_issue(tlane + bn * AT_BN + 32, r1);
+                fence_async_smem();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&p_full[pb]);
             }
-            prob_chunk(r1, nv - 32, blk, 4);
-            fence_async_smem();
+            // ---- merge the two key halves of each row (named barrier over the 256 softmax threads; the statistics are
+            //      double-buffered by item parity, so the next item's writes cannot overtake this item's reads)
+            stat_m[half * 128 + row] = m_used;
+            stat_l[half * 128 + row] = (l0 + l1) + (l2 + l3);
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            const float mA = stat_m[row], mB = stat_m[128 + row];
+            const float m = fmaxf(mA, mB);                       // key 0 always exists: finite
+            const float cA = ex2_approx(mA - m), cB = ex2_approx(mB - m);
+            const float l = stat_l[row] * cA + stat_l[128 + row] * cB;
+            const float inv_l = 1.f / l;
+            if (half == 0 && a.lse2 && grow < a.L) a.lse2[(size_t)bh * a.L + grow] = m + __log2f(l);
+            // ---- epilogue: (cA O_A + cB O_B) / l -> fp16, head-interleaved [N*L, heads*HD]; HD = 64: this warp's 32 of the 64
+            //      dims, HD = 32: the half-0 warps store the whole row.  The accumulators are handed back to the MMA warp as soon
+            //      as they are in registers.
+            mbar_wait(o_full, it & 1);
+            tc_fence_after();
+            const bool storer = (HD == 64 || half == 0);
+            const int doff = (HD == 64) ? half * 32 : 0;
+            if (storer) {
+                tmem_ld32_issue(tmem_o + lanes + doff, r0);
+                tmem_ld32_issue(tmem_o + HD + lanes + doff, r1);
+                tmem_ld_wait();
+            }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&p_full[pb]);
-        }
-        // ---- merge the two key halves of each row (named barrier over the 256 softmax threads)
-        stat_m[half * 128 + row] = m_used;
-        stat_l[half * 128 + row] = (l0 + l1) + (l2 + l3);
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        const float mA = stat_m[row], mB = stat_m[128 + row];
-        const float m = fmaxf(mA, mB);                       // key 0 always exists: finite
-        const float cA = ex2_approx(mA - m), cB = ex2_approx(mB - m);
-        const float l = stat_l[row] * cA + stat_l[128 + row] * cB;
-        const float inv_l = 1.f / l;
-        if (half == 0 && a.lse2 && grow < a.L) a.lse2[(size_t)bh * a.L + grow] = m + __log2f(l);
-        // ---- epilogue: (cA O_A + cB O_B) / l -> fp16, head-interleaved [N*L, heads*HD]; HD = 64: this warp's 32 of the 64 dims,
-        //      HD = 32: the half-0 warps store the whole row
-        mbar_wait(o_full, 0);
-        tc_fence_after();
-        if (HD == 64 || half == 0) {
-            const int doff = (HD == 64) ? half * 32 : 0;
-            h16* orow = a.o + ((size_t)img * a.L + grow) * (size_t)(a.heads * HD) + head * HD + doff;
-            tmem_ld32_issue(tmem_o + lanes + doff, r0);
-            tmem_ld32_issue(tmem_o + HD + lanes + doff, r1);
-            tmem_ld_wait();
-            const float fa = cA * inv_l, fb = cB * inv_l;
-            if (grow < a.L) {
+            if (lane == 0) mbar_arrive(o_empty);
+            if (storer && grow < a.L) {
+                h16* orow = a.o + ((size_t)img * a.L + grow) * (size_t)(a.heads * HD) + head * HD + doff;
+                const float fa = cA * inv_l, fb = cB * inv_l;
 #pragma unroll
                 for (int t = 0; t < 4; ++t) {
-                    uint32_t w[4];
+                    uint32_t wv[4];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int e = 8 * t + 2 * i;
+                    for (int e4 = 0; e4 < 4; ++e4) {
+                        const int e = 8 * t + 2 * e4;
                         const h16x2 h = __floats2half2_rn(fmaf(__uint_as_float(r0[e]), fa, __uint_as_float(r1[e]) * fb),
                                                           fmaf(__uint_as_float(r0[e + 1]), fa, __uint_as_float(r1[e + 1]) * fb));
-                        w[i] = *reinterpret_cast<const uint32_t*>(&h);
+                        wv[e4] = *reinterpret_cast<const uint32_t*>(&h);
                     }
-                    *reinterpret_cast<uint4*>(orow + t * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+                    *reinterpret_cast<uint4*>(orow + t * 8) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
                 }
             }
         }
@@ -642,6 +695,16 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
 }
 
 // ---------------------------------------------------------------------------------------------------
+static int attn_num_sms() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+    }
+    return n;
+}
+
 static int attn_maps(const h16* q, const h16* k, const h16* vt, int nh, int L, int Lp, int hd, CUtensorMap* mq, CUtensorMap* mk,
                      CUtensorMap* mv) {
     int u0, u1, rc;
@@ -678,8 +741,12 @@ int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, floa
     int rc = attn_maps(q, k, vt, n_img * heads, L, Lp, hd, &mq, &mk, &mv);
     if (rc) return rc;
     // a batch of 1 collapses the map's batch dimension; the kernel's batch coordinate is then 0 anyway
-    AttnArgs a{L, heads, ceil_div(L, AT_BN), o, lse2};
-    dim3 grid(ceil_div(L, AT_BM), heads, n_img);
+    const int n_qt = ceil_div(L, AT_BM);
+    const long n_items = (long)n_qt * heads * n_img;
+    WC_CHECK_ARG(n_items < (1L << 30));
+    AttnArgs a{L, heads, ceil_div(L, AT_BN), n_qt, (int)n_items, o, lse2};
+    const int sms = attn_num_sms();
+    dim3 grid((unsigned)(n_items < sms ? n_items : sms));
     ProfScope prof(PK_ATTENTION, 4.0 * L * L * hd * heads * n_img, st);
     if (g_prof_on) prof_tag(L, n_img, heads, hd);
     return hd == 64 ? launch_fwd_hd<64>(mq, mk, mv, a, grid, st) : launch_fwd_hd<32>(mq, mk, mv, a, grid, st);
