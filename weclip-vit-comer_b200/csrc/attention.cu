@@ -491,14 +491,15 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __gr
 //   row log-sum-exps; masked queries carry lse = +inf)  ->  fp16 tile in shared memory  ->  W' += P^T dO' (tcgen05, N = 80)
 // and the epilogue contracts W'_j with V'_j.  Same warp roles and barriers as attn_fwd_kernel's second pass.
 constexpr int BW_ND = 80;                          // 64 head dims + delta hi / lo + padding to a legal MMA N
-constexpr int BW_STAGES = 3;
+constexpr int BW_QST = 4;                          // Q ring (released by the score MMA, which runs two tiles ahead)
+constexpr int BW_DST = 3;                          // dO'^T ring (released by the P^T dO' MMA)
 constexpr int BW_DBLK = BW_ND * 128;               // one K-major [80][64 queries] block of dO'^T (10 KB)
-constexpr int BW_STAGE_BYTES = AT_TILE_BYTES + 2 * BW_DBLK + 3072;     // 40 KB: keeps every stage 1024-byte aligned
 constexpr int BW_MAX_L = 2048;
 struct BwdSmem {
     static constexpr int KT = 0;
-    static constexpr int RING = AT_TILE_BYTES;
-    static constexpr int P = RING + BW_STAGES * BW_STAGE_BYTES;
+    static constexpr int QRING = AT_TILE_BYTES;
+    static constexpr int DRING = QRING + BW_QST * AT_TILE_BYTES;
+    static constexpr int P = DRING + BW_DST * 2 * BW_DBLK;
     static constexpr int LSE = P + 2 * 2 * AT_TILE_BYTES;
     static constexpr int BARS = LSE + BW_MAX_L * 4;
     static constexpr int TOTAL = BARS + 256 + 1024;
@@ -519,9 +520,11 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~(uintptr_t)1023);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BwdSmem::BARS);
     uint64_t* k_full = bars;                       // [1]
-    uint64_t* qd_full = bars + 1;                  // [STAGES]
-    uint64_t* qd_empty = qd_full + BW_STAGES;      // [STAGES]
-    uint64_t* s_full = qd_empty + BW_STAGES;       // [3]
+    uint64_t* q_full = bars + 1;                   // [BW_QST]
+    uint64_t* q_empty = q_full + BW_QST;           // [BW_QST]
+    uint64_t* d_full = q_empty + BW_QST;           // [BW_DST]
+    uint64_t* d_empty = d_full + BW_DST;           // [BW_DST]
+    uint64_t* s_full = d_empty + BW_DST;           // [3]
     uint64_t* s_empty = s_full + AT_SBUF;          // [3]
     uint64_t* p_full = s_empty + AT_SBUF;          // [2]
     uint64_t* p_empty = p_full + 2;                // [2]
@@ -538,7 +541,8 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&mapK); prefetch_tmap(&mapQ); prefetch_tmap(&mapD);
         mbar_init(k_full, 1);
-        for (int s = 0; s < BW_STAGES; ++s) { mbar_init(&qd_full[s], 1); mbar_init(&qd_empty[s], 1); }
+        for (int s = 0; s < BW_QST; ++s) { mbar_init(&q_full[s], 1); mbar_init(&q_empty[s], 1); }
+        for (int s = 0; s < BW_DST; ++s) { mbar_init(&d_full[s], 1); mbar_init(&d_empty[s], 1); }
         for (int b = 0; b < AT_SBUF; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], AT_SM_WARPS); }
         for (int b = 0; b < 2; ++b) { mbar_init(&p_full[b], AT_SM_WARPS); mbar_init(&p_empty[b], 1); }
         mbar_init(w_full, 1);
@@ -559,15 +563,23 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
         if (lane == 0) {
             mbar_expect_tx(k_full, AT_TILE_BYTES);
             tma_load_4d(smem + BwdSmem::KT, &mapK, k_full, 0, jt * AT_BM, bh, 0);
+            // separate rings for the two operands of a query tile: both are requested three to four tiles before their use
+            auto load_d = [&](int it) {
+                const int s = it % BW_DST;
+                mbar_wait(&d_empty[s], ((it / BW_DST) & 1) ^ 1);
+                uint8_t* sd = smem + BwdSmem::DRING + s * 2 * BW_DBLK;
+                mbar_expect_tx(&d_full[s], 2 * BW_DBLK);
+                tma_load_4d(sd, &mapD, &d_full[s], it * AT_BN, 0, ih, 0);
+                tma_load_4d(sd + BW_DBLK, &mapD, &d_full[s], it * AT_BN + 64, 0, ih, 0);
+            };
             for (int it = 0; it < n_qt; ++it) {
-                const int s = it % BW_STAGES;
-                mbar_wait(&qd_empty[s], ((it / BW_STAGES) & 1) ^ 1);
-                uint8_t* sq = smem + BwdSmem::RING + s * BW_STAGE_BYTES;
-                mbar_expect_tx(&qd_full[s], AT_TILE_BYTES + 2 * BW_DBLK);
-                tma_load_4d(sq, &mapQ, &qd_full[s], 0, it * AT_BN, bh, 0);
-                tma_load_4d(sq + AT_TILE_BYTES, &mapD, &qd_full[s], it * AT_BN, 0, ih, 0);
-                tma_load_4d(sq + AT_TILE_BYTES + BW_DBLK, &mapD, &qd_full[s], it * AT_BN + 64, 0, ih, 0);
+                const int s = it % BW_QST;
+                mbar_wait(&q_empty[s], ((it / BW_QST) & 1) ^ 1);
+                mbar_expect_tx(&q_full[s], AT_TILE_BYTES);
+                tma_load_4d(smem + BwdSmem::QRING + s * AT_TILE_BYTES, &mapQ, &q_full[s], 0, it * AT_BN, bh, 0);
+                if (it >= 2) load_d(it - 2);
             }
+            for (int it = (n_qt >= 2 ? n_qt - 2 : 0); it < n_qt; ++it) load_d(it);
         }
     } else if (warp == 1) {
         if (lane == 0) {
@@ -576,25 +588,27 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
             mbar_wait(k_full, 0);
             uint32_t sc = 0;
             auto issue_s = [&](int it_) {          // S^T[sc % 3] = K Q^T for ring slot it_
-                const int s = it_ % BW_STAGES, b = sc % AT_SBUF;
-                mbar_wait(&qd_full[s], (it_ / BW_STAGES) & 1);
+                const int s = it_ % BW_QST, b = sc % AT_SBUF;
+                mbar_wait(&q_full[s], (it_ / BW_QST) & 1);
                 mbar_wait(&s_empty[b], ((sc / AT_SBUF) & 1) ^ 1);
                 tc_fence_after();
-                const uint64_t dq = make_smem_desc(smem_u32(smem + BwdSmem::RING + s * BW_STAGE_BYTES));
+                const uint64_t dq = make_smem_desc(smem_u32(smem + BwdSmem::QRING + s * AT_TILE_BYTES));
 #pragma unroll
                 for (int k = 0; k < AT_HD / 16; ++k) umma_f16(tmem_base + b * AT_BN, dk + 2 * k, dq + 2 * k, idesc_s, k != 0);
                 umma_commit(&s_full[b]);
+                umma_commit(&q_empty[s]);
                 ++sc;
             };
             issue_s(0);                             // scores run two tiles ahead of the P^T dO' product
             if (n_qt > 1) issue_s(1);
             for (int it = 0; it < n_qt; ++it) {
                 if (it + 2 < n_qt) issue_s(it + 2);
-                const int s = it % BW_STAGES, pb = it & 1;
+                const int s = it % BW_DST, pb = it & 1;
+                mbar_wait(&d_full[s], (it / BW_DST) & 1);
                 mbar_wait(&p_full[pb], (it >> 1) & 1);
                 tc_fence_after();
                 const uint32_t sp = smem_u32(smem + BwdSmem::P + pb * 2 * AT_TILE_BYTES);
-                const uint32_t sd = smem_u32(smem + BwdSmem::RING + s * BW_STAGE_BYTES + AT_TILE_BYTES);
+                const uint32_t sd = smem_u32(smem + BwdSmem::DRING + s * 2 * BW_DBLK);
 #pragma unroll
                 for (int kb = 0; kb < 2; ++kb) {
                     const uint64_t dp = make_smem_desc(sp + kb * AT_TILE_BYTES), dd = make_smem_desc(sd + kb * BW_DBLK);
@@ -602,7 +616,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
                     for (int k = 0; k < 4; ++k) umma_f16(tmem_w, dp + 2 * k, dd + 2 * k, idesc_w, (it | kb | k) != 0);
                 }
                 umma_commit(&p_empty[pb]);
-                umma_commit(&qd_empty[s]);
+                umma_commit(&d_empty[s]);
             }
             umma_commit(w_full);
         }
@@ -632,26 +646,26 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_colsum_kernel(const __
         mbar_wait(&s_full[0], 0);
         tc_fence_after();
         tmem_ld32_issue(tlane, r0);
+        tmem_ld32_issue(tlane + 32, r1);
         for (int it = 0; it < n_qt; ++it) {
             const int b = it % AT_SBUF, pb = it & 1;
             const float* lse = lse_s + it * AT_BN + half * 64;
             uint8_t* blk = smem + BwdSmem::P + pb * 2 * AT_TILE_BYTES + half * AT_TILE_BYTES + row * 128;
-            tmem_ld_wait();
-            tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
-            mbar_wait(&p_empty[pb], ((it >> 1) & 1) ^ 1);
-            prob_chunk(r0, lse, blk, 0);
-            tmem_ld_wait();
+            tmem_ld_wait();                                  // both halves were requested during the previous tile's exp work
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&s_empty[b]);
-            if (it + 1 < n_qt) {
-                const int bn = (it + 1) % AT_SBUF;
-                mbar_wait(&s_full[bn], ((it + 1) / AT_SBUF) & 1);
-                tc_fence_after();
-                tmem_ld32_issue(tlane + bn * AT_BN, r0);
-            }
+            const bool more = it + 1 < n_qt;
+            const int bn = (it + 1) % AT_SBUF;
+            mbar_wait(&p_empty[pb], ((it >> 1) & 1) ^ 1);
+            if (more) mbar_wait(&s_full[bn], ((it + 1) / AT_SBUF) & 1);
+            tc_fence_after();
+            prob_chunk(r0, lse, blk, 0);
+            if (more) tmem_ld32_issue(tlane + bn * AT_BN, r0);
             prob_chunk(r1, lse + 32, blk, 4);
+            if (more) tmem_ld32_issue(tlane + bn * AT_BN + 32, r1);
             fence_async_smem();
+            tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&p_full[pb]);
         }
