@@ -144,12 +144,13 @@ typedef struct wc_decoder_weights {         /* SegFormerHead (segformer_head.py:
  *   img       fp32 [N,3,H,W]
  *   taps      h16 [11, N*L, 768]   block outputs F_0..F_10 (token-major, image-major rows; L = h*w+1)
  *   x_last    fp32 [N*L, 768]       F_10 in fp32 (input of block 12 / Grad-CAM)
- *   attn_avg  fp32 [n_attn(+slack), N, L, L]  head-averaged attention (myAtt.py:323-326) of the LAST n_attn
- *             encoder blocks, oldest first; may be NULL when n_attn == 0
+ *   attn_avg  fp32 [n_attn(+slack), attn_imgs, L, L]  head-averaged attention (myAtt.py:323-326) of the LAST n_attn
+ *             encoder blocks, oldest first, for the first attn_imgs images of the batch (0 = all N): the CAM path only
+ *             runs for the images that have a name (model_attn_aff_voc.py:139); may be NULL when n_attn == 0
  * ---------------------------------------------------------------------------------------------- */
 size_t wc_encoder_workspace_bytes(int N, int H, int W);
 int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, int H, int W, void* taps, float* x_last,
-                   float* attn_avg, int n_attn, void* workspace, size_t workspace_bytes, void* stream);
+                   float* attn_avg, int n_attn, int attn_imgs, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Decoder: 11 per-layer MLPs + concat + linear_fuse (segformer_head.py:69-80), attn_pred = sigmoid(F^T F)
  * (model_attn_aff_voc.py:134-137), 3 transformer blocks + linear_pred (TransDecoder.py:113-125).

@@ -360,7 +360,9 @@ def weclip_forward(img: Tensor, label_maps: Sequence[np.ndarray], sd: Dict[str, 
                    bg_text: Tensor, mode: str = "val", iter_num: int = 1, dataset: str = "voc",
                    mimic_fp16: bool = True, return_intermediates: bool = False, box_masks=None):
     """WeCLIP_model/model_attn_aff_voc.py:107-175 (COCO twin model_attn_aff_coco.py:100-170) with
-    clip/clip_tool.py:106-197 inlined.  ``label_maps[i]`` is the decoded label PNG of image i.
+    clip/clip_tool.py:106-197 inlined.  ``label_maps[i]`` is the decoded label PNG of image i; like the reference's
+    ``for i, img_name in enumerate(img_names)`` (:139) the CAM / PAR path runs for the first len(label_maps) images only
+    (the msc+flip driver passes ONE name for its [image, flipped image] batch).
     Returns (seg [N,C,h,w], cam_labels [N,Hc,Wc] int64 | None, attn_pred [N,P,P])."""
     N, _, H, W = img.shape
     h, w = H // 16, W // 16
@@ -376,7 +378,7 @@ def weclip_forward(img: Tensor, label_maps: Sequence[np.ndarray], sd: Dict[str, 
     attn_stack = torch.stack(attns, dim=0).permute(1, 0, 2, 3)   # [N,11,L,L]
     labels_out = []
     inter.update(cams=[], cams_refined=[], cams_up=[], trans_mat=[], keys=[], par_in=[])
-    for i in range(N):
+    for i in range(len(label_maps)):
         ids = label_ids_from_map(label_maps[i])
         ori_h, ori_w = label_maps[i].shape[:2]
         text = torch.cat([fg_text[ids], bg_text], dim=0)
@@ -427,7 +429,7 @@ def msc_flip_image(img: Tensor, label_map: np.ndarray, sd, fg_text, bg_text, sca
     ratio = resize_long / max(h0, w0)
     inputs = F.interpolate(img, size=(int(h0 * ratio), int(w0 * ratio)), mode="bilinear", align_corners=False)
     cat = torch.cat([inputs, inputs.flip(-1)], dim=0)
-    segs_cat, cam, _ = weclip_forward(cat, [label_map, label_map], sd, fg_text, bg_text, "val", 1, dataset, mimic_fp16)
+    segs_cat, cam, _ = weclip_forward(cat, [label_map], sd, fg_text, bg_text, "val", 1, dataset, mimic_fp16)
     segs = segs_cat[0:1]
     segs_list = [(segs_cat[0] + segs_cat[1].flip(-1)) / 2]
     h, w = segs_cat.shape[-2:]
@@ -435,7 +437,7 @@ def msc_flip_image(img: Tensor, label_map: np.ndarray, sd, fg_text, bg_text, sca
         if s != 1.0:
             _in = F.interpolate(inputs, scale_factor=s, mode="bilinear", align_corners=False)
             cat = torch.cat([_in, _in.flip(-1)], dim=0)
-            sc, _, _ = weclip_forward(cat, [label_map, label_map], sd, fg_text, bg_text, "val", 1, dataset, mimic_fp16)
+            sc, _, _ = weclip_forward(cat, [label_map], sd, fg_text, bg_text, "val", 1, dataset, mimic_fp16)
             sc = F.interpolate(sc, size=(h, w), mode="bilinear", align_corners=False)
             segs_list.append((sc[0] + sc[1].flip(-1)) / 2)
     msc = torch.mean(torch.stack(segs_list, dim=0), dim=0).unsqueeze(0)

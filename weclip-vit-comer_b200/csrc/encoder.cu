@@ -28,7 +28,7 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
         if (b.attn_avg && (hd != 64 || !b.lse))
             return fail(WC_ERR_UNSUPPORTED, "%s: the head-mean map needs head_dim 64 and an lse buffer", __func__);
         if ((rc = launch_attention_fwd(b.q, b.k, b.vt, b.o, b.lse, n_img, heads, L, (int)Lp, hd, st))) return rc;
-        if (b.attn_avg && (rc = launch_attn_headmean(b.q, b.k, b.lse, b.attn_avg, n_img, heads, L, st))) return rc;
+        if (b.attn_avg && (rc = launch_attn_headmean(b.q, b.k, b.lse, b.attn_avg, b.attn_imgs > 0 ? b.attn_imgs : n_img, heads, L, st))) return rc;
     } else {
         // S = q k^T (myAtt.py:56), fp32 [N*heads, L, Lp]
         {
@@ -123,9 +123,10 @@ extern "C" size_t wc_encoder_workspace_bytes(int N, int H, int W) {
 }
 
 extern "C" int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, int H, int W, void* taps_, float* x_last,
-                              float* attn_avg, int n_attn, void* workspace, size_t workspace_bytes, void* stream) {
+                              float* attn_avg, int n_attn, int attn_imgs, void* workspace, size_t workspace_bytes, void* stream) {
     WC_CHECK_ARG(w && img && taps_ && x_last && workspace && N > 0 && H >= 16 && W >= 16);
-    WC_CHECK_ARG(n_attn >= 0 && n_attn <= 11 && (n_attn == 0 || attn_avg));
+    WC_CHECK_ARG(n_attn >= 0 && n_attn <= 11 && (n_attn == 0 || attn_avg) && attn_imgs >= 0 && attn_imgs <= N);
+    if (attn_imgs == 0) attn_imgs = N;
     cudaStream_t st = as_stream(stream);
     const int h = H / 16, wd = W / 16, P = h * wd, L = P + 1, E = 768;
     const long M = (long)N * L;
@@ -153,7 +154,8 @@ extern "C" int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, 
         b.x_in = x; b.x_mid = x; b.x_out = (i == 10) ? x_last : x;
         b.a = s.a; b.q = s.q; b.k = s.k; b.vt = s.vt; b.S = s.S; b.P = s.P; b.lse = s.lse; b.o = s.o; b.u = s.u;
         const int slot = i - (11 - n_attn);
-        b.attn_avg = (slot >= 0) ? attn_avg + (size_t)slot * N * L * L : nullptr;
+        b.attn_avg = (slot >= 0) ? attn_avg + (size_t)slot * attn_imgs * L * L : nullptr;
+        b.attn_imgs = attn_imgs;
         b.tap = taps + (size_t)i * M * E;
         if ((rc = run_block(w->blocks[i], b, N, L, E, 12, st))) return rc;
     }

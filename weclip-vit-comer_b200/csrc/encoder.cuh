@@ -34,6 +34,7 @@ struct BlockBuffers {
     h16* v;            // optional [N*heads, L, hd]
     float* S;           // [N*heads, L, Lp]   materialised scores (unfused path only)
     h16* P;            // [N*heads, L, Lp]   materialised probabilities (unfused path only; Grad-CAM's backward reads them)
+    int attn_imgs = 0;  // images (a prefix of the batch) whose head-mean map is wanted; 0 = all
     float* lse;         // [N*heads, L]       fused path (S == nullptr, head_dim 64): log2-domain row log-sum-exp
     h16* o;            // [M,E]
     h16* u;            // [M,4E]  QuickGELU(c_fc)

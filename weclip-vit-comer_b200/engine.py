@@ -115,9 +115,11 @@ class Engine:
         return ws
 
     # ------------------------------------------------------------------ calls
-    def encoder(self, img: torch.Tensor, n_attn: int = 0, attn_slots: Optional[int] = None):
-        """clip_tool.py:31-41 generate_clip_fts.  Returns (taps bf16 [11,N*L,768], x_last fp32 [N*L,768],
-        attn fp32 [attn_slots or n_attn, N, L, L] with the last n_attn encoder maps in slots 0..n_attn-1)."""
+    def encoder(self, img: torch.Tensor, n_attn: int = 0, attn_slots: Optional[int] = None,
+                attn_imgs: Optional[int] = None):
+        """clip_tool.py:31-41 generate_clip_fts.  Returns (taps fp16 [11,N*L,768], x_last fp32 [N*L,768],
+        attn fp32 [attn_slots or n_attn, attn_imgs or N, L, L] with the last n_attn encoder maps in slots
+        0..n_attn-1; attn_imgs = the leading images whose maps the CAM path will read)."""
         L = _lib.lib()
         img = img.contiguous().float()
         N, _, H, W = img.shape
@@ -126,10 +128,11 @@ class Engine:
         taps = torch.empty(N_TAPS, N * Lt, E_VIT, dtype=torch.float16, device=self.device)
         x_last = torch.empty(N * Lt, E_VIT, dtype=torch.float32, device=self.device)
         slots = attn_slots if attn_slots is not None else n_attn
-        attn = torch.empty(max(slots, 1), N, Lt, Lt, dtype=torch.float32, device=self.device) if slots else None
+        n_ai = N if attn_imgs is None else int(attn_imgs)
+        attn = torch.empty(max(slots, 1), n_ai, Lt, Lt, dtype=torch.float32, device=self.device) if slots else None
         ws = self._workspace("enc", L.wc_encoder_workspace_bytes(N, H, W))
         rc = L.wc_encoder_fwd(byref(self.vit), _lib.ptr(img), N, H, W, _lib.ptr(taps), _lib.ptr(x_last),
-                              _lib.ptr(attn), n_attn, _lib.ptr(ws), c_size_t(ws.numel()), _lib.stream_ptr())
+                              _lib.ptr(attn), n_attn, n_ai, _lib.ptr(ws), c_size_t(ws.numel()), _lib.stream_ptr())
         _lib.check(rc, "wc_encoder_fwd")
         return taps, x_last, attn
 

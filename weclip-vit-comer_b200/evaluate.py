@@ -62,18 +62,19 @@ class MscFlipEvaluator:
         so a (H,W) bucket is run as one [2B,3,H,W] forward per scale: B plain images followed by their B flipped
         twins).  inputs fp32 [B,3,H0,W0]; labels int16 [B,Hl,Wl]."""
         B = inputs.shape[0]
-        names2 = list(names) + list(names)
+        names = list(names)      # B names for 2B images: the CAM / PAR path runs for the B plain images only, exactly as the
+                                 # reference's one-name call does for its [image, flip] pair (model_attn_aff_voc.py:139)
         _, _, h0, w0 = inputs.shape
         ratio = self.resize_long / max(h0, w0)
         base = ops.resize_bilinear(inputs, size=(int(h0 * ratio), int(w0 * ratio)))          # :60-63
-        segs_cat, cam, _ = self.model(ops.flip_concat(base), names2, mode="val")             # :68-69
+        segs_cat, cam, _ = self.model(ops.flip_concat(base), names, mode="val")             # :68-69
         C, h, w = segs_cat.shape[1:]
         n_scales = 1 + sum(1 for s in self.scales if s != 1.0)
         msc = torch.empty(B, C, h, w, dtype=torch.float32, device=self.device)
         ops.msc_accumulate(segs_cat, msc, 1.0 / n_scales, True)                              # :74
         for s in self.scales:                                                                # :79-88
             if s != 1.0:
-                sc, _, _ = self.model(ops.flip_concat(ops.resize_bilinear(base, scale_factor=s)), names2, mode="val")
+                sc, _, _ = self.model(ops.flip_concat(ops.resize_bilinear(base, scale_factor=s)), names, mode="val")
                 ops.msc_accumulate(sc, msc, 1.0 / n_scales, False)
         size = labels.shape[-2:]
         labels = labels.contiguous()

@@ -135,10 +135,20 @@ class WeCLIP(nn.Module):
         cam_path = not (self.dataset == "coco" and mode == "val")     # model_attn_aff_coco.py:131-132
         require_seg_trans = self.iter_num > cfg["switch"] or mode == "val"
         nl = cfg["window"] if require_seg_trans else 8                 # clip_tool.py:155 / :173
-        taps, x_last, attn = eng.encoder(img, n_attn=(nl - 1) if cam_path else 0, attn_slots=nl if cam_path else 0)
+        # the CAM / PAR path runs once per NAME (model_attn_aff_voc.py:139 `for i, img_name in enumerate(img_names)`): the
+        # msc+flip driver passes one name for an [image, flipped image] batch, so only the leading images get pseudo-labels
+        if isinstance(img_names, str):
+            img_names = [img_names]
+        n_cam = len(img_names)
+        if n_cam > N:
+            raise IndexError("index %d is out of bounds for dimension 0 with size %d" % (N, N))   # img[i], reference :141
+        cam_path = cam_path and n_cam > 0
+        taps, x_last, attn = eng.encoder(img, n_attn=(nl - 1) if cam_path else 0, attn_slots=nl if cam_path else 0,
+                                         attn_imgs=n_cam if cam_path else None)
         seg, attn_pred, _ = eng.decoder(taps, N, h, w)
         if not cam_path:
             return seg, None, attn_pred
+        N_all, N = N, n_cam
 
         ids_all, sizes, text_off, k_off, rows = [], [], [0], [0], []
         fg = self.fg_text_features.to(eng.device, torch.float32)
@@ -150,7 +160,6 @@ class WeCLIP(nn.Module):
             rows += [fg[ids], bg]
             text_off.append(text_off[-1] + len(ids) + bg.shape[0])
             k_off.append(k_off[-1] + len(ids))
-        assert len(ids_all) == N, "one name per image"
         if any(len(i) == 0 for i in ids_all):
             raise RuntimeError("image without foreground label (torch.stack([]) in the reference, clip_tool.py:212)")
         text = torch.cat(rows, dim=0)
@@ -164,7 +173,7 @@ class WeCLIP(nn.Module):
         Hc, Wc = sizes[0]
         par_in = eng.cam_upsample_bg(refined, k_off, N, h, w, Hc, Wc, float(self.cam_bg_thres))
         ch_off = [k_off[i] + i for i in range(N + 1)]
-        par_out = self.par.refine_ragged(img, par_in, ch_off)
+        par_out = self.par.refine_ragged(img[:N], par_in, ch_off)
         lut = torch.tensor([v for ids in ids_all for v in [0] + [i + 1 for i in ids]], dtype=torch.int64)
         labels = argmax_lut(par_out, lut, ch_off)
         return seg, labels, attn_pred
