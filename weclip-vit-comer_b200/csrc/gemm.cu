@@ -16,6 +16,7 @@
 #include "tc_ptx.cuh"
 
 #include <cudaTypedefs.h>
+#include <stdlib.h>
 #include <mutex>
 #include <unordered_map>
 
@@ -456,6 +457,152 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 }
 
 // ---------------------------------------------------------------------------------------------------
+// CTA-pair variant (cta_group::2): the two CTAs of a (2,1,1) cluster share one 256 x 256 output tile.  Each CTA stages its own
+// 128 rows of A and HALF of the B tile (128 of the 256 n-rows); CTA 0 issues tcgen05.mma.cta_group::2 (M = 256), which reads A
+// and B from both CTAs' shared memory and writes each CTA's 128 accumulator rows into that CTA's tensor memory.  Per CTA and
+// k-block this halves the B bytes written by TMA and read by the tensor core (64 KB -> 32 KB of shared-memory traffic per 128
+// MMA cycles), which is what caps the single-CTA 128 x 256 kernel near 57 % of the tensor peak.  Ring: 6 stages of 32 KB.
+//   full_bar   (CTA 0's only)  both CTAs' TMA loads count their bytes on it
+//   empty_bar  (each CTA's)    multicast tcgen05.commit: the stage may be overwritten in both CTAs
+//   tfull_bar  (each CTA's)    multicast commit after a tile's last k-block: each CTA's epilogue drains its own 128 rows
+//   tempty_bar (CTA 0's only)  16 arrivals: the 8 epilogue warps of CTA 0 and, remotely, the 8 of CTA 1
+// ---------------------------------------------------------------------------------------------------
+struct Cfg2 {
+    static constexpr int BN = 256;
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = (BN / 2) * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = RING_BYTES / STAGE_BYTES;
+    static constexpr int STG_BYTES = EPI_WARPS * 32 * 32 * 4;
+    static constexpr int TMEM_COLS = 2 * BN;
+    static constexpr int TOTAL = STAGES * STAGE_BYTES + STG_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+                const __grid_constant__ KernelArgs args) {
+    using C = Cfg2;
+    constexpr int STAGES = C::STAGES, BN = C::BN;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    float* stg_all = reinterpret_cast<float*>(smem + STAGES * C::STAGE_BYTES);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES + C::STG_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tfull_bar = empty_bar + STAGES;
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+    const int num_kb = (args.K + BK - 1) / BK;
+    const int tiles_m2 = (args.tiles_m + 1) >> 1;
+    const int total = tiles_m2 * args.tiles_n * (args.total_tiles / (args.tiles_m * args.tiles_n));
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&mapA);
+        prefetch_tmap(&mapB);
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], 2 * EPI_WARPS); }
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc_pair(tmem_slot, C::TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();          // the peer's barriers exist before any remote arrive / TMA byte count can reach them
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int t = pair; t < total; t += npairs) {
+                const int m2 = t % tiles_m2, rest = t / tiles_m2;
+                const int nb = rest % args.tiles_n, bz = rest / args.tiles_n;
+                const int b0 = bz % args.nb0, b1 = bz / args.nb0;
+                const int mb = m2 * 2 + (int)rank;          // may be one past the last m-block: TMA zero-fills, epilogue skips
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    if (rank == 0) mbar_expect_tx(&full_bar[s], 2 * C::STAGE_BYTES);
+                    uint8_t* sa = smem + s * C::STAGE_BYTES;
+                    const uint32_t fb = mapa_u32(&full_bar[s], 0);
+                    tma_load_4d_pair(sa, &mapA, fb, kb * BK, mb * BM, b0 * args.a_b0, b1 * args.a_b1);
+                    tma_load_4d_pair(sa + C::A_BYTES, &mapB, fb, kb * BK, nb * BN + (int)rank * (BN / 2), b0 * args.b_b0,
+                                     b1 * args.b_b1);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = make_idesc(2 * BM, BN);
+            uint32_t it = 0, tl = 0;
+            for (int t = pair; t < total; t += npairs, ++tl) {
+                const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
+                mbar_wait(&tempty_bar[as], aph ^ 1);            // both CTAs' epilogues have drained this accumulator
+                tc_fence_after();
+                const uint32_t tacc = tmem_base + as * BN;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait(&full_bar[s], ph);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + s * C::STAGE_BYTES);
+                    const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + C::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) umma_f16_pair(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                    umma_commit_pair(&empty_bar[s]);
+                }
+                umma_commit_pair(&tfull_bar[as]);
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
+        constexpr int NCH = BN / 64;
+        const int c_begin = half * NCH;
+        float* stg = stg_all + (warp - 2) * 32 * 32;
+        const uint32_t tempty_remote0 = mapa_u32(&tempty_bar[0], 0), tempty_remote1 = mapa_u32(&tempty_bar[1], 0);
+        uint32_t tl = 0;
+        for (int t = pair; t < total; t += npairs, ++tl) {
+            const int m2 = t % tiles_m2, rest = t / tiles_m2;
+            const int nb = rest % args.tiles_n, bz = rest / args.tiles_n;
+            const int b0 = bz % args.nb0, b1 = bz / args.nb0;
+            const int mb = m2 * 2 + (int)rank;
+            const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
+            mbar_wait(&tfull_bar[as], aph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + as * BN + c_begin * 32 + ((uint32_t)(q * 32) << 16);
+            const int row0 = mb * BM + q * 32;
+            if (row0 < args.M && nb * BN + c_begin * 32 < args.N) {
+                uint32_t r[2][32];
+                tmem_ld32_issue(taddr, r[0]);
+#pragma unroll
+                for (int c = 0; c < NCH; ++c) {
+                    const int col0 = nb * BN + (c_begin + c) * 32;
+                    if (col0 >= args.N) break;          // warp-uniform
+                    tmem_ld_wait();
+                    if (c + 1 < NCH && col0 + 32 < args.N) tmem_ld32_issue(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+                    epilogue_chunk(args, r[c & 1], stg, lane, row0, col0, b0, b1, bz);
+                }
+                tmem_ld_wait();
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(as ? tempty_remote1 : tempty_remote0);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();          // neither CTA leaves (or frees tensor memory) while the other may still touch it
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, C::TMEM_COLS);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
 // Host side: tensor maps (driver entry point resolved at run time: no link against libcuda) + launch
 // ---------------------------------------------------------------------------------------------------
 static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
@@ -575,6 +722,38 @@ static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
     return WC_OK;
 }
 
+static int launch_pair(const GemmProblem& p, cudaStream_t st) {
+    using C = Cfg2;
+    static bool attr_set = false;
+    if (!attr_set) {
+        WC_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::TOTAL));
+        attr_set = true;
+    }
+    CUtensorMap mA, mB;
+    KernelArgs ka;
+    ka.M = p.M; ka.N = p.N; ka.K = p.K; ka.nb0 = p.nb0; ka.e = p.epi;
+    int rc = make_tma_map(&mA, p.A, p.K, p.nb0, p.nb1, BM, &ka.a_b0, &ka.a_b1);
+    if (rc) return rc;
+    rc = make_tma_map(&mB, p.B, p.K, p.nb0, p.nb1, C::BN / 2, &ka.b_b0, &ka.b_b1);
+    if (rc) return rc;
+    ka.tiles_m = ceil_div(p.M, BM);
+    ka.tiles_n = ceil_div(p.N, C::BN);
+    const long total = (long)ka.tiles_m * ka.tiles_n * p.nb0 * p.nb1;
+    if (total > 0x7fffffffL) return fail(WC_ERR_ARG, "%s: too many tiles", __func__);
+    ka.total_tiles = (int)total;
+    ka.vec_ok = epilogue_vec_ok(p.epi);
+    ka.variant = variant_id(p.epi.out_f16 ? 1 : 0, p.epi.act, p.epi.bias ? 1 : 0, p.epi.resid ? 1 : 0,
+                            p.epi.out2 ? (p.epi.out2_preact ? 2 : 1) : 0);
+    const long pair_tiles = (long)((ka.tiles_m + 1) / 2) * ka.tiles_n * p.nb0 * p.nb1;
+    const long pairs = num_sms() / 2;
+    const int grid = 2 * (int)(pair_tiles < pairs ? pair_tiles : pairs);
+    ProfScope prof(PK_GEMM, 2.0 * p.M * p.N * p.K * p.nb0 * p.nb1, st);
+    if (g_prof_on) prof_tag(p.M, p.N, p.K, p.nb0 * p.nb1);
+    gemm_tc2_kernel<<<grid, GEMM_THREADS, C::TOTAL, st>>>(mA, mB, ka);
+    WC_LAUNCH_CHECK();
+    return WC_OK;
+}
+
 int launch_gemm(const GemmProblem& p, cudaStream_t st) {
     WC_CHECK_ARG(p.M > 0 && p.N > 0 && p.K > 0 && p.nb0 > 0 && p.nb1 > 0 && p.A.ptr && p.B.ptr);
     if (p.epi.mode == GM_QKV) WC_CHECK_ARG(p.N % 32 == 0 && p.epi.hd % 32 == 0 && p.epi.bias && aligned(p.epi.bias, 16));
@@ -583,7 +762,12 @@ int launch_gemm(const GemmProblem& p, cudaStream_t st) {
     if (p.N <= 128) return launch_cfg<128>(p, st);
     // widest tile that still gives every SM at least one tile (tile quantisation matters more than tile shape on small M)
     const long per_n = (long)ceil_div(p.M, BM) * p.nb0 * p.nb1;
-    if (per_n * ceil_div(p.N, 256) >= num_sms()) return launch_cfg<256>(p, st);
+    if (per_n * ceil_div(p.N, 256) >= num_sms()) {
+        // enough 256-wide tiles for every SM: CTA pairs (256 x 256 tiles, cta_group::2) unless switched off for A/B runs
+        static const bool pair_ok = [] { const char* e = getenv("WC_GEMM_PAIR"); return !(e && e[0] == '0'); }();
+        if (pair_ok && ceil_div(p.M, BM) >= 2) return launch_pair(p, st);
+        return launch_cfg<256>(p, st);
+    }
     if (per_n * ceil_div(p.N, 128) >= num_sms()) return launch_cfg<128>(p, st);
     return launch_cfg<64>(p, st);
 }
