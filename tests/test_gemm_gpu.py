@@ -26,7 +26,9 @@ def _ref(A, B, bias, resid, act, alpha):
                                    (130, 21, 256), (100, 64, 32), (77, 200, 401), (1025, 3072, 768), (512, 768, 3072),
                                    # >= 148 tiles of 128 x 256: the CTA-pair kernel (cta_group::2, 256 x 256 tiles), with an odd
                                    # number of m-blocks, a ragged last n-tile and K not a multiple of 64
-                                   (9232, 768, 768), (4230, 1100, 328), (16400, 2304, 768)])
+                                   (9232, 768, 768), (4230, 1100, 328), (16400, 2304, 768),
+                                   # A > 48 MB with a small B: n-fastest tile raster
+                                   (8200, 520, 3072)])
 def test_gemm_shapes(M, N, K):
     torch.manual_seed(M + N + K)
     Kp = (K + 7) // 8 * 8

@@ -19,6 +19,29 @@ from . import _lib, synth
 
 IMAGES_PER_STEP = 8
 KINDS_TENSOR = ("gemm_tc", "attention")
+# profiler class -> kernel-name fragments in the ncu traffic summary (tools/ncu_traffic.py -> profiles/*ncu_traffic*.json)
+NCU_NAMES = {"gemm_tc": ("gemm_tc",), "attention": ("attn_fwd_kernel", "attn_bwd_colsum_kernel"),
+             "softmax_headmean": ("attn_headmean_kernel", "softmax_headmean_kernel"), "par_iter": ("par_iter",),
+             "par_affinity": ("par_aff", "par_resize"), "layernorm": ("layernorm_kernel",)}
+
+
+def ncu_traffic():
+    """DRAM bytes (read + write) per launch and per kernel class, from the newest committed ncu traffic summary of ONE
+    msc+flip step (same workload, 8 dataset images); None when no summary is in the tree."""
+    import glob
+    import json
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    files = sorted(glob.glob(os.path.join(repo, "profiles", "*ncu_traffic*.json")))
+    if not files:
+        return None
+    kern = json.load(open(files[-1]))["kernels"]
+    out = {"_file": os.path.relpath(files[-1], repo)}
+    for cls, frags in NCU_NAMES.items():
+        sel = [v for k, v in kern.items() if any(f in k for f in frags)]
+        n = sum(v["launches"] for v in sel)
+        if n:
+            out[cls] = int(sum(v["dram_bytes_total"] for v in sel) / n)
+    return out
 
 
 def prof_summary():
@@ -116,6 +139,10 @@ class MscFlipVoc:
                     a = work / (ms * 1e-3) / 1e9
                     row.update(achieved=round(a, 1), unit="GB/s", frac=round(a / peaks["hbm_gbs"], 4))
             rows[k] = row
+        traffic = ncu_traffic() or {}
+        for k, row in rows.items():
+            if k in traffic:
+                row["dram_bytes_per_launch_ncu"] = traffic[k]
         ms, work, cnt = prof[top]
         tensor = top in KINDS_TENSOR
         peak = peaks["bf16_tflops_sustained"] if tensor else peaks["hbm_gbs"]
@@ -123,7 +150,8 @@ class MscFlipVoc:
         return {"bound": "tensor" if tensor else "hbm", "kernel": top, "achieved": round(ach, 1) if ach else None,
                 "peak": peak, "peak_source": peaks["source"] + (" (sustained cuBLAS bf16)" if tensor else " (copy)"),
                 "unit": "TFLOP/s" if tensor else "GB/s", "frac": round(ach / peak, 4) if ach else None,
-                "traffic": None, "kernel_ms_per_launch": round(ms / max(cnt, 1), 4), "kernels": rows}
+                "traffic": traffic.get(top), "traffic_source": traffic.get("_file"),
+                "kernel_ms_per_launch": round(ms / max(cnt, 1), 4), "kernels": rows}
 
     # ---- CPU baseline / reference arm (oracle port of the evaluation loop; bounded sample) ---------------
     @classmethod

@@ -54,8 +54,25 @@ struct KernelArgs {
     int tiles_m, tiles_n, total_tiles;
     int vec_ok;                   // every pointer / stride of the epilogue allows 4-element vector access
     int variant;                  // variant_id() of the GM_STORE flags (fast epilogue dispatch)
+    int n_fastest;                // tile raster (decode_tile)
     GemmEpilogue e;
 };
+
+// Tile raster.  m fastest (default): the CTAs running together share one weight tile and stream A; the n-tiles of an m-block
+// run tiles_m tiles apart, so A is re-read from HBM once per n-tile unless it fits L2.  n fastest: the n-tiles of an m-block
+// run together and share the A tile through L2, the (small, L2-resident) weight matrix is re-read per m-block instead —
+// chosen by the host when A is large and B small (c_proj: A = M x 3072 fp16 is 100-157 MB, read 3x otherwise).
+__device__ __forceinline__ void decode_tile(int t, int tiles_m, int tiles_n, int n_fastest, int& mb, int& nb, int& bz) {
+    if (n_fastest) {
+        nb = t % tiles_n;
+        const int rest = t / tiles_n;
+        mb = rest % tiles_m; bz = rest / tiles_m;
+    } else {
+        mb = t % tiles_m;
+        const int rest = t / tiles_m;
+        nb = rest % tiles_n; bz = rest / tiles_n;
+    }
+}
 
 __device__ __forceinline__ void store_h4(h16* p, const float* x) {
     h16x2 lo = __floats2half2_rn(x[0], x[1]), hi = __floats2half2_rn(x[2], x[3]);
@@ -373,8 +390,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     if (warp == 0) {
         uint32_t it = 0;     // running k-block counter across tiles
         for (int t = blockIdx.x; t < args.total_tiles; t += gridDim.x) {
-            const int mb = t % args.tiles_m, rest = t / args.tiles_m;
-            const int nb = rest % args.tiles_n, bz = rest / args.tiles_n;
+            int mb, nb, bz;
+            decode_tile(t, args.tiles_m, args.tiles_n, args.n_fastest, mb, nb, bz);
             const int b0 = bz % args.nb0, b1 = bz / args.nb0;
             if (lane == 0) {
                 for (int kb = 0; kb < num_kb; ++kb, ++it) {
@@ -421,8 +438,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         float* stg = stg_all + (warp - 2) * 32 * 32;
         uint32_t tl = 0;
         for (int t = blockIdx.x; t < args.total_tiles; t += gridDim.x, ++tl) {
-            const int mb = t % args.tiles_m, rest = t / args.tiles_m;
-            const int nb = rest % args.tiles_n, bz = rest / args.tiles_n;
+            int mb, nb, bz;
+            decode_tile(t, args.tiles_m, args.tiles_n, args.n_fastest, mb, nb, bz);
             const int b0 = bz % args.nb0, b1 = bz / args.nb0;
             const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
             mbar_wait(&tfull_bar[as], aph);
@@ -517,8 +534,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
         if (lane == 0) {
             uint32_t it = 0;
             for (int t = pair; t < total; t += npairs) {
-                const int m2 = t % tiles_m2, rest = t / tiles_m2;
-                const int nb = rest % args.tiles_n, bz = rest / args.tiles_n;
+                int m2, nb, bz;
+                decode_tile(t, tiles_m2, args.tiles_n, args.n_fastest, m2, nb, bz);
                 const int b0 = bz % args.nb0, b1 = bz / args.nb0;
                 const int mb = m2 * 2 + (int)rank;          // may be one past the last m-block: TMA zero-fills, epilogue skips
                 for (int kb = 0; kb < num_kb; ++kb, ++it) {
@@ -566,8 +583,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
         const uint32_t tempty_remote0 = mapa_u32(&tempty_bar[0], 0), tempty_remote1 = mapa_u32(&tempty_bar[1], 0);
         uint32_t tl = 0;
         for (int t = pair; t < total; t += npairs, ++tl) {
-            const int m2 = t % tiles_m2, rest = t / tiles_m2;
-            const int nb = rest % args.tiles_n, bz = rest / args.tiles_n;
+            int m2, nb, bz;
+            decode_tile(t, tiles_m2, args.tiles_n, args.n_fastest, m2, nb, bz);
             const int b0 = bz % args.nb0, b1 = bz / args.nb0;
             const int mb = m2 * 2 + (int)rank;
             const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
@@ -691,6 +708,12 @@ static int epilogue_vec_ok(const GemmEpilogue& e) {
     return ok ? 1 : 0;
 }
 
+// A streamed once instead of once per n-tile: worth it when A does not fit L2 next to everything else and B does
+static int raster_n_fastest(const GemmProblem& p) {
+    const double a_bytes = 2.0 * p.M * p.K, b_bytes = 2.0 * p.N * p.K;
+    return (p.nb0 * p.nb1 == 1 && p.N > 256 && a_bytes > 48e6 && b_bytes < 16e6) ? 1 : 0;
+}
+
 template <int BN>
 static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
     using C = Cfg<BN>;
@@ -712,6 +735,7 @@ static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
     if (total > 0x7fffffffL) return fail(WC_ERR_ARG, "%s: too many tiles", __func__);
     ka.total_tiles = (int)total;
     ka.vec_ok = epilogue_vec_ok(p.epi);
+    ka.n_fastest = raster_n_fastest(p);
     ka.variant = variant_id(p.epi.out_f16 ? 1 : 0, p.epi.act, p.epi.bias ? 1 : 0, p.epi.resid ? 1 : 0,
                             p.epi.out2 ? (p.epi.out2_preact ? 2 : 1) : 0);
     const int grid = (int)(total < num_sms() ? total : num_sms());
@@ -742,6 +766,7 @@ static int launch_pair(const GemmProblem& p, cudaStream_t st) {
     if (total > 0x7fffffffL) return fail(WC_ERR_ARG, "%s: too many tiles", __func__);
     ka.total_tiles = (int)total;
     ka.vec_ok = epilogue_vec_ok(p.epi);
+    ka.n_fastest = raster_n_fastest(p);
     ka.variant = variant_id(p.epi.out_f16 ? 1 : 0, p.epi.act, p.epi.bias ? 1 : 0, p.epi.resid ? 1 : 0,
                             p.epi.out2 ? (p.epi.out2_preact ? 2 : 1) : 0);
     const long pair_tiles = (long)((ka.tiles_m + 1) / 2) * ka.tiles_n * p.nb0 * p.nb1;
