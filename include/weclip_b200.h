@@ -166,7 +166,8 @@ int wc_softmax_headmean(const float* S, void* P_f16, float* avg, int n_img, int 
 /* Fused attention of the encoder (head_dim 64) and decoder (head_dim 32) blocks: softmax(q k^T) v without materialising
  * the scores (clip/myAtt.py:53-64), output head-interleaved (myAtt.py:320), plus the head-mean probability map
  * (myAtt.py:323-326, head_dim 64 only).
- *   q, k fp16 [N*heads, L, hd] (q pre-scaled by 1/sqrt(hd)); vt fp16 [N*heads, hd, Lp] (V transposed, Lp = round_up(L,8));
+ *   q, k fp16 [N*heads, L, hd] (q pre-scaled by 1/sqrt(hd)); vt: head_dim 64 -> V itself, fp16 [N*heads, L, 64];
+ *   head_dim 32 -> V transposed, fp16 [N*heads, 32, Lp] (Lp = round_up(L,8));
  *   o fp16 [N*L, heads*hd]; lse2 fp32 [N*heads, L] or NULL (log2-domain row log-sum-exp);
  *   attn_avg fp32 [N, L, L] or NULL (needs lse2 and head_dim 64). */
 int wc_attention_fwd(const void* q, const void* k, const void* vt, void* o, float* lse2, float* attn_avg,

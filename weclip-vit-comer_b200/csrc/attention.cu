@@ -128,9 +128,15 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                     mbar_wait(&v_empty[s], ((g / VST) & 1) ^ 1);
                     uint8_t* sv = smem + FwdSmem::VRING + s * AT_TILE_BYTES;
                     mbar_expect_tx(&v_full[s], 2 * V_BLK);
-                    // V^T [HD dims][128 keys] as two K-major [HD][64] blocks (box = 64 keys x HD dims)
-                    tma_load_4d(sv, &mapV, &v_full[s], j * AT_BN, 0, bh, 0);
-                    tma_load_4d(sv + V_BLK, &mapV, &v_full[s], j * AT_BN + 64, 0, bh, 0);
+                    if (HD == 64) {
+                        // V [128 keys][64 dims] straight from the head-major QKV output: one 128-byte row per key = the
+                        // canonical MN-major (N = dims contiguous) 128B-swizzled B operand, no transposed copy of V anywhere
+                        tma_load_4d(sv, &mapV, &v_full[s], 0, j * AT_BN, bh, 0);
+                    } else {
+                        // V^T [HD dims][128 keys] as two K-major [HD][64] blocks (box = 64 keys x HD dims)
+                        tma_load_4d(sv, &mapV, &v_full[s], j * AT_BN, 0, bh, 0);
+                        tma_load_4d(sv + V_BLK, &mapV, &v_full[s], j * AT_BN + 64, 0, bh, 0);
+                    }
                 };
                 for (int j = 0; j < n_kt; ++j) {
                     const int g = g0 + j, s = g % AT_STAGES;
@@ -144,7 +150,10 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc_s = make_idesc(AT_BM, AT_BN), idesc_o = make_idesc(AT_BM, HD);
+            // HD = 64: B = V is MN-major (instruction-descriptor bit 16); a 16-key MMA step then advances 16 rows of 128 bytes
+            constexpr uint32_t idesc_s = make_idesc(AT_BM, AT_BN);
+            constexpr uint32_t idesc_o = make_idesc(AT_BM, HD) | (HD == 64 ? (1u << 16) : 0u);
+            constexpr uint32_t V_KSTEP = (HD == 64) ? (16 * 128) >> 4 : 2;
             int i = 0;
             for (int w = blockIdx.x; w < a.n_items; w += gridDim.x, ++i) {
                 const int g0 = i * n_kt, qb = i & 1;
@@ -178,7 +187,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                     for (int kb = 0; kb < 2; ++kb) {   // key half kb -> accumulator kb
                         const uint64_t dp = make_smem_desc(sp + kb * AT_TILE_BYTES), dv = make_smem_desc(sv + kb * V_BLK);
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) umma_f16(tmem_o + kb * HD, dp + 2 * k, dv + 2 * k, idesc_o, (j | k) != 0);
+                        for (int k = 0; k < 4; ++k) umma_f16(tmem_o + kb * HD, dp + 2 * k, dv + V_KSTEP * k, idesc_o, (j | k) != 0);
                     }
                     umma_commit(&p_empty[pb]);
                     umma_commit(&v_empty[s]);
@@ -726,9 +735,15 @@ static int attn_maps(const h16* q, const h16* k, const h16* vt, int nh, int L, i
     if ((rc = make_tma_map(mq, oq, hd, nh, 1, AT_BM, &u0, &u1))) return rc;
     if ((rc = make_tma_map(mk, ok, hd, nh, 1, AT_BN, &u0, &u1))) return rc;
     if (vt && mv) {
-        // V^T rows = head dims, K extent = L keys (NOT Lp): columns L..Lp-1 are never written and must read as zero
-        GemmOperand ov{vt, hd, Lp, (long)hd * Lp, 0};
-        if ((rc = make_tma_map(mv, ov, L, nh, 1, hd, &u0, &u1))) return rc;
+        if (hd == 64) {
+            // V itself, [nh, L, 64]: same geometry as the K map (rows beyond L read as zero)
+            GemmOperand ov{vt, L, hd, (long)L * hd, 0};
+            if ((rc = make_tma_map(mv, ov, hd, nh, 1, AT_BN, &u0, &u1))) return rc;
+        } else {
+            // V^T rows = head dims, K extent = L keys (NOT Lp): columns L..Lp-1 are never written and must read as zero
+            GemmOperand ov{vt, hd, Lp, (long)hd * Lp, 0};
+            if ((rc = make_tma_map(mv, ov, L, nh, 1, hd, &u0, &u1))) return rc;
+        }
     }
     return WC_OK;
 }

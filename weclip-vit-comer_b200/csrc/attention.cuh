@@ -5,10 +5,12 @@
 
 namespace wc {
 
-// q, k: [N*heads, L, hd] fp16 (q pre-scaled by 1/sqrt(hd), myAtt.py:54); vt: [N*heads, hd, Lp] fp16 (V transposed).
+// q, k: [N*heads, L, hd] fp16 (q pre-scaled by 1/sqrt(hd), myAtt.py:54).
+// v_or_vt: hd = 64 -> V itself, [N*heads, L, 64] (used as an MN-major tensor-core operand); hd = 32 -> V transposed,
+//          [N*heads, 32, Lp] fp16.
 // o: [N*L, heads*hd] fp16, head-interleaved (myAtt.py:320).  lse2 (optional): [N*heads, L] fp32, log2-domain
 // log-sum-exp of each score row (input of launch_attn_headmean).  hd in {64, 32}.
-int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, float* lse2, int n_img, int heads, int L, int Lp,
+int launch_attention_fwd(const h16* q, const h16* k, const h16* v_or_vt, h16* o, float* lse2, int n_img, int heads, int L, int Lp,
                          int hd, cudaStream_t st);
 
 // avg[n, i, j] = mean over heads of softmax(q k^T)[n, h, i, j] (myAtt.py:323-326), fp32 [N, L, L], each element written

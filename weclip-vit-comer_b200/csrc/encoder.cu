@@ -18,7 +18,11 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
     {
         GemmProblem p; p.M = M; p.N = 3 * E; p.K = E;
         p.A = op(b.a, M, E); p.B = op(reinterpret_cast<const h16*>(w.w_in), 3 * E, E);
-        p.epi.mode = GM_QKV; p.epi.bias = w.b_in; p.epi.q = b.q; p.epi.k = b.k; p.epi.v = b.v; p.epi.vt = b.vt;
+        // head_dim 64 on the fused path: V stays head-major like q / k (the attention kernel reads it as an MN-major operand);
+        // otherwise V^T for the K-major P V operand
+        const bool v_direct = (!b.S && hd == 64);
+        if (v_direct && !b.v) return fail(WC_ERR_ARG, "%s: head_dim 64 needs the v buffer", __func__);
+        p.epi.mode = GM_QKV; p.epi.bias = w.b_in; p.epi.q = b.q; p.epi.k = b.k; p.epi.v = b.v; p.epi.vt = v_direct ? nullptr : b.vt;
         p.epi.L = L; p.epi.Lp = (int)Lp; p.epi.heads = heads; p.epi.hd = hd; p.epi.qscale = 1.f / sqrtf((float)hd);
         if ((rc = launch_gemm(p, st))) return rc;
     }
@@ -27,7 +31,7 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
         // head-interleaved into [M,E] (myAtt.py:53-64,320), then the head-mean map from the row log-sum-exps (:323-326)
         if (b.attn_avg && (hd != 64 || !b.lse))
             return fail(WC_ERR_UNSUPPORTED, "%s: the head-mean map needs head_dim 64 and an lse buffer", __func__);
-        if ((rc = launch_attention_fwd(b.q, b.k, b.vt, b.o, b.lse, n_img, heads, L, (int)Lp, hd, st))) return rc;
+        if ((rc = launch_attention_fwd(b.q, b.k, hd == 64 ? b.v : b.vt, b.o, b.lse, n_img, heads, L, (int)Lp, hd, st))) return rc;
         if (b.attn_avg && (rc = launch_attn_headmean(b.q, b.k, b.lse, b.attn_avg, b.attn_imgs > 0 ? b.attn_imgs : n_img, heads, L, st))) return rc;
     } else {
         // S = q k^T (myAtt.py:56), fp32 [N*heads, L, Lp]
@@ -75,7 +79,7 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
 }
 
 // Attention scratch shared by every block of one call.
-struct AttnScratch { h16 *a, *q, *k, *vt, *P, *o, *u; float *S, *lse; };
+struct AttnScratch { h16 *a, *q, *k, *v, *vt, *P, *o, *u; float *S, *lse; };
 
 // fused: no materialised score / probability tensors, a [N*heads, L] log-sum-exp vector instead
 static AttnScratch carve_block(Arena& ar, int n_img, int L, int E, int heads, bool fused) {
@@ -84,7 +88,8 @@ static AttnScratch carve_block(Arena& ar, int n_img, int L, int E, int heads, bo
     s.a = ar.get<h16>(M * E);
     s.q = ar.get<h16>(M * E);
     s.k = ar.get<h16>(M * E);
-    s.vt = ar.get<h16>((long)n_img * heads * hd * Lp);
+    s.v = (fused && hd == 64) ? ar.get<h16>(M * E) : nullptr;
+    s.vt = (fused && hd == 64) ? nullptr : ar.get<h16>((long)n_img * heads * hd * Lp);
     s.S = fused ? nullptr : ar.get<float>((long)n_img * heads * L * Lp);
     s.P = fused ? nullptr : ar.get<h16>((long)n_img * heads * L * Lp);
     s.lse = fused ? ar.get<float>((long)n_img * heads * L) : nullptr;
@@ -152,7 +157,7 @@ extern "C" int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, 
     for (int i = 0; i < 11; ++i) {
         BlockBuffers b{};
         b.x_in = x; b.x_mid = x; b.x_out = (i == 10) ? x_last : x;
-        b.a = s.a; b.q = s.q; b.k = s.k; b.vt = s.vt; b.S = s.S; b.P = s.P; b.lse = s.lse; b.o = s.o; b.u = s.u;
+        b.a = s.a; b.q = s.q; b.k = s.k; b.v = s.v; b.vt = s.vt; b.S = s.S; b.P = s.P; b.lse = s.lse; b.o = s.o; b.u = s.u;
         const int slot = i - (11 - n_attn);
         b.attn_avg = (slot >= 0) ? attn_avg + (size_t)slot * attn_imgs * L * L : nullptr;
         b.attn_imgs = attn_imgs;
@@ -214,7 +219,7 @@ extern "C" int wc_decoder_fwd(const wc_decoder_weights* w, const void* taps_, in
     for (int i = 0; i < 3; ++i) {   // TransDecoder.py:113-119 (the three attention maps are unused downstream)
         BlockBuffers b{};
         b.x_in = x; b.x_mid = x; b.x_out = x;
-        b.a = s.a; b.q = s.q; b.k = s.k; b.vt = s.vt; b.S = s.S; b.P = s.P; b.lse = s.lse; b.o = s.o; b.u = s.u;
+        b.a = s.a; b.q = s.q; b.k = s.k; b.v = s.v; b.vt = s.vt; b.S = s.S; b.P = s.P; b.lse = s.lse; b.o = s.o; b.u = s.u;
         b.tap = (i == 2) ? xb : nullptr;
         if ((rc = run_block(w->blocks[i], b, N, P, D, 8, st))) return rc;
     }

@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msu
                                                    float logit_scale, int P, float* __restrict__ dm,
                                                    float* __restrict__ gscale, float* __restrict__ probs_out) {
     __shared__ float mvec[GC_E];
-    __shared__ float g[GC_EMB], dgh[GC_EMB];
+    __shared__ __align__(16) float g[GC_EMB], dgh[GC_EMB];
     __shared__ float logit[GC_MAX_T], tnorm[GC_MAX_T], dl[GC_MAX_T];
     __shared__ float red[32];
     const int img = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -112,9 +112,16 @@ __global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msu
     for (int c = tid; c < GC_E; c += 512) mvec[c] = msum[(size_t)img * GC_E + c] / (float)P;
     __syncthreads();
     {   // g = mean @ proj  (model.py:414-415)
-        float s = 0.f;
-        for (int c = 0; c < GC_E; ++c) s = fmaf(mvec[c], __ldg(proj + (size_t)c * GC_EMB + tid), s);
-        g[tid] = s;
+        // 768 dependent-free loads per thread: four accumulators and a deep unroll keep ~16 L2 requests in flight per thread
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll 4
+        for (int c = 0; c < GC_E; c += 4) {
+            s0 = fmaf(mvec[c], __ldg(proj + (size_t)c * GC_EMB + tid), s0);
+            s1 = fmaf(mvec[c + 1], __ldg(proj + (size_t)(c + 1) * GC_EMB + tid), s1);
+            s2 = fmaf(mvec[c + 2], __ldg(proj + (size_t)(c + 2) * GC_EMB + tid), s2);
+            s3 = fmaf(mvec[c + 3], __ldg(proj + (size_t)(c + 3) * GC_EMB + tid), s3);
+        }
+        g[tid] = (s0 + s1) + (s2 + s3);
     }
     __syncthreads();
     const float gn = sqrtf(block_sum(g[tid] * g[tid], red));
@@ -146,15 +153,22 @@ __global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msu
         for (int t = tid; t < T; t += 512) dl[t] = pk * ((t == k ? 1.f : 0.f) - logit[t]);   // d p_k / d logit_t
         __syncthreads();
         float s = 0.f;   // d p_k / d ghat_j
+#pragma unroll 8
         for (int t = 0; t < T; ++t) s = fmaf(dl[t] / tnorm[t], __ldg(text + (size_t)(t0 + t) * GC_EMB + tid), s);
         s *= logit_scale;
         const float dot = block_sum(s * g[tid], red);
         dgh[tid] = (s - g[tid] * dot) / gn;          // through the L2 normalisation
         __syncthreads();
+#pragma unroll 2
         for (int c = warp; c < GC_E; c += 16) {      // d / d mean = proj @ dg ; every patch row gets 1/P of it
-            const float* pr = proj + (size_t)c * GC_EMB;
+            const float4* pr = reinterpret_cast<const float4*>(proj + (size_t)c * GC_EMB);
             float a = 0.f;
-            for (int j = lane; j < GC_EMB; j += 32) a = fmaf(__ldg(pr + j), dgh[j], a);
+#pragma unroll
+            for (int j = 0; j < GC_EMB / 128; ++j) {
+                const float4 w4 = __ldg(pr + lane + 32 * j);
+                const float4 d4 = reinterpret_cast<const float4*>(dgh)[lane + 32 * j];
+                a += w4.x * d4.x + w4.y * d4.y + w4.z * d4.z + w4.w * d4.w;
+            }
             a = warp_sum(a);
             if (lane == 0) dm[(size_t)inst * GC_E + c] = a / (float)P;
         }
@@ -429,7 +443,7 @@ static void gc_layout(Arena& ar, GcLayout& g, int N, int L, int total_inst, int 
     g.dqkv = ar.get<float>((long)total_inst * 3 * E); g.wvec = ar.get<float>((long)total_inst * E);
     g.gscale = ar.get<float>((long)total_inst);
     g.a = ar.get<h16>(M * E); g.q = ar.get<h16>(M * E); g.k = ar.get<h16>(M * E); g.v = ar.get<h16>(M * E);
-    g.vt = ar.get<h16>((long)N * GC_HEADS * GC_HD * Lp);
+    g.vt = nullptr;   // head_dim 64: the fused attention reads V itself
     g.o = ar.get<h16>(M * E); g.u = ar.get<h16>(M * 4 * E); g.upre = ar.get<h16>(M * 4 * E);
     const long R = (long)chunk * L;
     g.dx2 = ar.get<float>(R * E); g.da2 = ar.get<float>(R * E);

@@ -121,8 +121,11 @@ def attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, want_avg: b
     N, heads, L, hd = q.shape
     assert hd in (64, 32) and q.dtype == torch.float16
     Lp = (L + 7) // 8 * 8
-    vt = torch.full((N, heads, hd, Lp), float("nan"), dtype=torch.float16, device=q.device)   # pad columns must not matter
-    vt[..., :L] = v.transpose(-1, -2)
+    if hd == 64:
+        vt = v.contiguous()          # head_dim 64: V itself (MN-major tensor-core operand), no transposed copy
+    else:
+        vt = torch.full((N, heads, hd, Lp), float("nan"), dtype=torch.float16, device=q.device)   # pad columns must not matter
+        vt[..., :L] = v.transpose(-1, -2)
     o = torch.empty(N, L, heads * hd, dtype=torch.float16, device=q.device)
     lse = torch.empty(N, heads, L, dtype=torch.float32, device=q.device)
     avg = torch.empty(N, L, L, dtype=torch.float32, device=q.device) if want_avg else None
