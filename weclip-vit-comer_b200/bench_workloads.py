@@ -183,4 +183,64 @@ class MscFlipCoco(MscFlipVoc):
     subdir = os.path.join("SegmentationClass", "train")
 
 
-WORKLOADS = {"mscflip": MscFlipVoc, "mscflip_coco": MscFlipCoco}
+class PseudoLabelVoc(MscFlipVoc):
+    """BASELINE.json configs[1]: the training-time CAM + PAR pseudo-label step (scripts/dist_clip_voc.py:238-267 calls
+    WeCLIP.forward(img, img_name, mode='train')): batch 32 crops of 320x320, 21 classes, one name per crop, so every image
+    goes through encoder, decoder, Grad-CAM, affinity refinement (iter_num > 15000: RFM branch), upsample and PAR at crop
+    resolution.  Unit = one crop; the step returns (seg, pseudo labels, attn_pred) on the device, e2e copies the labels out."""
+    name = "cfg2: WeCLIP VOC CAM+PAR pseudo-label step, batch 32 at 320x320 crop, 21 classes, mode='train' (RFM branch)"
+    H = W = 320
+    BATCH = 32
+
+    def __init__(self, rank: int, device):
+        from .model import WeCLIP
+        self.dev = device
+        self.root = tempfile.mkdtemp(prefix="wcbench")
+        self.sd = synth.make_state_dict(0, self.n_classes)
+        self.fg, self.bg = synth.make_text_features(7, self.n_fg, self.n_bg)
+        self.names, self.labs, imgs = self._make_data(300 + rank, self.BATCH, self.root)
+        self.model = WeCLIP(num_classes=self.n_classes, dataset_root_path=self.root, device=device,
+                            dataset=self.dataset, state_dict=self.sd, fg_text_features=self.fg,
+                            bg_text_features=self.bg)
+        self.imgs_h = imgs.pin_memory()
+        self.imgs_d = self.imgs_h.to(device)
+        self.labels_h = torch.empty(self.BATCH, self.H, self.W, dtype=torch.int64).pin_memory()
+        self.units = self.BATCH
+        self.h2d = self.imgs_h.numel() * 4
+        self.d2h = self.labels_h.numel() * 8
+        self.launches = None
+        self.l2_note = "working set larger than L2 (32 crops: 157 MB of MLP activations per block, 315 MB of PAR affinities)"
+
+    def step_device(self, record=False):
+        self.model.iter_num = 20000            # RFM branch of clip_tool.py:152-175
+        return self.model(self.imgs_d, self.names, mode="train")
+
+    def step_e2e(self):
+        img = self.imgs_h.to(self.dev, non_blocking=True)
+        self.model.iter_num = 20000
+        _, labels, _ = self.model(img, self.names, mode="train")
+        self.labels_h.copy_(labels, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self.labels_h
+
+    @classmethod
+    def cpu(cls):
+        wl = cls.__new__(cls)
+        wl.root = tempfile.mkdtemp(prefix="wcbench")
+        wl.sd = synth.make_state_dict(0, cls.n_classes)
+        wl.fg, wl.bg = synth.make_text_features(7, cls.n_fg, cls.n_bg)
+        wl.names, wl.labs, wl.imgs_h = wl._make_data(300, 2, wl.root)
+        return wl
+
+    def cpu_sample(self, n_img=2):
+        from oracle import weclip_oracle as O
+        n_img = min(n_img, 2)
+        t0 = time.perf_counter()
+        O.weclip_forward(self.imgs_h[:n_img].clone(), [np.asarray(l) for l in self.labs[:n_img]], self.sd, self.fg, self.bg,
+                         mode="train", iter_num=20001, dataset=self.dataset)
+        dt = time.perf_counter() - t0
+        return n_img / dt, (f"{n_img} of the step's {self.BATCH} crops (full forward incl. Grad-CAM, affinity refinement, PAR), "
+                            "oracle port of WeCLIP.forward(mode='train'), torch CPU fp32")
+
+
+WORKLOADS = {"mscflip": MscFlipVoc, "mscflip_coco": MscFlipCoco, "cfg2": PseudoLabelVoc}

@@ -88,7 +88,8 @@ __device__ __forceinline__ void store_h4(h16* p, const float* x) {
 // Preconditions (checked by the caller): full 32-column chunk, 4-element vector access allowed.
 // ---------------------------------------------------------------------------------------------------
 constexpr int variant_id(int f16, int act, int bias, int resid, int out2) {
-    return f16 | (act << 1) | (bias << 3) | (resid << 4) | (out2 << 5);     // out2: 0 none, 1 after act+resid, 2 before
+    // resid: 0 none, 1 loaded and added in registers, 2 in place through an L2 reduction; out2: 0 none, 1 after act+resid, 2 before
+    return f16 | (act << 1) | (bias << 3) | (resid << 4) | (out2 << 6);
 }
 
 template <int F16, int ACT, int BIAS, int RESID, int OUT2>
@@ -101,7 +102,7 @@ __device__ __forceinline__ void fast_store(const KernelArgs& a, const float* stg
     float4 x[8], rs[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) x[i] = *reinterpret_cast<const float4*>(stg + stg_off(i * 4 + rsub, lane & 7));
-    if (RESID) {
+    if (RESID == 1) {
         const float* rp = e.resid + b0 * e.resid_bs0 + b1 * e.resid_bs1 + (long)r_first * e.ldr + col;
 #pragma unroll
         for (int i = 0; i < 8; ++i)
@@ -109,6 +110,19 @@ __device__ __forceinline__ void fast_store(const KernelArgs& a, const float* stg
     }
     const long ob = b0 * e.out_bs0 + b1 * e.out_bs1 + (long)r_first * e.ldo + col;
     const long o2b = OUT2 ? b0 * e.out2_bs0 + b1 * e.out2_bs1 + (long)r_first * e.ld2 + col : 0;
+    if (RESID == 2) {
+        // in-place residual (out == resid, fp32): x += alpha*acc + bias as a vector reduction performed by L2
+        // (red.global.add.v4.f32) — one fp32 add per element exactly like the register path, but the epilogue warps never
+        // wait for the residual tile to come back from HBM
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (r_first + 4 * i >= a.M) break;
+            float* p = reinterpret_cast<float*>(e.out) + ob + (long)(4 * i) * e.ldo;
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(e.alpha * x[i].x + bias.x),
+                         "f"(e.alpha * x[i].y + bias.y), "f"(e.alpha * x[i].z + bias.z), "f"(e.alpha * x[i].w + bias.w) : "memory");
+        }
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         if (r_first + 4 * i >= a.M) break;
@@ -116,7 +130,7 @@ __device__ __forceinline__ void fast_store(const KernelArgs& a, const float* stg
         if (OUT2 == 2) store_h4(e.out2 + o2b + (long)(4 * i) * e.ld2, v);
 #pragma unroll
         for (int t = 0; t < 4; ++t) v[t] = apply_act(v[t], ACT);
-        if (RESID) { v[0] += rs[i].x; v[1] += rs[i].y; v[2] += rs[i].z; v[3] += rs[i].w; }
+        if (RESID == 1) { v[0] += rs[i].x; v[1] += rs[i].y; v[2] += rs[i].z; v[3] += rs[i].w; }
         if (OUT2 == 1) store_h4(e.out2 + o2b + (long)(4 * i) * e.ld2, v);
         if (F16) store_h4(reinterpret_cast<h16*>(e.out) + ob + (long)(4 * i) * e.ldo, v);
         else *reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + ob + (long)(4 * i) * e.ldo) = make_float4(v[0], v[1], v[2], v[3]);
@@ -132,6 +146,7 @@ __device__ __forceinline__ bool fast_store_dispatch(const KernelArgs& a, const f
         WC_V(0, ACT_NONE, 0, 0, 0)        // plain fp32 (scores, dP, c_fc^T)
         WC_V(1, ACT_NONE, 0, 0, 0)        // plain fp16 (P V, out_proj^T)
         WC_V(0, ACT_NONE, 1, 1, 0)        // out-proj / c_proj + residual
+        WC_V(0, ACT_NONE, 1, 2, 0)        // out-proj + residual in place: L2 reduction
         WC_V(0, ACT_NONE, 1, 1, 1)        // c_proj + residual + fp16 feature tap
         WC_V(1, ACT_QUICKGELU, 1, 0, 0)   // c_fc
         WC_V(1, ACT_QUICKGELU, 1, 0, 2)   // c_fc keeping the pre-activation (Grad-CAM block)
@@ -708,6 +723,16 @@ static int epilogue_vec_ok(const GemmEpilogue& e) {
     return ok ? 1 : 0;
 }
 
+// 2 = the residual is the output buffer itself (fp32, no second output, no activation): add through red.global instead of
+// loading it; 1 = load + add; 0 = none
+static int resid_mode(const GemmEpilogue& e) {
+    if (!e.resid) return 0;
+    static const bool red_ok = [] { const char* v = getenv("WC_GEMM_RED"); return !(v && v[0] == '0'); }();
+    const bool in_place = e.resid == e.out && !e.out_f16 && !e.out2 && !e.out_trans && e.act == ACT_NONE && e.bias &&
+                          e.ldr == e.ldo && e.resid_bs0 == e.out_bs0 && e.resid_bs1 == e.out_bs1 && e.mode == GM_STORE;
+    return (in_place && red_ok) ? 2 : 1;
+}
+
 // A streamed once instead of once per n-tile: worth it when A does not fit L2 next to everything else and B does
 static int raster_n_fastest(const GemmProblem& p) {
     const double a_bytes = 2.0 * p.M * p.K, b_bytes = 2.0 * p.N * p.K;
@@ -736,7 +761,7 @@ static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
     ka.total_tiles = (int)total;
     ka.vec_ok = epilogue_vec_ok(p.epi);
     ka.n_fastest = raster_n_fastest(p);
-    ka.variant = variant_id(p.epi.out_f16 ? 1 : 0, p.epi.act, p.epi.bias ? 1 : 0, p.epi.resid ? 1 : 0,
+    ka.variant = variant_id(p.epi.out_f16 ? 1 : 0, p.epi.act, p.epi.bias ? 1 : 0, resid_mode(p.epi),
                             p.epi.out2 ? (p.epi.out2_preact ? 2 : 1) : 0);
     const int grid = (int)(total < num_sms() ? total : num_sms());
     ProfScope prof(PK_GEMM, 2.0 * p.M * p.N * p.K * p.nb0 * p.nb1, st);
@@ -767,7 +792,7 @@ static int launch_pair(const GemmProblem& p, cudaStream_t st) {
     ka.total_tiles = (int)total;
     ka.vec_ok = epilogue_vec_ok(p.epi);
     ka.n_fastest = raster_n_fastest(p);
-    ka.variant = variant_id(p.epi.out_f16 ? 1 : 0, p.epi.act, p.epi.bias ? 1 : 0, p.epi.resid ? 1 : 0,
+    ka.variant = variant_id(p.epi.out_f16 ? 1 : 0, p.epi.act, p.epi.bias ? 1 : 0, resid_mode(p.epi),
                             p.epi.out2 ? (p.epi.out2_preact ? 2 : 1) : 0);
     const long pair_tiles = (long)((ka.tiles_m + 1) / 2) * ka.tiles_n * p.nb0 * p.nb1;
     const long pairs = num_sms() / 2;
