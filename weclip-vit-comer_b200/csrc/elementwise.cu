@@ -11,7 +11,8 @@ namespace wc {
 template <int VPL>   // float4 vectors per lane: E = 128 * VPL
 __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                         const float* __restrict__ b, h16* __restrict__ out_h,
-                                                        float* __restrict__ out_f, long rows, int E) {
+                                                        float* __restrict__ out_f, h16* __restrict__ raw_h, long rows,
+                                                        int E) {
     const long row = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= rows) return;
@@ -22,6 +23,13 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
     for (int i = 0; i < VPL; ++i) {
         v[i] = xr[lane + 32 * i];
         s += v[i].x + v[i].y + v[i].z + v[i].w;
+        if (raw_h) {   // fp16 copy of the un-normalised row (the previous block's output tap)
+            h16x2 lo = __floats2half2_rn(v[i].x, v[i].y), hi = __floats2half2_rn(v[i].z, v[i].w);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t*>(&lo);
+            pk.y = *reinterpret_cast<uint32_t*>(&hi);
+            reinterpret_cast<uint2*>(raw_h + row * E)[lane + 32 * i] = pk;
+        }
     }
     const float mean = warp_sum(s) / (float)E;
     float q = 0.f;
@@ -53,15 +61,15 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
 }
 
 int launch_layernorm(const float* x, const float* w, const float* b, h16* out_h, float* out_f, long rows,
-                     int E, cudaStream_t st) {
+                     int E, cudaStream_t st, h16* raw_h) {
     WC_CHECK_ARG(x && w && b && rows > 0 && (out_h || out_f));
     const unsigned grid = (unsigned)ceil_div(rows, 8L);
-    ProfScope prof(PK_LAYERNORM, (double)rows * E * (4.0 + (out_h ? 2.0 : 0.0) + (out_f ? 4.0 : 0.0)), st);
+    ProfScope prof(PK_LAYERNORM, (double)rows * E * (4.0 + (out_h ? 2.0 : 0.0) + (out_f ? 4.0 : 0.0) + (raw_h ? 2.0 : 0.0)), st);
     switch (E) {
-        case 256: layernorm_kernel<2><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, rows, E); break;
-        case 512: layernorm_kernel<4><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, rows, E); break;
-        case 768: layernorm_kernel<6><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, rows, E); break;
-        case 1024: layernorm_kernel<8><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, rows, E); break;
+        case 256: layernorm_kernel<2><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, raw_h, rows, E); break;
+        case 512: layernorm_kernel<4><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, raw_h, rows, E); break;
+        case 768: layernorm_kernel<6><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, raw_h, rows, E); break;
+        case 1024: layernorm_kernel<8><<<grid, 256, 0, st>>>(x, w, b, out_h, out_f, raw_h, rows, E); break;
         default: return fail(WC_ERR_UNSUPPORTED, "%s: LayerNorm width %ld not instantiated", __func__, (long)E);
     }
     WC_LAUNCH_CHECK();

@@ -4,7 +4,7 @@
 
 namespace wc {
 int launch_layernorm(const float* x, const float* w, const float* b, h16* out_h, float* out_f, long rows,
-                     int E, cudaStream_t st);
+                     int E, cudaStream_t st, h16* raw_h = nullptr);   // raw_h: optional fp16 copy of x itself
 int launch_softmax_headmean(const float* S, h16* P, float* avg, int n_img, int heads, int L, int Lp,
                             cudaStream_t st);
 int launch_im2col16(const float* img, h16* out, int N, int H, int W, cudaStream_t st);

@@ -13,7 +13,7 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
     const long Lp = round8(L);
     int rc;
     // ln_1 (clip/model.py:211)
-    if ((rc = launch_layernorm(b.x_in, w.ln1_w, w.ln1_b, b.a, b.a_f32, M, E, st))) return rc;
+    if ((rc = launch_layernorm(b.x_in, w.ln1_w, w.ln1_b, b.a, b.a_f32, M, E, st, b.tap_in))) return rc;
     // packed in-proj + head split, q pre-scaled by 1/sqrt(hd) (myAtt.py:199-201,257-268,54)
     {
         GemmProblem p; p.M = M; p.N = 3 * E; p.K = E;
@@ -161,7 +161,10 @@ extern "C" int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, 
         const int slot = i - (11 - n_attn);
         b.attn_avg = (slot >= 0) ? attn_avg + (size_t)slot * attn_imgs * L * L : nullptr;
         b.attn_imgs = attn_imgs;
-        b.tap = taps + (size_t)i * M * E;
+        // tap i = fp16 copy of block i's output: blocks 0..9 add their MLP output into x in place (L2 reduction, no second
+        // epilogue output), so the next block's ln_1 - which reads x anyway - writes the copy; block 10 writes its own
+        b.tap_in = (i > 0) ? taps + (size_t)(i - 1) * M * E : nullptr;
+        b.tap = (i == 10) ? taps + (size_t)i * M * E : nullptr;
         if ((rc = run_block(w->blocks[i], b, N, L, E, 12, st))) return rc;
     }
     return WC_OK;

@@ -41,6 +41,7 @@ struct BlockBuffers {
     h16* u_pre;        // optional [M,4E] pre-activation
     float* attn_avg;    // optional [N,L,L]
     h16* tap;          // optional h16 copy of x_out
+    h16* tap_in;       // optional h16 copy of x_in, written by ln_1 (the previous block's tap when its c_proj adds in place)
 };
 
 // clip/model.py:210-214 with clip/myAtt.py:199-326 inside.
