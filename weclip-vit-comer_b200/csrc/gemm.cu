@@ -55,6 +55,7 @@ struct KernelArgs {
     int vec_ok;                   // every pointer / stride of the epilogue allows 4-element vector access
     int variant;                  // variant_id() of the GM_STORE flags (fast epilogue dispatch)
     int n_fastest;                // tile raster (decode_tile)
+    int dbg;                      // developer knob (WC_GEMM_DBG): 1 = epilogue drains tensor memory but stores nothing
     GemmEpilogue e;
 };
 
@@ -179,6 +180,83 @@ __device__ __forceinline__ void fast_qkv(const KernelArgs& a, const float* stg, 
         row += 4; l += 4;
         if (l >= e.L) { l -= e.L; ++img; }          // L >= 4 is guaranteed by the caller
     }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// fp16-output fast path (c_fc, decoder MLPs, packed in-proj).  Bias / scale / activation are applied in the accumulator
+// layout (lane = row, 32 consecutive columns in registers; the bias float4s are warp-uniform broadcast loads) and the chunk
+// is staged as PACKED fp16: 2 KB each way through shared memory instead of 4 KB — the staging traffic competes with the
+// tensor core's operand reads (64 B/clk of the SM's 128) — and 4 x (STS.128, LDS.128, STG.128) per lane instead of 8.
+// Read-back layout: lane -> (row group lane >> 2, 16-byte slot lane & 3): a warp instruction writes 8 rows x 64 B.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int stg16_off(int row, int slot) { return row * 64 + ((slot ^ ((row >> 1) & 3)) << 4); }   // bytes
+
+template <int ACT, int BIAS, int SCALE_AFTER_BIAS>
+__device__ __forceinline__ void pack_stage16(const uint32_t* r, float* stg, int lane, const float* bias, float alpha) {
+    uint8_t* sb = reinterpret_cast<uint8_t*>(stg);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        uint4 pk;
+        uint32_t* pw = reinterpret_cast<uint32_t*>(&pk);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (BIAS) b = __ldg(reinterpret_cast<const float4*>(bias) + 2 * j + h);
+            const int c = 8 * j + 4 * h;
+            float v[4] = {__uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3])};
+            const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                v[t] = SCALE_AFTER_BIAS ? (v[t] + bb[t]) * alpha : alpha * v[t] + bb[t];
+                v[t] = apply_act(v[t], ACT);
+            }
+            h16x2 lo = __floats2half2_rn(v[0], v[1]), hi = __floats2half2_rn(v[2], v[3]);
+            pw[2 * h] = *reinterpret_cast<uint32_t*>(&lo);
+            pw[2 * h + 1] = *reinterpret_cast<uint32_t*>(&hi);
+        }
+        *reinterpret_cast<uint4*>(sb + stg16_off(lane, j)) = pk;
+    }
+}
+
+template <int ACT, int BIAS>
+__device__ __forceinline__ void fast_store16(const KernelArgs& a, const uint32_t* r, float* stg, int lane, int row0, int col0,
+                                             int b0, int b1) {
+    const GemmEpilogue& e = a.e;
+    pack_stage16<ACT, BIAS, 0>(r, stg, lane, BIAS ? e.bias + b0 * e.bias_bs0 + b1 * e.bias_bs1 + col0 : nullptr, e.alpha);
+    __syncwarp();
+    const uint8_t* sb = reinterpret_cast<const uint8_t*>(stg);
+    const int rg = lane >> 2, slot = lane & 3;
+    h16* o = reinterpret_cast<h16*>(e.out) + b0 * e.out_bs0 + b1 * e.out_bs1 + (long)(row0 + rg) * e.ldo + col0 + slot * 8;
+    uint4 v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = *reinterpret_cast<const uint4*>(sb + stg16_off(i * 8 + rg, slot));
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        if (row0 + rg + 8 * i < a.M) *reinterpret_cast<uint4*>(o + (long)(8 * i) * e.ldo) = v[i];
+    __syncwarp();
+}
+
+// packed in-proj + head split on the same scheme; q is scaled by 1/sqrt(hd) after the bias (myAtt.py:54).  L >= 8.
+__device__ __forceinline__ void fast_qkv16(const KernelArgs& a, const uint32_t* r, float* stg, int lane, int row0, int col0,
+                                           int which, int head, int d0) {
+    const GemmEpilogue& e = a.e;
+    pack_stage16<ACT_NONE, 1, 1>(r, stg, lane, e.bias + col0, (which == 0) ? e.qscale : 1.f);
+    __syncwarp();
+    const uint8_t* sb = reinterpret_cast<const uint8_t*>(stg);
+    const int rg = lane >> 2, slot = lane & 3;
+    h16* dst = (which == 0) ? e.q : (which == 1) ? e.k : e.v;
+    uint4 v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = *reinterpret_cast<const uint4*>(sb + stg16_off(i * 8 + rg, slot));
+    int row = row0 + rg;
+    int img = row / e.L, l = row - img * e.L;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (row < a.M) *reinterpret_cast<uint4*>(dst + (((long)img * e.heads + head) * e.L + l) * e.hd + d0 + slot * 8) = v[i];
+        row += 8; l += 8;
+        if (l >= e.L) { l -= e.L; ++img; }
+    }
+    __syncwarp();
 }
 
 // GM_MUL_QGELU_GRAD fast path: out = acc * alpha * quickgelu'(u), u = saved pre-activation (fp16).  The 8 aux loads are issued
@@ -471,7 +549,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
                     if (col0 >= args.N) break;          // warp-uniform
                     tmem_ld_wait();
                     if (c + 1 < NCH && col0 + 32 < args.N) tmem_ld32_issue(taddr + (c + 1) * 32, r[(c + 1) & 1]);
-                    epilogue_chunk(args, r[c & 1], stg, lane, row0, col0, b0, b1, bz);
+                    if (!args.dbg) epilogue_chunk(args, r[c & 1], stg, lane, row0, col0, b0, b1, bz);
                 }
                 tmem_ld_wait();
             }
@@ -487,6 +565,59 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         tmem_dealloc(tmem_base, C::TMEM_COLS);
     }
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Kernel-level epilogue specialisation.  The generic epilogue_chunk carries every mode and every fast variant; inlined
+// once per 32-column chunk it makes the kernel ~30 k instructions and the epilogue warps run out of the instruction
+// cache (measured: the K = 768 GEMMs were epilogue-bound at 950 TF/s with a 1400 TF/s main loop).  The hot shapes get a
+// kernel instantiated for exactly one epilogue: FE >= 0 is a variant_id() of fast_store, FE_QKV / FE_QGRAD the two
+// special modes; FE_GENERIC keeps the full dispatch.  Host-checked preconditions of a specialised kernel: N % 32 == 0
+// (only full chunks), vector access allowed, GM_QKV: L >= 4.
+// ---------------------------------------------------------------------------------------------------
+constexpr int FE_GENERIC = -1, FE_QKV = -2, FE_QGRAD = -3;
+
+template <int FE>
+__device__ __forceinline__ void epilogue_chunk_t(const KernelArgs& a, const uint32_t* r, float* stg, int lane, int row0,
+                                                 int col0, int b0, int b1, int bz) {
+    if constexpr (FE == FE_GENERIC) {
+        epilogue_chunk(a, r, stg, lane, row0, col0, b0, b1, bz);
+    } else {
+        const GemmEpilogue& e = a.e;
+        int which = 0, head = 0, d0 = 0;
+        if constexpr (FE == FE_QKV) {
+            const int E = e.heads * e.hd;
+            which = col0 / E;
+            const int within = col0 - which * E;
+            head = within / e.hd;
+            d0 = within - head * e.hd;
+            const int myrow = row0 + lane;
+            if (which == 2 && e.vt && myrow < a.M) {
+                const int img = myrow / e.L, l = myrow - img * e.L;
+                h16* o = e.vt + (((long)img * e.heads + head) * e.hd + d0) * (long)e.Lp + l;
+                const float* bias = e.bias + col0;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) o[(long)j * e.Lp] = __float2half_rn(__uint_as_float(r[j]) + __ldg(bias + j));
+            }
+            if ((which == 0 && !e.q) || (which == 1 && !e.k) || (which == 2 && !e.v)) return;
+        }
+        constexpr bool STORE16 = FE >= 0 && (FE & 1) && ((FE >> 4) & 3) == 0 && ((FE >> 6) & 3) == 0;
+        if constexpr (FE == FE_QKV) {
+            fast_qkv16(a, r, stg, lane, row0, col0, which, head, d0);
+        } else if constexpr (STORE16) {
+            fast_store16<((FE >> 1) & 3), ((FE >> 3) & 1)>(a, r, stg, lane, row0, col0, b0, b1);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<float4*>(stg + stg_off(lane, j)) = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                                                                 __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+            __syncwarp();
+            if constexpr (FE == FE_QGRAD) fast_qgelu_grad(a, stg, lane, row0, col0, b0, b1, bz);
+            else fast_store<(FE & 1), ((FE >> 1) & 3), ((FE >> 3) & 1), ((FE >> 4) & 3), ((FE >> 6) & 3)>(a, stg, lane, row0, col0, b0, b1);
+            __syncwarp();
+        }
+    }
+}
+
 
 // ---------------------------------------------------------------------------------------------------
 // CTA-pair variant (cta_group::2): the two CTAs of a (2,1,1) cluster share one 256 x 256 output tile.  Each CTA stages its own
@@ -510,6 +641,7 @@ struct Cfg2 {
     static constexpr int TOTAL = STAGES * STAGE_BYTES + STG_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
+template <int FE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                 const __grid_constant__ KernelArgs args) {
@@ -616,7 +748,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
                     if (col0 >= args.N) break;          // warp-uniform
                     tmem_ld_wait();
                     if (c + 1 < NCH && col0 + 32 < args.N) tmem_ld32_issue(taddr + (c + 1) * 32, r[(c + 1) & 1]);
-                    epilogue_chunk(args, r[c & 1], stg, lane, row0, col0, b0, b1, bz);
+                    if (!args.dbg) epilogue_chunk_t<FE>(args, r[c & 1], stg, lane, row0, col0, b0, b1, bz);
                 }
                 tmem_ld_wait();
             }
@@ -733,6 +865,11 @@ static int resid_mode(const GemmEpilogue& e) {
     return (in_place && red_ok) ? 2 : 1;
 }
 
+static int dbg_knob() {
+    static const int v = [] { const char* e = getenv("WC_GEMM_DBG"); return e ? atoi(e) : 0; }();
+    return v;
+}
+
 // A streamed once instead of once per n-tile: worth it when A does not fit L2 next to everything else and B does
 static int raster_n_fastest(const GemmProblem& p) {
     const double a_bytes = 2.0 * p.M * p.K, b_bytes = 2.0 * p.N * p.K;
@@ -761,6 +898,7 @@ static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
     ka.total_tiles = (int)total;
     ka.vec_ok = epilogue_vec_ok(p.epi);
     ka.n_fastest = raster_n_fastest(p);
+    ka.dbg = dbg_knob();
     ka.variant = variant_id(p.epi.out_f16 ? 1 : 0, p.epi.act, p.epi.bias ? 1 : 0, resid_mode(p.epi),
                             p.epi.out2 ? (p.epi.out2_preact ? 2 : 1) : 0);
     const int grid = (int)(total < num_sms() ? total : num_sms());
@@ -771,13 +909,38 @@ static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
     return WC_OK;
 }
 
-static int launch_pair(const GemmProblem& p, cudaStream_t st) {
-    using C = Cfg2;
+template <int FE>
+static int launch_pair_fe(const CUtensorMap& mA, const CUtensorMap& mB, const KernelArgs& ka, int grid, cudaStream_t st) {
     static bool attr_set = false;
     if (!attr_set) {
-        WC_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::TOTAL));
+        WC_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<FE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2::TOTAL));
         attr_set = true;
     }
+    gemm_tc2_kernel<FE><<<grid, GEMM_THREADS, Cfg2::TOTAL, st>>>(mA, mB, ka);
+    return WC_OK;
+}
+
+// epilogue specialisation of the pair kernel for this problem (FE_GENERIC when no instantiation matches)
+static int pick_fast_epilogue(const GemmProblem& p, const KernelArgs& ka) {
+    static const bool on = [] { const char* v = getenv("WC_GEMM_FE"); return !(v && v[0] == '0'); }();
+    if (!on || (p.N & 31) || !ka.vec_ok) return FE_GENERIC;
+    auto a16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    if (p.epi.mode == GM_QKV) {
+        const GemmEpilogue& e = p.epi;
+        const bool ok = e.L >= 8 && (e.hd & 7) == 0 && (!e.q || a16(e.q)) && (!e.k || a16(e.k)) && (!e.v || a16(e.v));
+        return ok ? FE_QKV : FE_GENERIC;
+    }
+    if (p.epi.mode == GM_MUL_QGELU_GRAD) return FE_QGRAD;
+    if (p.epi.mode != GM_STORE || p.epi.out_trans) return FE_GENERIC;
+    // fp16 outputs without residual / second output go through 16-byte vector stores
+    if (p.epi.out_f16 && !p.epi.resid && !p.epi.out2 &&
+        !(a16(p.epi.out) && (p.epi.ldo & 7) == 0 && (p.epi.out_bs0 & 7) == 0 && (p.epi.out_bs1 & 7) == 0))
+        return FE_GENERIC;
+    return ka.variant;
+}
+
+static int launch_pair(const GemmProblem& p, cudaStream_t st) {
+    using C = Cfg2;
     CUtensorMap mA, mB;
     KernelArgs ka;
     ka.M = p.M; ka.N = p.N; ka.K = p.K; ka.nb0 = p.nb0; ka.e = p.epi;
@@ -792,6 +955,7 @@ static int launch_pair(const GemmProblem& p, cudaStream_t st) {
     ka.total_tiles = (int)total;
     ka.vec_ok = epilogue_vec_ok(p.epi);
     ka.n_fastest = raster_n_fastest(p);
+    ka.dbg = dbg_knob();
     ka.variant = variant_id(p.epi.out_f16 ? 1 : 0, p.epi.act, p.epi.bias ? 1 : 0, resid_mode(p.epi),
                             p.epi.out2 ? (p.epi.out2_preact ? 2 : 1) : 0);
     const long pair_tiles = (long)((ka.tiles_m + 1) / 2) * ka.tiles_n * p.nb0 * p.nb1;
@@ -799,7 +963,24 @@ static int launch_pair(const GemmProblem& p, cudaStream_t st) {
     const int grid = 2 * (int)(pair_tiles < pairs ? pair_tiles : pairs);
     ProfScope prof(PK_GEMM, 2.0 * p.M * p.N * p.K * p.nb0 * p.nb1, st);
     if (g_prof_on) prof_tag(p.M, p.N, p.K, p.nb0 * p.nb1);
-    gemm_tc2_kernel<<<grid, GEMM_THREADS, C::TOTAL, st>>>(mA, mB, ka);
+#define WC_FE(id) case id: rc = launch_pair_fe<id>(mA, mB, ka, grid, st); break;
+    switch (pick_fast_epilogue(p, ka)) {
+        WC_FE(FE_QKV)                                       // packed in-proj + head split
+        WC_FE(FE_QGRAD)                                     // Grad-CAM c_proj^T with the QuickGELU' factor
+        WC_FE(variant_id(1, ACT_QUICKGELU, 1, 0, 0))        // c_fc
+        WC_FE(variant_id(1, ACT_QUICKGELU, 1, 0, 2))        // c_fc keeping the pre-activation (Grad-CAM block)
+        WC_FE(variant_id(0, ACT_NONE, 1, 2, 0))             // out-proj / c_proj adding into x in place
+        WC_FE(variant_id(0, ACT_NONE, 1, 1, 1))             // c_proj + residual + fp16 tap (last encoder block)
+        WC_FE(variant_id(0, ACT_NONE, 1, 1, 0))             // + residual into another buffer
+        WC_FE(variant_id(1, ACT_RELU, 1, 0, 0))             // decoder fuse MLP layer 1
+        WC_FE(variant_id(1, ACT_NONE, 1, 0, 0))             // decoder fuse MLP layer 2
+        WC_FE(variant_id(0, ACT_NONE, 1, 0, 1))             // linear_fuse (+ fp16 copy)
+        WC_FE(variant_id(0, ACT_NONE, 0, 0, 0))             // plain fp32
+        WC_FE(variant_id(1, ACT_NONE, 0, 0, 0))             // plain fp16
+        default: rc = launch_pair_fe<FE_GENERIC>(mA, mB, ka, grid, st); break;
+    }
+#undef WC_FE
+    if (rc) return rc;
     WC_LAUNCH_CHECK();
     return WC_OK;
 }
