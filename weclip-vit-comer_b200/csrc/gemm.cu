@@ -55,7 +55,7 @@ struct KernelArgs {
     int vec_ok;                   // every pointer / stride of the epilogue allows 4-element vector access
     int variant;                  // variant_id() of the GM_STORE flags (fast epilogue dispatch)
     int n_fastest;                // tile raster (decode_tile)
-    int dbg;                      // developer knob (WC_GEMM_DBG): 1 = epilogue drains tensor memory but stores nothing
+    int dbg;                      // developer knob (WC_GEMM_DBG): 1 = epilogue only drains tensor memory, 3 = everything but the global stores
     GemmEpilogue e;
 };
 
@@ -117,7 +117,7 @@ __device__ __forceinline__ void fast_store(const KernelArgs& a, const float* stg
         // wait for the residual tile to come back from HBM
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            if (r_first + 4 * i >= a.M) break;
+            if (r_first + 4 * i >= a.M || a.dbg == 3) break;
             float* p = reinterpret_cast<float*>(e.out) + ob + (long)(4 * i) * e.ldo;
             asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(e.alpha * x[i].x + bias.x),
                          "f"(e.alpha * x[i].y + bias.y), "f"(e.alpha * x[i].z + bias.z), "f"(e.alpha * x[i].w + bias.w) : "memory");
@@ -232,7 +232,7 @@ __device__ __forceinline__ void fast_store16(const KernelArgs& a, const uint32_t
     for (int i = 0; i < 4; ++i) v[i] = *reinterpret_cast<const uint4*>(sb + stg16_off(i * 8 + rg, slot));
 #pragma unroll
     for (int i = 0; i < 4; ++i)
-        if (row0 + rg + 8 * i < a.M) *reinterpret_cast<uint4*>(o + (long)(8 * i) * e.ldo) = v[i];
+        if (row0 + rg + 8 * i < a.M && a.dbg != 3) *reinterpret_cast<uint4*>(o + (long)(8 * i) * e.ldo) = v[i];
     __syncwarp();
 }
 
@@ -252,7 +252,7 @@ __device__ __forceinline__ void fast_qkv16(const KernelArgs& a, const uint32_t* 
     int img = row / e.L, l = row - img * e.L;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        if (row < a.M) *reinterpret_cast<uint4*>(dst + (((long)img * e.heads + head) * e.L + l) * e.hd + d0 + slot * 8) = v[i];
+        if (row < a.M && a.dbg != 3) *reinterpret_cast<uint4*>(dst + (((long)img * e.heads + head) * e.L + l) * e.hd + d0 + slot * 8) = v[i];
         row += 8; l += 8;
         if (l >= e.L) { l -= e.L; ++img; }
     }
@@ -549,7 +549,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
                     if (col0 >= args.N) break;          // warp-uniform
                     tmem_ld_wait();
                     if (c + 1 < NCH && col0 + 32 < args.N) tmem_ld32_issue(taddr + (c + 1) * 32, r[(c + 1) & 1]);
-                    if (!args.dbg) epilogue_chunk(args, r[c & 1], stg, lane, row0, col0, b0, b1, bz);
+                    if (args.dbg != 1) epilogue_chunk(args, r[c & 1], stg, lane, row0, col0, b0, b1, bz);
                 }
                 tmem_ld_wait();
             }
@@ -748,7 +748,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
                     if (col0 >= args.N) break;          // warp-uniform
                     tmem_ld_wait();
                     if (c + 1 < NCH && col0 + 32 < args.N) tmem_ld32_issue(taddr + (c + 1) * 32, r[(c + 1) & 1]);
-                    if (!args.dbg) epilogue_chunk_t<FE>(args, r[c & 1], stg, lane, row0, col0, b0, b1, bz);
+                    if (args.dbg != 1) epilogue_chunk_t<FE>(args, r[c & 1], stg, lane, row0, col0, b0, b1, bz);
                 }
                 tmem_ld_wait();
             }
