@@ -271,6 +271,8 @@ def main():
     e0.record()
     for _ in range(args.steps):
         wl.step_device(record=True)
+    if hasattr(wl, "join"):
+        wl.join()            # the step's passes run on the workload's own streams: order the timing stream after them
     e1.record()
     barrier()
     ms_dev = e0.elapsed_time(e1)

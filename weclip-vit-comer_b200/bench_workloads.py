@@ -84,7 +84,8 @@ class MscFlipVoc:
         self.model = WeCLIP(num_classes=self.n_classes, dataset_root_path=self.root, device=device,
                             dataset=self.dataset, state_dict=self.sd, fg_text_features=self.fg,
                             bg_text_features=self.bg)
-        self.ev = MscFlipEvaluator(self.model, self.n_classes, self.scales, 512, device)
+        self.ev = MscFlipEvaluator(self.model, self.n_classes, self.scales, 512, device,
+                                   overlap_scales=os.environ.get("WC_OVERLAP_SCALES", "1") != "0")
         self.imgs_h = imgs.pin_memory()
         self.labs_h = torch.from_numpy(np.stack(labs).astype(np.int16)).pin_memory()
         self.imgs_d = self.imgs_h.to(device)
@@ -102,11 +103,15 @@ class MscFlipVoc:
         # the step's images share one (H,W) bucket: one [2B,3,H,W] forward per scale
         self.ev.process_batch(self.names, self.imgs_d, self.labs_d)
 
+    def join(self):
+        """Order the current stream after every step enqueued so far (the passes run on the evaluator's own streams)."""
+        self.ev.join()
+
     def step_e2e(self):
         img = self.imgs_h.to(self.dev, non_blocking=True)
         lab = self.labs_h.to(self.dev, non_blocking=True)
         self.ev.process_batch(self.names, img, lab)
-        self.hist_h.copy_(self.ev.hist, non_blocking=True)
+        self.hist_h.copy_(self.ev.hist, non_blocking=True)      # .hist orders this stream after the step's passes
         torch.cuda.current_stream().synchronize()
         return self.hist_h
 
@@ -114,8 +119,14 @@ class MscFlipVoc:
         """Separate pass with the C-side profiler on: per-kernel-class device time and algorithmic work."""
         L = _lib.lib()
         L.wc_prof_reset(); L.wc_prof_enable(1)
+        ev = getattr(self, "ev", None)
+        overlap = ev.overlap_scales if ev is not None else False
+        if ev is not None:
+            ev.overlap_scales = False      # per-kernel times are taken with each kernel alone on the device
         for _ in range(steps):
             self.step_device()
+        if ev is not None:
+            ev.overlap_scales = overlap
         summ = prof_summary()
         L.wc_prof_enable(0); L.wc_prof_reset()
         self._prof = {k: (ms / steps, work / steps, cnt // steps) for k, (ms, work, cnt) in summ.items()}

@@ -45,7 +45,7 @@ class Engine:
         self.device = torch.device(device)
         self.num_classes = num_classes
         self._keep: List[torch.Tensor] = []
-        self._ws: Dict[str, torch.Tensor] = {}
+        self._ws: Dict[tuple, torch.Tensor] = {}
         self.vit = VitW()
         self.dec = DecW()
         self.load_state_dict(state_dict)
@@ -108,10 +108,12 @@ class Engine:
 
     # ------------------------------------------------------------------ workspaces
     def _workspace(self, name: str, nbytes: int) -> torch.Tensor:
-        ws = self._ws.get(name)
+        # one scratch arena per (call kind, CUDA stream): the msc+flip driver runs its scales on separate streams
+        key = (name, torch.cuda.current_stream(self.device).cuda_stream if self.device.type == "cuda" else 0)
+        ws = self._ws.get(key)
         if ws is None or ws.numel() < nbytes:
             ws = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
-            self._ws[name] = ws
+            self._ws[key] = ws
         return ws
 
     # ------------------------------------------------------------------ calls

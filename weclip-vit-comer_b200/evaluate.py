@@ -35,14 +35,61 @@ def shard_indices(n_items: int, rank: int, world: int) -> range:
 
 class MscFlipEvaluator:
     def __init__(self, model, num_classes: int = 21, test_scales: Sequence[float] = (1.0, 0.75, 1.25),
-                 resize_long: int = 512, device="cuda"):
+                 resize_long: int = 512, device="cuda", overlap_scales: bool = True):
         self.model = model
         self.C = num_classes
         self.scales = list(test_scales)
         self.resize_long = resize_long
         self.device = torch.device(device)
-        self.hist = torch.zeros(3, num_classes, num_classes, dtype=torch.int64, device=self.device)  # seg, msc, cam
+        self._hist = torch.zeros(3, num_classes, num_classes, dtype=torch.int64, device=self.device)  # seg, msc, cam
         self.n_images = 0
+        # The scales of one image are independent forward passes: each runs on its own CUDA stream so that one pass's
+        # tail waves and bandwidth-bound kernels (LayerNorm, PAR) fill in under another pass's tensor-core kernels.  The
+        # fusion / histogram tail runs on a fourth stream and the caller's stream is NOT made to wait for it, so the
+        # next image's passes start while this image's longest pass is still running; join() (called by all_reduce /
+        # scores, or by the caller) orders the caller's stream after everything enqueued so far.
+        self.overlap_scales = bool(overlap_scales) and self.device.type == "cuda"
+        self._side_streams = []
+        self._acc_stream = None
+
+    def _streams(self, n):
+        while len(self._side_streams) < n:
+            self._side_streams.append(torch.cuda.Stream(self.device))
+        if self._acc_stream is None:
+            self._acc_stream = torch.cuda.Stream(self.device)
+        return self._side_streams[:n], self._acc_stream
+
+    @property
+    def hist(self) -> torch.Tensor:
+        """The three C x C confusion matrices (seg, msc seg, CAM), valid on the current stream."""
+        self.join()
+        return self._hist
+
+    def join(self):
+        """Order the current stream after all evaluation work enqueued so far (no host synchronisation)."""
+        if self._acc_stream is not None:
+            main = torch.cuda.current_stream(self.device)
+            main.wait_stream(self._acc_stream)
+            for st in self._side_streams:
+                main.wait_stream(st)
+
+    def _forward_scales(self, base: torch.Tensor, names, side):
+        """model([x_s, flip(x_s)]) for scale 1.0 and every other test scale -> list of (segs, cam), scale 1.0 first.
+        side: one stream per scale (already ordered after `base`), or None to run on the current stream."""
+        scales = [1.0] + [s for s in self.scales if s != 1.0]
+
+        def fwd(s):
+            x = base if s == 1.0 else ops.resize_bilinear(base, scale_factor=s)
+            segs, cam, _ = self.model(ops.flip_concat(x), names, mode="val")
+            return segs, cam
+
+        if side is None:
+            return [fwd(s) for s in scales]
+        outs = [None] * len(scales)
+        for i in sorted(range(len(scales)), key=lambda i: -scales[i]):      # longest pass first
+            with torch.cuda.stream(side[i]):
+                outs[i] = fwd(scales[i])
+        return outs
 
     def reset(self):
         self.hist.zero_()
@@ -66,22 +113,49 @@ class MscFlipEvaluator:
                                  # reference's one-name call does for its [image, flip] pair (model_attn_aff_voc.py:139)
         _, _, h0, w0 = inputs.shape
         ratio = self.resize_long / max(h0, w0)
+        n_sc = 1 + sum(1 for s in self.scales if s != 1.0)
+        labels = labels.contiguous()
         base = ops.resize_bilinear(inputs, size=(int(h0 * ratio), int(w0 * ratio)))          # :60-63
-        segs_cat, cam, _ = self.model(ops.flip_concat(base), names, mode="val")             # :68-69
+        if not self.overlap_scales:
+            return self._fuse(self._forward_scales(base, names, None), B, labels, want_preds)
+        main = torch.cuda.current_stream(self.device)
+        side, acc = self._streams(n_sc)
+        ready = torch.cuda.Event()
+        ready.record(main)
+        for st in side + [acc]:
+            st.wait_event(ready)
+        outs = self._forward_scales(base, names, side)                                       # :68-69, :79-88
+        for st in side:
+            acc.wait_stream(st)
+            base.record_stream(st)           # allocated on the caller's stream, read on the side streams
+        for t in (labels, inputs):
+            t.record_stream(acc)
+        for segs, cam in outs:               # allocated on a side stream, read on the fusion stream
+            segs.record_stream(acc)
+            if cam is not None:
+                cam.record_stream(acc)
+        with torch.cuda.stream(acc):
+            res = self._fuse(outs, B, labels, want_preds)
+        if want_preds:
+            main.wait_stream(acc)
+            for t in res:
+                if t is not None:
+                    t.record_stream(main)
+        return res
+
+    def _fuse(self, outs, B, labels, want_preds):
+        segs_cat, cam = outs[0]
         C, h, w = segs_cat.shape[1:]
-        n_scales = 1 + sum(1 for s in self.scales if s != 1.0)
+        n_scales = len(outs)
         msc = torch.empty(B, C, h, w, dtype=torch.float32, device=self.device)
         ops.msc_accumulate(segs_cat, msc, 1.0 / n_scales, True)                              # :74
-        for s in self.scales:                                                                # :79-88
-            if s != 1.0:
-                sc, _, _ = self.model(ops.flip_concat(ops.resize_bilinear(base, scale_factor=s)), names, mode="val")
-                ops.msc_accumulate(sc, msc, 1.0 / n_scales, False)
+        for sc, _ in outs[1:]:
+            ops.msc_accumulate(sc, msc, 1.0 / n_scales, False)
         size = labels.shape[-2:]
-        labels = labels.contiguous()
-        seg_pred = ops.upsample_argmax_hist(segs_cat[:B], size, labels, self.hist[0], want_preds)  # :93-94
-        msc_pred = ops.upsample_argmax_hist(msc, size, labels, self.hist[1], want_preds)           # :95-96
+        seg_pred = ops.upsample_argmax_hist(segs_cat[:B], size, labels, self._hist[0], want_preds)  # :93-94
+        msc_pred = ops.upsample_argmax_hist(msc, size, labels, self._hist[1], want_preds)           # :95-96
         if cam is not None:                                                                  # :71, :107
-            ops.confusion_hist(cam[:B], labels, self.hist[2])
+            ops.confusion_hist(cam[:B], labels, self._hist[2])
         self.n_images += B
         if want_preds:
             return seg_pred, msc_pred, (cam[:B] if cam is not None else None), msc
@@ -90,9 +164,10 @@ class MscFlipEvaluator:
     def all_reduce(self):
         """The only collective of the path: sum the three C x C histograms over ranks (NCCL over NVLink)."""
         import torch.distributed as dist
+        hist = self.hist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-            dist.all_reduce(self.hist, op=dist.ReduceOp.SUM)
-        return self.hist
+            dist.all_reduce(hist, op=dist.ReduceOp.SUM)
+        return hist
 
     def scores(self) -> dict:
         h = self.hist.cpu().numpy()

@@ -55,6 +55,13 @@ class LabelReader:
         return ids, lab.shape[0], lab.shape[1]
 
 
+def _to_device_async(t: torch.Tensor, device) -> torch.Tensor:
+    """Small host tensor -> device without a stream synchronisation (pinned staging, asynchronous copy)."""
+    if torch.device(device).type != "cuda":
+        return t.to(device)
+    return t.pin_memory().to(device, non_blocking=True)
+
+
 class WeCLIP(nn.Module):
     def __init__(self, num_classes=None, clip_model=None, embedding_dim=256, in_channels=512, dataset_root_path=None,
                  device="cuda", dataset: str = "voc", fg_text_features: Optional[torch.Tensor] = None,
@@ -123,6 +130,17 @@ class WeCLIP(nn.Module):
         return os.path.join(self.root_path, self._label_subdir, str(name) + ".png")
 
     @torch.no_grad()
+    def _text_table(self, device):
+        """[fg; bg] text features as one fp32 device table (rebuilt only when the attributes change)."""
+        fg, bg = self.fg_text_features, self.bg_text_features
+        key = (fg.data_ptr(), bg.data_ptr(), fg._version, bg._version, tuple(fg.shape), tuple(bg.shape), str(device))
+        if getattr(self, "_text_key", None) != key:
+            self._text_tbl = torch.cat([fg.to(device, torch.float32), bg.to(device, torch.float32)], dim=0).contiguous()
+            self._text_key = key
+            if torch.device(device).type == "cuda":
+                torch.cuda.current_stream(device).synchronize()   # one-time: other streams may read the table next
+        return self._text_tbl, fg.shape[0], bg.shape[0]
+
     def forward(self, img, img_names="2007_000032", mode="train"):
         _lib.require_device()
         if self.engine is None:
@@ -150,19 +168,22 @@ class WeCLIP(nn.Module):
             return seg, None, attn_pred
         N_all, N = N, n_cam
 
+        # nothing below may block the host on the stream (a pageable host->device copy does): the text rows are gathered
+        # on the device from a cached [fg; bg] table with an index vector that travels from pinned memory
         ids_all, sizes, text_off, k_off, rows = [], [], [0], [0], []
-        fg = self.fg_text_features.to(eng.device, torch.float32)
-        bg = self.bg_text_features.to(eng.device, torch.float32)
+        table, n_fg, n_bg = self._text_table(eng.device)
         for name in img_names:
             ids, oh, ow = self.label_reader(self._label_path(name))
             ids_all.append(ids)
             sizes.append((H, W) if mode == "train" else (oh, ow))     # clip_tool.py:194-197
-            rows += [fg[ids], bg]
-            text_off.append(text_off[-1] + len(ids) + bg.shape[0])
+            rows += list(ids) + list(range(n_fg, n_fg + n_bg))
+            text_off.append(text_off[-1] + len(ids) + n_bg)
             k_off.append(k_off[-1] + len(ids))
         if any(len(i) == 0 for i in ids_all):
             raise RuntimeError("image without foreground label (torch.stack([]) in the reference, clip_tool.py:212)")
-        text = torch.cat(rows, dim=0)
+        if any(i < 0 or i >= n_fg for ids in ids_all for i in ids):
+            raise IndexError("label id outside the foreground text features")
+        text = table.index_select(0, _to_device_async(torch.tensor(rows, dtype=torch.int64), eng.device))
         cams, _, _ = eng.gradcam(x_last, N, h, w, text, text_off, k_off, attn_last_out=attn[nl - 1])
         refined, bmasks = eng.affinity_refine(attn, nl, attn_pred, N, h, w, require_seg_trans, cams, k_off,
                                               cfg["box_thr"], want_masks=self.keep_intermediates)
@@ -174,6 +195,7 @@ class WeCLIP(nn.Module):
         par_in = eng.cam_upsample_bg(refined, k_off, N, h, w, Hc, Wc, float(self.cam_bg_thres))
         ch_off = [k_off[i] + i for i in range(N + 1)]
         par_out = self.par.refine_ragged(img[:N], par_in, ch_off)
-        lut = torch.tensor([v for ids in ids_all for v in [0] + [i + 1 for i in ids]], dtype=torch.int64)
+        lut = _to_device_async(torch.tensor([v for ids in ids_all for v in [0] + [i + 1 for i in ids]], dtype=torch.int64),
+                               eng.device)
         labels = argmax_lut(par_out, lut, ch_off)
         return seg, labels, attn_pred

@@ -32,12 +32,16 @@ class PAR(nn.Module):
         self.dim = 2
         self.w1 = 0.3
         self.w2 = 0.01
-        self._ws = None
+        self._ws = {}
 
     def _workspace(self, nbytes: int, device) -> torch.Tensor:
-        if self._ws is None or self._ws.numel() < nbytes or self._ws.device != device:
-            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
-        return self._ws
+        # one scratch arena per (device, CUDA stream): callers may run independent batches on separate streams
+        key = (str(device), torch.cuda.current_stream(device).cuda_stream if device.type == "cuda" else 0)
+        ws = self._ws.get(key)
+        if ws is None or ws.numel() < nbytes:
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+            self._ws[key] = ws
+        return ws
 
     def refine_ragged(self, imgs: torch.Tensor, masks: torch.Tensor, ch_off) -> torch.Tensor:
         """imgs [B,3,Hi,Wi]; masks packed [sumKc,H,W] with image b owning channels ch_off[b]:ch_off[b+1]."""
