@@ -234,6 +234,37 @@ int wc_upsample_argmax_hist(const float* logits, int B, int C, int h, int w, int
  * pred int64 [n], gt int16 [n], hist int64 [C,C] accumulated in place. */
 int wc_confusion_hist(const int64_t* pred, const int16_t* gt, long n, int C, int64_t* hist, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Training-time label prep and losses on the hot path's outputs: the step right after
+ * WeCLIP.forward in scripts/dist_clip_voc.py:246-258.  workspace: wc_labelprep_workspace_bytes(B,H,W) bytes
+ * (64 are enough for wc_aff_loss / wc_seg_loss); each call zeroes the part it uses.
+ * ---------------------------------------------------------------------------------------------- */
+size_t wc_labelprep_workspace_bytes(int B, int H, int W);
+/* get_mask_by_radius (scripts/dist_clip_voc.py:116-133): mask uint8 [h*w, h*w], 1 where |dy| <= radius and
+ * |dx| <= radius between patches. */
+int wc_radius_mask(int h, int w, int radius, uint8_t* mask, void* stream);
+/* cams_to_affinity_label (utils/camutils.py:226-247): cam_label int64 [B,H,W] -> nearest down-sample to
+ * (H/16, W/16) -> aff_label int64 [B,P,P]: 1 equal labels, 0 different, ignore_index where radius_mask == 0
+ * (uint8 [P,P], may be NULL) or either patch label == ignore_index. */
+int wc_affinity_label(const int64_t* cam_label, int B, int H, int W, const uint8_t* radius_mask, int ignore_index,
+                      int64_t* aff_label, void* workspace, size_t workspace_bytes, void* stream);
+/* get_aff_loss (utils/losses.py:11-22): loss[0] = 0.5 sum_{t==1}(1-x)/(n_pos+1) + 0.5 sum_{t==0} x/(n_neg+1),
+ * counts = {n_pos+1, n_neg+1}; grad (fp32 [n], may be NULL) = d loss / d inputs.  128-bit accesses when n % 4 == 0
+ * and the pointers are 16-byte aligned, scalar otherwise. */
+int wc_aff_loss(const float* inputs, const int64_t* targets, long n, float* loss, int64_t* counts, float* grad,
+                void* workspace, size_t workspace_bytes, void* stream);
+/* The same loss straight from the pseudo-labels: targets are derived on the fly (cams_to_affinity_label with the
+ * get_mask_by_radius(radius) mask; radius < 0 = no mask), so the [B,P,P] int64 label tensor is never written or
+ * read.  attn_pred fp32 [B,P,P], P = (H/16)*(W/16) (128-bit accesses when P % 4 == 0). */
+int wc_aff_loss_fused(const float* attn_pred, const int64_t* cam_label, int B, int H, int W, int radius,
+                      int ignore_index, float* loss, int64_t* counts, float* grad, void* workspace,
+                      size_t workspace_bytes, void* stream);
+/* get_seg_loss (utils/losses.py:24-33): 0.5 * (CE over label==0 pixels + CE over foreground pixels), each a mean
+ * over its own pixels (nan when it has none, like F.cross_entropy).  pred fp32 [B,C,H,W], label int64 [B,H,W];
+ * grad fp32 [B,C,H,W] (may be NULL) = d loss / d pred. */
+int wc_seg_loss(const float* pred, const int64_t* label, int B, int C, int H, int W, int ignore_index, float* loss,
+                float* grad, void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -143,6 +143,46 @@ def golden_weclip(dataset, num_classes, n_fg, n_bg, subdir):
               probs0=probs.detach().numpy(), attn_last0=attn_last.detach().numpy())
 
 
+def training_case(seed=17, B=3, H=96, W=112, C=21):
+    """Seeded inputs of the label-prep / loss golden case (regenerated bit-identically by the tests)."""
+    g = torch.Generator().manual_seed(seed)
+    cam = torch.randint(0, 4, (B, H // 8, W // 8), generator=g).repeat_interleave(8, 1).repeat_interleave(8, 2)
+    cam = cam * 5                                             # classes {0, 5, 10, 15}
+    cam[:, :9, :] = 255                                       # ignored stripe (covers whole 16-px patch rows)
+    cam[1, 40:70, 50:90] = 255
+    P = (H // 16) * (W // 16)
+    attn = torch.rand(B, P, P, generator=g)
+    pred = torch.randn(B, C, H, W, generator=g) * 3
+    return cam, attn, pred
+
+
+def golden_training():
+    fns = ref_harness.reference_training_fns()
+    cam, attn, pred = training_case()
+    B, H, W = cam.shape
+    h, w = H // 16, W // 16
+    out = {}
+    for r in (2, 8):
+        mask = fns["get_mask_by_radius"](h=h, w=w, radius=r)
+        aff = fns["cams_to_affinity_label"](cam.clone(), mask=mask, ignore_index=255)
+        loss, pc, nc = fns["get_aff_loss"](attn, aff)
+        out[f"mask_r{r}"] = mask.astype(np.uint8)
+        out[f"aff_r{r}"] = aff.numpy().astype(np.int16)
+        out[f"affloss_r{r}"] = np.array([float(loss), float(pc), float(nc)])
+    aff = fns["cams_to_affinity_label"](cam.clone(), mask=None, ignore_index=255)
+    out["aff_nomask"] = aff.numpy().astype(np.int16)
+    x = attn.clone().requires_grad_(True)
+    loss, _, _ = fns["get_aff_loss"](x, torch.from_numpy(out["aff_r2"].astype(np.int64)))
+    loss.backward()
+    out["affgrad_r2"] = x.grad.numpy()
+    p = pred.clone().requires_grad_(True)
+    sl = fns["get_seg_loss"](p, cam.long(), ignore_index=255)
+    sl.backward()
+    out["segloss"] = np.array([float(sl)])
+    out["seggrad_sample"] = p.grad[:, :, ::7, ::5].contiguous().numpy()
+    _save("training.npz", **out)
+
+
 def main():
     assert ref_harness.available(), "/root/reference is required (build container only)"
     os.makedirs(OUT, exist_ok=True)
@@ -150,6 +190,7 @@ def main():
     ref = ref_harness.reference_modules()
     golden_par(ref)
     golden_small_ops(ref)
+    golden_training()
     golden_weclip("voc", 21, 20, 25, "SegmentationClassAug")
     golden_weclip("coco", 81, 80, 23, os.path.join("SegmentationClass", "train"))
 

@@ -111,3 +111,30 @@ def reference_modules():
     from utils import evaluate
     return dict(PAR=PAR, compute_trans_mat=compute_trans_mat, scoremap2bbox=scoremap2bbox,
                 scale_cam_image=scale_cam_image, generate_cam_label=generate_cam_label, evaluate=evaluate)
+
+
+def reference_training_fns():
+    """The label-prep / loss functions of SURVEY.md §8f-3.  ``get_mask_by_radius`` lives in a script whose top level
+    needs omegaconf etc., so only that one function's source is extracted (ast) and executed from where it lies."""
+    import ast
+    import numpy as np
+    _install_shims()
+    if "matplotlib" not in sys.modules:          # utils/imutils.py:5 imports pyplot for plotting helpers only
+        m = types.ModuleType("matplotlib"); pp = types.ModuleType("matplotlib.pyplot"); m.pyplot = pp
+        sys.modules["matplotlib"] = m; sys.modules["matplotlib.pyplot"] = pp
+    if "pydensecrf" not in sys.modules:          # utils/dcrf.py (CRF post-processing, off the path)
+        m = types.ModuleType("pydensecrf"); d = types.ModuleType("pydensecrf.densecrf")
+        u = types.ModuleType("pydensecrf.utils"); u.unary_from_labels = u.unary_from_softmax = None
+        m.densecrf = d; m.utils = u
+        sys.modules["pydensecrf"] = m; sys.modules["pydensecrf.densecrf"] = d; sys.modules["pydensecrf.utils"] = u
+    if "imageio" not in sys.modules:             # utils/camutils.py:6, image dumps only
+        sys.modules["imageio"] = types.ModuleType("imageio")
+    from utils.camutils import cams_to_affinity_label
+    from utils.losses import get_aff_loss, get_seg_loss
+    path = os.path.join(REFERENCE_ROOT, "scripts", "dist_clip_voc.py")
+    tree = ast.parse(open(path).read())
+    fn = next(n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "get_mask_by_radius")
+    ns = {"np": np}
+    exec(compile(ast.Module(body=[fn], type_ignores=[]), path, "exec"), ns)
+    return dict(cams_to_affinity_label=cams_to_affinity_label, get_aff_loss=get_aff_loss, get_seg_loss=get_seg_loss,
+                get_mask_by_radius=ns["get_mask_by_radius"])

@@ -401,6 +401,50 @@ def weclip_forward(img: Tensor, label_maps: Sequence[np.ndarray], sd: Dict[str, 
 
 
 # --------------------------------------------------------------------------------------------------
+# training-time label prep and losses on the path's outputs
+# --------------------------------------------------------------------------------------------------
+def mask_by_radius(h: int = 20, w: int = 20, radius: int = 8) -> np.ndarray:
+    """scripts/dist_clip_voc.py:116-133 (closed form: the reference's symmetric double write marks exactly the
+    pairs whose row and column offsets are both <= radius)."""
+    ys, xs = np.divmod(np.arange(h * w), w)
+    return ((np.abs(ys[:, None] - ys[None, :]) <= radius) & (np.abs(xs[:, None] - xs[None, :]) <= radius)).astype(
+        np.float64)
+
+
+def affinity_label(cam_label: Tensor, mask=None, ignore_index: int = 255) -> Tensor:
+    """utils/camutils.py:226-247: nearest down-sample by 16, pairwise label equality, ignore outside the radius mask
+    and on rows / columns whose own label is ignore_index."""
+    b, h, w = cam_label.shape
+    small = F.interpolate(cam_label.unsqueeze(1).float(), size=[h // 16, w // 16], mode="nearest").reshape(b, -1)
+    aff = (small[:, None, :] == small[:, :, None]).long()
+    if mask is not None:
+        aff[:, torch.as_tensor(np.asarray(mask) == 0)] = ignore_index
+    ign = small == ignore_index
+    aff[ign[:, None, :].expand_as(aff)] = ignore_index
+    aff[ign[:, :, None].expand_as(aff)] = ignore_index
+    return aff
+
+
+def aff_loss(inputs: Tensor, targets: Tensor):
+    """utils/losses.py:11-22."""
+    pos, neg = targets == 1, targets == 0
+    pos_count, neg_count = pos.sum() + 1, neg.sum() + 1
+    pos_loss = (1 - inputs)[pos].double().sum() / pos_count
+    neg_loss = inputs[neg].double().sum() / neg_count
+    return (0.5 * pos_loss + 0.5 * neg_loss).float(), pos_count, neg_count
+
+
+def seg_loss(pred: Tensor, label: Tensor, ignore_index: int = 255) -> Tensor:
+    """utils/losses.py:24-33: mean NLL over label==0 pixels and over foreground pixels, averaged."""
+    logp = torch.log_softmax(pred.double(), dim=1)
+    lab = label.long()
+    valid = lab != ignore_index
+    nll = -logp.gather(1, lab.clamp(0, pred.shape[1] - 1).unsqueeze(1)).squeeze(1)
+    bg, fg = valid & (lab == 0), valid & (lab != 0)
+    return ((nll[bg].sum() / bg.sum() + nll[fg].sum() / fg.sum()) * 0.5).float()
+
+
+# --------------------------------------------------------------------------------------------------
 # a15/a16 msc+flip driver and scores
 # --------------------------------------------------------------------------------------------------
 def fast_hist(gt: np.ndarray, pred: np.ndarray, num_classes: int) -> np.ndarray:

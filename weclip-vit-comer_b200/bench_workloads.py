@@ -105,7 +105,9 @@ class MscFlipVoc:
 
     def join(self):
         """Order the current stream after every step enqueued so far (the passes run on the evaluator's own streams)."""
-        self.ev.join()
+        ev = getattr(self, "ev", None)      # workloads without an evaluator run on the current stream already
+        if ev is not None:
+            ev.join()
 
     def step_e2e(self):
         img = self.imgs_h.to(self.dev, non_blocking=True)
