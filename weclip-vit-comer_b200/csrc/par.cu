@@ -356,22 +356,13 @@ __device__ __forceinline__ void par_iter_tile_body(float* par_tile, const AffT* 
     const int H = a.H, W = a.W;
     const size_t iplane = (size_t)H * a.in_pitch, oplane = (size_t)H * a.out_pitch, aplane = (size_t)H * a.wp;
     const int ch0 = ch.ch0[c];
+    fill_tile<SH, PT_THREADS>(par_tile, in + (size_t)ch0 * iplane, iplane, a.in_pitch, KC, x0, y0, H, W, a.in_vec);
+    __syncthreads();
     const uint64_t pol = l2_evict_first_policy();
     const int tx4 = threadIdx.x & 15, tyb = threadIdx.x >> 4;
     const int x = x0 + 4 * tx4;
-    const bool live = x < W;
-    const AffT* abase = aff + (size_t)ch.b[c] * 48 * aplane + (live ? x : 0);
-    // the first row pass's affinity loads (HBM) are issued BEFORE the tile fill, so the stream from DRAM is already
-    // running while the halo tile comes in from L2
-    typename AffIO<AffT>::Raw wa[8], wb[8];
-    if (live && y0 + tyb < H) {
-        const AffT* ap = abase + (size_t)(y0 + tyb) * a.wp;
-        load_weights<AffT>(wa, ap, aplane, 0, pol);
-        load_weights<AffT>(wb, ap, aplane, 1, pol);
-    }
-    fill_tile<SH, PT_THREADS>(par_tile, in + (size_t)ch0 * iplane, iplane, a.in_pitch, KC, x0, y0, H, W, a.in_vec);
-    __syncthreads();
-    if (!live) return;
+    if (x >= W) return;
+    const AffT* abase = aff + (size_t)ch.b[c] * 48 * aplane + x;
 #pragma unroll 1
     for (int pass = 0; pass < TH / 16; ++pass) {
         const int ty = tyb + 16 * pass, y = y0 + ty;
@@ -381,12 +372,11 @@ __device__ __forceinline__ void par_iter_tile_body(float* par_tile, const AffT* 
         float acc[KC][4];
 #pragma unroll
         for (int k = 0; k < KC; ++k) acc[k][0] = acc[k][1] = acc[k][2] = acc[k][3] = 0.f;
-        if (pass > 0) {
-            load_weights<AffT>(wa, ap, aplane, 0, pol);
-            load_weights<AffT>(wb, ap, aplane, 1, pol);
-        }
+        typename AffIO<AffT>::Raw wa[8], wb[8];
         if (AffIO<AffT>::LOOKAHEAD == 2) {
             typename AffIO<AffT>::Raw wc[8];
+            load_weights<AffT>(wa, ap, aplane, 0, pol);
+            load_weights<AffT>(wb, ap, aplane, 1, pol);
             load_weights<AffT>(wc, ap, aplane, 2, pol);
             accumulate_dilation<AffT, KC, SH, 1>(acc, sc, wa);
             load_weights<AffT>(wa, ap, aplane, 3, pol);
@@ -398,6 +388,8 @@ __device__ __forceinline__ void par_iter_tile_body(float* par_tile, const AffT* 
             accumulate_dilation<AffT, KC, SH, 12>(acc, sc, wb);
             accumulate_dilation<AffT, KC, SH, 24>(acc, sc, wc);
         } else {
+            load_weights<AffT>(wa, ap, aplane, 0, pol);
+            load_weights<AffT>(wb, ap, aplane, 1, pol);
             accumulate_dilation<AffT, KC, SH, 1>(acc, sc, wa);
             load_weights<AffT>(wa, ap, aplane, 2, pol);
             accumulate_dilation<AffT, KC, SH, 2>(acc, sc, wb);
