@@ -30,7 +30,7 @@ extern "C" {
 #define WC_ERR_WORKSPACE (-3)
 #define WC_ERR_UNSUPPORTED (-4)
 
-#define WC_ABI_VERSION 6
+#define WC_ABI_VERSION 7
 #define WC_PAR_MAX_DIL 8
 
 /* ABI version (bumped whenever a signature changes) and last error text. */
