@@ -25,6 +25,8 @@ constexpr int AT_STAGES = 4;
 constexpr int AT_SBUF = 3;             // score tiles buffered in tensor memory (3 x 128 columns + the output accumulator <= 512)
 constexpr int AT_SM_WARPS = 8;          // softmax warps: two per TMEM lane quarter, each owning 64 of a tile's 128 key columns
 constexpr int AT_THREADS = 64 + 32 * AT_SM_WARPS;
+constexpr int FW_PV_WARP = 2 + AT_SM_WARPS;          // forward kernel: one more warp, the P V issuer (after the softmax warps)
+constexpr int FW_THREADS = AT_THREADS + 32;
 constexpr int AT_TILE_BYTES = 128 * 64 * 2;          // one [128][64] fp16 operand tile (Q, K, V^T pair, half of P)
 constexpr float AT_LOG2E = 1.4426950408889634f;
 
@@ -64,7 +66,7 @@ struct FwdSmem {
 // rows of its accumulator (tcgen05.ld / st) — after the first tile this is rare — so P = exp2(S log2e - m) stays below 256 in
 // fp16.  The epilogue merges the halves: O = (c_A O_A + c_B O_B) / (c_A l_A + c_B l_B), c_h = 2^(m_h - max(m_A, m_B)).
 template <int HD>
-__global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap mapQ,
+__global__ void __launch_bounds__(FW_THREADS, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap mapQ,
                                                                   const __grid_constant__ CUtensorMap mapK,
                                                                   const __grid_constant__ CUtensorMap mapV,
                                                                   const __grid_constant__ AttnArgs a) {
@@ -149,18 +151,18 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             }
         }
     } else if (warp == 1) {
+        // score issuer: S[g % 3] = Q K_j^T, as far ahead as the three S buffers allow.  The P V products have their OWN issuing
+        // warp (below): one thread issuing all twelve MMAs of a tile plus its five barrier waits took ~2000 clk per tile
+        // (clock64 trace), as long as the softmax itself, and tcgen05.commit only tracks the issuing thread's MMAs anyway.
         if (lane == 0) {
-            // HD = 64: B = V is MN-major (instruction-descriptor bit 16); a 16-key MMA step then advances 16 rows of 128 bytes
             constexpr uint32_t idesc_s = make_idesc(AT_BM, AT_BN);
-            constexpr uint32_t idesc_o = make_idesc(AT_BM, HD) | (HD == 64 ? (1u << 16) : 0u);
-            constexpr uint32_t V_KSTEP = (HD == 64) ? (16 * 128) >> 4 : 2;
             int i = 0;
             for (int w = blockIdx.x; w < a.n_items; w += gridDim.x, ++i) {
                 const int g0 = i * n_kt, qb = i & 1;
                 const uint64_t dq = make_smem_desc(smem_u32(smem + FwdSmem::Q + qb * AT_TILE_BYTES));
                 mbar_wait(&q_full[qb], (i >> 1) & 1);
-                auto issue_s = [&](int j_) {           // S[g % 3] = Q K_j^T
-                    const int g = g0 + j_, s = g % AT_STAGES, b = g % AT_SBUF;
+                for (int j = 0; j < n_kt; ++j) {
+                    const int g = g0 + j, s = g % AT_STAGES, b = g % AT_SBUF;
                     mbar_wait(&k_full[s], (g / AT_STAGES) & 1);
                     mbar_wait(&s_empty[b], ((g / AT_SBUF) & 1) ^ 1);
                     tc_fence_after();
@@ -169,14 +171,21 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                     for (int k = 0; k < HD / 16; ++k) umma_f16(tmem_base + b * AT_BN, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
                     umma_commit(&s_full[b]);
                     umma_commit(&k_empty[s]);
-                    if (j_ == n_kt - 1) umma_commit(&q_empty[qb]);
-                };
-                // the scores run two tiles ahead of the P V products (three S buffers in tensor memory)
-                issue_s(0);
-                if (n_kt > 1) issue_s(1);
+                    if (j == n_kt - 1) umma_commit(&q_empty[qb]);
+                }
+            }
+        }
+    } else if (warp == FW_PV_WARP) {
+        // P V issuer: O_A += P_A V_A, O_B += P_B V_B
+        if (lane == 0) {
+            // HD = 64: B = V is MN-major (instruction-descriptor bit 16); a 16-key MMA step then advances 16 rows of 128 bytes
+            constexpr uint32_t idesc_o = make_idesc(AT_BM, HD) | (HD == 64 ? (1u << 16) : 0u);
+            constexpr uint32_t V_KSTEP = (HD == 64) ? (16 * 128) >> 4 : 2;
+            int i = 0;
+            for (int w = blockIdx.x; w < a.n_items; w += gridDim.x, ++i) {
+                const int g0 = i * n_kt;
                 mbar_wait(o_empty, (i & 1) ^ 1);        // the previous item's accumulators have been read out
                 for (int j = 0; j < n_kt; ++j) {
-                    if (j + 2 < n_kt) issue_s(j + 2);
                     const int g = g0 + j, s = g % VST, pb = g & 1;
                     mbar_wait(&v_full[s], (g / VST) & 1);
                     mbar_wait(&p_full[pb], (g >> 1) & 1);
@@ -236,6 +245,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             for (int t = 0; t < 4; ++t)
                 *reinterpret_cast<uint4*>(blk + (((cc0 + t) ^ (row & 7)) << 4)) = make_uint4(pk[4 * t], pk[4 * t + 1], pk[4 * t + 2], pk[4 * t + 3]);
         };
+        if (half == 1) asm volatile("bar.arrive 2, 256;" ::: "memory");      // the first turn goes to half 0
         int it = 0;
         for (int w = blockIdx.x; w < a.n_items; w += gridDim.x, ++it) {
             const int qt = w % a.n_qt, bh = w / a.n_qt, head = bh % a.heads, img = bh / a.heads;
@@ -252,6 +262,12 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                 const int nv = a.L - j * AT_BN - half * 64;      // this warp's columns of the tile that exist (may be <= 0)
                 uint8_t* blk = smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES + half * AT_TILE_BYTES + row * 128;
                 tmem_ld_wait();                                  // both halves were requested during the previous tile's exp work
+                // the two barrier round trips this tile needs before its exp phase (~200 clk each even when already complete) are
+                // put in flight here, under the running-maximum work
+                const bool more = j + 1 < n_kt;
+                const int bn = (g + 1) % AT_SBUF;
+                const uint32_t ok_p = mbar_try(&p_empty[pb], ((g >> 1) & 1) ^ 1);
+                const uint32_t ok_s = more ? mbar_try(&s_full[bn], ((g + 1) / AT_SBUF) & 1) : 1u;
                 const bool full = nv >= 64;                      // every tile but the last: no column masking (compile-time paths)
                 float mx = full ? max_chunk(r0, 32) : nv > 0 ? max_chunk(r0, nv) : -INFINITY;
                 tc_fence_before();
@@ -283,11 +299,10 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                     if (need) m_used = m_new;
                 }
                 // both waits come before the exp work; the next tile's TMEM loads are issued as soon as r0 / r1 have been consumed
-                mbar_wait(&p_empty[pb], ((g >> 1) & 1) ^ 1);
-                const bool more = j + 1 < n_kt;
-                const int bn = (g + 1) % AT_SBUF;
-                if (more) mbar_wait(&s_full[bn], ((g + 1) / AT_SBUF) & 1);
+                if (!ok_p) mbar_wait(&p_empty[pb], ((g >> 1) & 1) ^ 1);
+                if (!ok_s) mbar_wait(&s_full[bn], ((g + 1) / AT_SBUF) & 1);
                 tc_fence_after();
+                asm volatile("bar.sync %0, 256;" ::"r"(2 + half) : "memory");
                 if (full) {
                     prob_chunk(r0, 32, blk, 0);
                     if (more) tmem_ld32_issue(tlane + bn * AT_BN, r0);
@@ -297,6 +312,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                     if (more) tmem_ld32_issue(tlane + bn * AT_BN, r0);
                     prob_chunk(r1, nv - 32, blk, 4);
                 }
+                asm volatile("bar.arrive %0, 256;" ::"r"(2 + (half ^ 1)) : "memory");
                 if (more) tmem_ld32_issue(tlane + bn * AT_BN + 32, r1);
                 fence_async_smem();
                 tc_fence_before();
@@ -346,6 +362,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
                 }
             }
         }
+        if (half == 0) asm volatile("bar.sync 2, 256;" ::: "memory");        // consume half 1's last hand-over
         tc_fence_before();
     }
     tc_fence_before();
@@ -756,7 +773,7 @@ static int launch_fwd_hd(const CUtensorMap& mq, const CUtensorMap& mk, const CUt
         WC_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::TOTAL));
         attr_set = true;
     }
-    attn_fwd_kernel<HD><<<grid, AT_THREADS, FwdSmem::TOTAL, st>>>(mq, mk, mv, a);
+    attn_fwd_kernel<HD><<<grid, FW_THREADS, FwdSmem::TOTAL, st>>>(mq, mk, mv, a);
     WC_LAUNCH_CHECK();
     return WC_OK;
 }
