@@ -1,3 +1,6 @@
+"""Developer trace (GPU box): per-tile clock64 breakdown of attn_fwd_kernel's softmax warps.
+    make -C weclip-vit-comer_b200/csrc EXTRA=-DAT_TRACE (after touching attention.cu) && python tools/attn_trace.py
+Nothing here is a bench value."""
 import sys, os, ctypes
 sys.path.insert(0, os.getcwd())
 import torch
@@ -16,18 +19,12 @@ for _ in range(3):
 torch.cuda.synchronize()
 raw = lse.view(torch.int32).flatten().cpu()
 off = N * heads * L
-for name, base in (("warp2", off), ("other softmax warps (last writer)", off + 4096)):
+for name, base in (("warp2", off), ("warp6 (half 1, same scheduler)", off + 4096)):
     t = raw[base: base + 13 * 8].view(13, 8).to(torch.int64) & 0xffffffff
-    print(name, "per tile: [ld_wait, max+s_empty, any/rescale, p_empty wait, s_full(next) wait, exp+P, fence+arrive] total, gap to next tile start")
+    print(name, "per tile: [ld_wait+probes, max+s_empty, any/rescale, residual barrier waits, turn wait, exp+P+hand-over, fence+arrive] total, gap to next tile start")
     for j in range(13):
         d = [(int(t[j, i + 1]) - int(t[j, i])) & 0xffffffff for i in range(7)]
         tot = (int(t[j, 7]) - int(t[j, 0])) & 0xffffffff
         gap = ((int(t[j + 1, 0]) - int(t[j, 7])) & 0xffffffff) if j < 12 else -1
         print(j, d, tot, gap)
 
-t = raw[off + 8192: off + 8192 + 13 * 8].view(13, 8).to(torch.int64) & 0xffffffff
-print("MMA thread per tile j: [issue_s(j+2) total, v_full wait, p_full wait, PV issue] | inside issue_s for tile j: k_full wait, s_empty wait | gap to next iteration")
-for j in range(13):
-    d = [(int(t[j, i + 1]) - int(t[j, i])) & 0xffffffff for i in range(4)]
-    gap = ((int(t[j + 1, 0]) - int(t[j, 4])) & 0xffffffff) if j < 12 else -1
-    print(j, d, "|", int(t[j, 5]), int(t[j, 6]), "|", gap)

@@ -31,7 +31,11 @@ def ncu_traffic():
     import glob
     import json
     repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    files = sorted(glob.glob(os.path.join(repo, "profiles", "*ncu_traffic*.json")))
+    import re
+
+    def version(path):      # r01_ncu_traffic_v13.json -> (1, 13): numeric, so that v13 sorts after v8
+        return tuple(int(x) for x in re.findall(r"\d+", os.path.basename(path)))
+    files = sorted(glob.glob(os.path.join(repo, "profiles", "*ncu_traffic*.json")), key=version)
     if not files:
         return None
     kern = json.load(open(files[-1]))["kernels"]

@@ -37,11 +37,19 @@ __device__ __forceinline__ float ex2_approx(float x) {
 }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// -DAT_TRACE (developer builds only, tools/attn_trace.py): clock64 stamps of one softmax warp pair for the second item of CTA 0,
+// written past the end of the lse buffer (the tool allocates the extra room)
+#ifdef AT_TRACE
+#define AT_TR(slot) do { if (blockIdx.x == 0 && lane == 0 && it == 1 && j < 16) tr[j * 8 + (slot)] = (uint32_t)clock64(); } while (0)
+#else
+#define AT_TR(slot) do { } while (0)
+#endif
 struct AttnArgs {
     int L, heads, n_kt;
     int n_qt, n_items;       // work items = (query tile, head, image), walked persistently: item w -> qt = w % n_qt, bh = w / n_qt
     h16* o;
     float* lse2;
+    long trace_off;          // AT_TRACE only: element offset of the trace area behind the lse rows
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -245,6 +253,9 @@ __global__ void __launch_bounds__(FW_THREADS, 1) attn_fwd_kernel(const __grid_co
             for (int t = 0; t < 4; ++t)
                 *reinterpret_cast<uint4*>(blk + (((cc0 + t) ^ (row & 7)) << 4)) = make_uint4(pk[4 * t], pk[4 * t + 1], pk[4 * t + 2], pk[4 * t + 3]);
         };
+#ifdef AT_TRACE
+        uint32_t* tr = reinterpret_cast<uint32_t*>(a.lse2) + (size_t)a.trace_off + (warp == 2 ? 0 : warp == 6 ? 4096 : 12288);
+#endif
         if (half == 1) asm volatile("bar.arrive 2, 256;" ::: "memory");      // the first turn goes to half 0
         int it = 0;
         for (int w = blockIdx.x; w < a.n_items; w += gridDim.x, ++it) {
@@ -261,7 +272,9 @@ __global__ void __launch_bounds__(FW_THREADS, 1) attn_fwd_kernel(const __grid_co
                 const int g = g0 + j, b = g % AT_SBUF, pb = g & 1;
                 const int nv = a.L - j * AT_BN - half * 64;      // this warp's columns of the tile that exist (may be <= 0)
                 uint8_t* blk = smem + FwdSmem::P + pb * 2 * AT_TILE_BYTES + half * AT_TILE_BYTES + row * 128;
+                AT_TR(0);
                 tmem_ld_wait();                                  // both halves were requested during the previous tile's exp work
+                AT_TR(1);
                 // the two barrier round trips this tile needs before its exp phase (~200 clk each even when already complete) are
                 // put in flight here, under the running-maximum work
                 const bool more = j + 1 < n_kt;
@@ -275,6 +288,7 @@ __global__ void __launch_bounds__(FW_THREADS, 1) attn_fwd_kernel(const __grid_co
                 if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the MMA warp may overwrite it
                 if (full) mx = fmaxf(mx, max_chunk(r1, 32));
                 else if (nv > 32) mx = fmaxf(mx, max_chunk(r1, nv - 32));
+                AT_TR(2);
                 const float m_new = mx * AT_LOG2E;
                 const bool need = m_new > m_used + RESCALE_THR;   // first tile: m_used = -inf
                 if (__any_sync(0xffffffffu, need)) {
@@ -299,10 +313,13 @@ __global__ void __launch_bounds__(FW_THREADS, 1) attn_fwd_kernel(const __grid_co
                     if (need) m_used = m_new;
                 }
                 // both waits come before the exp work; the next tile's TMEM loads are issued as soon as r0 / r1 have been consumed
+                AT_TR(3);
                 if (!ok_p) mbar_wait(&p_empty[pb], ((g >> 1) & 1) ^ 1);
                 if (!ok_s) mbar_wait(&s_full[bn], ((g + 1) / AT_SBUF) & 1);
                 tc_fence_after();
+                AT_TR(4);
                 asm volatile("bar.sync %0, 256;" ::"r"(2 + half) : "memory");
+                AT_TR(5);
                 if (full) {
                     prob_chunk(r0, 32, blk, 0);
                     if (more) tmem_ld32_issue(tlane + bn * AT_BN, r0);
@@ -313,11 +330,13 @@ __global__ void __launch_bounds__(FW_THREADS, 1) attn_fwd_kernel(const __grid_co
                     prob_chunk(r1, nv - 32, blk, 4);
                 }
                 asm volatile("bar.arrive %0, 256;" ::"r"(2 + (half ^ 1)) : "memory");
+                AT_TR(6);
                 if (more) tmem_ld32_issue(tlane + bn * AT_BN + 32, r1);
                 fence_async_smem();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&p_full[pb]);
+                AT_TR(7);
             }
             // ---- merge the two key halves of each row (named barrier over the 256 softmax threads; the statistics are
             //      double-buffered by item parity, so the next item's writes cannot overtake this item's reads)
@@ -790,7 +809,7 @@ int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, floa
     const int n_qt = ceil_div(L, AT_BM);
     const long n_items = (long)n_qt * heads * n_img;
     WC_CHECK_ARG(n_items < (1L << 30));
-    AttnArgs a{L, heads, ceil_div(L, AT_BN), n_qt, (int)n_items, o, lse2};
+    AttnArgs a{L, heads, ceil_div(L, AT_BN), n_qt, (int)n_items, o, lse2, (long)n_img * heads * L};
     const int sms = attn_num_sms();
     dim3 grid((unsigned)(n_items < sms ? n_items : sms));
     ProfScope prof(PK_ATTENTION, 4.0 * L * L * hd * heads * n_img, st);
