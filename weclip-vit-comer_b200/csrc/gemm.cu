@@ -501,7 +501,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = make_idesc(BM, BN);
-            uint32_t it = 0, tl = 0;
+            uint32_t it = 0, tl = 0, full_ok = 0;
             for (int t = blockIdx.x; t < args.total_tiles; t += gridDim.x, ++tl) {
                 const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
                 mbar_wait(&tempty_bar[as], aph ^ 1);            // epilogue has drained this accumulator
@@ -510,7 +510,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
                 for (int kb = 0; kb < num_kb; ++kb, ++it) {
                     const int s = it % STAGES;
                     const uint32_t ph = (it / STAGES) & 1;
-                    mbar_wait(&full_bar[s], ph);
+                    if (!full_ok) mbar_wait(&full_bar[s], ph);
+                    // the NEXT stage's barrier round trip (~200 clk even when the stage has long landed) runs under this stage's
+                    // MMA issue instead of in front of the next one
+                    full_ok = mbar_try(&full_bar[(it + 1) % STAGES], ((it + 1) / STAGES) & 1);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + s * C::STAGE_BYTES);
                     const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + C::A_BYTES);
@@ -701,7 +704,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {
             constexpr uint32_t idesc = make_idesc(2 * BM, BN);
-            uint32_t it = 0, tl = 0;
+            uint32_t it = 0, tl = 0, full_ok = 0;
             for (int t = pair; t < total; t += npairs, ++tl) {
                 const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
                 mbar_wait(&tempty_bar[as], aph ^ 1);            // both CTAs' epilogues have drained this accumulator
@@ -710,7 +713,10 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
                 for (int kb = 0; kb < num_kb; ++kb, ++it) {
                     const int s = it % STAGES;
                     const uint32_t ph = (it / STAGES) & 1;
-                    mbar_wait(&full_bar[s], ph);
+                    if (!full_ok) mbar_wait(&full_bar[s], ph);
+                    // the NEXT stage's barrier round trip (~200 clk even when the stage has long landed) runs under this stage's
+                    // MMA issue instead of in front of the next one
+                    full_ok = mbar_try(&full_bar[(it + 1) % STAGES], ((it + 1) / STAGES) & 1);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + s * C::STAGE_BYTES);
                     const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + C::A_BYTES);
