@@ -448,8 +448,12 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __gr
             constexpr uint32_t idesc_s = make_idesc(AT_BM, AT_BN);
             for (int h = 0; h < a.heads; ++h) {
                 const int s = h % AT_STAGES, b = h & 1;
-                mbar_wait(&full[s], (h / AT_STAGES) & 1);
-                mbar_wait(&s_empty[b], ((h >> 1) & 1) ^ 1);
+                {   // both barrier round trips in flight together
+                    const uint32_t ok_f = mbar_try(&full[s], (h / AT_STAGES) & 1);
+                    const uint32_t ok_e = mbar_try(&s_empty[b], ((h >> 1) & 1) ^ 1);
+                    if (!ok_f) mbar_wait(&full[s], (h / AT_STAGES) & 1);
+                    if (!ok_e) mbar_wait(&s_empty[b], ((h >> 1) & 1) ^ 1);
+                }
                 tc_fence_after();
                 const uint32_t sq = smem_u32(smem + MeanSmem::RING + s * 2 * AT_TILE_BYTES);
                 const uint64_t dq = make_smem_desc(sq), dk = make_smem_desc(sq + AT_TILE_BYTES);
@@ -479,6 +483,8 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __gr
             // the TMEM load of the second 32 columns / of the next head's first 32 runs under the exp2 work
             tmem_ld_wait();
             tmem_ld32_issue(tlane + b * AT_BN + 32, r1);
+            // the next head's score barrier is probed here, so its round trip runs under the first 32 exponentials
+            const uint32_t ok_s = (h + 1 < a.heads) ? mbar_try(&s_full[b ^ 1], ((h + 1) >> 1) & 1) : 1u;
 #pragma unroll
             for (int i = 0; i < 32; ++i) acc[i] += ex2_approx(fmaf(__uint_as_float(r0[i]), AT_LOG2E, -lse));
             tmem_ld_wait();
@@ -486,7 +492,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __gr
             __syncwarp();
             if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the next head's MMA may overwrite it
             if (h + 1 < a.heads) {
-                mbar_wait(&s_full[b ^ 1], ((h + 1) >> 1) & 1);
+                if (!ok_s) mbar_wait(&s_full[b ^ 1], ((h + 1) >> 1) & 1);
                 tc_fence_after();
                 tmem_ld32_issue(tlane + (b ^ 1) * AT_BN, r0);
             }
