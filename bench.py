@@ -7,7 +7,15 @@ One JSON line on stdout (rank 0).  A "step" = one pass of the hot path over one 
 N>1 is launched by torchrun (one rank per GPU); images are sharded across ranks with no data-path
 collective (weak scaling); the timed region is bracketed by barrier + synchronize and the max over ranks
 is taken.  `--impl reference` times the CPU oracle port (the reference is Python and cannot travel to the
-GPU box; oracle/weclip_oracle.py is its pinned restatement) on the host cores with a bounded sample.
+GPU box; oracle/weclip_oracle.py is its pinned restatement) on the host cores, one dataset image per step, honouring
+--steps / --warmup as given.
+
+Keys beyond the base contract (msc+flip workloads):
+  value / e2e           the reference's call pattern: names = name+name with every [x, flip(x)] call
+                        (test_msc_flip_voc.py:52,69,84) -> config.cam_passes_per_image = 6
+  value_live_outputs    the same step with the passes whose labels the driver never reads eliminated (1 pass; identical
+                        histograms, tests/test_evaluate_gpu.py::test_cam_passes_live_equals_reference_call_pattern)
+  gpu_library_baseline  the same loop as ATen/cuBLAS library calls on this GPU in the reference's mixed precision (N=1 only)
 """
 from __future__ import annotations
 
@@ -96,6 +104,8 @@ class ParPseudoLabel:
     320x320, K+1 = 3 CAM channels per image, dilations 1/2/4/8/12/24, 20 iterations)."""
     name = "cfg2-tail: PAR(20 it, 6 dil, fp16 affinity)+argmax on 32 x 320x320 crops, K+1=3"
     aff_dtype, s_a = torch.float16, 2
+    units = 32
+    l2_note = "inputs larger than L2 (affinity 315 MB fp16 / 629 MB fp32 per step)"
 
     def __init__(self, rank: int, device):
         from weclip_b200 import synth
@@ -113,13 +123,10 @@ class ParPseudoLabel:
         self.imgs_d = self.imgs_h.to(device)
         self.masks_d = self.masks_h.to(device)
         self.labels_h = torch.empty(self.B, self.H, self.W, dtype=torch.int64).pin_memory()
-        self.units = self.B
         self.launches = 1 + 20 + self.B           # affinity + 20 propagation + per-image argmax
         self.h2d = self.imgs_h.numel() * 4 + self.masks_h.numel() * 4
         self.d2h = self.labels_h.numel() * 8
         self.kernel_events = []
-        # aff (614 MB) + masks > 126 MB L2: every iteration streams from HBM
-        self.l2_note = f"inputs larger than L2 (affinity {self.B * 48 * self.H * self.W * self.s_a / 1e6:.0f} MB per step)"
 
     def step_device(self, record=False):
         from weclip_b200.par import argmax_lut
@@ -194,7 +201,19 @@ except ImportError:
 DEFAULT_WORKLOAD = "mscflip" if "mscflip" in WORKLOADS else "par"
 
 
-def run_reference(args, rank):
+def _config(wl_or_cls, world):
+    cfg = {"workload": wl_or_cls.name, "images_per_step_per_gpu": getattr(wl_or_cls, "units", None),
+           "parallelism": f"image-sharded x{world}", "l2": getattr(wl_or_cls, "l2_note", None)}
+    if getattr(wl_or_cls, "cam_passes_per_image", None) is not None:
+        cfg["cam_passes_per_image"] = wl_or_cls.cam_passes_per_image
+    return cfg
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the reference's own CPU implementation of the path (oracle port: the reference is Python and cannot
+    travel) on all host cores of rank 0; a step = ONE dataset image of the same workload (a bounded sample of our arm's
+    8-image step).  --steps / --warmup are honoured as given.  At N > 1 still ONE CPU process runs: the value is not
+    scaled by N (stated in `note`)."""
     if rank != 0:
         return
     torch.set_num_threads(os.cpu_count() or 1)
@@ -205,14 +224,16 @@ def run_reference(args, rank):
     vals = []
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        v, sample = wl.cpu_sample()
+        v, sample = wl.cpu_sample(1)
         vals.append(v)
     dt = time.perf_counter() - t0
     v = statistics.mean(vals)
+    cfg = _config(cls, world)        # the same keys and values as our arm's line
     line = {"impl": "reference", "metric": METRIC, "value": round(v, 4), "unit": "images/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * dt / args.steps, 2),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": cls.name},
+            "config": cfg,
+            "note": "one CPU process on rank 0 using all host cores; not multiplied by --gpus",
             "cpu_baseline": {"value": round(v, 4), "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
                              "sample": sample},
             "e2e": {"value": round(v, 4), "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -234,10 +255,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
 
     if args.impl == "reference":
-        if args.steps > 5:
-            args.steps = 3
-        args.warmup = min(args.warmup, 1)
-        run_reference(args, rank)
+        run_reference(args, rank, world)
         return
 
     from weclip_b200 import _lib
@@ -296,6 +314,20 @@ def main():
     e1.record()
     barrier()
     ms_e2e = max(e0.elapsed_time(e1), 1e3 * (time.perf_counter() - t0))
+    hist_total_e2e = int(wl.hist_h.sum()) if hasattr(wl, "hist_h") else None
+    # --- the same step with dead CAM / PAR passes eliminated (cam_passes="live")
+    ms_live = None
+    if hasattr(wl, "step_device_live"):
+        for _ in range(2):
+            wl.step_device_live()
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            wl.step_device_live()
+        wl.join()
+        e1.record()
+        barrier()
+        ms_live = e0.elapsed_time(e1)
     clocks = sampler.stop() if sampler else None
     # --- kernel-class breakdown for the roofline object: separate pass with the C-side profiler (events around
     #     every launch on the launching stream); never overlaps the timed regions above
@@ -304,9 +336,10 @@ def main():
         barrier()
 
     if dist is not None:
-        t = torch.tensor([ms_dev, ms_e2e], device=dev, dtype=torch.float64)
+        t = torch.tensor([ms_dev, ms_e2e, ms_live or 0.0], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_dev, ms_e2e = t.tolist()
+        ms_dev, ms_e2e, ms_live_r = t.tolist()
+        ms_live = ms_live_r if ms_live is not None else None
 
     if rank == 0:
         units = wl.units * world * args.steps
@@ -315,14 +348,29 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_dev / args.steps, 4),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": getattr(wl, "dtype", "f32"),
             "data": "synthetic (seeded images / CAMs / random-init weights; no datasets or checkpoints offline)",
-            "config": {"workload": wl.name, "images_per_step_per_gpu": wl.units, "parallelism": f"image-sharded x{world}",
-                       "l2": wl.l2_note},
+            "config": _config(wl, world),
             "clocks": clocks,
             "e2e": {"value": round(units / (ms_e2e * 1e-3), 2), "unit": "images/s",
                     "h2d_bytes_per_step": wl.h2d, "d2h_bytes_per_step": wl.d2h},
             "gpu_launches": int(wl.launches) * args.steps,
             "roofline": wl.roofline(peaks),
         }
+        if ms_live is not None:
+            line["value_live_outputs"] = round(units / (ms_live * 1e-3), 2)
+            line["value_live_outputs_note"] = ("same step, cam_passes='live': 1 CAM/PAR pass per dataset image instead of the "
+                                               "reference call pattern's 6; identical histograms")
+        if hist_total_e2e is not None:
+            # the e2e region ends with the cross-rank histogram sum: every rank's step counts the same number of valid pixels
+            line["e2e"]["hist_total_after_allreduce"] = hist_total_e2e
+            line["e2e"]["collective"] = "all_reduce(SUM) of the 3 CxC int64 histograms inside the timed region" if world > 1 \
+                else "none at world size 1"
+        if world == 1 and hasattr(wl, "gpu_library_sample") and os.environ.get("WC_BENCH_GPU_LIB", "1") != "0":
+            try:
+                v, sample = wl.gpu_library_sample()
+                line["gpu_library_baseline"] = {"value": round(v, 3), "unit": "images/s", "kind": "oracle loop on cuda "
+                                                "(ATen/cuBLAS library calls)", "sample": sample}
+            except Exception as exc:  # noqa: BLE001 - a baseline leg must never take the bench line down
+                line["gpu_library_baseline"] = {"value": None, "error": repr(exc)[:200]}
         if world == 1:
             torch.set_num_threads(os.cpu_count() or 1)
             v, sample = wl.cpu_sample()

@@ -30,7 +30,7 @@ extern "C" {
 #define WC_ERR_WORKSPACE (-3)
 #define WC_ERR_UNSUPPORTED (-4)
 
-#define WC_ABI_VERSION 7
+#define WC_ABI_VERSION 8
 #define WC_PAR_MAX_DIL 8
 
 /* ABI version (bumped whenever a signature changes) and last error text. */
@@ -197,10 +197,11 @@ int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int h, int wd, 
  * nl = 8), compute_trans_mat (:64-80), scoremap2bbox box mask (clip/utils.py:115-142; box_thr 0.4 / 0.7) and
  * cam' = (T * mask) @ cam.
  *   attn fp32 [nl,N,L,L] (oldest first, block 12 last); attn_pred fp32 [N,P,P]; cams / cams_refined fp32 [sumK,P];
- *   box_masks fp32 [sumK,P] or NULL (exported for the parity tests). */
+ *   box_masks fp32 [sumK,P] or NULL (exported for the parity tests).  box_thr is a double: the reference evaluates
+ *   int(thr * max(uint8)) in float64 (clip/utils.py:118-121); 0.7f * 250 would give 174 instead of 175. */
 size_t wc_affinity_workspace_bytes(int N, int h, int w, int total_inst, int nl);
 int wc_affinity_refine(const float* attn, int nl, const float* attn_pred, int N, int h, int wd, int use_rfm,
-                       const float* cams, const int* k_off_host, float box_thr, float* cams_refined,
+                       const float* cams, const int* k_off_host, double box_thr, float* cams_refined,
                        float* box_masks, void* workspace, size_t workspace_bytes, void* stream);
 
 /* generate_cam_label (clip/clip_tool.py:202-216: per-class min-max + cv2.resize INTER_LINEAR to Wc x Hc) and the

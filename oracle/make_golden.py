@@ -143,6 +143,53 @@ def golden_weclip(dataset, num_classes, n_fg, n_bg, subdir):
               probs0=probs.detach().numpy(), attn_last0=attn_last.detach().numpy())
 
 
+MSCFLIP_CASE = dict(weights_seed=0, text_seed=7, label_seed=21, image_seed=31, resize_long=160, scales=(1.0, 0.75, 1.25),
+                    sizes=((93, 130), (120, 88)), names=("m0", "m1"))
+
+
+def mscflip_case(n_fg=20):
+    """Seeded inputs of the msc+flip golden case (regenerated bit-identically by the tests): per dataset image
+    (name, image [3,H0,W0] fp32, label map [H0,W0] uint8)."""
+    c = MSCFLIP_CASE
+    rng = np.random.default_rng(c["label_seed"])
+    items = []
+    for i, (h0, w0) in enumerate(c["sizes"]):
+        lab = synth.make_label_map(rng, h0, w0, synth.draw_label_set(rng, n_fg))
+        img = synth.make_images(c["image_seed"] + i, 1, h0, w0)[0]
+        items.append((c["names"][i], img, lab))
+    return items
+
+
+def golden_mscflip():
+    """The REAL validate() loop of test_msc_flip_voc.py:30-113 (names = name+name, DataLoader batch_size=1, .npy logit
+    dump) on two small dataset images of different sizes, followed by main()'s evaluate.scores calls (:202-204)."""
+    c = MSCFLIP_CASE
+    sd = synth.make_state_dict(c["weights_seed"], 21)
+    fg, bg = synth.make_text_features(c["text_seed"], 20, 25)
+    root = tempfile.mkdtemp()
+    items = mscflip_case()
+    for name, _, lab in items:
+        synth.write_label_png(root, "SegmentationClassAug", name, lab)
+    model = ref_harness.build_reference_model(sd, fg, bg, root, "voc", 21)
+    validate, args = ref_harness.reference_validate("voc")
+    args.resize_long = c["resize_long"]
+    dataset = [(name, img.numpy(), lab.astype(np.int64), np.zeros(20, np.float32)) for name, img, lab in items]
+    calls = []
+    fwd = model.forward
+    model.forward = lambda img, names, mode="train": (calls.append(len(names)), fwd(img, names, mode=mode))[1]
+    gts, preds, msc_preds, cams, ph, mh, ch = validate(model=model, dataset=dataset, test_scales=list(c["scales"]))
+    ev = ref_harness.reference_modules()["evaluate"]
+    ph, _ = ev.scores(gts, preds, ph)
+    mh, _ = ev.scores(gts, msc_preds, mh)
+    ch, _ = ev.scores(gts, cams, ch)
+    out = dict(hist=np.stack([ph, mh, ch]).astype(np.int64), names_per_call=np.array(calls))
+    for i, (name, _, _) in enumerate(items):
+        d = np.load(os.path.join(args.work_dir, "logit", name + ".npy"), allow_pickle=True).item()   # :111
+        out[f"segs{i}"], out[f"msc_segs{i}"] = d["segs"], d["msc_segs"]
+        out[f"seg_pred{i}"], out[f"msc_pred{i}"], out[f"cam{i}"] = preds[i], msc_preds[i], cams[i]
+    _save("mscflip_voc.npz", **out)
+
+
 def training_case(seed=17, B=3, H=96, W=112, C=21):
     """Seeded inputs of the label-prep / loss golden case (regenerated bit-identically by the tests)."""
     g = torch.Generator().manual_seed(seed)
@@ -191,6 +238,7 @@ def main():
     golden_par(ref)
     golden_small_ops(ref)
     golden_training()
+    golden_mscflip()
     golden_weclip("voc", 21, 20, 25, "SegmentationClassAug")
     golden_weclip("coco", 81, 80, 23, os.path.join("SegmentationClass", "train"))
 

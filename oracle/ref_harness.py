@@ -138,3 +138,23 @@ def reference_training_fns():
     exec(compile(ast.Module(body=[fn], type_ignores=[]), path, "exec"), ns)
     return dict(cams_to_affinity_label=cams_to_affinity_label, get_aff_loss=get_aff_loss, get_seg_loss=get_seg_loss,
                 get_mask_by_radius=ns["get_mask_by_radius"])
+
+
+def reference_validate(dataset: str = "voc"):
+    """``validate(model, dataset, test_scales)`` of test_msc_flip_voc.py:30-113 (coco twin test_msc_flip_coco.py:31-116),
+    executed from where it lies.  The script's top level needs omegaconf / imageio / pydensecrf / datasets.*, so only that
+    one function's source is extracted (ast) and executed unmodified in a namespace holding the names it uses
+    (torch, F, np, tqdm, the reference's utils.evaluate, and ``args`` with resize_long / work_dir).
+    Returns (validate, args): set ``args.resize_long`` / ``args.work_dir`` before calling."""
+    import ast
+    import torch.nn.functional as F
+    _install_shims()
+    from utils import evaluate
+    path = os.path.join(REFERENCE_ROOT, f"test_msc_flip_{dataset}.py")
+    tree = ast.parse(open(path).read())
+    fn = next(n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "validate")
+    args = types.SimpleNamespace(resize_long=512, work_dir=tempfile.mkdtemp(prefix="refval"))
+    os.makedirs(os.path.join(args.work_dir, "logit"), exist_ok=True)
+    ns = {"np": np, "torch": torch, "F": F, "tqdm": lambda it, **kw: it, "evaluate": evaluate, "args": args, "os": os}
+    exec(compile(ast.Module(body=[fn], type_ignores=[]), path, "exec"), ns)
+    return ns["validate"], args

@@ -3,7 +3,11 @@
 Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl reference`` legs
 may import this file; the product path (``weclip-vit-comer_b200/``) must never import it.
 
-Plain PyTorch (CPU, fp32) / numpy, functional style over a state dict with the reference's key names.
+Plain PyTorch (fp32) / numpy, functional style over a state dict with the reference's key names.  Tensors may live on
+``cuda`` as well: then every op is the ATen / cuBLAS library call the reference itself makes on a GPU (with the
+reference's host round trips for OpenCV / numpy), and ``gpu_mixed=True`` reproduces its hard-wired GPU mixed precision
+(clip/model.py:461-476: fp16 conv1 / out-proj / MLP weights and activations, fp32 in-proj + softmax, clip/myAtt.py:199,321)
+— that is bench.py's ``gpu_library_baseline`` leg, the "library-call bar" of SURVEY.md §8(d).
 Every function cites the reference file:line it restates (paths relative to /root/reference).
 
 Parity status: PINNED.  The reference has no tests or golden vectors of its own, so
@@ -55,6 +59,19 @@ def quick_gelu(x: Tensor) -> Tensor:
     return x * torch.sigmoid(1.702 * x)
 
 
+_HALF_CACHE: Dict[int, Tensor] = {}
+
+
+def _h(t: Tensor) -> Tensor:
+    """fp16 copy of a weight (convert_weights, clip/model.py:461-476), cached per tensor."""
+    key = id(t)
+    hit = _HALF_CACHE.get(key)
+    if hit is None or hit.device != t.device or hit.shape != t.shape:
+        hit = t.half()
+        _HALF_CACHE[key] = hit
+    return hit
+
+
 def mha(x: Tensor, sd: Dict[str, Tensor], p: str, heads: int, mimic_fp16: bool = True):
     """clip/myAtt.py:199-201 (fp32 packed in-proj), :257-268 (head split), :53-64 (softmax(q/sqrt(d) k^T) v),
     :320-321 (fp16 out-proj), :323-326 (mean over heads).  x: [L,N,E] -> ([L,N,E], [N,L,L])."""
@@ -68,7 +85,9 @@ def mha(x: Tensor, sd: Dict[str, Tensor], p: str, heads: int, mimic_fp16: bool =
     attn = torch.softmax(torch.bmm(q, k.transpose(-2, -1)), dim=-1)
     o = torch.bmm(attn, v).transpose(0, 1).contiguous().view(L, N, E)
     wo, bo = sd[p + ".out_proj.weight"], sd[p + ".out_proj.bias"]
-    if mimic_fp16:
+    if mimic_fp16 == "gpu":
+        o = F.linear(o.half(), _h(wo), _h(bo))                        # stays fp16 on the GPU path (myAtt.py:321)
+    elif mimic_fp16:
         o = F.linear(o.half(), wo.half(), bo.half()).float()
     else:
         o = F.linear(o, wo, bo)
@@ -78,6 +97,16 @@ def mha(x: Tensor, sd: Dict[str, Tensor], p: str, heads: int, mimic_fp16: bool =
 def resblock(x: Tensor, sd: Dict[str, Tensor], p: str, heads: int, mimic_fp16: bool = True, ln1_out=None):
     """clip/model.py:210-214.  ``ln1_out`` lets the Grad-CAM oracle substitute the hooked ln_1 output."""
     a = layer_norm(x, sd[p + ".ln_1.weight"], sd[p + ".ln_1.bias"]) if ln1_out is None else ln1_out
+    if mimic_fp16 == "gpu":
+        # the reference's GPU dtype flow: fp16 residual stream, LayerNorm in fp32 cast back to fp16 (model.py:177-183),
+        # attention input up-cast to fp32 (myAtt.py:199), fp16 out-proj and MLP
+        x = x.half()
+        o, w = mha(a.half() if ln1_out is None else a, sd, p + ".attn", heads, "gpu")
+        x = x + o.to(x.dtype)
+        h = layer_norm(x, sd[p + ".ln_2.weight"], sd[p + ".ln_2.bias"]).half()
+        h = F.linear(h, _h(sd[p + ".mlp.c_fc.weight"]), _h(sd[p + ".mlp.c_fc.bias"]))
+        h = F.linear(quick_gelu(h), _h(sd[p + ".mlp.c_proj.weight"]), _h(sd[p + ".mlp.c_proj.bias"]))
+        return x + h, w
     o, w = mha(a, sd, p + ".attn", heads, mimic_fp16)
     x = x + o
     h = layer_norm(x, sd[p + ".ln_2.weight"], sd[p + ".ln_2.bias"])
@@ -93,7 +122,10 @@ def encode_image(img: Tensor, sd: Dict[str, Tensor], mimic_fp16: bool = True):
     N, _, H, W = img.shape
     h, w = H // 16, W // 16
     pos = upsample_pos_emb(sd[v + ".positional_embedding"], (h, w))
-    x = F.conv2d(img.float(), sd[v + ".conv1.weight"], stride=16)
+    if mimic_fp16 == "gpu":
+        x = F.conv2d(img.half(), _h(sd[v + ".conv1.weight"]), stride=16).float()
+    else:
+        x = F.conv2d(img.float(), sd[v + ".conv1.weight"], stride=16)
     x = x.reshape(N, x.shape[1], -1).permute(0, 2, 1)
     cls = sd[v + ".class_embedding"].reshape(1, 1, -1).expand(N, 1, -1)
     x = torch.cat([cls, x], dim=1) + pos
@@ -103,7 +135,7 @@ def encode_image(img: Tensor, sd: Dict[str, Tensor], mimic_fp16: bool = True):
     for i in range(11):
         x, a = resblock(x, sd, f"{v}.transformer.resblocks.{i}", 12, mimic_fp16)
         taps.append(x)
-        attns.append(a)
+        attns.append(a.float())
     return taps, attns
 
 
@@ -130,8 +162,8 @@ def decoder(fts: Tensor, sd: Dict[str, Tensor], mimic_fp16: bool = True) -> Tens
     """WeCLIP_model/Decoder/TransDecoder.py:113-125 — 3 blocks (256 wide, 8 heads) + 1x1 conv -> [N,C,h,w]."""
     N, C, h, w = fts.shape
     x = fts.reshape(N, C, h * w).permute(2, 0, 1)
-    for i in range(3):
-        x, _ = resblock(x, sd, f"decoder.transformer.resblocks.{i}", 8, mimic_fp16)
+    for i in range(3):      # the decoder's own weights stay fp32 on the GPU too (only its out-proj is forced to fp16)
+        x, _ = resblock(x, sd, f"decoder.transformer.resblocks.{i}", 8, bool(mimic_fp16))
     x = x.permute(1, 2, 0).reshape(N, C, h, w)
     return F.conv2d(x, sd["decoder.linear_pred.weight"], sd["decoder.linear_pred.bias"])
 
@@ -160,6 +192,7 @@ def forward_last_layer(x11: Tensor, text: Tensor, sd: Dict[str, Tensor], mimic_f
     x = x.permute(1, 0, 2)
     x = layer_norm(x, sd[v + ".ln_post.weight"], sd[v + ".ln_post.bias"])
     g = torch.mean(x[:, 1:, :], dim=1) @ sd[v + ".proj"]
+    attn = attn.float()
     g = g / g.norm(dim=1, keepdim=True)
     t = text / text.norm(dim=1, keepdim=True)
     logits = sd["encoder.logit_scale"].exp() * g @ t.t()
@@ -181,8 +214,9 @@ def grad_cam(x11: Tensor, text: Tensor, targets: Sequence[int], sd: Dict[str, Te
         A = layer_norm(x11, sd[p + ".ln_1.weight"], sd[p + ".ln_1.bias"]).detach().requires_grad_(True)
         probs, attn_last = forward_last_layer(x11.detach(), text, sd, mimic_fp16, ln1_out=A)
         probs[:, k].sum().backward()
-        act = A.detach()[1:, 0, :].reshape(h, w, -1).permute(2, 0, 1).numpy()       # [768,h,w]
-        grd = A.grad[1:, 0, :].reshape(h, w, -1).permute(2, 0, 1).numpy()
+        # .cpu(): the reference's own device -> host round trips (activations_and_gradients.py:24,35)
+        act = A.detach()[1:, 0, :].float().reshape(h, w, -1).permute(2, 0, 1).cpu().numpy()       # [768,h,w]
+        grd = A.grad[1:, 0, :].float().reshape(h, w, -1).permute(2, 0, 1).cpu().numpy()
         wts = grd.mean(axis=(1, 2))
         cam = np.maximum((wts[:, None, None] * act).sum(axis=0), 0).astype(np.float32)
         cam = scale_cam_image(cam)
@@ -246,8 +280,8 @@ def refine_cams(cams: np.ndarray, trans_mat: Tensor, threshold: float, masks=Non
     for k, cam in enumerate(cams):
         h, w = cam.shape
         bm = box_mask(cam, threshold) if masks is None else np.asarray(masks[k], dtype=np.float32)
-        m = torch.from_numpy(bm).view(1, h * w)
-        out.append(torch.matmul(trans_mat * m, torch.from_numpy(cam).view(-1, 1)).reshape(h, w))
+        m = torch.from_numpy(bm).view(1, h * w).to(trans_mat.device)            # .cuda() as clip_tool.py:180,188
+        out.append(torch.matmul(trans_mat * m, torch.from_numpy(cam).view(-1, 1).to(trans_mat.device)).reshape(h, w))
     return out
 
 
@@ -280,7 +314,7 @@ def cv2_resize_linear(src: np.ndarray, dsize: Tuple[int, int]) -> np.ndarray:
 
 def generate_cam_label(cam_refined: Sequence[Tensor], size_wh: Tuple[int, int]) -> Tensor:
     """clip/clip_tool.py:202-216 — per class min-max then cv2.resize to (w,h) -> [K,Hc,Wc] float32."""
-    out = [cv2_resize_linear(scale_cam_image(c.numpy().astype(np.float32)), size_wh) for c in cam_refined]
+    out = [cv2_resize_linear(scale_cam_image(c.cpu().numpy().astype(np.float32)), size_wh) for c in cam_refined]
     return torch.from_numpy(np.stack(out, 0))
 
 
@@ -302,8 +336,8 @@ def par_offsets(dilations=PAR_DILATIONS):
 def par_neighbors(x: Tensor, dilations=PAR_DILATIONS) -> Tensor:
     """WeCLIP_model/PAR.py:39-49 — replicate-padded dilated neighbours [B,C,H,W] -> [B,C,48,H,W] (by index clamp)."""
     B, C, H, W = x.shape
-    ys = torch.arange(H).view(H, 1)
-    xs = torch.arange(W).view(1, W)
+    ys = torch.arange(H, device=x.device).view(H, 1)
+    xs = torch.arange(W, device=x.device).view(1, W)
     out = []
     for dy, dx in par_offsets(dilations):
         yy = (ys + dy).clamp(0, H - 1).expand(H, W)
@@ -329,7 +363,7 @@ def par_affinity(imgs: Tensor, dilations=PAR_DILATIONS, w1: float = 0.3, w2: flo
     sd = torch.std(nb, dim=2, keepdim=True)
     aff = -(ab / (sd + 1e-8) / w1) ** 2
     aff = aff.mean(dim=1)
-    return F.softmax(aff, dim=1) + w2 * par_pos_aff(dilations, w1).view(1, -1, 1, 1)
+    return F.softmax(aff, dim=1) + w2 * par_pos_aff(dilations, w1).view(1, -1, 1, 1).to(imgs.device)
 
 
 def par_forward(imgs: Tensor, masks: Tensor, dilations=PAR_DILATIONS, num_iter: int = PAR_NUM_ITER) -> Tensor:
@@ -381,21 +415,22 @@ def weclip_forward(img: Tensor, label_maps: Sequence[np.ndarray], sd: Dict[str, 
     for i in range(len(label_maps)):
         ids = label_ids_from_map(label_maps[i])
         ori_h, ori_w = label_maps[i].shape[:2]
-        text = torch.cat([fg_text[ids], bg_text], dim=0)
-        x11 = taps[-1][:, i:i + 1, :]
+        text = torch.cat([fg_text[ids], bg_text], dim=0).to(img.device)
+        x11 = taps[-1][:, i:i + 1, :].float()
         cams, attn_last, _ = grad_cam(x11, text, list(range(len(ids))), sd, h, w, mimic_fp16)
         stack = torch.cat([attn_stack[i], attn_last], dim=0)
         aff = rfm_attention(stack, attn_pred[i:i + 1], require_seg_trans, window)
         tm = compute_trans_mat(aff)
         refined = refine_cams(cams, tm, thr, None if box_masks is None else box_masks[i])
         size_wh = (W, H) if mode == "train" else (ori_w, ori_h)
-        up = generate_cam_label(refined, size_wh)
+        up = generate_cam_label(refined, size_wh).to(img.device)              # .cuda(), model_attn_aff_voc.py:160
         full = cams_with_bg(up)
-        valid_key = torch.from_numpy(np.pad(np.asarray(ids) + 1, (1, 0), mode="constant"))
+        valid_key = torch.from_numpy(np.pad(np.asarray(ids) + 1, (1, 0), mode="constant")).to(img.device)
         labels_out.append(refine_labels(img[i], full, valid_key))
         inter["cams"].append(cams); inter["cams_refined"].append(torch.stack(refined)); inter["cams_up"].append(up)
         inter["trans_mat"].append(tm); inter["keys"].append(ids); inter["par_in"].append(full)
-        inter.setdefault("box_masks", []).append(np.stack([box_mask(c, thr) for c in cams]))
+        if return_intermediates:
+            inter.setdefault("box_masks", []).append(np.stack([box_mask(c, thr) for c in cams]))
     out = (seg, torch.stack(labels_out, dim=0), attn_pred)
     return out + (inter,) if return_intermediates else out
 
@@ -467,13 +502,16 @@ def scores(hist: np.ndarray) -> dict:
 
 def msc_flip_image(img: Tensor, label_map: np.ndarray, sd, fg_text, bg_text, scales=(1.0, 0.75, 1.25),
                    resize_long: int = 512, dataset: str = "voc", mimic_fp16: bool = True):
-    """test_msc_flip_voc.py:60-96 for one dataset image.  img [1,3,H0,W0]; label_map [Hl,Wl] uint8.
+    """test_msc_flip_voc.py:50-96 for one dataset image.  img [1,3,H0,W0]; label_map [Hl,Wl] uint8.
+    ``names = name+name`` (:52): every model call gets TWO names for its [x, flip(x)] batch, so the CAM / affinity / PAR
+    path runs for both images at every scale (2 x n_scales passes); only ``cam[0]`` of the scale-1.0 call is kept (:71).
     Returns (seg_pred [Hl,Wl], msc_pred [Hl,Wl], cam_label [Hl,Wl] | None, msc_segs [1,C,h,w])."""
     _, _, h0, w0 = img.shape
     ratio = resize_long / max(h0, w0)
     inputs = F.interpolate(img, size=(int(h0 * ratio), int(w0 * ratio)), mode="bilinear", align_corners=False)
     cat = torch.cat([inputs, inputs.flip(-1)], dim=0)
-    segs_cat, cam, _ = weclip_forward(cat, [label_map], sd, fg_text, bg_text, "val", 1, dataset, mimic_fp16)
+    names = [label_map, label_map]                                                  # names = name+name (:52)
+    segs_cat, cam, _ = weclip_forward(cat, names, sd, fg_text, bg_text, "val", 1, dataset, mimic_fp16)
     segs = segs_cat[0:1]
     segs_list = [(segs_cat[0] + segs_cat[1].flip(-1)) / 2]
     h, w = segs_cat.shape[-2:]
@@ -481,7 +519,7 @@ def msc_flip_image(img: Tensor, label_map: np.ndarray, sd, fg_text, bg_text, sca
         if s != 1.0:
             _in = F.interpolate(inputs, scale_factor=s, mode="bilinear", align_corners=False)
             cat = torch.cat([_in, _in.flip(-1)], dim=0)
-            sc, _, _ = weclip_forward(cat, [label_map], sd, fg_text, bg_text, "val", 1, dataset, mimic_fp16)
+            sc, _, _ = weclip_forward(cat, names, sd, fg_text, bg_text, "val", 1, dataset, mimic_fp16)     # cam_cat unused (:84)
             sc = F.interpolate(sc, size=(h, w), mode="bilinear", align_corners=False)
             segs_list.append((sc[0] + sc[1].flip(-1)) / 2)
     msc = torch.mean(torch.stack(segs_list, dim=0), dim=0).unsqueeze(0)

@@ -8,7 +8,9 @@ single small image when the inputs carry 16-bit rounding noise (SURVEY.md §7.2 
     step of int(thr*max) may land on either side, which moves a whole bounding box.
 The helpers below keep the 99.5 % bar for everything else: ties are excluded only where the REFERENCE margin is
 below the tolerance, and a box flip is accepted only if every differing cell is within one uint8 step of the
-threshold — in which case the labels must still agree >= 99.5 % with the oracle re-run on the same boxes.
+threshold (checked cell by cell on the thresholded maps) — in which case the labels must still agree >= 99.5 % with
+the oracle re-run on the same boxes.  The full-size tests (tests/test_fullsize_gpu.py) and the aggregate test use the
+raw 99.5 % with no exclusions.
 """
 import numpy as np
 import torch
@@ -47,19 +49,26 @@ def label_checks(model, cam: torch.Tensor, cam_ref, oracle_call, thr: float):
     ours = last["box_masks"].cpu().numpy()
     k_off = last["k_off"]
     flipped = False
+    cams_g = last["cams"].cpu().numpy()
     for i, m_o in enumerate(inter["box_masks"]):
         m = ours[k_off[i]:k_off[i + 1]]
         for k in range(m.shape[0]):
             if np.array_equal(m[k], m_o[k]):
                 continue
             flipped = True
-            # the flip must be numerically justified: some cell of the oracle's CAM lies within one uint8 step of the
-            # threshold (clip/utils.py:118-121: u8 > int(thr * max(u8)))
-            c = inter["cams"][i][k]
-            u8 = np.floor(c * 255.0)
-            t = int(thr * u8.max())
-            near = np.abs(c * 255.0 - (t + 1)) < 1.0
-            assert near.any(), "box mask differs without any cell near the uint8 threshold"
+            # the flip must be numerically justified cell by cell: the binarisations u8 > int(thr * max(u8))
+            # (clip/utils.py:118-121) of our Grad-CAM and of the oracle's may only differ in cells whose oracle value lies
+            # within (the measured CAM error + one uint8 step) of the threshold — not "some cell somewhere in the map"
+            c = inter["cams"][i][k].numpy() if hasattr(inter["cams"][i][k], "numpy") else np.asarray(inter["cams"][i][k])
+            g = cams_g[k_off[i] + k].reshape(c.shape)
+            err = float(np.abs(g - c).max())
+            assert err < SEG_TOL, f"Grad-CAM error {err}"
+            u8_o, u8_g = np.floor(c * 255.0), np.floor(g * 255.0)
+            t_o, t_g = int(thr * u8_o.max()), int(thr * u8_g.max())
+            differ = (u8_o > t_o) != (u8_g > t_g)
+            assert differ.any(), "box mask differs although the thresholded maps are identical"
+            near = np.abs(c * 255.0 - (t_o + 1)) <= 255.0 * err + 1.0
+            assert near[differ].all(), "a thresholded cell differs that is not within the numeric error of the threshold"
     assert flipped, f"pseudo-label agreement {agree} < {AGREE} with identical box masks"
     masks = [ours[k_off[i]:k_off[i + 1]] for i in range(len(inter["box_masks"]))]
     cam_fixed, _ = oracle_call(masks)

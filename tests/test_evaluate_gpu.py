@@ -98,6 +98,81 @@ def test_msc_flip_image_matches_oracle():
     assert 0.0 <= sc["msc_seg"]["miou"] <= 1.0
 
 
+def test_cam_passes_live_equals_reference_call_pattern():
+    """cam_passes="reference" (names = name+name with every [x, flip(x)] call, test_msc_flip_voc.py:52,69,84: six CAM / PAR
+    passes per dataset image) and cam_passes="live" (only the pass whose labels are read, :71) give the same three
+    confusion matrices and predictions."""
+    sd = synth.make_state_dict(0, 21)
+    fg, bg = synth.make_text_features(7, 20, 25)
+    rng = np.random.default_rng(12)
+    root = tempfile.mkdtemp()
+    B, H, W = 2, 96, 128
+    labs, names = [], []
+    for i in range(B):
+        lab = synth.make_label_map(rng, H, W, synth.draw_label_set(rng, 20))
+        synth.write_label_png(root, "SegmentationClassAug", f"c{i}", lab)
+        labs.append(lab); names.append(f"c{i}")
+    img = synth.make_images(14, B, H, W).cuda()
+    gt = torch.from_numpy(np.stack(labs).astype(np.int16)).cuda()
+    model = WeCLIP(num_classes=21, dataset_root_path=root, device="cuda", state_dict=sd, fg_text_features=fg,
+                   bg_text_features=bg)
+    calls = []
+    fwd = model.forward
+    model.forward = lambda x, names_, mode="train": (calls.append(len(names_)), fwd(x, names_, mode=mode))[1]
+    ref = MscFlipEvaluator(model, 21, (1.0, 0.75, 1.25), resize_long=128, cam_passes="reference")
+    live = MscFlipEvaluator(model, 21, (1.0, 0.75, 1.25), resize_long=128, cam_passes="live")
+    assert ref.cam_passes_per_image == 6 and live.cam_passes_per_image == 1
+    r = ref.process_batch(names, img, gt, want_preds=True)
+    assert calls == [2 * B] * 3
+    del calls[:]
+    l_ = live.process_batch(names, img, gt, want_preds=True)
+    assert sorted(calls) == [0, 0, B]
+    assert torch.equal(r[0], l_[0]) and torch.equal(r[1], l_[1]) and torch.equal(r[3], l_[3])
+    assert (r[2] == l_[2]).float().mean().item() >= 0.999        # fp atomics order on the CAM path
+    assert torch.equal(ref.hist[:2], live.hist[:2])
+    assert int((ref.hist[2] - live.hist[2]).abs().sum()) <= 2e-3 * int(ref.hist[2].sum())
+
+
+def test_msc_flip_matches_reference_validate_golden(golden_dir):
+    """The evaluation driver against the REAL validate() loop of test_msc_flip_voc.py:30-113 (tests/golden/mscflip_voc.npz,
+    generated by oracle/make_golden.py::golden_mscflip): two dataset images of different sizes (short sides not multiples
+    of 16 after the long-side resize), one image per call as the reference's DataLoader(batch_size=1) does, plus the
+    .npy logit dump of :111."""
+    import os
+    from oracle.make_golden import MSCFLIP_CASE, mscflip_case
+    g = np.load(os.path.join(golden_dir, "mscflip_voc.npz"))
+    c = MSCFLIP_CASE
+    sd = synth.make_state_dict(c["weights_seed"], 21)
+    fg, bg = synth.make_text_features(c["text_seed"], 20, 25)
+    root, dump = tempfile.mkdtemp(), tempfile.mkdtemp()
+    items = mscflip_case()
+    for name, _, lab in items:
+        synth.write_label_png(root, "SegmentationClassAug", name, lab)
+    model = WeCLIP(num_classes=21, dataset_root_path=root, device="cuda", state_dict=sd, fg_text_features=fg,
+                   bg_text_features=bg)
+    ev = MscFlipEvaluator(model, 21, c["scales"], resize_long=c["resize_long"], logit_dir=dump)
+    agree = np.zeros(3); total = 0
+    for i, (name, img, lab) in enumerate(items):
+        gt = torch.from_numpy(lab.astype(np.int16)).cuda()
+        seg_pred, msc_pred, cam, msc = ev.process(name, img[None].cuda(), gt, want_preds=True)
+        ref_msc = torch.from_numpy(g[f"msc_segs{i}"])
+        assert ((msc.cpu() - ref_msc[0]).abs().max() / ref_msc.abs().max()).item() < 2e-2
+        for j, (got, key) in enumerate(((seg_pred, "seg_pred"), (msc_pred, "msc_pred"), (cam, "cam"))):
+            agree[j] += (got.cpu().numpy() == g[f"{key}{i}"]).sum()
+        total += lab.size
+    assert (agree / total >= 0.995).all(), agree / total
+    h = ev.hist.cpu().numpy()
+    assert h.sum(axis=(1, 2)).tolist() == g["hist"].sum(axis=(1, 2)).tolist()        # same valid-pixel counts, exactly
+    assert (np.abs(h - g["hist"]).sum(axis=(1, 2)) <= 2 * 0.005 * g["hist"].sum(axis=(1, 2))).all()
+    ev.scores()                                                                       # drains the logit dumper
+    for i, (name, _, _) in enumerate(items):
+        d = np.load(os.path.join(dump, name + ".npy"), allow_pickle=True).item()       # the CRF stage's read, :140-141
+        assert set(d) == {"segs", "msc_segs"} and d["segs"].shape == g[f"segs{i}"].shape
+        assert d["msc_segs"].dtype == np.float32 and d["msc_segs"].shape == g[f"msc_segs{i}"].shape
+        assert np.abs(d["segs"] - g[f"segs{i}"]).max() / np.abs(g[f"segs{i}"]).max() < 2e-2
+        assert np.abs(d["msc_segs"] - g[f"msc_segs{i}"]).max() / np.abs(g[f"msc_segs{i}"]).max() < 2e-2
+
+
 def test_batched_bucket_equals_image_by_image():
     """A (H,W) bucket of B dataset images run as one [2B,...] forward per scale gives the same three confusion
     matrices as the reference's image-by-image loop (images are independent)."""

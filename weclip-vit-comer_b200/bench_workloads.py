@@ -2,8 +2,11 @@
 
 ``mscflip`` = BASELINE.json configs[2]: test_msc_flip_voc inference, scales 1.0/0.75/1.25 + flip at 512x512,
 21 classes, images sharded across ranks.  One step = IMAGES_PER_STEP dataset images through
-``evaluate.MscFlipEvaluator.process`` (6 WeCLIP forwards each: encoder, decoder, Grad-CAM, affinity refinement,
-CAM upsample, PAR at label resolution, then fusion + argmax + 3 confusion matrices).
+``evaluate.MscFlipEvaluator.process_batch`` (6 WeCLIP forwards each: encoder, decoder and — with the reference's
+``names = name+name`` call pattern, test_msc_flip_voc.py:52 — Grad-CAM, affinity refinement, CAM upsample and PAR at label
+resolution for all six images; then fusion + argmax + 3 confusion matrices).  ``value`` / ``e2e`` are measured with that
+call pattern (cam_passes="reference": 6 CAM/PAR passes per dataset image); ``value_live_outputs`` is the same step with
+the dead passes eliminated (cam_passes="live": 1 pass, identical histograms).
 """
 from __future__ import annotations
 
@@ -64,6 +67,10 @@ class MscFlipVoc:
     n_classes, n_fg, n_bg, dataset, subdir = 21, 20, 25, "voc", "SegmentationClassAug"
     scales = (1.0, 0.75, 1.25)
     H = W = 512
+    units = IMAGES_PER_STEP
+    # per forward pair at 512x512 the attention scores alone are 2*12*1025*1032*4 B = 101 MB per block; with taps, MLP
+    # activations and PAR affinities the working set per image is > 126 MB
+    l2_note = "working set larger than L2 (>= 101 MB of attention scores per block at 512x512, x3 scales)"
 
     def _make_data(self, seed, n_img, root):
         rng = np.random.default_rng(seed)
@@ -88,36 +95,42 @@ class MscFlipVoc:
         self.model = WeCLIP(num_classes=self.n_classes, dataset_root_path=self.root, device=device,
                             dataset=self.dataset, state_dict=self.sd, fg_text_features=self.fg,
                             bg_text_features=self.bg)
-        self.ev = MscFlipEvaluator(self.model, self.n_classes, self.scales, 512, device,
-                                   overlap_scales=os.environ.get("WC_OVERLAP_SCALES", "1") != "0")
+        overlap = os.environ.get("WC_OVERLAP_SCALES", "1") != "0"
+        self.ev = MscFlipEvaluator(self.model, self.n_classes, self.scales, 512, device, overlap_scales=overlap,
+                                   cam_passes="reference")
+        self.ev_live = MscFlipEvaluator(self.model, self.n_classes, self.scales, 512, device, overlap_scales=overlap,
+                                        cam_passes="live")
+        self.cam_passes_per_image = self.ev.cam_passes_per_image if self.dataset == "voc" else 0
         self.imgs_h = imgs.pin_memory()
         self.labs_h = torch.from_numpy(np.stack(labs).astype(np.int16)).pin_memory()
         self.imgs_d = self.imgs_h.to(device)
         self.labs_d = self.labs_h.to(device)
         self.hist_h = torch.empty(3, self.n_classes, self.n_classes, dtype=torch.int64).pin_memory()
-        self.units = IMAGES_PER_STEP
         self.h2d = self.imgs_h.numel() * 4 + self.labs_h.numel() * 2
         self.d2h = self.hist_h.numel() * 8
         self.launches = None
-        # per forward pair at 512x512 the attention scores alone are 2*12*1025*1032*4 B = 101 MB, rewritten by each
-        # of the 12 blocks; with taps, MLP activations and PAR affinities the working set per image is > 126 MB
-        self.l2_note = "working set larger than L2 (>= 101 MB of attention scores per block at 512x512, x3 scales)"
 
     def step_device(self, record=False):
         # the step's images share one (H,W) bucket: one [2B,3,H,W] forward per scale
         self.ev.process_batch(self.names, self.imgs_d, self.labs_d)
 
+    def step_device_live(self):
+        """Same step with cam_passes="live": only the CAM / PAR pass whose labels the driver reads."""
+        self.ev_live.process_batch(self.names, self.imgs_d, self.labs_d)
+
     def join(self):
         """Order the current stream after every step enqueued so far (the passes run on the evaluator's own streams)."""
-        ev = getattr(self, "ev", None)      # workloads without an evaluator run on the current stream already
-        if ev is not None:
-            ev.join()
+        for ev in (getattr(self, "ev", None), getattr(self, "ev_live", None)):
+            if ev is not None:              # workloads without an evaluator run on the current stream already
+                ev.join()
 
     def step_e2e(self):
+        """Host buffers in, histograms out: H2D of the step's images + labels from pinned memory, the step, the cross-rank
+        histogram sum (the path's only collective; a no-op at world size 1) and the D2H read of the result."""
         img = self.imgs_h.to(self.dev, non_blocking=True)
         lab = self.labs_h.to(self.dev, non_blocking=True)
         self.ev.process_batch(self.names, img, lab)
-        self.hist_h.copy_(self.ev.hist, non_blocking=True)      # .hist orders this stream after the step's passes
+        self.hist_h.copy_(self.ev.all_reduce(in_place=False), non_blocking=True)   # .hist orders this stream after the passes
         torch.cuda.current_stream().synchronize()
         return self.hist_h
 
@@ -147,7 +160,7 @@ class MscFlipVoc:
         for k, (ms, work, cnt) in prof.items():
             if cnt == 0:
                 continue
-            row = {"ms_per_step": round(ms, 3), "share": round(ms / total, 4), "launches_per_step": cnt}
+            row = {"ms_per_step": round(ms, 3), "share_of_profile_pass": round(ms / total, 4), "launches_per_step": cnt}
             if work > 0 and ms > 0:
                 if k in KINDS_TENSOR:
                     a = work / (ms * 1e-3) / 1e12
@@ -168,7 +181,11 @@ class MscFlipVoc:
                 "peak": peak, "peak_source": peaks["source"] + (" (sustained cuBLAS bf16)" if tensor else " (copy)"),
                 "unit": "TFLOP/s" if tensor else "GB/s", "frac": round(ach / peak, 4) if ach else None,
                 "traffic": traffic.get(top), "traffic_source": traffic.get("_file"),
-                "kernel_ms_per_launch": round(ms / max(cnt, 1), 4), "kernels": rows}
+                "kernel_ms_per_launch": round(ms / max(cnt, 1), 4),
+                "kernels_note": "per-class device time from a separate SERIALISED profile pass (one stream, events around every "
+                                "launch); the timed step overlaps its three scale passes, so the classes sum to more than "
+                                "ms_per_step",
+                "kernels": rows}
 
     # ---- CPU baseline / reference arm (oracle port of the evaluation loop; bounded sample) ---------------
     @classmethod
@@ -189,11 +206,40 @@ class MscFlipVoc:
             O.msc_flip_image(self.imgs_h[i:i + 1].clone(), self.labs[i], self.sd, self.fg, self.bg, self.scales, 512,
                              self.dataset)
         dt = time.perf_counter() - t0
-        return n_img / dt, (f"{n_img} of the step's {IMAGES_PER_STEP} dataset images (6 forwards + fusion each), "
-                            "oracle port of the reference loop, torch CPU fp32")
+        return n_img / dt, (f"{n_img} of the step's {IMAGES_PER_STEP} dataset images (6 forwards with names = name+name, i.e. "
+                            f"{self.cam_passes_per_image} CAM/PAR passes, + fusion each), oracle port of the reference loop "
+                            "(pinned against the real validate(), tests/golden/mscflip_voc.npz), torch CPU fp32")
+
+    def gpu_library_sample(self, n_img=3):
+        """The "library-call bar" (SURVEY §8d): the same loop as ATen / cuBLAS / cuDNN library calls on this GPU, in the
+        reference's own GPU mixed precision (fp32 in-proj + softmax, fp16 conv1 / out-proj / MLP: clip/model.py:461-476,
+        clip/myAtt.py:199,321), with the reference's host round trips (OpenCV boxes, cv2.resize, numpy CAM weights).
+        It is the oracle run on cuda: a baseline, never a product path."""
+        from oracle import weclip_oracle as O
+        dev = self.dev
+        sd = {k: v.to(dev) for k, v in self.sd.items()}
+        fg, bg = self.fg.to(dev), self.bg.to(dev)
+        labs = [self.labs_h[i].numpy().astype(np.uint8) for i in range(min(n_img, IMAGES_PER_STEP))]
+
+        def run(i):
+            return O.msc_flip_image(self.imgs_d[i:i + 1], labs[i], sd, fg, bg, self.scales, 512, self.dataset,
+                                    mimic_fp16="gpu")
+        run(0)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(len(labs)):
+            run(i)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        return len(labs) / dt, (f"{len(labs)} dataset images after 1 warm-up, oracle loop on cuda: torch {torch.__version__} "
+                                "ATen/cuBLAS library calls, reference GPU mixed precision, host OpenCV/numpy round trips")
+
+
+MscFlipVoc.cam_passes_per_image = 6
 
 
 class MscFlipCoco(MscFlipVoc):
+    cam_passes_per_image = 0
     name = ("cfg4: test_msc_flip_coco val, scales 1.0/0.75/1.25 + flip, 512x512, 81 classes "
             "(val mode returns before CAM/PAR, model_attn_aff_coco.py:131-132)")
     n_classes, n_fg, n_bg, dataset = 81, 80, 23, "coco"
@@ -208,6 +254,9 @@ class PseudoLabelVoc(MscFlipVoc):
     name = "cfg2: WeCLIP VOC CAM+PAR pseudo-label step, batch 32 at 320x320 crop, 21 classes, mode='train' (RFM branch)"
     H = W = 320
     BATCH = 32
+    units = BATCH
+    cam_passes_per_image = 1          # one name per crop: one CAM / PAR pass per crop
+    l2_note = "working set larger than L2 (32 crops: 157 MB of MLP activations per block, 315 MB of PAR affinities)"
 
     def __init__(self, rank: int, device):
         from .model import WeCLIP
@@ -222,11 +271,9 @@ class PseudoLabelVoc(MscFlipVoc):
         self.imgs_h = imgs.pin_memory()
         self.imgs_d = self.imgs_h.to(device)
         self.labels_h = torch.empty(self.BATCH, self.H, self.W, dtype=torch.int64).pin_memory()
-        self.units = self.BATCH
         self.h2d = self.imgs_h.numel() * 4
         self.d2h = self.labels_h.numel() * 8
         self.launches = None
-        self.l2_note = "working set larger than L2 (32 crops: 157 MB of MLP activations per block, 315 MB of PAR affinities)"
 
     def step_device(self, record=False):
         self.model.iter_num = 20000            # RFM branch of clip_tool.py:152-175

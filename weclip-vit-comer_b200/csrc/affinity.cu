@@ -295,7 +295,7 @@ extern "C" size_t wc_affinity_workspace_bytes(int N, int h, int w, int total_ins
 }
 
 extern "C" int wc_affinity_refine(const float* attn, int nl, const float* attn_pred, int N, int h, int wd, int use_rfm,
-                                  const float* cams, const int* k_off_host, float box_thr, float* cams_refined,
+                                  const float* cams, const int* k_off_host, double box_thr, float* cams_refined,
                                   float* box_masks, void* workspace, size_t workspace_bytes, void* stream) {
     WC_CHECK_ARG(attn && cams && k_off_host && cams_refined && workspace && nl >= 1 && nl <= 16);
     WC_CHECK_ARG(N > 0 && N <= AFF_MAX_IMG && h > 0 && wd > 0 && (!use_rfm || attn_pred));
@@ -336,12 +336,8 @@ extern "C" int wc_affinity_refine(const float* attn, int nl, const float* attn_p
     }
     // box masks -> v0 = mask * cam
     const size_t box_smem = (size_t)P * 21 + 16;
-    static bool attr_set = false;
-    if (!attr_set) {
-        WC_CUDA(cudaFuncSetAttribute(box_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
-    }
-    box_mask_kernel<<<total, 256, box_smem, st>>>(cams, v0, box_masks, h, wd, (double)box_thr);
+    WC_SET_MAX_SMEM(box_mask_kernel, 200 * 1024);
+    box_mask_kernel<<<total, 256, box_smem, st>>>(cams, v0, box_masks, h, wd, box_thr);
     WC_LAUNCH_CHECK();
     // cam' = T_s (T_s v0)
     const float* src = v0;

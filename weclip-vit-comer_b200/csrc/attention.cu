@@ -793,11 +793,7 @@ static int attn_maps(const h16* q, const h16* k, const h16* vt, int nh, int L, i
 template <int HD>
 static int launch_fwd_hd(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const AttnArgs& a, dim3 grid,
                          cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        WC_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::TOTAL));
-        attr_set = true;
-    }
+    WC_SET_MAX_SMEM(attn_fwd_kernel<HD>, FwdSmem::TOTAL);
     attn_fwd_kernel<HD><<<grid, FW_THREADS, FwdSmem::TOTAL, st>>>(mq, mk, mv, a);
     WC_LAUNCH_CHECK();
     return WC_OK;
@@ -826,11 +822,7 @@ int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, floa
 int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* avg, int n_img, int heads, int L,
                          cudaStream_t st) {
     WC_CHECK_ARG(q && k && lse2 && avg && n_img > 0 && heads > 0 && L > 0 && n_img <= 65535);
-    static bool attr_set = false;
-    if (!attr_set) {
-        WC_CUDA(cudaFuncSetAttribute(attn_headmean_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MeanSmem::TOTAL));
-        attr_set = true;
-    }
+    WC_SET_MAX_SMEM(attn_headmean_kernel, MeanSmem::TOTAL);
     CUtensorMap mq, mk;
     int rc = attn_maps(q, k, nullptr, n_img * heads, L, 0, AT_HD, &mq, &mk, nullptr);
     if (rc) return rc;
@@ -847,11 +839,7 @@ int launch_attn_bwd_colsum(const h16* q, const h16* k, const h16* v, const h16* 
                            const BwdInstTable& tab, int n_inst, int n_img, int heads, int L, int Lp, cudaStream_t st) {
     WC_CHECK_ARG(q && k && v && dOT && lse2 && colsum && n_inst > 0 && n_inst <= BWD_MAX_INST && n_img > 0 && heads > 0);
     WC_CHECK_ARG(L > 1 && Lp >= L && (Lp & 7) == 0 && ceil_div(L, AT_BN) * AT_BN <= BW_MAX_L && heads <= 65535);
-    static bool attr_set = false;
-    if (!attr_set) {
-        WC_CUDA(cudaFuncSetAttribute(attn_bwd_colsum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::TOTAL));
-        attr_set = true;
-    }
+    WC_SET_MAX_SMEM(attn_bwd_colsum_kernel, BwdSmem::TOTAL);
     CUtensorMap mq, mk, md;
     int rc = attn_maps(q, k, nullptr, n_img * heads, L, 0, AT_HD, &mq, &mk, nullptr);
     if (rc) return rc;

@@ -5,6 +5,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <atomic>
 
 #include "../../include/weclip_b200.h"
 
@@ -36,6 +37,20 @@ inline int fail(int code, const char* fmt, const char* a = "", long b = 0, long 
     } while (0)
 
 #define WC_LAUNCH_CHECK() WC_CUDA(cudaGetLastError())
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device (per-context) attribute: set it once per call site AND
+// device, so that one process driving several GPUs gets it on each of them (bit d of the mask = device d done).
+#define WC_SET_MAX_SMEM(func, bytes)                                                                       \
+    do {                                                                                                   \
+        static std::atomic<unsigned long long> done__{0ull};                                               \
+        int dev__ = 0;                                                                                     \
+        WC_CUDA(cudaGetDevice(&dev__));                                                                    \
+        const unsigned long long bit__ = 1ull << (dev__ & 63);                                             \
+        if (!(done__.load(std::memory_order_acquire) & bit__)) {                                           \
+            WC_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+            done__.fetch_or(bit__, std::memory_order_release);                                             \
+        }                                                                                                  \
+    } while (0)
 
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 

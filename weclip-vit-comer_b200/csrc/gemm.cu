@@ -885,11 +885,7 @@ static int raster_n_fastest(const GemmProblem& p) {
 template <int BN>
 static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
     using C = Cfg<BN>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        WC_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::TOTAL));
-        attr_set = true;
-    }
+    WC_SET_MAX_SMEM(gemm_tc_kernel<BN>, C::TOTAL);
     CUtensorMap mA, mB;
     KernelArgs ka;
     ka.M = p.M; ka.N = p.N; ka.K = p.K; ka.nb0 = p.nb0; ka.e = p.epi;
@@ -917,11 +913,7 @@ static int launch_cfg(const GemmProblem& p, cudaStream_t st) {
 
 template <int FE>
 static int launch_pair_fe(const CUtensorMap& mA, const CUtensorMap& mB, const KernelArgs& ka, int grid, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        WC_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<FE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2::TOTAL));
-        attr_set = true;
-    }
+    WC_SET_MAX_SMEM(gemm_tc2_kernel<FE>, Cfg2::TOTAL);
     gemm_tc2_kernel<FE><<<grid, GEMM_THREADS, Cfg2::TOTAL, st>>>(mA, mB, ka);
     return WC_OK;
 }

@@ -167,11 +167,13 @@ __global__ void __launch_bounds__(256) aff_loss_grad_kernel(const int64_t* __res
 struct SegAcc { double bg_sum, fg_sum; unsigned long long bg_n, fg_n; };
 
 // Pass 0: how many background (label 0) and foreground (label != 0, != ignore) pixels (the two CE means' denominators).
-__global__ void __launch_bounds__(256) seg_count_kernel(const int64_t* __restrict__ label, long n, int ignore, SegAcc* acc) {
+__global__ void __launch_bounds__(256) seg_count_kernel(const int64_t* __restrict__ label, long n, int C, int ignore, SegAcc* acc) {
     unsigned long long bn = 0, fn = 0;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
         const long long l = label[i];
-        if (l == 0) ++bn; else if (l != ignore) ++fn;
+        // only labels the loss kernel sums over: 0 <= l < C (an out-of-range label that is not ignore_index is a device
+        // assert in F.cross_entropy; here it is dropped from the numerator AND the denominator)
+        if (l == 0) ++bn; else if (l != ignore && l > 0 && l < C) ++fn;
     }
     bn = warp_sum_u(bn); fn = warp_sum_u(fn);
     if ((threadIdx.x & 31) == 0) { if (bn) atomicAdd(&acc->bg_n, bn); if (fn) atomicAdd(&acc->fg_n, fn); }
@@ -361,7 +363,7 @@ extern "C" int wc_seg_loss(const float* pred, const int64_t* label, int B, int C
     SegAcc* acc = static_cast<SegAcc*>(workspace);
     WC_CUDA(cudaMemsetAsync(acc, 0, sizeof(SegAcc), st));
     const long HW = (long)H * W, n = (long)B * HW;
-    seg_count_kernel<<<grid_for(n, 256), 256, 0, st>>>(label, n, ignore_index, acc);
+    seg_count_kernel<<<grid_for(n, 256), 256, 0, st>>>(label, n, C, ignore_index, acc);
     WC_LAUNCH_CHECK();
     const bool vec = HW % 4 == 0 && (reinterpret_cast<uintptr_t>(pred) & 15) == 0 &&
                      (!grad || (reinterpret_cast<uintptr_t>(grad) & 15) == 0);

@@ -521,11 +521,7 @@ template <typename AffT>
 static int launch_iter_tile(const AffT* aff, const float* src, float* dst, const TileArgs& ta, const ParChunks& chunks,
                             int n, int max_cnt, cudaStream_t st) {
     constexpr int PLANE = (PT_TH + 2 * PT_HALO) * PT_SW * (int)sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
-        WC_CUDA(cudaFuncSetAttribute(par_iter_tile_kernel<AffT>, cudaFuncAttributeMaxDynamicSharedMemorySize, PT_KC * PLANE));
-        attr_set = true;
-    }
+    WC_SET_MAX_SMEM(par_iter_tile_kernel<AffT>, PT_KC * PLANE);
     dim3 grid(ceil_div(ta.W, PT_W), ceil_div(ta.H, PT_TH), n);
     par_iter_tile_kernel<AffT><<<grid, PT_THREADS, max_cnt * PLANE, st>>>(aff, src, dst, ta, chunks);
     WC_LAUNCH_CHECK();
@@ -600,11 +596,7 @@ static int affinity(const float* img, AffT* aff, int B, const ParGeom& g, const 
     ProfScope prof(PK_PAR_AFF, (double)B * g.H * g.W * (12.0 + (double)sizeof(AffT) * g.nn), st);
     if (fast) {
         constexpr int SMEM = 3 * PA_SH * PT_SW * (int)sizeof(float);
-        static bool attr_set = false;
-        if (!attr_set) {
-            WC_CUDA(cudaFuncSetAttribute(par_aff_tile_kernel<AffT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-            attr_set = true;
-        }
+        WC_SET_MAX_SMEM(par_aff_tile_kernel<AffT>, SMEM);
         dim3 grid(ceil_div(g.W, PT_W), ceil_div(g.H, PA_TH), B);
         const int vec = (g.W % 4 == 0) && aligned16(img);
         par_aff_tile_kernel<AffT><<<grid, PA_THREADS, SMEM, st>>>(img, aff, g.H, g.W, g.wp, vec, pos);

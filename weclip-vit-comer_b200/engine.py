@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import ctypes
 import math
-from ctypes import POINTER, Structure, byref, c_float, c_int, c_size_t, c_void_p
+from ctypes import POINTER, Structure, byref, c_double, c_float, c_int, c_size_t, c_void_p
 from typing import Dict, List, Optional, Sequence
 
 import torch
@@ -181,7 +181,7 @@ class Engine:
         masks = torch.empty(total, h, w, dtype=torch.float32, device=self.device) if want_masks else None
         ws = self._workspace("aff", L.wc_affinity_workspace_bytes(N, h, w, total, nl))
         rc = L.wc_affinity_refine(_lib.ptr(attn), nl, _lib.ptr(attn_pred), N, h, w, int(use_rfm), _lib.ptr(cams),
-                                  _lib.int_array(k_off), c_float(box_thr), _lib.ptr(out), _lib.ptr(masks),
+                                  _lib.int_array(k_off), c_double(box_thr), _lib.ptr(out), _lib.ptr(masks),
                                   _lib.ptr(ws), c_size_t(ws.numel()), _lib.stream_ptr())
         _lib.check(rc, "wc_affinity_refine")
         return out, masks

@@ -28,6 +28,43 @@ def scores(hist: np.ndarray) -> dict:
         return {"pAcc": acc, "mAcc": acc_cls, "miou": np.nanmean(iu[valid]), "iou": dict(enumerate(iu))}
 
 
+class LogitDumper:
+    """Per-image ``.npy`` logit dump of test_msc_flip_voc.py:111 — ``np.save(work_dir/logit/<name>.npy, {"segs": [1,C,h,w],
+    "msc_segs": [1,C,h,w]})``, the file the CRF stage reads back with ``np.load(..., allow_pickle=True).item()`` (:140-141).
+    Device -> pinned-host copies are asynchronous; files are written when their copy has completed (``drain``), so the
+    evaluation loop is never synchronised per image."""
+
+    def __init__(self, logit_dir: str):
+        import os
+        self.dir = logit_dir
+        os.makedirs(logit_dir, exist_ok=True)
+        self._pending = []
+
+    def add(self, names, segs: torch.Tensor, msc: torch.Tensor):
+        """segs / msc fp32 [B,C,h,w] on the device, valid on the current stream."""
+        hs = torch.empty(segs.shape, dtype=torch.float32, pin_memory=True)
+        hm = torch.empty(msc.shape, dtype=torch.float32, pin_memory=True)
+        hs.copy_(segs, non_blocking=True)
+        hm.copy_(msc, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._pending.append((ev, list(names), hs, hm))
+        self.drain(block=False)
+
+    def drain(self, block: bool = True):
+        import os
+        keep = []
+        for ev, names, hs, hm in self._pending:
+            if not block and not ev.query():
+                keep.append((ev, names, hs, hm))
+                continue
+            ev.synchronize()
+            for i, name in enumerate(names):
+                np.save(os.path.join(self.dir, str(name) + ".npy"),
+                        {"segs": hs[i:i + 1].numpy().copy(), "msc_segs": hm[i:i + 1].numpy().copy()})
+        self._pending = keep
+
+
 def shard_indices(n_items: int, rank: int, world: int) -> range:
     """Round-robin image sharding (the reference's own multi-GPU idiom, clip/generate_cams_voc12.py:96-100)."""
     return range(rank, n_items, world)
@@ -35,7 +72,19 @@ def shard_indices(n_items: int, rank: int, world: int) -> range:
 
 class MscFlipEvaluator:
     def __init__(self, model, num_classes: int = 21, test_scales: Sequence[float] = (1.0, 0.75, 1.25),
-                 resize_long: int = 512, device="cuda", overlap_scales: bool = True):
+                 resize_long: int = 512, device="cuda", overlap_scales: bool = True, cam_passes: str = "reference",
+                 logit_dir: Optional[str] = None):
+        """cam_passes: how often the CAM / affinity / PAR path runs per dataset image.
+        "reference" = the reference's call pattern: ``names = name+name`` (test_msc_flip_voc.py:52, coco :53) is passed
+        with EVERY ``[x_s, flip(x_s)]`` batch (:69, :84), so pseudo-labels are built for the plain AND the flipped image at
+        every scale: 2 x n_scales passes per dataset image (6 for scales 1.0/0.75/1.25).
+        "live" = dead-output elimination: the caller only reads ``cam[0]`` of the scale-1.0 call (:71; ``cam_cat`` of :84
+        is never read), so ONE pass per dataset image produces the same three histograms."""
+        if cam_passes not in ("reference", "live"):
+            raise ValueError("cam_passes must be 'reference' or 'live'")
+        self.cam_passes = cam_passes
+        self.dumper = LogitDumper(logit_dir) if logit_dir else None
+        self._names = None
         self.model = model
         self.C = num_classes
         self.scales = list(test_scales)
@@ -80,7 +129,11 @@ class MscFlipEvaluator:
 
         def fwd(s):
             x = base if s == 1.0 else ops.resize_bilinear(base, scale_factor=s)
-            segs, cam, _ = self.model(ops.flip_concat(x), names, mode="val")
+            if self.cam_passes == "reference":
+                nm = names + names                       # names = name+name (test_msc_flip_voc.py:52): plain + flipped
+            else:
+                nm = names if s == 1.0 else []           # only cam[0] of the scale-1.0 call is read (:71)
+            segs, cam, _ = self.model(ops.flip_concat(x), nm, mode="val")
             return segs, cam
 
         if side is None:
@@ -90,6 +143,12 @@ class MscFlipEvaluator:
             with torch.cuda.stream(side[i]):
                 outs[i] = fwd(scales[i])
         return outs
+
+    @property
+    def cam_passes_per_image(self) -> int:
+        """CAM / affinity / PAR passes per dataset image under the current ``cam_passes`` mode."""
+        n_sc = 1 + sum(1 for s in self.scales if s != 1.0)
+        return 2 * n_sc if self.cam_passes == "reference" else 1
 
     def reset(self):
         self.hist.zero_()
@@ -109,8 +168,8 @@ class MscFlipEvaluator:
         so a (H,W) bucket is run as one [2B,3,H,W] forward per scale: B plain images followed by their B flipped
         twins).  inputs fp32 [B,3,H0,W0]; labels int16 [B,Hl,Wl]."""
         B = inputs.shape[0]
-        names = list(names)      # B names for 2B images: the CAM / PAR path runs for the B plain images only, exactly as the
-                                 # reference's one-name call does for its [image, flip] pair (model_attn_aff_voc.py:139)
+        names = list(names)      # one name per dataset image; _forward_scales repeats them for the flipped twins
+        self._names = names
         _, _, h0, w0 = inputs.shape
         ratio = self.resize_long / max(h0, w0)
         n_sc = 1 + sum(1 for s in self.scales if s != 1.0)
@@ -157,28 +216,35 @@ class MscFlipEvaluator:
         if cam is not None:                                                                  # :71, :107
             ops.confusion_hist(cam[:B], labels, self._hist[2])
         self.n_images += B
+        if self.dumper is not None:                                                          # :111
+            self.dumper.add(self._names, segs_cat[:B], msc)
         if want_preds:
             return seg_pred, msc_pred, (cam[:B] if cam is not None else None), msc
         return None
 
-    def all_reduce(self):
-        """The only collective of the path: sum the three C x C histograms over ranks (NCCL over NVLink)."""
+    def all_reduce(self, in_place: bool = True):
+        """The only collective of the path: sum the three C x C histograms over ranks (NCCL over NVLink).
+        in_place=False reduces a copy (a running evaluation keeps accumulating its local histograms)."""
         import torch.distributed as dist
-        hist = self.hist
+        hist = self.hist if in_place else self.hist.clone()
         if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
             dist.all_reduce(hist, op=dist.ReduceOp.SUM)
         return hist
 
     def scores(self) -> dict:
+        if self.dumper is not None:
+            self.dumper.drain()
         h = self.hist.cpu().numpy()
         return {"seg": scores(h[0]), "msc_seg": scores(h[1]), "cam": scores(h[2])}
 
 
 def validate(model, dataset: Iterable, test_scales=None, num_classes: int = 21, resize_long: int = 512,
-             rank: int = 0, world: int = 1, device="cuda"):
+             rank: int = 0, world: int = 1, device="cuda", cam_passes: str = "reference",
+             logit_dir: Optional[str] = None):
     """Drop-in for validate() of test_msc_flip_voc.py: dataset yields (name, image CHW fp32, label HW, cls_label).
     Returns the three score dicts after the cross-rank histogram reduction."""
-    ev = MscFlipEvaluator(model, num_classes, test_scales or [1.0, 0.75], resize_long, device)
+    ev = MscFlipEvaluator(model, num_classes, test_scales or [1.0, 0.75], resize_long, device, cam_passes=cam_passes,
+                          logit_dir=logit_dir)
     items = list(dataset) if not hasattr(dataset, "__getitem__") else dataset
     for i in shard_indices(len(items), rank, world):
         name, image, label = items[i][:3]

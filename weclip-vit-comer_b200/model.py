@@ -55,6 +55,21 @@ class LabelReader:
         return ids, lab.shape[0], lab.shape[1]
 
 
+def load_clip_checkpoint(path: str) -> dict:
+    """clip/clip.py:127-140 (clip.load): the configured checkpoint (configs/*.yaml clip_pretrain_path: ViT-B-16.pt) is a
+    TorchScript archive, so ``torch.jit.load`` is tried first and its ``state_dict()`` taken; a plain pickled state dict
+    (optionally wrapped as ``{"state_dict": ...}``) is the fallback, exactly as in the reference."""
+    try:
+        return dict(torch.jit.load(path, map_location="cpu").eval().state_dict())
+    except RuntimeError:
+        obj = torch.load(path, map_location="cpu", weights_only=False)
+    if isinstance(obj, dict) and "state_dict" in obj and isinstance(obj["state_dict"], dict):
+        obj = obj["state_dict"]
+    if hasattr(obj, "state_dict") and not isinstance(obj, dict):
+        obj = obj.state_dict()
+    return dict(obj)
+
+
 def _to_device_async(t: torch.Tensor, device) -> torch.Tensor:
     """Small host tensor -> device without a stream synchronisation (pinned staging, asynchronous copy)."""
     if torch.device(device).type != "cuda":
@@ -90,7 +105,7 @@ class WeCLIP(nn.Module):
         self._sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
         self.engine: Optional[Engine] = None
         if state_dict is None and clip_model is not None:
-            clip_sd = torch.load(clip_model, map_location="cpu")
+            clip_sd = load_clip_checkpoint(clip_model)
             state_dict = {("encoder." + k.replace("module.", "")): v for k, v in clip_sd.items()
                           if k.replace("module.", "").startswith(("visual.", "logit_scale"))}
         if state_dict is not None:
@@ -153,8 +168,10 @@ class WeCLIP(nn.Module):
         cam_path = not (self.dataset == "coco" and mode == "val")     # model_attn_aff_coco.py:131-132
         require_seg_trans = self.iter_num > cfg["switch"] or mode == "val"
         nl = cfg["window"] if require_seg_trans else 8                 # clip_tool.py:155 / :173
-        # the CAM / PAR path runs once per NAME (model_attn_aff_voc.py:139 `for i, img_name in enumerate(img_names)`): the
-        # msc+flip driver passes one name for an [image, flipped image] batch, so only the leading images get pseudo-labels
+        # the CAM / PAR path runs once per NAME (model_attn_aff_voc.py:139 `for i, img_name in enumerate(img_names)`); the
+        # reference's msc+flip driver passes names = name+name (test_msc_flip_voc.py:52), i.e. one name per image of its
+        # [image, flipped image] batch.  Fewer names than images is allowed (only the leading images get pseudo-labels):
+        # evaluate.MscFlipEvaluator(cam_passes="live") uses that to skip passes whose labels the driver never reads
         if isinstance(img_names, str):
             img_names = [img_names]
         n_cam = len(img_names)
