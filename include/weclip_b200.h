@@ -30,7 +30,7 @@ extern "C" {
 #define WC_ERR_WORKSPACE (-3)
 #define WC_ERR_UNSUPPORTED (-4)
 
-#define WC_ABI_VERSION 8
+#define WC_ABI_VERSION 9
 #define WC_PAR_MAX_DIL 8
 
 /* ABI version (bumped whenever a signature changes) and last error text. */
@@ -192,17 +192,32 @@ int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int h, int wd, 
                const int* text_off_host, const int* k_off_host, float* cams, float* attn_last, float* probs,
                void* workspace, size_t workspace_bytes, void* stream);
 
+/* The reference runs the out-projection of every attention block in fp16 (clip/myAtt.py:321), hence its autograd backward
+ * too: with near-uniform class probabilities the gradient there (~1e-7) falls into fp16's subnormal range and the
+ * reference keeps 2-3 significant bits of it.  wc_gradcam reproduces those two roundings by default (exactly: the chain is
+ * scaled by a power of two); wc_gradcam_set_exact(1) switches them off (exact analytic gradient).  Returns the old mode.
+ * Process-wide; set it before launching work. */
+int wc_gradcam_set_exact(int exact);
+
+/* Test hook (no reference counterpart): byte offsets, from a 256-byte aligned workspace pointer, of wc_gradcam's
+ * intermediate buffers (activations, gradients, column sums) for the last backward chunk; offs has 23 entries in the
+ * order documented in csrc/gradcam.cu.  Returns the backward chunk size (instances), negative on error. */
+int wc_gradcam_debug_offsets(int N, int h, int w, int total_inst, int max_k, size_t* offs);
+
 /* Attention-affinity refinement.  Replaces clip/clip_tool.py:152-191 (VOC) / :274-314 (COCO): RFM layer
  * selection against attn_pred (use_rfm=1; nl = 6 VOC / 10 COCO) or plain mean of the nl maps (use_rfm=0,
  * nl = 8), compute_trans_mat (:64-80), scoremap2bbox box mask (clip/utils.py:115-142; box_thr 0.4 / 0.7) and
  * cam' = (T * mask) @ cam.
  *   attn fp32 [nl,N,L,L] (oldest first, block 12 last); attn_pred fp32 [N,P,P]; cams / cams_refined fp32 [sumK,P];
  *   box_masks fp32 [sumK,P] or NULL (exported for the parity tests).  box_thr is a double: the reference evaluates
- *   int(thr * max(uint8)) in float64 (clip/utils.py:118-121); 0.7f * 250 would give 174 instead of 175. */
+ *   int(thr * max(uint8)) in float64 (clip/utils.py:118-121); 0.7f * 250 would give 174 instead of 175.
+ *   rfm_sel fp32 [N,2,nl] or NULL (test hook): per image the 0/1 layer selection of clip_tool.py:161-165 and the margins
+ *   d_l - mean(d) it was decided by.  The layer sums are accumulated in fp64 here; the reference's fp32 torch.sum over
+ *   P^2 ~ 1e6 terms resolves ~0.1-0.25 at that magnitude, which is the size of the margins. */
 size_t wc_affinity_workspace_bytes(int N, int h, int w, int total_inst, int nl);
 int wc_affinity_refine(const float* attn, int nl, const float* attn_pred, int N, int h, int wd, int use_rfm,
                        const float* cams, const int* k_off_host, double box_thr, float* cams_refined,
-                       float* box_masks, void* workspace, size_t workspace_bytes, void* stream);
+                       float* box_masks, float* rfm_sel, void* workspace, size_t workspace_bytes, void* stream);
 
 /* generate_cam_label (clip/clip_tool.py:202-216: per-class min-max + cv2.resize INTER_LINEAR to Wc x Hc) and the
  * background channel (model_attn_aff_voc.py:162-163).  out fp32 [sumK+N, Hc, Wc]: image i owns channels

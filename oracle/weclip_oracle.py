@@ -228,9 +228,14 @@ def grad_cam(x11: Tensor, text: Tensor, targets: Sequence[int], sd: Dict[str, Te
 # --------------------------------------------------------------------------------------------------
 # A.4 affinity refinement
 # --------------------------------------------------------------------------------------------------
-def rfm_attention(attn_stack: Tensor, seg_attn: Tensor, require_seg_trans: bool, window: int = 6) -> Tensor:
+def rfm_attention(attn_stack: Tensor, seg_attn: Tensor, require_seg_trans: bool, window: int = 6, layer_mask=None,
+                  info: dict = None) -> Tensor:
     """clip/clip_tool.py:152-175 (VOC window -6; COCO -10 at :277; no-RFM branch: mean of last 8).
-    attn_stack [12,L,L] (11 encoder maps + block 12), seg_attn [1,P,P] -> [P,P]."""
+    attn_stack [12,L,L] (11 encoder maps + block 12), seg_attn [1,P,P] -> [P,P].
+    ``layer_mask`` (test hook, like ``box_masks``) overrides the kept-layer decision ``diff <= mean(diff)``; ``info``
+    receives that decision as the reference takes it (fp32 ``torch.sum`` over P^2 terms) and the same sums in fp64:
+    at P >= 1024 the sums are ~1e6 and their differences between layers ~1, i.e. a few fp32 ulps — the reference's own
+    decision then depends on torch's summation order (tests/parity.py::rfm_checks)."""
     aw = attn_stack[:, 1:, 1:]
     if require_seg_trans:
         aw = aw[-window:]
@@ -238,6 +243,11 @@ def rfm_attention(attn_stack: Tensor, seg_attn: Tensor, require_seg_trans: bool,
         th = torch.mean(diff)
         mask = torch.zeros_like(diff)
         mask[diff <= th] = 1
+        if info is not None:
+            d64 = torch.sum((seg_attn.double() - aw.double()).flatten(1), dim=1)
+            info.update(mask=mask.clone(), diff32=diff.clone(), diff64=d64, margin64=d64 - d64.mean(), P=int(aw.shape[-1]))
+        if layer_mask is not None:
+            mask = torch.as_tensor(layer_mask, dtype=diff.dtype, device=diff.device).reshape(-1)
         mask = mask.reshape(-1, 1, 1).expand_as(aw)
         out = torch.sum(mask * aw, dim=0) / (torch.sum(mask, dim=0) + 1e-5)
         return out * seg_attn.squeeze(0)
@@ -392,7 +402,7 @@ def label_ids_from_map(lab: np.ndarray) -> List[int]:
 
 def weclip_forward(img: Tensor, label_maps: Sequence[np.ndarray], sd: Dict[str, Tensor], fg_text: Tensor,
                    bg_text: Tensor, mode: str = "val", iter_num: int = 1, dataset: str = "voc",
-                   mimic_fp16: bool = True, return_intermediates: bool = False, box_masks=None):
+                   mimic_fp16: bool = True, return_intermediates: bool = False, box_masks=None, rfm_masks=None):
     """WeCLIP_model/model_attn_aff_voc.py:107-175 (COCO twin model_attn_aff_coco.py:100-170) with
     clip/clip_tool.py:106-197 inlined.  ``label_maps[i]`` is the decoded label PNG of image i; like the reference's
     ``for i, img_name in enumerate(img_names)`` (:139) the CAM / PAR path runs for the first len(label_maps) images only
@@ -419,7 +429,11 @@ def weclip_forward(img: Tensor, label_maps: Sequence[np.ndarray], sd: Dict[str, 
         x11 = taps[-1][:, i:i + 1, :].float()
         cams, attn_last, _ = grad_cam(x11, text, list(range(len(ids))), sd, h, w, mimic_fp16)
         stack = torch.cat([attn_stack[i], attn_last], dim=0)
-        aff = rfm_attention(stack, attn_pred[i:i + 1], require_seg_trans, window)
+        rinfo = {} if return_intermediates else None
+        aff = rfm_attention(stack, attn_pred[i:i + 1], require_seg_trans, window,
+                            None if rfm_masks is None else rfm_masks[i], rinfo)
+        if return_intermediates:
+            inter.setdefault("rfm", []).append(rinfo)
         tm = compute_trans_mat(aff)
         refined = refine_cams(cams, tm, thr, None if box_masks is None else box_masks[i])
         size_wh = (W, H) if mode == "train" else (ori_w, ori_h)

@@ -24,7 +24,7 @@ def _refine(attn_pp: np.ndarray, cams: np.ndarray, h: int, w: int, thr: float):
     out, masks = torch.empty(K, P, device="cuda"), torch.empty(K, P, device="cuda")
     ws = torch.empty(L.wc_affinity_workspace_bytes(1, h, w, K, 1), dtype=torch.uint8, device="cuda")
     rc = L.wc_affinity_refine(_lib.ptr(attn), 1, None, 1, h, w, 0, _lib.ptr(cams_d), _lib.int_array([0, K]),
-                              ctypes.c_double(thr), _lib.ptr(out), _lib.ptr(masks), _lib.ptr(ws),
+                              ctypes.c_double(thr), _lib.ptr(out), _lib.ptr(masks), None, _lib.ptr(ws),
                               ctypes.c_size_t(ws.numel()), _lib.stream_ptr())
     _lib.check(rc, "wc_affinity_refine")
     return out.cpu().numpy(), masks.cpu().numpy()
@@ -53,7 +53,7 @@ def test_box_threshold_is_evaluated_in_float64():
     cam = np.zeros((h, w), np.float32)
     cam[1, 1] = 250.4 / 255.0          # uint8 250 = the maximum
     cam[4:6, 4:6] = 175.4 / 255.0      # uint8 175 == int(0.7 * 250): not above the threshold
-    assert int(np.float64(0.7) * 250) == 175 and int(np.float32(0.7) * np.float32(250)) == 174
+    assert int(np.float64(0.7) * 250) == 175 and int(np.float64(np.float32(0.7)) * 250) == 174   # (double)0.7f * 250
     a = np.random.default_rng(1).random((h * w, h * w)).astype(np.float32) + 0.05
     _, got = _refine(a, cam[None], h, w, 0.7)
     want = np.zeros((h, w), np.float32)

@@ -44,7 +44,8 @@ __global__ void __launch_bounds__(256) aff_layer_sums_kernel(const float* __rest
 // B = RFM fusion (clip_tool.py:158-170) or the plain layer mean (:173-174); also the first column sums.
 __global__ void __launch_bounds__(256) aff_build_kernel(const float* __restrict__ attn, const float* __restrict__ ap,
                                                         const double* __restrict__ sums, float* __restrict__ Bm,
-                                                        float* __restrict__ colz, int nl, int N, int L, int use_rfm) {
+                                                        float* __restrict__ colz, int nl, int N, int L, int use_rfm,
+                                                        float* __restrict__ sel_out) {
     __shared__ float wl[16];
     const int P = L - 1, img = blockIdx.y, r0 = blockIdx.x * 16, r1 = min(r0 + 16, P);
     if (threadIdx.x == 0) {
@@ -56,9 +57,13 @@ __global__ void __launch_bounds__(256) aff_build_kernel(const float* __restrict_
             mean /= (float)nl;
             float cnt = 0.f;
             for (int l = 0; l < nl; ++l) { wl[l] = (d[l] <= mean) ? 1.f : 0.f; cnt += wl[l]; }
+            if (sel_out && blockIdx.x == 0)        // test hook: which layers were kept, and the margins they were kept by
+                for (int l = 0; l < nl; ++l) { sel_out[((size_t)img * 2) * nl + l] = wl[l]; sel_out[((size_t)img * 2 + 1) * nl + l] = d[l] - mean; }
             for (int l = 0; l < nl; ++l) wl[l] /= (cnt + 1e-5f);
         } else {
             for (int l = 0; l < nl; ++l) wl[l] = 1.f / (float)nl;
+            if (sel_out && blockIdx.x == 0)
+                for (int l = 0; l < nl; ++l) { sel_out[((size_t)img * 2) * nl + l] = 1.f; sel_out[((size_t)img * 2 + 1) * nl + l] = 0.f; }
         }
     }
     __syncthreads();
@@ -296,7 +301,7 @@ extern "C" size_t wc_affinity_workspace_bytes(int N, int h, int w, int total_ins
 
 extern "C" int wc_affinity_refine(const float* attn, int nl, const float* attn_pred, int N, int h, int wd, int use_rfm,
                                   const float* cams, const int* k_off_host, double box_thr, float* cams_refined,
-                                  float* box_masks, void* workspace, size_t workspace_bytes, void* stream) {
+                                  float* box_masks, float* rfm_sel, void* workspace, size_t workspace_bytes, void* stream) {
     WC_CHECK_ARG(attn && cams && k_off_host && cams_refined && workspace && nl >= 1 && nl <= 16);
     WC_CHECK_ARG(N > 0 && N <= AFF_MAX_IMG && h > 0 && wd > 0 && (!use_rfm || attn_pred));
     cudaStream_t st = as_stream(stream);
@@ -323,7 +328,7 @@ extern "C" int wc_affinity_refine(const float* attn, int nl, const float* attn_p
         WC_LAUNCH_CHECK();
     }
     WC_CUDA(cudaMemsetAsync(z, 0, sizeof(float) * NP, st));
-    aff_build_kernel<<<dim3(ceil_div(P, 16), N), 256, 0, st>>>(attn, attn_pred, sums, Bm, z, nl, N, L, use_rfm);
+    aff_build_kernel<<<dim3(ceil_div(P, 16), N), 256, 0, st>>>(attn, attn_pred, sums, Bm, z, nl, N, L, use_rfm, rfm_sel);
     WC_LAUNCH_CHECK();
     for (int round = 0; round < 3; ++round) {   // clip_tool.py:67-72
         if (round > 0) {

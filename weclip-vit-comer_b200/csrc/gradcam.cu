@@ -23,6 +23,10 @@
 
 namespace wc {
 
+// 0 (default): reproduce the reference's fp16 rounding of the out-projection's backward (ref_half_round below);
+// 1: exact gradient (no reference rounding) — wc_gradcam_set_exact, for analysis.
+static int g_gradcam_exact = 0;
+
 constexpr int GC_MAX_IMG = 64;
 constexpr int GC_MAX_INST = 64;      // instances processed per backward chunk
 constexpr int GC_MAX_T = 128;        // text rows per image (VOC 20+25, COCO 80+23)
@@ -184,6 +188,34 @@ __global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msu
     }
 }
 
+// The reference forces the attention out-projection to fp16 on every device (clip/myAtt.py:321), so autograd runs that
+// linear's backward in fp16 too: the incoming gradient is cast to half, multiplied by the half weight (fp32 accumulate)
+// and the result is rounded to half again.  With near-uniform class probabilities the gradient there is ~1e-7, i.e.
+// inside fp16's SUBNORMAL range (quantum 2^-24 = 6e-8): the reference keeps only 2-3 significant bits of it, and that
+// quantisation — not arithmetic error — is what its Grad-CAM weights carry (measured: oracle with vs without it differs by
+// 1.8e-2 / 3.6e-2 in the normalised CAM at L = 1025 / 1601, tools/gradcam_debug.py).  To return the reference's result this
+// chain reproduces the two roundings: the power-of-two scaled gradient g is divided by its scale, rounded to fp16
+// (round-to-nearest-even, subnormals kept) and scaled back — exact, because the scale is a power of two.
+__device__ __forceinline__ float ref_half_round(float g_scaled, float scale) {
+    return __half2float(__float2half_rn(g_scaled / scale)) * scale;
+}
+
+// dO (fp32, scaled) -> fp16 operand with the reference's rounding of the out-projection's input gradient (see above).
+__global__ void __launch_bounds__(256) quant_ref_half_kernel(const float* __restrict__ in, h16* __restrict__ out,
+                                                             const float* __restrict__ gscale, int inst0, long per_inst,
+                                                             long total) {
+    const long i = ((long)blockIdx.x * 256 + threadIdx.x) * 4;
+    if (i >= total) return;
+    const float s = gscale[inst0 + (int)(i / per_inst)];
+    const float4 v = *reinterpret_cast<const float4*>(in + i);
+    h16x2 lo = __floats2half2_rn(ref_half_round(v.x, s), ref_half_round(v.y, s));
+    h16x2 hi = __floats2half2_rn(ref_half_round(v.z, s), ref_half_round(v.w, s));
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(out + i) = pk;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // LayerNorm input-gradient.  out[r] = add[r] + rstd * (g - mean(g) - xhat * mean(g*xhat)),  g = gamma * dy.
 // dy is either a matrix [rows,768] (dy_mat) or one vector per instance broadcast over the patch rows with the
@@ -193,7 +225,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
                                                      const float* __restrict__ dy_mat, const float* __restrict__ dy_vec,
                                                      const float* __restrict__ add, float* __restrict__ out_f,
                                                      h16* __restrict__ out_h, const __grid_constant__ InstTable it,
-                                                     int L, const float* __restrict__ gscale) {
+                                                     int L, const float* __restrict__ gscale, int quant_ref) {
     const long row = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= (long)it.n * L) return;
@@ -213,6 +245,8 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
     const float rstd = rsqrtf(warp_sum(q) / GC_E + 1e-5f);
     const bool zero = (dy_vec != nullptr && l == 0);
     const float gs = (dy_vec != nullptr && gscale != nullptr) ? gscale[it.inst0 + inst] : 1.f;
+    // quant_ref: out_h is rounded to the fp16 grid of the UNSCALED gradient (see ref_half_round below)
+    const float qs = (quant_ref && gscale != nullptr) ? gscale[it.inst0 + inst] : 0.f;
     const float4* dyr = dy_mat ? reinterpret_cast<const float4*>(dy_mat + (size_t)row * GC_E)
                                : reinterpret_cast<const float4*>(dy_vec + (size_t)(it.inst0 + inst) * GC_E);
     float c1 = 0.f, c2 = 0.f;
@@ -241,6 +275,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
         }
         if (out_f) reinterpret_cast<float4*>(out_f + (size_t)row * GC_E)[c4] = o;
         if (out_h) {
+            if (qs != 0.f) { o.x = ref_half_round(o.x, qs); o.y = ref_half_round(o.y, qs); o.z = ref_half_round(o.z, qs); o.w = ref_half_round(o.w, qs); }
             h16x2 lo = __floats2half2_rn(o.x, o.y), hi = __floats2half2_rn(o.z, o.w);
             uint2 pk;
             pk.x = *reinterpret_cast<uint32_t*>(&lo);
@@ -472,6 +507,25 @@ extern "C" size_t wc_gradcam_workspace_bytes(int N, int h, int w, int total_inst
     return ar.off + 512;
 }
 
+extern "C" int wc_gradcam_set_exact(int exact) { const int old = g_gradcam_exact; g_gradcam_exact = exact ? 1 : 0; return old; }
+
+// Test hook: byte offsets (from the workspace pointer passed to wc_gradcam, which must be 256-byte aligned) of the
+// intermediate buffers of the LAST backward chunk, in the order
+//   0 a32, 1 x1, 2 x2, 3 lse, 4 dm, 5 dqkv, 6 wvec, 7 gscale, 8 o(h16), 9 upre(h16), 10 dx2, 11 da2, 12 colsum, 13 ds0, 14 p0,
+//   15 dx2b(h16), 16 dh(h16), 17 dx1b(h16), 18 dO(h16), 19 dOT(h16), 20 q(h16), 21 k(h16), 22 v(h16); returns the chunk size.
+extern "C" int wc_gradcam_debug_offsets(int N, int h, int w, int total_inst, int max_k, size_t* offs) {
+    WC_CHECK_ARG(offs && N > 0 && h > 0 && w > 0 && total_inst > 0);
+    Arena ar(reinterpret_cast<void*>((uintptr_t)1 << 40), (size_t)1 << 50);     // fake aligned base: only offsets are read
+    GcLayout g;
+    const int chunk = chunk_size(total_inst, max_k);
+    gc_layout(ar, g, N, h * w + 1, total_inst, chunk);
+    const uint8_t* b = reinterpret_cast<const uint8_t*>((uintptr_t)1 << 40);
+    const void* ptrs[23] = {g.a32, g.x1, g.x2, g.lse, g.dm, g.dqkv, g.wvec, g.gscale, g.o, g.upre, g.dx2, g.da2, g.colsum,
+                            g.ds0, g.p0, g.dx2b, g.dh, g.dx1b, g.dO, g.dOT, g.q, g.k, g.v};
+    for (int i = 0; i < 23; ++i) offs[i] = (size_t)(reinterpret_cast<const uint8_t*>(ptrs[i]) - b);
+    return chunk;
+}
+
 extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int h, int wd, const float* text,
                           const int* text_off_host, const int* k_off_host, float* cams, float* attn_last, float* probs,
                           void* workspace, size_t workspace_bytes, void* stream) {
@@ -527,7 +581,7 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
         const long R = (long)n_inst * L;
         const unsigned ln_grid = (unsigned)ceil_div(R, 8L);
         // ln_post backward (dy = dm broadcast over patch rows, class row zero)
-        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x2, w->ln_post_w, nullptr, g.dm, nullptr, g.dx2, g.dx2b, it, L, g.gscale));
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x2, w->ln_post_w, nullptr, g.dm, nullptr, g.dx2, g.dx2b, it, L, g.gscale, 0));
         WC_LAUNCH_CHECK();
         // c_proj^T and the QuickGELU derivative (model.py:198-203): ONE launch batched over the chunk's instances; the saved
         // pre-activation u_pre belongs to the image, so the epilogue maps instance -> image through inst_map
@@ -549,14 +603,22 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
             if ((rc = launch_gemm(p, st))) return rc;
         }
         // ln_2 backward + the residual branch: dx1 = dx2 + LN2'(da2)
-        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x1, w->blocks[11].ln2_w, g.da2, nullptr, g.dx2, nullptr, g.dx1b, it, L, nullptr));
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(g.x1, w->blocks[11].ln2_w, g.da2, nullptr, g.dx2, nullptr, g.dx1b, it, L, g.gscale, g_gradcam_exact ? 0 : 1));
         WC_LAUNCH_CHECK();
         {   // out_proj^T (myAtt.py:321)
             GemmProblem p; p.M = (int)R; p.N = E; p.K = E;
             p.A = GemmOperand{g.dx1b, R, E, 0, 0};
             p.B = GemmOperand{reinterpret_cast<const h16*>(w->w_out_t), E, E, 0, 0};
-            p.epi.out = g.dO; p.epi.out_f16 = 1; p.epi.ldo = E;
+            if (g_gradcam_exact) { p.epi.out = g.dO; p.epi.out_f16 = 1; }
+            else p.epi.out = g.da2;            // fp32 (da2 is free again), rounded like the reference's half result below
+            p.epi.ldo = E;
             if ((rc = launch_gemm(p, st))) return rc;
+        }
+        if (!g_gradcam_exact) {
+            const long tot = R * E;
+            WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, quant_ref_half_kernel<<<(unsigned)ceil_div(tot / 4, 256L), 256, 0, st>>>(
+                g.da2, g.dO, g.gscale, it.inst0, (long)L * E, tot));
+            WC_LAUNCH_CHECK();
         }
         // delta, dO'^T, dS_i0, P_i0; then the column sums of dS without materialising P or dP (attention.cu)
         WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, do_prep_kernel<<<dim3(ceil_div(L, 64), GC_HEADS, n_inst), 256, 0, st>>>(

@@ -174,15 +174,18 @@ class Engine:
 
     def affinity_refine(self, attn: torch.Tensor, nl: int, attn_pred: torch.Tensor, N: int, h: int, w: int,
                         use_rfm: bool, cams: torch.Tensor, k_off: Sequence[int], box_thr: float, want_masks=False):
-        """clip_tool.py:152-191.  attn fp32 [nl,N,L,L]; returns (cams_refined [sumK,h,w], box masks|None)."""
+        """clip_tool.py:152-191.  attn fp32 [nl,N,L,L]; returns (cams_refined [sumK,h,w], box masks|None); with want_masks the
+        RFM layer selection + margins [N,2,nl] are kept in ``self.last_rfm_sel`` (test hook)."""
         L = _lib.lib()
         total = int(k_off[-1])
         out = torch.empty(total, h, w, dtype=torch.float32, device=self.device)
         masks = torch.empty(total, h, w, dtype=torch.float32, device=self.device) if want_masks else None
+        sel = torch.zeros(N, 2, nl, dtype=torch.float32, device=self.device) if want_masks else None
+        self.last_rfm_sel = sel
         ws = self._workspace("aff", L.wc_affinity_workspace_bytes(N, h, w, total, nl))
         rc = L.wc_affinity_refine(_lib.ptr(attn), nl, _lib.ptr(attn_pred), N, h, w, int(use_rfm), _lib.ptr(cams),
                                   _lib.int_array(k_off), c_double(box_thr), _lib.ptr(out), _lib.ptr(masks),
-                                  _lib.ptr(ws), c_size_t(ws.numel()), _lib.stream_ptr())
+                                  _lib.ptr(sel), _lib.ptr(ws), c_size_t(ws.numel()), _lib.stream_ptr())
         _lib.check(rc, "wc_affinity_refine")
         return out, masks
 

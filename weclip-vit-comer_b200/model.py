@@ -205,7 +205,8 @@ class WeCLIP(nn.Module):
         refined, bmasks = eng.affinity_refine(attn, nl, attn_pred, N, h, w, require_seg_trans, cams, k_off,
                                               cfg["box_thr"], want_masks=self.keep_intermediates)
         if self.keep_intermediates:
-            self.last = dict(cams=cams, box_masks=bmasks, refined=refined, k_off=k_off, ids=ids_all)
+            self.last = dict(cams=cams, box_masks=bmasks, refined=refined, k_off=k_off, ids=ids_all,
+                             rfm_sel=eng.last_rfm_sel)
         if len(set(sizes)) != 1:
             raise RuntimeError("stack expects each tensor to be equal size (model_attn_aff_voc.py:173)")
         Hc, Wc = sizes[0]
