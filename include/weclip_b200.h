@@ -68,13 +68,16 @@ int wc_par_fwd(const float* imgs, int Hi, int Wi, const float* masks, float* out
                const int* ch_off_host, int B, int H, int W,
                const int* dilations_host, int n_dil, int num_iter, int aff_f16,
                void* workspace, size_t workspace_bytes, void* stream);
-/* The two halves of wc_par_fwd, exposed for the roofline micro-bench (BASELINE.json configs[4]):
- * affinity build (PAR.py:70-86) -> aff [B, 8*n_dil, H, wc_par_aff_pitch(W)] fp32 or fp16 (aff_f16);
+/* The two halves of wc_par_fwd, exposed for the roofline micro-bench (BASELINE.json configs[4]) and the stage tests:
+ * affinity build (PAR.py:70-86) -> aff fp32 or fp16 (aff_f16) in the BLOCKED layout [B, H, Wb, 8*n_dil, 64] with
+ * Wb = wc_par_aff_pitch(W) / 64 = ceil(W/64): element (b, n, y, x) lives at
+ * (((b*H + y)*Wb + x/64)*8*n_dil + n)*64 + x%64 (B*H*wc_par_aff_pitch(W)*8*n_dil elements in all).
  * img must already be HxW. */
 int wc_par_aff_pitch(int W);
 int wc_par_affinity(const float* img, void* aff, int aff_f16, int B, int H, int W,
                     const int* dilations_host, int n_dil, void* stream);
-/* num_iter propagation steps (PAR.py:88-90); scratch holds 2*sum_kc*H*wc_par_aff_pitch(W) floats. */
+/* num_iter propagation steps (PAR.py:88-90); scratch holds 2*sum_kc*H*round_up(W,8) floats
+ * (2*sum_kc*H*wc_par_aff_pitch(W) is always enough). */
 int wc_par_propagate(const void* aff, int aff_f16, const float* masks, float* out, float* scratch,
                      const int* ch_off_host, int B, int H, int W,
                      const int* dilations_host, int n_dil, int num_iter, void* stream);

@@ -96,3 +96,40 @@ def test_par_tile_edges_match_generic_path():
         want = O.par_forward(imgs, masks, num_iter=2)
         got = PAR(DIL, 2).cuda()(imgs.cuda(), masks.cuda()).cpu()
         assert (got - want).abs().max().item() < 2e-5, (H, W)
+
+
+@pytest.mark.parametrize("tag", ["same", "resize", "tiny"])
+def test_affinity_kernel_matches_reference_golden(golden_dir, tag):
+    """wc_par_affinity alone (PAR.py:70-86) against the reference's own affinity tensor, through the blocked
+    [B,H,Wb,48,64] layout the propagation kernel streams; rows sum to 1 + w2."""
+    import torch.nn.functional as F
+    from weclip_b200 import ops
+    g = np.load(os.path.join(golden_dir, f"par_{tag}.npz"))
+    imgs, want = torch.from_numpy(g["imgs"]), g["aff"]
+    im = F.interpolate(imgs, size=want.shape[-2:], mode="bilinear", align_corners=True)     # PAR.py:67
+    got = ops.par_affinity(im.cuda(), DIL).cpu().numpy()
+    assert got.shape == want.shape
+    assert np.abs(got - want).max() < 5e-6
+    assert np.abs(got.sum(1) - 1.01).max() < 1e-5
+    got16 = ops.par_affinity(im.cuda(), DIL, dtype=torch.float16).float().cpu().numpy()
+    assert np.abs(got16 - want).max() < 6e-4            # fp16 storage of values in [0, 1.01]
+
+
+def test_affinity_flat_and_single_dilations():
+    """Exactly flat regions (std = 0: the reference divides 0 by 1e-8) and every single dilation of BASELINE configs[4]
+    (generic kernels), affinity + 3 propagation steps against the oracle."""
+    from weclip_b200 import ops
+    img = synth.make_images(5, 1, 72, 100)
+    img[:, :, 20:60, 30:90] = 0.25                         # flat patch larger than the 49-pixel window
+    want = O.par_affinity(img)
+    got = ops.par_affinity(img.cuda(), DIL).cpu()
+    assert (got - want).abs().max().item() < 5e-6
+    masks = torch.rand(1, 3, 72, 100, generator=torch.Generator().manual_seed(2))
+    for d in DIL:
+        w_aff = O.par_affinity(img, dilations=[d])
+        raw = ops.par_affinity(img.cuda(), [d], raw=True)
+        g_aff = ops.par_affinity(img.cuda(), [d]).cpu()
+        assert (g_aff - w_aff).abs().max().item() < 5e-6
+        got_m = ops.par_propagate(raw, masks[0].cuda(), [0, 3], [d], 3).cpu()
+        want_m = O.par_forward(img, masks, dilations=[d], num_iter=3)[0]
+        assert (got_m - want_m).abs().max().item() < 2e-5

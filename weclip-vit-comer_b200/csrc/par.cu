@@ -2,8 +2,11 @@
 //
 // Memory-bound stencil family.  Data layout in HBM:
 //   img   [B,3,H,W]    fp32 planar (resized copy lives in the workspace when Hi,Wi != H,W)
-//   aff   [B,NN,H,Wp]  planar, NN = 8*n_dil (48), row pitch Wp = round_up(W,8); stored as fp32 (exact path) or
-//                      fp16 (pipeline path: halves the bytes every propagation step streams)
+//   aff   [B,H,Wb,NN,64]  blocked: NN = 8*n_dil (48) neighbours x 64 consecutive pixels form one contiguous block
+//                      (Wb = ceil(W/64) blocks per image row), so the 48 weights a 4-pixel thread needs sit at IMMEDIATE
+//                      offsets n*64 from one base pointer (no address arithmetic per load) and a tile row streams one
+//                      contiguous 6 KB (fp16) span instead of touching 48 planes 0.5 MB apart; stored as fp32 (exact path)
+//                      or fp16 (pipeline path: halves the bytes every propagation step streams)
 //   masks [sumKc,H,W]  fp32 planar, ragged over images; two ping-pong buffers [sumKc,H,Wp] in the workspace
 // Kernels (fast path = the module's own dilation set 1/2/4/8/12/24):
 //   par_resize_kernel     bilinear align_corners=True (PAR.py:67)
@@ -29,9 +32,12 @@ constexpr int PAR_TY = 16;
 constexpr int PAR_KC = 4;    // mask channels per thread / per chunk
 constexpr int PAR_MAX_CHUNKS = 240;
 
+constexpr int PB = 64;       // pixels per affinity block (= tile width of the fast path)
+
 struct ParGeom {
     int H, W, nn;
-    int wp;                  // row pitch of the affinity / ping-pong planes
+    int wp;                  // row pitch of the ping-pong mask planes
+    int wb;                  // affinity blocks per image row
     short dy[PAR_MAX_NN];
     short dx[PAR_MAX_NN];
 };
@@ -45,12 +51,17 @@ struct ParChunks {
 };
 
 inline int par_pitch(int W) { return (W + 7) & ~7; }
+inline int par_aff_pitch(int W) { return (W + PB - 1) / PB * PB; }
+// element index of affinity (b, n, y, x) in the blocked layout
+__host__ __device__ __forceinline__ size_t aff_index(int H, int wb, int nn, int b, int n, int y, int x) {
+    return ((((size_t)b * H + y) * wb + (x / PB)) * nn + n) * PB + (x % PB);
+}
 
 static int make_geom(ParGeom& g, ParPos* pos, int H, int W, const int* dil, int n_dil) {
     if (n_dil < 1 || n_dil > WC_PAR_MAX_DIL) return -1;
     static const int by[8] = {-1, -1, -1, 0, 0, 1, 1, 1};   // PAR.py:10-24 raster order without the centre
     static const int bx[8] = {-1, 0, 1, -1, 1, -1, 0, 1};
-    g.H = H; g.W = W; g.nn = 8 * n_dil; g.wp = par_pitch(W);
+    g.H = H; g.W = W; g.nn = 8 * n_dil; g.wp = par_pitch(W); g.wb = (W + PB - 1) / PB;
     for (int d = 0; d < n_dil; ++d)
         for (int j = 0; j < 8; ++j) {
             g.dy[d * 8 + j] = (short)(by[j] * dil[d]);
@@ -87,6 +98,16 @@ __device__ __forceinline__ uint64_t l2_evict_first_policy() {
     uint64_t pol;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
     return pol;
+}
+__device__ __forceinline__ uint64_t l2_evict_normal_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ float ex2_approx(float x) {      // one MUFU; x <= 0 here
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
 template <typename T> struct AffIO;
 template <> struct AffIO<float> {
@@ -203,10 +224,9 @@ __global__ void __launch_bounds__(256) par_aff_kernel(const float* __restrict__ 
 #pragma unroll 8
     for (int n = 0; n < nn; ++n) sum += expf(logit(n) - mx);
     const float inv = 1.f / sum;
-    const size_t plane = (size_t)H * g.wp;
-    AffT* a = aff + (size_t)b * nn * plane + (size_t)y * g.wp + x;
+    AffT* a = aff + aff_index(H, g.wb, nn, b, 0, y, x);
 #pragma unroll 8
-    for (int n = 0; n < nn; ++n) AffIO<AffT>::st(a + (size_t)n * plane, expf(logit(n) - mx) * inv + pos.v[n]);
+    for (int n = 0; n < nn; ++n) AffIO<AffT>::st(a + (size_t)n * PB, expf(logit(n) - mx) * inv + pos.v[n]);
 }
 
 template <typename AffT>
@@ -222,15 +242,15 @@ __global__ void __launch_bounds__(PAR_TX* PAR_TY) par_iter_kernel(const AffT* __
     if (x >= W || y >= H) return;
     const int nn = g.nn;
     const int cnt = ch.cnt[c];
-    const size_t aplane = (size_t)H * g.wp, iplane = (size_t)H * in_pitch, oplane = (size_t)H * out_pitch;
-    const AffT* a = aff + (size_t)ch.b[c] * nn * aplane + (size_t)y * g.wp + x;
+    const size_t iplane = (size_t)H * in_pitch, oplane = (size_t)H * out_pitch;
+    const AffT* a = aff + aff_index(H, g.wb, nn, ch.b[c], 0, y, x);
     const float* m = in + (size_t)ch.ch0[c] * iplane;
     float acc[PAR_KC];
 #pragma unroll
     for (int k = 0; k < PAR_KC; ++k) acc[k] = 0.f;
     for (int n = 0; n < nn; ++n) {
         const int yy = min(max(y + g.dy[n], 0), H - 1), xx = min(max(x + g.dx[n], 0), W - 1);
-        const float w = AffIO<AffT>::ld(a + (size_t)n * aplane);
+        const float w = AffIO<AffT>::ld(a + (size_t)n * PB);
         const float* p = m + (size_t)yy * in_pitch + xx;
 #pragma unroll
         for (int k = 0; k < PAR_KC; ++k)
@@ -251,7 +271,8 @@ constexpr int PT_SW = PT_W + 2 * PT_HALO;   // 112 floats per shared-memory row 
 constexpr int PT_THREADS = 256;
 
 struct TileArgs {
-    int H, W, wp;            // wp: affinity pitch
+    int H, W, wb;            // wb: affinity blocks per image row
+    int evict_first;         // the affinity does not fit in L2: stream it with an evict-first policy
     int in_pitch, out_pitch; // mask plane pitches of this step's source / destination
     int in_vec, out_vec;     // 128-bit global access allowed (pitch % 4 == 0 and base 16 B aligned)
 };
@@ -259,33 +280,50 @@ struct TileArgs {
 __host__ __device__ constexpr int std_dil(int d) { return d == 0 ? 1 : d == 1 ? 2 : d == 2 ? 4 : d == 3 ? 8 : d == 4 ? 12 : 24; }
 
 // Fill `planes` shared-memory planes [SH][PT_SW] with the (x0-24.., y0-24..) window of src planes, coordinates clamped
-// to the image (= F.pad(mode='replicate'), PAR.py:44).
+// to the image (= F.pad(mode='replicate'), PAR.py:44).  One warp per tile row: lanes 0..27 own the row's 28 16-byte
+// vectors, so the only per-iteration index work is the row clamp (the old flat index cost ~25 instructions per vector).
 template <int SH, int NT>
 __device__ __forceinline__ void fill_tile(float* tile, const float* __restrict__ src, size_t plane, int pitch, int planes,
                                           int x0, int y0, int H, int W, int vec) {
-    constexpr int VPR = PT_SW / 4;   // 28 vectors per row
-    const int total = planes * SH * VPR;
-    for (int i = threadIdx.x; i < total; i += NT) {
-        const int v = i % VPR, rk = i / VPR;
-        const int r = rk % SH, k = rk / SH;
-        const int gy = min(max(y0 - PT_HALO + r, 0), H - 1);
-        const int gx = x0 - PT_HALO + 4 * v;
-        const float* rowp = src + (size_t)k * plane + (size_t)gy * pitch;
-        float* dst = tile + ((size_t)k * SH + r) * PT_SW + 4 * v;
-        if (vec && gx >= 0 && gx + 3 < W) {
-            // interior vector: asynchronous 16-byte global->shared copy (no register staging, many in flight)
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)),
-                         "l"(rowp + gx) : "memory");
-        } else {
-            float4 val;
-            val.x = __ldg(rowp + min(max(gx, 0), W - 1));
-            val.y = __ldg(rowp + min(max(gx + 1, 0), W - 1));
-            val.z = __ldg(rowp + min(max(gx + 2, 0), W - 1));
-            val.w = __ldg(rowp + min(max(gx + 3, 0), W - 1));
-            *reinterpret_cast<float4*>(dst) = val;
+    constexpr int NW = NT / 32;
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    if (lane < PT_SW / 4) {
+        const int gx = x0 - PT_HALO + 4 * lane;
+        const bool fast = vec && gx >= 0 && gx + 3 < W;
+        const int c0 = min(max(gx, 0), W - 1), c1 = min(max(gx + 1, 0), W - 1), c2 = min(max(gx + 2, 0), W - 1),
+                  c3 = min(max(gx + 3, 0), W - 1);
+        const int rows = planes * SH;
+        for (int rk = wrp; rk < rows; rk += NW) {
+            const int k = rk / SH, r = rk - k * SH;
+            const int gy = min(max(y0 - PT_HALO + r, 0), H - 1);
+            const float* rowp = src + (size_t)k * plane + (size_t)gy * pitch;
+            float* dst = tile + (size_t)rk * PT_SW + 4 * lane;
+            if (fast) {
+                // interior vector: asynchronous 16-byte global->shared copy (no register staging, many in flight)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)),
+                             "l"(rowp + gx) : "memory");
+            } else {
+                // edge vector (clamped columns, or an unaligned source): four asynchronous 4-byte copies — a register-staged
+                // load + store here made every row iteration of an edge tile wait a full L2 round trip (14 % of the
+                // kernel's stall samples, ncu r02)
+                const uint32_t d32 = (uint32_t)__cvta_generic_to_shared(dst);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d32), "l"(rowp + c0) : "memory");
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d32 + 4), "l"(rowp + c1) : "memory");
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d32 + 8), "l"(rowp + c2) : "memory");
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d32 + 12), "l"(rowp + c3) : "memory");
+            }
         }
     }
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+// Two fp32 FMAs in one instruction (FFMA2, sm_100): halves the issue slots and fma-pipe cycles of the 48 x Kc x 4 products
+// a thread accumulates per pass.  The operand pairs are adjacent registers (LDS.128 results, accumulator pairs), so the
+// mov.b64 packs below are register renames.
+__device__ __forceinline__ void ffma2(float& a0, float& a1, float w0, float w1, float m0, float m1) {
+    asm("{\n\t.reg .b64 ra, rw, rm;\n\tmov.b64 ra, {%0, %1};\n\tmov.b64 rw, {%2, %3};\n\tmov.b64 rm, {%4, %5};\n\t"
+        "fma.rn.f32x2 ra, rw, rm, ra;\n\tmov.b64 {%0, %1}, ra;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(w0), "f"(w1), "f"(m0), "f"(m1));
 }
 
 // acc[k][i] += w * mask(k, row, x+i+shift): the four pixels of this thread against one neighbour
@@ -295,6 +333,11 @@ __device__ __forceinline__ void fma4(float (&acc)[KC][4], int k, const float4& w
     acc[k][1] = fmaf(w.y, b, acc[k][1]);
     acc[k][2] = fmaf(w.z, c, acc[k][2]);
     acc[k][3] = fmaf(w.w, d, acc[k][3]);
+}
+template <int KC>
+__device__ __forceinline__ void fma4p(float (&acc)[KC][4], int k, const float4& w, float a, float b, float c, float d) {
+    ffma2(acc[k][0], acc[k][1], w.x, w.y, a, b);
+    ffma2(acc[k][2], acc[k][3], w.z, w.w, c, d);
 }
 
 // One dilation DD: 8 neighbours x KC channels for 4 consecutive pixels.  sc -> centre pixel 0 of channel 0 in the tile.
@@ -314,34 +357,34 @@ __device__ __forceinline__ void accumulate_dilation(float (&acc)[KC][4], const f
             if (DD % 4 == 0) {
                 const float4 L = *reinterpret_cast<const float4*>(rowp - DD);
                 const float4 R = *reinterpret_cast<const float4*>(rowp + DD);
-                fma4<KC>(acc, k, w[jl], L.x, L.y, L.z, L.w);
-                fma4<KC>(acc, k, w[jr], R.x, R.y, R.z, R.w);
+                fma4p<KC>(acc, k, w[jl], L.x, L.y, L.z, L.w);
+                fma4p<KC>(acc, k, w[jr], R.x, R.y, R.z, R.w);
                 if (r != 0) {
                     const float4 C = *reinterpret_cast<const float4*>(rowp);
-                    fma4<KC>(acc, k, w[jl + 1], C.x, C.y, C.z, C.w);
+                    fma4p<KC>(acc, k, w[jl + 1], C.x, C.y, C.z, C.w);
                 }
             } else {
                 const float4 L = *reinterpret_cast<const float4*>(rowp - 4);
                 const float4 C = *reinterpret_cast<const float4*>(rowp);
                 const float4 R = *reinterpret_cast<const float4*>(rowp + 4);
-                if (DD == 1) {
+                if (DD == 1) {      // shifted by one: the value pairs straddle register pairs -> scalar FMAs
                     fma4<KC>(acc, k, w[jl], L.w, C.x, C.y, C.z);
                     fma4<KC>(acc, k, w[jr], C.y, C.z, C.w, R.x);
                 } else {   // DD == 2
-                    fma4<KC>(acc, k, w[jl], L.z, L.w, C.x, C.y);
-                    fma4<KC>(acc, k, w[jr], C.z, C.w, R.x, R.y);
+                    fma4p<KC>(acc, k, w[jl], L.z, L.w, C.x, C.y);
+                    fma4p<KC>(acc, k, w[jr], C.z, C.w, R.x, R.y);
                 }
-                if (r != 0) fma4<KC>(acc, k, w[jl + 1], C.x, C.y, C.z, C.w);
+                if (r != 0) fma4p<KC>(acc, k, w[jl + 1], C.x, C.y, C.z, C.w);
             }
         }
     }
 }
 
+// the 8 weights of dilation d for this thread's 4 pixels: immediate offsets (d*8+j)*64 elements from the block base
 template <typename AffT>
-__device__ __forceinline__ void load_weights(typename AffIO<AffT>::Raw (&w)[8], const AffT* ap, size_t aplane, int d,
-                                             uint64_t pol) {
+__device__ __forceinline__ void load_weights(typename AffIO<AffT>::Raw (&w)[8], const AffT* ap, int d, uint64_t pol) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) w[j] = AffIO<AffT>::ld4(ap + (size_t)(d * 8 + j) * aplane, pol);
+    for (int j = 0; j < 8; ++j) w[j] = AffIO<AffT>::ld4(ap + (d * 8 + j) * PB, pol);
 }
 
 constexpr int PT_KC = 3;                 // channels per chunk on the tile path: 3 x 35 KB planes -> two CTAs per SM
@@ -354,52 +397,68 @@ __device__ __forceinline__ void par_iter_tile_body(float* par_tile, const AffT* 
     const int c = blockIdx.z;
     const int x0 = blockIdx.x * PT_W, y0 = blockIdx.y * TH;
     const int H = a.H, W = a.W;
-    const size_t iplane = (size_t)H * a.in_pitch, oplane = (size_t)H * a.out_pitch, aplane = (size_t)H * a.wp;
+    const size_t iplane = (size_t)H * a.in_pitch, oplane = (size_t)H * a.out_pitch;
+    const size_t arow = (size_t)a.wb * (48 * PB);          // affinity elements per image row
     const int ch0 = ch.ch0[c];
-    fill_tile<SH, PT_THREADS>(par_tile, in + (size_t)ch0 * iplane, iplane, a.in_pitch, KC, x0, y0, H, W, a.in_vec);
-    __syncthreads();
-    const uint64_t pol = l2_evict_first_policy();
+    const uint64_t pol = a.evict_first ? l2_evict_first_policy() : l2_evict_normal_policy();
     const int tx4 = threadIdx.x & 15, tyb = threadIdx.x >> 4;
     const int x = x0 + 4 * tx4;
-    if (x >= W) return;
-    const AffT* abase = aff + (size_t)ch.b[c] * 48 * aplane + x;
+    const bool active = x < W;             // (the affinity blocks are padded to 64 pixels: loads beyond W stay in bounds)
+    const AffT* abase = aff + ((size_t)ch.b[c] * H * a.wb + blockIdx.x) * (48 * PB) + 4 * tx4;
+    // Software pipeline over (row pass, dilation): three weight sets rotate, each refilled as soon as its dilation has been
+    // accumulated — the refills at the end of a pass already fetch the NEXT row's first three dilations, and the very first
+    // three are requested before the tile fill, so no pass starts with an exposed HBM round trip.
+    // (fp16 weights: three sets of 16 registers; fp32: two sets of 32)
+    constexpr bool THREE = AffIO<AffT>::LOOKAHEAD == 2;
+    typename AffIO<AffT>::Raw wa[8], wb[8], wc[THREE ? 8 : 1];
+    if (active && y0 + tyb < H) {
+        const AffT* ap = abase + (size_t)(y0 + tyb) * arow;
+        load_weights<AffT>(wa, ap, 0, pol);
+        if constexpr (THREE) { load_weights<AffT>(wb, ap, 1, pol); load_weights<AffT>(wc, ap, 2, pol); }
+    }
+    fill_tile<SH, PT_THREADS>(par_tile, in + (size_t)ch0 * iplane, iplane, a.in_pitch, KC, x0, y0, H, W, a.in_vec);
+    __syncthreads();
+    if (!active) return;
+    if constexpr (!THREE) {      // fp32 weights: the second set would spill across the fill loop
+        if (y0 + tyb < H) load_weights<AffT>(wb, abase + (size_t)(y0 + tyb) * arow, 1, pol);
+    }
 #pragma unroll 1
     for (int pass = 0; pass < TH / 16; ++pass) {
         const int ty = tyb + 16 * pass, y = y0 + ty;
         if (y >= H) break;
-        const AffT* ap = abase + (size_t)y * a.wp;
+        const AffT* ap = abase + (size_t)y * arow;
+        const bool more = pass + 1 < TH / 16 && y + 16 < H;
+        const AffT* apn = ap + 16 * arow;
         const float* sc = par_tile + (ty + PT_HALO) * PT_SW + PT_HALO + 4 * tx4;
         float acc[KC][4];
 #pragma unroll
         for (int k = 0; k < KC; ++k) acc[k][0] = acc[k][1] = acc[k][2] = acc[k][3] = 0.f;
-        typename AffIO<AffT>::Raw wa[8], wb[8];
-        if (AffIO<AffT>::LOOKAHEAD == 2) {
-            typename AffIO<AffT>::Raw wc[8];
-            load_weights<AffT>(wa, ap, aplane, 0, pol);
-            load_weights<AffT>(wb, ap, aplane, 1, pol);
-            load_weights<AffT>(wc, ap, aplane, 2, pol);
+        if constexpr (THREE) {
             accumulate_dilation<AffT, KC, SH, 1>(acc, sc, wa);
-            load_weights<AffT>(wa, ap, aplane, 3, pol);
+            load_weights<AffT>(wa, ap, 3, pol);
             accumulate_dilation<AffT, KC, SH, 2>(acc, sc, wb);
-            load_weights<AffT>(wb, ap, aplane, 4, pol);
+            load_weights<AffT>(wb, ap, 4, pol);
             accumulate_dilation<AffT, KC, SH, 4>(acc, sc, wc);
-            load_weights<AffT>(wc, ap, aplane, 5, pol);
+            load_weights<AffT>(wc, ap, 5, pol);
             accumulate_dilation<AffT, KC, SH, 8>(acc, sc, wa);
+            if (more) load_weights<AffT>(wa, apn, 0, pol);
             accumulate_dilation<AffT, KC, SH, 12>(acc, sc, wb);
+            if (more) load_weights<AffT>(wb, apn, 1, pol);
             accumulate_dilation<AffT, KC, SH, 24>(acc, sc, wc);
+            if (more) load_weights<AffT>(wc, apn, 2, pol);
         } else {
-            load_weights<AffT>(wa, ap, aplane, 0, pol);
-            load_weights<AffT>(wb, ap, aplane, 1, pol);
             accumulate_dilation<AffT, KC, SH, 1>(acc, sc, wa);
-            load_weights<AffT>(wa, ap, aplane, 2, pol);
+            load_weights<AffT>(wa, ap, 2, pol);
             accumulate_dilation<AffT, KC, SH, 2>(acc, sc, wb);
-            load_weights<AffT>(wb, ap, aplane, 3, pol);
+            load_weights<AffT>(wb, ap, 3, pol);
             accumulate_dilation<AffT, KC, SH, 4>(acc, sc, wa);
-            load_weights<AffT>(wa, ap, aplane, 4, pol);
+            load_weights<AffT>(wa, ap, 4, pol);
             accumulate_dilation<AffT, KC, SH, 8>(acc, sc, wb);
-            load_weights<AffT>(wb, ap, aplane, 5, pol);
+            load_weights<AffT>(wb, ap, 5, pol);
             accumulate_dilation<AffT, KC, SH, 12>(acc, sc, wa);
+            if (more) load_weights<AffT>(wa, apn, 0, pol);
             accumulate_dilation<AffT, KC, SH, 24>(acc, sc, wb);
+            if (more) load_weights<AffT>(wb, apn, 1, pol);
         }
         float* op = out + (size_t)ch0 * oplane + (size_t)y * a.out_pitch + x;
 #pragma unroll
@@ -431,16 +490,18 @@ __global__ void __launch_bounds__(PT_THREADS, 2) par_iter_tile_kernel(const AffT
     }
 }
 
-// Affinity build on a 64x24 tile: the 3 image planes + halo live in shared memory (96.8 KB, 2 CTAs per SM); 192 threads
-// (170 registers each: the 48 logits stay in registers), each walks 8 pixels (lanes = consecutive x: conflict-free scalar
-// LDS), 3 passes over the 48 compile-time neighbour offsets.
+// Affinity build on a 64x24 tile: the 3 image planes + halo live in shared memory (96.8 KB, 2 CTAs per SM); 192 threads,
+// each walks 8 pixels (lanes = consecutive x: conflict-free scalar LDS), TWO passes over the 48 compile-time neighbour
+// offsets: (1) sum and sum of squares of d = v - centre per channel -> unbiased variance (shifted two-moment form: exact
+// zero on flat regions, no cancellation against the pixel's own level), (2) the 48 logits, kept in registers, with the
+// softmax scale folded into one ex2 per neighbour.
 constexpr int PA_TH = 24;
 constexpr int PA_THREADS = 192;
 constexpr int PA_SH = PA_TH + 2 * PT_HALO;
 
 template <typename AffT>
 __global__ void __launch_bounds__(PA_THREADS, 2) par_aff_tile_kernel(const float* __restrict__ img, AffT* __restrict__ aff,
-                                                                      int H, int W, int wp, int vec,
+                                                                      int H, int W, int wb, int vec,
                                                                       const __grid_constant__ ParPos pos) {
     extern __shared__ __align__(16) float par_tile[];
     constexpr int PLANE = PA_SH * PT_SW;
@@ -449,38 +510,33 @@ __global__ void __launch_bounds__(PA_THREADS, 2) par_aff_tile_kernel(const float
     const size_t hw = (size_t)H * W;
     fill_tile<PA_SH, PA_THREADS>(par_tile, img + (size_t)b * 3 * hw, hw, W, 3, x0, y0, H, W, vec);
     __syncthreads();
-    const size_t aplane = (size_t)H * wp;
     const int tx = threadIdx.x & 63, ty0 = threadIdx.x >> 6;
     const int x = x0 + tx;
     if (x >= W) return;
     constexpr int by[8] = {-1, -1, -1, 0, 0, 1, 1, 1};
     constexpr int bx[8] = {-1, 0, 1, -1, 1, -1, 0, 1};
+    constexpr float LOG2E = 1.4426950408889634f;
 #pragma unroll 1
     for (int i = 0; i < PA_TH / 3; ++i) {
         const int ty = ty0 + 3 * i, y = y0 + ty;
         if (y >= H) break;
         const float* sc = par_tile + (ty + PT_HALO) * PT_SW + PT_HALO + tx;
         const float c0 = sc[0], c1 = sc[PLANE], c2 = sc[2 * PLANE];
-        // pass 1: per-channel mean of the 48 neighbour values
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+        // pass 1: moments of d = v - centre over the 48 neighbours; var = (sum d^2 - (sum d)^2 / 48) / 47 (torch.std, PAR.py:77)
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f;
 #pragma unroll
         for (int n = 0; n < 48; ++n) {
             const int o = by[n & 7] * std_dil(n >> 3) * PT_SW + bx[n & 7] * std_dil(n >> 3);
-            s0 += sc[o]; s1 += sc[PLANE + o]; s2 += sc[2 * PLANE + o];
-        }
-        const float m0 = s0 * (1.f / 48.f), m1 = s1 * (1.f / 48.f), m2 = s2 * (1.f / 48.f);
-        // pass 2: centred sum of squares -> unbiased std (torch.std, PAR.py:77)
-        float q0 = 0.f, q1 = 0.f, q2 = 0.f;
-#pragma unroll
-        for (int n = 0; n < 48; ++n) {
-            const int o = by[n & 7] * std_dil(n >> 3) * PT_SW + bx[n & 7] * std_dil(n >> 3);
-            const float d0 = sc[o] - m0, d1 = sc[PLANE + o] - m1, d2 = sc[2 * PLANE + o] - m2;
+            const float d0 = sc[o] - c0, d1 = sc[PLANE + o] - c1, d2 = sc[2 * PLANE + o] - c2;
+            s0 += d0; s1 += d1; s2 += d2;
             q0 = fmaf(d0, d0, q0); q1 = fmaf(d1, d1, q1); q2 = fmaf(d2, d2, q2);
         }
-        const float e0 = sqrtf(q0 * (1.f / 47.f)) + 1e-8f, e1 = sqrtf(q1 * (1.f / 47.f)) + 1e-8f,
-                    e2 = sqrtf(q2 * (1.f / 47.f)) + 1e-8f;
-        // pass 3: logits = -mean_c((|v-c|/(std+1e-8)/w1)^2) (PAR.py:80-81), kept in registers; the two divisions per
-        // term are one multiplication by r = 1/(std+1e-8)/w1 (1-2 ulp from the reference's order)
+        const float v0 = fmaxf(fmaf(-s0 * (1.f / 48.f), s0, q0), 0.f), v1 = fmaxf(fmaf(-s1 * (1.f / 48.f), s1, q1), 0.f),
+                    v2 = fmaxf(fmaf(-s2 * (1.f / 48.f), s2, q2), 0.f);
+        const float e0 = sqrtf(v0 * (1.f / 47.f)) + 1e-8f, e1 = sqrtf(v1 * (1.f / 47.f)) + 1e-8f,
+                    e2 = sqrtf(v2 * (1.f / 47.f)) + 1e-8f;
+        // pass 2: logits = -mean_c((|v-c|/(std+1e-8)/w1)^2) (PAR.py:80-81) in the log2 domain, kept in registers; the two
+        // divisions per term are one multiplication by r = 1/(std+1e-8)/w1 (1-2 ulp from the reference's order)
         const float r0 = 1.f / e0 / 0.3f, r1 = 1.f / e1 / 0.3f, r2 = 1.f / e2 / 0.3f;
         float l[48];
         float mx = -INFINITY;
@@ -488,16 +544,16 @@ __global__ void __launch_bounds__(PA_THREADS, 2) par_aff_tile_kernel(const float
         for (int n = 0; n < 48; ++n) {
             const int o = by[n & 7] * std_dil(n >> 3) * PT_SW + bx[n & 7] * std_dil(n >> 3);
             const float t0 = (sc[o] - c0) * r0, t1 = (sc[PLANE + o] - c1) * r1, t2 = (sc[2 * PLANE + o] - c2) * r2;
-            l[n] = (t0 * t0 + t1 * t1 + t2 * t2) * (-1.f / 3.f);
+            l[n] = (t0 * t0 + t1 * t1 + t2 * t2) * (-LOG2E / 3.f);
             mx = fmaxf(mx, l[n]);
         }
         float sum = 0.f;
 #pragma unroll
-        for (int n = 0; n < 48; ++n) { l[n] = expf(l[n] - mx); sum += l[n]; }
+        for (int n = 0; n < 48; ++n) { l[n] = ex2_approx(l[n] - mx); sum += l[n]; }
         const float inv = 1.f / sum;
-        AffT* ap = aff + (size_t)b * 48 * aplane + (size_t)y * wp + x;
+        AffT* ap = aff + (((size_t)b * H + y) * wb + blockIdx.x) * (48 * PB) + tx;
 #pragma unroll
-        for (int n = 0; n < 48; ++n) AffIO<AffT>::st(ap + (size_t)n * aplane, l[n] * inv + pos.v[n]);   // PAR.py:86
+        for (int n = 0; n < 48; ++n) AffIO<AffT>::st(ap + n * PB, l[n] * inv + pos.v[n]);   // PAR.py:86
     }
 }
 
@@ -562,7 +618,9 @@ static int propagate(const AffT* aff, const float* masks, float* out, float* scr
         const float* src = first ? masks : ((it & 1) ? ping : pong);
         float* dst = last ? out : ((it & 1) ? pong : ping);
         TileArgs ta;
-        ta.H = g.H; ta.W = g.W; ta.wp = g.wp;
+        ta.H = g.H; ta.W = g.W; ta.wb = g.wb;
+        // 126 MB of L2: an affinity tensor that fits stays resident across the iterations (no evict-first hint then)
+        ta.evict_first = (double)B * g.H * g.wb * PB * g.nn * sizeof(AffT) > 80e6 ? 1 : 0;
         ta.in_pitch = first ? g.W : g.wp;
         ta.out_pitch = last ? g.W : g.wp;
         ta.in_vec = (ta.in_pitch % 4 == 0) && aligned16(src);
@@ -571,13 +629,16 @@ static int propagate(const AffT* aff, const float* masks, float* out, float* scr
         for (size_t off = 0; off < v.size(); off += PAR_MAX_CHUNKS) {
             const int n = (int)min((size_t)PAR_MAX_CHUNKS, v.size() - off);
             ParChunks chunks;
-            int chs = 0, max_cnt = 1;
+            int chs = 0, max_cnt = 1, imgs = 0;
             for (int i = 0; i < n; ++i) {
                 chunks.b[i] = v[off + i].b; chunks.ch0[i] = v[off + i].ch0; chunks.cnt[i] = v[off + i].cnt;
                 chs += v[off + i].cnt;
                 max_cnt = max(max_cnt, (int)v[off + i].cnt);
+                if (i == 0 || v[off + i].b != v[off + i - 1].b) ++imgs;
             }
-            ProfScope prof(PK_PAR_ITER, (double)hw * ((double)sizeof(AffT) * g.nn * n + 8.0 * chs), st);
+            // algorithmic bytes: every image's affinity ONCE per step (an image with more than 3 channels is
+            // walked by several chunks; their re-reads are not credited) + read and write of every mask channel
+            ProfScope prof(PK_PAR_ITER, (double)hw * ((double)sizeof(AffT) * g.nn * imgs + 8.0 * chs), st);
             if (fast) {
                 int rc = launch_iter_tile<AffT>(aff, src, dst, ta, chunks, n, max_cnt, st);
                 if (rc) return rc;
@@ -599,7 +660,7 @@ static int affinity(const float* img, AffT* aff, int B, const ParGeom& g, const 
         WC_SET_MAX_SMEM(par_aff_tile_kernel<AffT>, SMEM);
         dim3 grid(ceil_div(g.W, PT_W), ceil_div(g.H, PA_TH), B);
         const int vec = (g.W % 4 == 0) && aligned16(img);
-        par_aff_tile_kernel<AffT><<<grid, PA_THREADS, SMEM, st>>>(img, aff, g.H, g.W, g.wp, vec, pos);
+        par_aff_tile_kernel<AffT><<<grid, PA_THREADS, SMEM, st>>>(img, aff, g.H, g.W, g.wb, vec, pos);
     } else {
         dim3 block(32, 8), grid(ceil_div(g.W, 32), ceil_div(g.H, 8), B);
         par_aff_kernel<AffT><<<grid, block, 0, st>>>(img, aff, g, pos);
@@ -619,11 +680,11 @@ static int check_ragged(const int* ch_off, int B) {
 
 using namespace wc;
 
-extern "C" int wc_par_aff_pitch(int W) { return par_pitch(W); }
+extern "C" int wc_par_aff_pitch(int W) { return par_aff_pitch(W); }
 
 extern "C" size_t wc_par_workspace_bytes(int B, int sum_kc, int H, int W, int n_dil) {
-    const size_t hw = (size_t)H * W, hwp = (size_t)H * par_pitch(W);
-    return sizeof(float) * (hw * (size_t)B * 3 + hwp * ((size_t)B * 8 * n_dil + 2 * (size_t)sum_kc)) + 1024;
+    const size_t hw = (size_t)H * W, hwp = (size_t)H * par_pitch(W), hwa = (size_t)H * par_aff_pitch(W);
+    return sizeof(float) * (hw * (size_t)B * 3 + hwa * (size_t)B * 8 * n_dil + hwp * 2 * (size_t)sum_kc) + 1024;
 }
 
 extern "C" int wc_par_affinity(const float* img, void* aff, int aff_f16, int B, int H, int W, const int* dil, int n_dil,

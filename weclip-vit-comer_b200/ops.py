@@ -133,3 +133,36 @@ def attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, want_avg: b
                                      _lib.ptr(lse), _lib.ptr(avg), N, heads, L, Lp, hd, _lib.stream_ptr())
     _lib.check(rc, "wc_attention_fwd")
     return o, avg
+
+
+def par_affinity(img: torch.Tensor, dilations, dtype=torch.float32, raw: bool = False) -> torch.Tensor:
+    """wc_par_affinity (PAR.py:70-86): img fp32 [B,3,H,W] -> affinity [B,NN,H,W] (``raw``: the kernel's own blocked
+    [B,H,Wb,NN,64] tensor, the layout wc_par_propagate streams)."""
+    _lib.require_device()
+    L = _lib.lib()
+    img = img.contiguous().float()
+    B, _, H, W = img.shape
+    nn_ = 8 * len(dilations)
+    wa = L.wc_par_aff_pitch(W)
+    aff = torch.zeros(B, H, wa // 64, nn_, 64, dtype=dtype, device=img.device)
+    rc = L.wc_par_affinity(_lib.ptr(img), _lib.ptr(aff), int(dtype == torch.float16), B, H, W, _lib.int_array(dilations),
+                           len(dilations), _lib.stream_ptr())
+    _lib.check(rc, "wc_par_affinity")
+    if raw:
+        return aff
+    return aff.permute(0, 3, 1, 2, 4).reshape(B, nn_, H, wa)[..., :W].contiguous()
+
+
+def par_propagate(aff_raw: torch.Tensor, masks: torch.Tensor, ch_off, dilations, num_iter: int) -> torch.Tensor:
+    """wc_par_propagate (PAR.py:88-90) on a blocked affinity tensor from par_affinity(raw=True); masks packed [sumKc,H,W]."""
+    _lib.require_device()
+    L = _lib.lib()
+    masks = masks.contiguous().float()
+    sum_kc, H, W = masks.shape
+    out = torch.empty_like(masks)
+    scratch = torch.empty(2 * sum_kc * H * L.wc_par_aff_pitch(W), dtype=torch.float32, device=masks.device)
+    rc = L.wc_par_propagate(_lib.ptr(aff_raw), int(aff_raw.dtype == torch.float16), _lib.ptr(masks), _lib.ptr(out),
+                            _lib.ptr(scratch), _lib.int_array(ch_off), len(ch_off) - 1, H, W, _lib.int_array(dilations),
+                            len(dilations), int(num_iter), _lib.stream_ptr())
+    _lib.check(rc, "wc_par_propagate")
+    return out
