@@ -317,7 +317,7 @@ def main():
     hist_total_e2e = int(wl.hist_h.sum()) if hasattr(wl, "hist_h") else None
     # --- the same step with dead CAM / PAR passes eliminated (cam_passes="live")
     ms_live = None
-    if hasattr(wl, "step_device_live"):
+    if hasattr(wl, "ev_live"):
         for _ in range(2):
             wl.step_device_live()
         barrier()
@@ -328,6 +328,23 @@ def main():
         e1.record()
         barrier()
         ms_live = e0.elapsed_time(e1)
+    # --- one dataset image per call (the reference's batch_size = 1 loop), 512x512 and a VOC-like size mix
+    ms_b1 = ms_b1v = None
+    if hasattr(wl, "ev_b1"):
+        for fn, tag in ((wl.step_b1, "b1"), (wl.step_b1_voc_sizes, "b1v")):
+            for _ in range(3):
+                fn()
+            barrier()
+            e0.record()
+            for _ in range(args.steps):
+                fn()
+            wl.join()
+            e1.record()
+            barrier()
+            if tag == "b1":
+                ms_b1 = e0.elapsed_time(e1)
+            else:
+                ms_b1v = e0.elapsed_time(e1)
     clocks = sampler.stop() if sampler else None
     # --- kernel-class breakdown for the roofline object: separate pass with the C-side profiler (events around
     #     every launch on the launching stream); never overlaps the timed regions above
@@ -336,10 +353,12 @@ def main():
         barrier()
 
     if dist is not None:
-        t = torch.tensor([ms_dev, ms_e2e, ms_live or 0.0], device=dev, dtype=torch.float64)
+        t = torch.tensor([ms_dev, ms_e2e, ms_live or 0.0, ms_b1 or 0.0, ms_b1v or 0.0], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_dev, ms_e2e, ms_live_r = t.tolist()
+        ms_dev, ms_e2e, ms_live_r, ms_b1_r, ms_b1v_r = t.tolist()
         ms_live = ms_live_r if ms_live is not None else None
+        ms_b1 = ms_b1_r if ms_b1 is not None else None
+        ms_b1v = ms_b1v_r if ms_b1v is not None else None
 
     if rank == 0:
         units = wl.units * world * args.steps
@@ -359,6 +378,15 @@ def main():
             line["value_live_outputs"] = round(units / (ms_live * 1e-3), 2)
             line["value_live_outputs_note"] = ("same step, cam_passes='live': 1 CAM/PAR pass per dataset image instead of the "
                                                "reference call pattern's 6; identical histograms")
+        if ms_b1 is not None:
+            line["value_b1"] = round(units / (ms_b1 * 1e-3), 2)
+            line["value_b1_voc_sizes"] = round(units / (ms_b1v * 1e-3), 2)
+            line["value_b1_note"] = ("one dataset image per model call (the reference's DataLoader(batch_size=1)), reference call "
+                                     "pattern; value_b1: the step's 512x512 images; value_b1_voc_sizes: 8 images of VOC-like sizes "
+                                     f"{sorted(set(wl.voc_sizes))} (long side 500 -> 512, short sides mostly not multiples of 16); "
+                                     f"CUDA graphs per bucket: {'on' if wl.graphs else 'off'}, graphs captured "
+                                     f"{wl.ev_b1.graph_captures}, replays {wl.ev_b1.graph_replays}")
+            line["config"]["cuda_graphs"] = bool(wl.graphs)
         if hist_total_e2e is not None:
             # the e2e region ends with the cross-rank histogram sum: every rank's step counts the same number of valid pixels
             line["e2e"]["hist_total_after_allreduce"] = hist_total_e2e

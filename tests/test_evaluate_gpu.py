@@ -243,3 +243,62 @@ def test_scales_on_separate_streams_equal_sequential():
     assert int((ho[2] - 4 * hs[2]).abs().sum()) <= 2e-3 * int(ho[2].sum())
     ovl.reset()
     assert int(ovl.hist.sum()) == 0
+
+
+def _small_dataset(root, seed=21):
+    """Six dataset images of three different sizes (short sides not multiples of 16 after the resize) and varying K."""
+    rng = np.random.default_rng(seed)
+    items = []
+    for i, (h0, w0) in enumerate([(93, 130), (120, 88), (93, 130), (101, 135), (120, 88), (93, 130)]):
+        lab = synth.make_label_map(rng, h0, w0, synth.draw_label_set(rng, 20))
+        synth.write_label_png(root, "SegmentationClassAug", f"g{i}", lab)
+        items.append((f"g{i}", synth.make_images(40 + i, 1, h0, w0)[0], lab))
+    return items
+
+
+def test_cuda_graph_buckets_equal_the_eager_driver():
+    """use_graphs: one CUDA graph per (image size, label size, classes-per-image) bucket and replay slot holds the whole
+    step; replays (incl. re-used buckets, both slots, several images in flight) give the eager driver's histograms —
+    bit-identical for the segmentation outputs, within the fp-atomics tolerance for the CAM pseudo-labels."""
+    sd = synth.make_state_dict(0, 21)
+    fg, bg = synth.make_text_features(7, 20, 25)
+    root = tempfile.mkdtemp()
+    items = _small_dataset(root)
+    model = WeCLIP(num_classes=21, dataset_root_path=root, device="cuda", state_dict=sd, fg_text_features=fg,
+                   bg_text_features=bg)
+    eager = MscFlipEvaluator(model, 21, (1.0, 0.75, 1.25), resize_long=160, overlap_scales=False)
+    graphed = MscFlipEvaluator(model, 21, (1.0, 0.75, 1.25), resize_long=160, use_graphs=True)
+    assert graphed.use_graphs
+    for rep in range(2):
+        for name, img, lab in items:
+            gt = torch.from_numpy(lab.astype(np.int16)).cuda()
+            eager.process(name, img[None].cuda(), gt)
+            graphed.process(name, img[None].cuda().clone(), gt.clone())
+    he, hg = eager.hist, graphed.hist
+    assert graphed.n_images == eager.n_images == 12 and graphed.graph_replays == 12
+    assert 3 <= graphed.graph_captures <= 12              # buckets x 2 slots at most; far fewer captures than images
+    assert torch.equal(he[:2], hg[:2])
+    assert int(he[2].sum()) == int(hg[2].sum())
+    assert int((he[2] - hg[2]).abs().sum()) <= 2e-3 * int(he[2].sum())
+    before = graphed.graph_captures
+    for name, img, lab in items:                          # third pass: every bucket / slot pair that recurs is a pure replay
+        graphed.process(name, img[None].cuda(), torch.from_numpy(lab.astype(np.int16)).cuda())
+    assert graphed.graph_captures <= before + 3
+    assert torch.equal(graphed.hist[:2] * 2, he[:2] * 3)
+
+
+def test_validate_with_pinned_ring_and_graphs_matches_eager():
+    """evaluate.validate(): one image per call from a pinned input ring, CUDA graphs per bucket, final all-reduce."""
+    from weclip_b200.evaluate import validate
+    sd = synth.make_state_dict(0, 21)
+    fg, bg = synth.make_text_features(7, 20, 25)
+    root = tempfile.mkdtemp()
+    items = _small_dataset(root, seed=22)
+    model = WeCLIP(num_classes=21, dataset_root_path=root, device="cuda", state_dict=sd, fg_text_features=fg,
+                   bg_text_features=bg)
+    dataset = [(n, im.numpy(), lab.astype(np.int64), None) for n, im, lab in items]
+    got = validate(model, dataset, test_scales=[1.0, 0.75], resize_long=160, use_graphs=True)
+    want = validate(model, dataset, test_scales=[1.0, 0.75], resize_long=160, use_graphs=False)
+    for k in ("seg", "msc_seg"):
+        assert got[k]["miou"] == want[k]["miou"] and got[k]["pAcc"] == want[k]["pAcc"]
+    assert abs(got["cam"]["pAcc"] - want["cam"]["pAcc"]) < 2e-3

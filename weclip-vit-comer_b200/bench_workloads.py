@@ -96,10 +96,20 @@ class MscFlipVoc:
                             dataset=self.dataset, state_dict=self.sd, fg_text_features=self.fg,
                             bg_text_features=self.bg)
         overlap = os.environ.get("WC_OVERLAP_SCALES", "1") != "0"
+        graphs = os.environ.get("WC_BENCH_GRAPHS", "1") != "0"
+        self.graphs = graphs
         self.ev = MscFlipEvaluator(self.model, self.n_classes, self.scales, 512, device, overlap_scales=overlap,
-                                   cam_passes="reference")
+                                   cam_passes="reference", use_graphs=graphs)
         self.ev_live = MscFlipEvaluator(self.model, self.n_classes, self.scales, 512, device, overlap_scales=overlap,
-                                        cam_passes="live")
+                                        cam_passes="live", use_graphs=graphs)
+        # one dataset image per call (the reference's DataLoader(batch_size=1)): the same 512x512 images, and a VOC-like
+        # size mix (long side 500 -> short sides 384 / 341 / 340 / 287 ... after the resize, mostly not multiples of 16)
+        self.ev_b1 = MscFlipEvaluator(self.model, self.n_classes, self.scales, 512, device, overlap_scales=overlap,
+                                      cam_passes="reference", use_graphs=graphs,
+                                      graph_slots=int(os.environ.get("WC_GRAPH_SLOTS", "4")))
+        voc = synth.make_voc_like_dataset(500 + rank, IMAGES_PER_STEP, self.root, self.subdir, self.n_fg)
+        self.voc_items = [(n, im[None].to(device), torch.from_numpy(lab.astype(np.int16)).to(device)) for n, im, lab in voc]
+        self.voc_sizes = [tuple(im.shape[-2:]) for _, im, _ in self.voc_items]
         self.cam_passes_per_image = self.ev.cam_passes_per_image if self.dataset == "voc" else 0
         self.imgs_h = imgs.pin_memory()
         self.labs_h = torch.from_numpy(np.stack(labs).astype(np.int16)).pin_memory()
@@ -118,9 +128,18 @@ class MscFlipVoc:
         """Same step with cam_passes="live": only the CAM / PAR pass whose labels the driver reads."""
         self.ev_live.process_batch(self.names, self.imgs_d, self.labs_d)
 
+    def step_b1(self):
+        """The step's 8 images ONE PER CALL, as the reference's batch_size-1 loop drives the model."""
+        for i in range(IMAGES_PER_STEP):
+            self.ev_b1.process(self.names[i], self.imgs_d[i:i + 1], self.labs_d[i])
+
+    def step_b1_voc_sizes(self):
+        for name, img, lab in self.voc_items:
+            self.ev_b1.process(name, img, lab)
+
     def join(self):
         """Order the current stream after every step enqueued so far (the passes run on the evaluator's own streams)."""
-        for ev in (getattr(self, "ev", None), getattr(self, "ev_live", None)):
+        for ev in (getattr(self, "ev", None), getattr(self, "ev_live", None), getattr(self, "ev_b1", None)):
             if ev is not None:              # workloads without an evaluator run on the current stream already
                 ev.join()
 
@@ -140,12 +159,15 @@ class MscFlipVoc:
         L.wc_prof_reset(); L.wc_prof_enable(1)
         ev = getattr(self, "ev", None)
         overlap = ev.overlap_scales if ev is not None else False
+        graphs = ev.use_graphs if ev is not None else False
         if ev is not None:
-            ev.overlap_scales = False      # per-kernel times are taken with each kernel alone on the device
+            ev.overlap_scales = False      # per-kernel times are taken with each kernel alone on the device,
+            ev.use_graphs = False          # launched eagerly (the profiler brackets launches, not graph nodes)
         for _ in range(steps):
             self.step_device()
         if ev is not None:
-            ev.overlap_scales = overlap
+            ev.join()
+            ev.overlap_scales, ev.use_graphs = overlap, graphs
         summ = prof_summary()
         L.wc_prof_enable(0); L.wc_prof_reset()
         self._prof = {k: (ms / steps, work / steps, cnt // steps) for k, (ms, work, cnt) in summ.items()}

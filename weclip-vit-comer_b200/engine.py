@@ -46,6 +46,7 @@ class Engine:
         self.num_classes = num_classes
         self._keep: List[torch.Tensor] = []
         self._ws: Dict[tuple, torch.Tensor] = {}
+        self.generation = 0          # bumped whenever the device weights are replaced (captured CUDA graphs become stale)
         self.vit = VitW()
         self.dec = DecW()
         self.load_state_dict(state_dict)
@@ -72,6 +73,7 @@ class Engine:
     def load_state_dict(self, sd: Dict[str, torch.Tensor]):
         """Keys as in the reference checkpoint: encoder.visual.*, decoder_fts_fuse.*, decoder.*"""
         self._keep.clear()
+        self.generation += 1
         v, w = "encoder.visual", self.vit
         w.conv1_w = self._bf(sd[v + ".conv1.weight"].reshape(E_VIT, -1))
         w.class_emb = self._f32(sd[v + ".class_embedding"])
@@ -108,6 +110,10 @@ class Engine:
 
     # ------------------------------------------------------------------ workspaces
     def _workspace(self, name: str, nbytes: int) -> torch.Tensor:
+        # under CUDA-graph capture the scratch must outlive this call at a FIXED address for every replay: it comes from the
+        # graph's own memory pool (the shared arena below may be re-allocated when a later, larger call grows it)
+        if self.device.type == "cuda" and torch.cuda.is_current_stream_capturing():
+            return torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
         # one scratch arena per (call kind, CUDA stream): the msc+flip driver runs its scales on separate streams
         key = (name, torch.cuda.current_stream(self.device).cuda_stream if self.device.type == "cuda" else 0)
         ws = self._ws.get(key)

@@ -9,6 +9,7 @@ C x C int64 histograms stay on the device and are summed over ranks with ONE all
 """
 from __future__ import annotations
 
+import math
 from typing import Iterable, Optional, Sequence
 
 import numpy as np
@@ -65,6 +66,59 @@ class LogitDumper:
         self._pending = keep
 
 
+class PinnedRing:
+    """Input staging for the evaluation loop: a few pinned host slots and a copy stream, so that the
+    host->device copy of image i+1 runs under the kernels of image i.  put() fills a slot from host memory and issues its
+    copies; get() makes the current stream wait for them; done() marks the slot reusable once the work enqueued so far on
+    the current stream has finished."""
+
+    def __init__(self, device="cuda", slots: int = 3):
+        self.device = torch.device(device)
+        self.copy_stream = torch.cuda.Stream(self.device)
+        self.slots = [dict(img=None, lab=None, ready=None, free=None) for _ in range(slots)]
+        self._next = 0
+        self.h2d_bytes = 0
+
+    @staticmethod
+    def _fit(buf, shape, dtype):
+        n = int(np.prod(shape))
+        if buf is None or buf.numel() < n or buf.dtype != dtype:
+            buf = torch.empty(n, dtype=dtype, pin_memory=True)
+        return buf
+
+    def put(self, image, label):
+        """image [3,H,W] float32, label [H,W] integer (numpy arrays or CPU tensors) -> slot handle."""
+        i = self._next
+        self._next = (i + 1) % len(self.slots)
+        s = self.slots[i]
+        if s["free"] is not None:
+            s["free"].synchronize()                      # the step that read this slot last has completed
+        img = torch.as_tensor(np.asarray(image), dtype=torch.float32)
+        lab = torch.as_tensor(np.asarray(label)).to(torch.int16)
+        s["img"], s["lab"] = self._fit(s["img"], img.shape, torch.float32), self._fit(s["lab"], lab.shape, torch.int16)
+        pi, pl = s["img"][:img.numel()].view(img.shape), s["lab"][:lab.numel()].view(lab.shape)
+        pi.copy_(img); pl.copy_(lab)
+        with torch.cuda.stream(self.copy_stream):
+            s["d_img"] = pi.to(self.device, non_blocking=True)
+            s["d_lab"] = pl.to(self.device, non_blocking=True)
+            s["ready"] = torch.cuda.Event()
+            s["ready"].record(self.copy_stream)
+        self.h2d_bytes += img.numel() * 4 + lab.numel() * 2
+        return i
+
+    def get(self, i):
+        s = self.slots[i]
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(s["ready"])
+        s["d_img"].record_stream(cur); s["d_lab"].record_stream(cur)
+        return s["d_img"], s["d_lab"]
+
+    def done(self, i):
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self.slots[i]["free"] = ev
+
+
 def shard_indices(n_items: int, rank: int, world: int) -> range:
     """Round-robin image sharding (the reference's own multi-GPU idiom, clip/generate_cams_voc12.py:96-100)."""
     return range(rank, n_items, world)
@@ -73,7 +127,7 @@ def shard_indices(n_items: int, rank: int, world: int) -> range:
 class MscFlipEvaluator:
     def __init__(self, model, num_classes: int = 21, test_scales: Sequence[float] = (1.0, 0.75, 1.25),
                  resize_long: int = 512, device="cuda", overlap_scales: bool = True, cam_passes: str = "reference",
-                 logit_dir: Optional[str] = None):
+                 logit_dir: Optional[str] = None, use_graphs: bool = False, graph_slots: int = 2):
         """cam_passes: how often the CAM / affinity / PAR path runs per dataset image.
         "reference" = the reference's call pattern: ``names = name+name`` (test_msc_flip_voc.py:52, coco :53) is passed
         with EVERY ``[x_s, flip(x_s)]`` batch (:69, :84), so pseudo-labels are built for the plain AND the flipped image at
@@ -82,6 +136,20 @@ class MscFlipEvaluator:
         is never read), so ONE pass per dataset image produces the same three histograms."""
         if cam_passes not in ("reference", "live"):
             raise ValueError("cam_passes must be 'reference' or 'live'")
+        # use_graphs: one CUDA graph per (image size, label size, batch, classes-per-image signature) bucket holds the
+        # whole step — long-side resize, the three [x, flip(x)] forwards with their CAM / PAR passes on forked streams,
+        # fusion, argmax, histograms (~500 launches) — and every later image of the bucket is ONE graph launch
+        # (SURVEY §8f-1).  graph_slots replay slots with their own streams, workspaces and static buffers take turns so
+        # that image i+1 starts under the tail of image i (one image per call leaves most of the 148 SMs idle in the narrow
+        # kernels; more slots = more images in flight).
+        self.use_graphs = bool(use_graphs) and torch.device(device).type == "cuda"
+        self.graph_slots = max(1, int(graph_slots))
+        self._graphs = {}
+        self._slots = []
+        self._slot = 0
+        self._pool = None
+        self.graph_captures = 0
+        self.graph_replays = 0
         self.cam_passes = cam_passes
         self.dumper = LogitDumper(logit_dir) if logit_dir else None
         self._names = None
@@ -116,11 +184,13 @@ class MscFlipEvaluator:
 
     def join(self):
         """Order the current stream after all evaluation work enqueued so far (no host synchronisation)."""
+        main = torch.cuda.current_stream(self.device) if self.device.type == "cuda" else None
         if self._acc_stream is not None:
-            main = torch.cuda.current_stream(self.device)
             main.wait_stream(self._acc_stream)
             for st in self._side_streams:
                 main.wait_stream(st)
+        for slot in self._slots:
+            main.wait_stream(slot["launch"])
 
     def _forward_scales(self, base: torch.Tensor, names, side):
         """model([x_s, flip(x_s)]) for scale 1.0 and every other test scale -> list of (segs, cam), scale 1.0 first.
@@ -170,6 +240,8 @@ class MscFlipEvaluator:
         B = inputs.shape[0]
         names = list(names)      # one name per dataset image; _forward_scales repeats them for the flipped twins
         self._names = names
+        if self.use_graphs and not want_preds and self.dumper is None:
+            return self._process_graphed(names, inputs, labels.contiguous())
         _, _, h0, w0 = inputs.shape
         ratio = self.resize_long / max(h0, w0)
         n_sc = 1 + sum(1 for s in self.scales if s != 1.0)
@@ -202,7 +274,123 @@ class MscFlipEvaluator:
                     t.record_stream(main)
         return res
 
-    def _fuse(self, outs, B, labels, want_preds):
+    # ---- CUDA-graph path -----------------------------------------------------------------------------------------
+    def _scale_list(self):
+        return [1.0] + [s for s in self.scales if s != 1.0]
+
+    def _names_for(self, s, names):
+        if self.cam_passes == "reference":
+            return names + names                         # names = name+name (test_msc_flip_voc.py:52)
+        return names if s == 1.0 else []                 # only cam[0] of the scale-1.0 call is read (:71)
+
+    def _host_metas(self, names, B, h0, w0):
+        """WeCLIP.prepare() for every scale's [x_s, flip(x_s)] call (host lists only; sizes as F.interpolate computes them)."""
+        ratio = self.resize_long / max(h0, w0)
+        hb, wb = int(h0 * ratio), int(w0 * ratio)
+        metas = []
+        for s in self._scale_list():
+            hs, ws = (hb, wb) if s == 1.0 else (int(math.floor(hb * s)), int(math.floor(wb * s)))
+            metas.append(self.model.prepare(self._names_for(s, names), "val", 2 * B, hs, ws, device_tensors=False))
+        return metas
+
+    def _slot_state(self):
+        if not self._slots:
+            for _ in range(self.graph_slots):
+                # graphs of one slot replay in order on its launch stream and may share one memory pool; the two slots
+                # run concurrently, so each has its own pool, streams and (through the per-stream arenas) workspaces
+                self._slots.append(dict(launch=torch.cuda.Stream(self.device), acc=torch.cuda.Stream(self.device),
+                                        side=[torch.cuda.Stream(self.device) for _ in self._scale_list()],
+                                        pool=torch.cuda.graph_pool_handle()))
+        slot = self._slots[self._slot]
+        self._slot = (self._slot + 1) % len(self._slots)
+        return slot
+
+    def _graph_step(self, slot, ent):
+        """The step as it is captured: every launch goes to the slot's streams, forked from / joined to its launch stream."""
+        launch, side, acc = slot["launch"], slot["side"], slot["acc"]
+        inputs, labels, metas = ent["inputs"], ent["labels"], ent["metas"]
+        B = inputs.shape[0]
+        _, _, h0, w0 = inputs.shape
+        ratio = self.resize_long / max(h0, w0)
+        base = ops.resize_bilinear(inputs, size=(int(h0 * ratio), int(w0 * ratio)))          # :60-63
+        scales = self._scale_list()
+        for st in side + [acc]:
+            st.wait_stream(launch)
+        outs = [None] * len(scales)
+        for i in sorted(range(len(scales)), key=lambda i: -scales[i]):                        # longest pass first
+            with torch.cuda.stream(side[i]):
+                x = base if scales[i] == 1.0 else ops.resize_bilinear(base, scale_factor=scales[i])
+                segs, cam, _ = self.model.run(ops.flip_concat(x), metas[i])
+                outs[i] = (segs, cam)
+        for st in side:
+            acc.wait_stream(st)
+        with torch.cuda.stream(acc):
+            self._fuse(outs, B, labels, False, count=False)
+        launch.wait_stream(acc)
+
+    def _capture(self, key, slot, inputs, labels, metas_h):
+        from .model import ForwardMeta
+        launch = slot["launch"]
+        ent = dict(inputs=torch.empty_like(inputs), labels=torch.empty_like(labels), metas=[])
+        for m_h in metas_h:
+            m = ForwardMeta()
+            m.__dict__.update(m_h.__dict__)
+            if m_h.cam_path:
+                m.rows = torch.empty(m_h.rows_host.shape, dtype=torch.int64, device=self.device)
+                m.lut = torch.empty(m_h.lut_host.shape, dtype=torch.int64, device=self.device)
+            ent["metas"].append(m)
+        self._refresh(ent, inputs, labels, metas_h)
+        # warm-up on the slot's own streams: sizes every workspace the capture will use (per-stream arenas), sets the
+        # kernels' shared-memory attributes; its histogram counts are taken back
+        torch.cuda.synchronize(self.device)       # nothing else may be adding to the histograms while they are saved / restored
+        saved = self._hist.clone()
+        self._graph_step(slot, ent)
+        launch.synchronize()
+        self._hist.copy_(saved)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, pool=slot["pool"], stream=launch):
+            self._graph_step(slot, ent)
+        ent["graph"] = g
+        self._graphs[key] = ent
+        self.graph_captures += 1
+        return ent
+
+    def _refresh(self, ent, inputs, labels, metas_h):
+        ent["inputs"].copy_(inputs, non_blocking=True)
+        ent["labels"].copy_(labels, non_blocking=True)
+        for m, m_h in zip(ent["metas"], metas_h):
+            if m_h.cam_path:
+                m.rows.copy_(m_h.rows_host.pin_memory(), non_blocking=True)
+                m.lut.copy_(m_h.lut_host.pin_memory(), non_blocking=True)
+
+    def _process_graphed(self, names, inputs, labels):
+        B = inputs.shape[0]
+        _, _, h0, w0 = inputs.shape
+        metas_h = self._host_metas(names, B, h0, w0)
+        slot = self._slot_state()
+        launch = slot["launch"]
+        caller = torch.cuda.current_stream(self.device)
+        launch.wait_stream(caller)                        # the caller's stream produced inputs / labels
+        eng = self.model.engine
+        if any(m.cam_path for m in metas_h):
+            self.model._text_table(self.device)           # (re)build the cached text table before it becomes part of the key
+        key = (id(slot), B, h0, w0, tuple(labels.shape[-2:]), self.cam_passes, tuple(m.signature() for m in metas_h),
+               id(eng), eng.generation, getattr(self.model, "_text_key", None))
+        with torch.cuda.stream(launch):
+            ent = self._graphs.get(key)
+            if ent is None:
+                ent = self._capture(key, slot, inputs, labels, metas_h)
+            else:
+                self._refresh(ent, inputs, labels, metas_h)
+            ent["graph"].replay()
+        inputs.record_stream(launch)
+        labels.record_stream(launch)
+        self.graph_replays += 1
+        self.n_images += B
+        self.model.iter_num += len(metas_h)
+        return None
+
+    def _fuse(self, outs, B, labels, want_preds, count=True):
         segs_cat, cam = outs[0]
         C, h, w = segs_cat.shape[1:]
         n_scales = len(outs)
@@ -215,7 +403,8 @@ class MscFlipEvaluator:
         msc_pred = ops.upsample_argmax_hist(msc, size, labels, self._hist[1], want_preds)           # :95-96
         if cam is not None:                                                                  # :71, :107
             ops.confusion_hist(cam[:B], labels, self._hist[2])
-        self.n_images += B
+        if count:
+            self.n_images += B
         if self.dumper is not None:                                                          # :111
             self.dumper.add(self._names, segs_cat[:B], msc)
         if want_preds:
@@ -240,16 +429,25 @@ class MscFlipEvaluator:
 
 def validate(model, dataset: Iterable, test_scales=None, num_classes: int = 21, resize_long: int = 512,
              rank: int = 0, world: int = 1, device="cuda", cam_passes: str = "reference",
-             logit_dir: Optional[str] = None):
+             logit_dir: Optional[str] = None, use_graphs: bool = True):
     """Drop-in for validate() of test_msc_flip_voc.py: dataset yields (name, image CHW fp32, label HW, cls_label).
-    Returns the three score dicts after the cross-rank histogram reduction."""
+    One dataset image per model call like the reference's DataLoader(batch_size=1); images are sharded round-robin over
+    ranks, staged through a pinned ring (copy of image i+1 under the kernels of image i) and — with use_graphs — replayed
+    from one CUDA graph per (size, classes-per-image) bucket.  Returns the three score dicts after the cross-rank
+    histogram reduction."""
     ev = MscFlipEvaluator(model, num_classes, test_scales or [1.0, 0.75], resize_long, device, cam_passes=cam_passes,
-                          logit_dir=logit_dir)
+                          logit_dir=logit_dir, use_graphs=use_graphs and logit_dir is None)
     items = list(dataset) if not hasattr(dataset, "__getitem__") else dataset
-    for i in shard_indices(len(items), rank, world):
-        name, image, label = items[i][:3]
-        image = torch.as_tensor(image, dtype=torch.float32).unsqueeze(0).to(ev.device, non_blocking=True)
-        label = torch.as_tensor(np.asarray(label)).to(torch.int16).to(ev.device, non_blocking=True).contiguous()
-        ev.process(str(name), image, label)
+    idx = list(shard_indices(len(items), rank, world))
+    ring = PinnedRing(ev.device)
+    pending = ring.put(items[idx[0]][1], items[idx[0]][2]) if idx else None
+    for n, i in enumerate(idx):
+        slot = pending
+        if n + 1 < len(idx):
+            nxt = items[idx[n + 1]]
+            pending = ring.put(nxt[1], nxt[2])           # staged while image i computes
+        image, label = ring.get(slot)
+        ev.process(str(items[i][0]), image.unsqueeze(0), label.contiguous())
+        ring.done(slot)
     ev.all_reduce()
     return ev.scores()

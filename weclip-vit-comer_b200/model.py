@@ -77,6 +77,21 @@ def _to_device_async(t: torch.Tensor, device) -> torch.Tensor:
     return t.pin_memory().to(device, non_blocking=True)
 
 
+class ForwardMeta:
+    """What forward() derives from the image names before any kernel runs (see WeCLIP.prepare)."""
+    mode = "val"
+    cam_path = False
+    require_seg_trans = True
+    nl = 0
+    n_cam = 0
+    ids_all = size = text_off = k_off = ch_off = rows = lut = rows_host = lut_host = None
+
+    def signature(self):
+        """Everything that shapes the launches (grid sizes, by-value tables): equal signatures can share a CUDA graph."""
+        return (self.mode, self.cam_path, self.require_seg_trans, self.nl, self.n_cam,
+                tuple(self.k_off) if self.k_off else None, self.size)
+
+
 class WeCLIP(nn.Module):
     def __init__(self, num_classes=None, clip_model=None, embedding_dim=256, in_channels=512, dataset_root_path=None,
                  device="cuda", dataset: str = "voc", fg_text_features: Optional[torch.Tensor] = None,
@@ -156,39 +171,26 @@ class WeCLIP(nn.Module):
                 torch.cuda.current_stream(device).synchronize()   # one-time: other streams may read the table next
         return self._text_tbl, fg.shape[0], bg.shape[0]
 
-    def forward(self, img, img_names="2007_000032", mode="train"):
-        _lib.require_device()
-        if self.engine is None:
-            raise _lib.WeclipError("WeCLIP weights are not loaded (encoder + decoder state dict required)")
-        eng, cfg = self.engine, self.cfg
-        img = img.to(eng.device, torch.float32)
-        N, _, H, W = img.shape
-        h, w = H // 16, W // 16
-        self.iter_num += 1
-        cam_path = not (self.dataset == "coco" and mode == "val")     # model_attn_aff_coco.py:131-132
-        require_seg_trans = self.iter_num > cfg["switch"] or mode == "val"
-        nl = cfg["window"] if require_seg_trans else 8                 # clip_tool.py:155 / :173
-        # the CAM / PAR path runs once per NAME (model_attn_aff_voc.py:139 `for i, img_name in enumerate(img_names)`); the
-        # reference's msc+flip driver passes names = name+name (test_msc_flip_voc.py:52), i.e. one name per image of its
-        # [image, flipped image] batch.  Fewer names than images is allowed (only the leading images get pseudo-labels):
-        # evaluate.MscFlipEvaluator(cam_passes="live") uses that to skip passes whose labels the driver never reads
+    def prepare(self, img_names, mode: str, N: int, H: int, W: int, device_tensors: bool = True) -> "ForwardMeta":
+        """Host half of forward(): read the label sets (clip_tool.py:111-118), build the per-image text-row / class-offset
+        tables and the valid_key LUT.  The two index vectors travel to the device from pinned memory (no host blocking);
+        ``device_tensors=False`` leaves them on the host (CUDA-graph replay copies them into the graph's own buffers)."""
+        cfg = self.cfg
         if isinstance(img_names, str):
             img_names = [img_names]
-        n_cam = len(img_names)
-        if n_cam > N:
+        m = ForwardMeta()
+        m.mode = mode
+        m.cam_path = not (self.dataset == "coco" and mode == "val") and len(img_names) > 0   # model_attn_aff_coco.py:131-132
+        m.require_seg_trans = self.iter_num > cfg["switch"] or mode == "val"
+        m.nl = cfg["window"] if m.require_seg_trans else 8                 # clip_tool.py:155 / :173
+        m.n_cam = len(img_names)
+        if m.n_cam > N:
             raise IndexError("index %d is out of bounds for dimension 0 with size %d" % (N, N))   # img[i], reference :141
-        cam_path = cam_path and n_cam > 0
-        taps, x_last, attn = eng.encoder(img, n_attn=(nl - 1) if cam_path else 0, attn_slots=nl if cam_path else 0,
-                                         attn_imgs=n_cam if cam_path else None)
-        seg, attn_pred, _ = eng.decoder(taps, N, h, w)
-        if not cam_path:
-            return seg, None, attn_pred
-        N_all, N = N, n_cam
-
-        # nothing below may block the host on the stream (a pageable host->device copy does): the text rows are gathered
-        # on the device from a cached [fg; bg] table with an index vector that travels from pinned memory
+        if not m.cam_path:
+            return m
+        fg, bg = self.fg_text_features, self.bg_text_features
+        n_fg, n_bg = fg.shape[0], bg.shape[0]
         ids_all, sizes, text_off, k_off, rows = [], [], [0], [0], []
-        table, n_fg, n_bg = self._text_table(eng.device)
         for name in img_names:
             ids, oh, ow = self.label_reader(self._label_path(name))
             ids_all.append(ids)
@@ -200,20 +202,53 @@ class WeCLIP(nn.Module):
             raise RuntimeError("image without foreground label (torch.stack([]) in the reference, clip_tool.py:212)")
         if any(i < 0 or i >= n_fg for ids in ids_all for i in ids):
             raise IndexError("label id outside the foreground text features")
-        text = table.index_select(0, _to_device_async(torch.tensor(rows, dtype=torch.int64), eng.device))
-        cams, _, _ = eng.gradcam(x_last, N, h, w, text, text_off, k_off, attn_last_out=attn[nl - 1])
-        refined, bmasks = eng.affinity_refine(attn, nl, attn_pred, N, h, w, require_seg_trans, cams, k_off,
-                                              cfg["box_thr"], want_masks=self.keep_intermediates)
-        if self.keep_intermediates:
-            self.last = dict(cams=cams, box_masks=bmasks, refined=refined, k_off=k_off, ids=ids_all,
-                             rfm_sel=eng.last_rfm_sel)
         if len(set(sizes)) != 1:
             raise RuntimeError("stack expects each tensor to be equal size (model_attn_aff_voc.py:173)")
-        Hc, Wc = sizes[0]
-        par_in = eng.cam_upsample_bg(refined, k_off, N, h, w, Hc, Wc, float(self.cam_bg_thres))
-        ch_off = [k_off[i] + i for i in range(N + 1)]
-        par_out = self.par.refine_ragged(img[:N], par_in, ch_off)
-        lut = _to_device_async(torch.tensor([v for ids in ids_all for v in [0] + [i + 1 for i in ids]], dtype=torch.int64),
-                               eng.device)
-        labels = argmax_lut(par_out, lut, ch_off)
+        m.ids_all, m.size, m.text_off, m.k_off = ids_all, sizes[0], text_off, k_off
+        m.ch_off = [k_off[i] + i for i in range(m.n_cam + 1)]
+        m.rows_host = torch.tensor(rows, dtype=torch.int64)
+        m.lut_host = torch.tensor([v for ids in ids_all for v in [0] + [i + 1 for i in ids]], dtype=torch.int64)
+        if device_tensors:
+            dev = self.engine.device if self.engine is not None else self._device
+            m.rows, m.lut = _to_device_async(m.rows_host, dev), _to_device_async(m.lut_host, dev)
+        return m
+
+    def run(self, img, m: "ForwardMeta"):
+        """Device half of forward(): every launch goes to the current stream; nothing here blocks the host or reads a
+        host value back, so the whole call can be captured into a CUDA graph (evaluate.MscFlipEvaluator, use_graphs)."""
+        eng, cfg = self.engine, self.cfg
+        N, _, H, W = img.shape
+        h, w = H // 16, W // 16
+        n_cam, nl = m.n_cam, m.nl
+        taps, x_last, attn = eng.encoder(img, n_attn=(nl - 1) if m.cam_path else 0, attn_slots=nl if m.cam_path else 0,
+                                         attn_imgs=n_cam if m.cam_path else None)
+        seg, attn_pred, _ = eng.decoder(taps, N, h, w)
+        if not m.cam_path:
+            return seg, None, attn_pred
+        # the text rows are gathered on the device from a cached [fg; bg] table with the index vector of prepare()
+        table, _, _ = self._text_table(eng.device)
+        text = table.index_select(0, m.rows)
+        cams, _, _ = eng.gradcam(x_last, n_cam, h, w, text, m.text_off, m.k_off, attn_last_out=attn[nl - 1])
+        refined, bmasks = eng.affinity_refine(attn, nl, attn_pred, n_cam, h, w, m.require_seg_trans, cams, m.k_off,
+                                              cfg["box_thr"], want_masks=self.keep_intermediates)
+        if self.keep_intermediates:
+            self.last = dict(cams=cams, box_masks=bmasks, refined=refined, k_off=m.k_off, ids=m.ids_all,
+                             rfm_sel=eng.last_rfm_sel)
+        Hc, Wc = m.size
+        par_in = eng.cam_upsample_bg(refined, m.k_off, n_cam, h, w, Hc, Wc, float(self.cam_bg_thres))
+        par_out = self.par.refine_ragged(img[:n_cam], par_in, m.ch_off)
+        labels = argmax_lut(par_out, m.lut, m.ch_off)
         return seg, labels, attn_pred
+
+    def forward(self, img, img_names="2007_000032", mode="train"):
+        _lib.require_device()
+        if self.engine is None:
+            raise _lib.WeclipError("WeCLIP weights are not loaded (encoder + decoder state dict required)")
+        img = img.to(self.engine.device, torch.float32)
+        N, _, H, W = img.shape
+        self.iter_num += 1
+        # the CAM / PAR path runs once per NAME (model_attn_aff_voc.py:139 `for i, img_name in enumerate(img_names)`); the
+        # reference's msc+flip driver passes names = name+name (test_msc_flip_voc.py:52), i.e. one name per image of its
+        # [image, flipped image] batch.  Fewer names than images is allowed (only the leading images get pseudo-labels):
+        # evaluate.MscFlipEvaluator(cam_passes="live") uses that to skip passes whose labels the driver never reads
+        return self.run(img, self.prepare(img_names, mode, N, H, W))

@@ -35,6 +35,9 @@ class PAR(nn.Module):
         self._ws = {}
 
     def _workspace(self, nbytes: int, device) -> torch.Tensor:
+        # under CUDA-graph capture: a private allocation from the graph's pool (fixed address for every replay)
+        if device.type == "cuda" and torch.cuda.is_current_stream_capturing():
+            return torch.empty(nbytes, dtype=torch.uint8, device=device)
         # one scratch arena per (device, CUDA stream): callers may run independent batches on separate streams
         key = (str(device), torch.cuda.current_stream(device).cuda_stream if device.type == "cuda" else 0)
         ws = self._ws.get(key)

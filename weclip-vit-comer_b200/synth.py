@@ -153,3 +153,28 @@ def write_label_png(root: str, subdir: str, name: str, lab: np.ndarray) -> str:
     path = os.path.join(d, str(name) + ".png")
     Image.fromarray(lab).save(path)
     return path
+
+
+# (H0, W0) of VOC-style JPEGs (long side 500) with rough frequencies: after the evaluation's long-side-512 resize
+# (test_msc_flip_voc.py:60-63, short side int(h * 512/500)) most short sides are NOT multiples of 16 (341, 340, 342, 287 ...)
+VOC_LIKE_SIZES = [((375, 500), 0.42), ((500, 375), 0.13), ((333, 500), 0.14), ((500, 333), 0.05), ((334, 500), 0.04),
+                  ((332, 500), 0.04), ((374, 500), 0.04), ((281, 500), 0.03), ((500, 334), 0.02), ((500, 500), 0.02),
+                  ((400, 500), 0.02), ((356, 500), 0.02), ((480, 360), 0.02), ((335, 500), 0.01)]
+
+
+def draw_voc_like_sizes(rng: np.random.Generator, n: int):
+    sizes, ps = zip(*VOC_LIKE_SIZES)
+    idx = rng.choice(len(sizes), size=n, p=np.array(ps) / sum(ps))
+    return [sizes[i] for i in idx]
+
+
+def make_voc_like_dataset(seed: int, n: int, root: str, subdir: str = "SegmentationClassAug", n_fg: int = 20, prefix: str = "v"):
+    """n dataset items (name, image [3,H0,W0] fp32, label [H0,W0] uint8) with VOC-like sizes; label PNGs written under root."""
+    rng = np.random.default_rng(seed)
+    items = []
+    for i, (h0, w0) in enumerate(draw_voc_like_sizes(rng, n)):
+        lab = make_label_map(rng, h0, w0, draw_label_set(rng, n_fg))
+        name = f"{prefix}{seed}_{i}"
+        write_label_png(root, subdir, name, lab)
+        items.append((name, make_images(7000 + seed * 131 + i, 1, h0, w0)[0], lab))
+    return items
