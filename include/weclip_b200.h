@@ -30,7 +30,7 @@ extern "C" {
 #define WC_ERR_WORKSPACE (-3)
 #define WC_ERR_UNSUPPORTED (-4)
 
-#define WC_ABI_VERSION 9
+#define WC_ABI_VERSION 10
 #define WC_PAR_MAX_DIL 8
 
 /* ABI version (bumped whenever a signature changes) and last error text. */
@@ -102,6 +102,14 @@ int wc_argmax_lut(const float* masks, const int64_t* lut, int64_t* labels,
 int wc_gemm_f16(const void* A, const void* B, void* out, const float* bias, const float* resid,
                  int M, int N, int K, int batch, long lda, long ldb, long ldo, long a_bs, long b_bs, long o_bs,
                  int out_f16, int out_trans, int act, float alpha, void* stream);
+
+/* The same product with TWO batch dimensions (b = b0 + nb0*b1; e.g. heads x images of an attention product), each with
+ * its own element strides for A, B, out / resid and the bias vector. */
+int wc_gemm_f16_ex(const void* A, const void* B, void* out, const float* bias, const float* resid,
+                    int M, int N, int K, int nb0, int nb1, long lda, long ldb, long ldo,
+                    long a_bs0, long a_bs1, long b_bs0, long b_bs1, long o_bs0, long o_bs1,
+                    long bias_bs0, long bias_bs1,
+                    int out_f16, int out_trans, int act, float alpha, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Weights.  "h16" pointers are h16 row-major [out_features, in_features] (nn.Linear layout,
@@ -283,6 +291,33 @@ int wc_aff_loss_fused(const float* attn_pred, const int64_t* cam_label, int B, i
  * grad fp32 [B,C,H,W] (may be NULL) = d loss / d pred. */
 int wc_seg_loss(const float* pred, const int64_t* label, int B, int C, int H, int W, int ignore_index, float* loss,
                 float* grad, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Trainable decoder: the non-GEMM pieces of the backward of decoder_fts_fuse + decoder + attn_pred
+ * (scripts/dist_clip_voc.py:246-267 trains them with torch autograd; segformer_head.py:49-80,
+ * Decoder/TransDecoder.py:70-125, model_attn_aff_voc.py:134-137).  Every matrix product of the forward, the input
+ * gradients and the weight gradients goes through wc_gemm_f16 / wc_gemm_f16_ex; host side: weclip_b200/train.py.
+ * ---------------------------------------------------------------------------------------------- */
+/* out[b][c][r] = alpha * in[b][r][c] as h16 (in: fp32 when in_f32, else h16) for r < R, c < C; element strides; the
+ * pad columns R..ld_out-1 of the output rows are not written (allocate the output zeroed when ld_out > R). */
+int wc_transpose_f16(const void* in, int in_f32, void* out, int batch, int R, int C, long ld_in, long ld_out,
+                     long in_bs, long out_bs, float alpha, void* stream);
+/* out h16 = alpha * in.  ref_scale > 0 additionally reproduces the reference's fp16 rounding of a gradient that is carried
+ * here with a power-of-two scale (clip/myAtt.py:321, see wc_gradcam_set_exact): half(alpha*in / ref_scale) * ref_scale. */
+int wc_cast_f16(const float* in, void* out, long n, float alpha, float ref_scale, void* stream);
+/* LayerNorm backward (eps 1e-5): dx = LN'(dy) [+ add]; dgamma / dbeta [E] are ACCUMULATED (zero them first). E in {256,512,768}. */
+int wc_layernorm_bwd(const float* x, const float* gamma, const float* dy, const float* add, float* dx,
+                     float* dgamma, float* dbeta, long rows, int E, void* stream);
+/* Softmax backward per row: dS = P * (dP - sum_j P_j dP_j); P h16, dP fp32, dS h16, row pitch Lp (pad columns zeroed). */
+int wc_softmax_bwd(const void* P, const float* dP, void* dS, long rows, int L, int Lp, void* stream);
+/* out[c] = alpha * sum_r x[r][c] (bias gradients); x fp32 or h16 [M, N] with row stride ld. */
+int wc_colsum(const void* x, int x_f16, float* out, long M, int N, long ld, float alpha, void* stream);
+/* out h16 = alpha * dy * f'(.): kind 1 ReLU (aux = activation output), kind 2 QuickGELU (aux = pre-activation). */
+int wc_act_bwd(int kind, const float* dy, const void* aux, void* out, long n, float alpha, void* stream);
+/* attn_pred = sigmoid(F F^T): G h16 [N,P,Pp] = alpha * (g + g^T), g = dA * s * (1 - s); then dF = G F. */
+int wc_sigmoid_gram_bwd(const float* dA, const float* S, void* G, int N, int P, int Pp, float alpha, void* stream);
+/* Dropout2d (segformer_head.py:79): y[n][p][c] = x[n][p][c] * mask[n][c], mask = 0 or 1/(1-p); y fp32 and/or h16. */
+int wc_dropout2d(const float* x, const float* mask, float* y, void* y_f16, int N, int P, int C, void* stream);
 
 #ifdef __cplusplus
 }

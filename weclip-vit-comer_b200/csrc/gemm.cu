@@ -1019,3 +1019,22 @@ extern "C" int wc_gemm_f16(const void* A, const void* B, void* out, const float*
     p.epi.resid = resid; p.epi.ldr = ldo; p.epi.resid_bs0 = o_bs;
     return launch_gemm(p, as_stream(stream));
 }
+
+// Two batch dimensions (e.g. heads x images of an attention product) with independent strides for A, B and out.
+extern "C" int wc_gemm_f16_ex(const void* A, const void* B, void* out, const float* bias, const float* resid,
+                               int M, int N, int K, int nb0, int nb1, long lda, long ldb, long ldo,
+                               long a_bs0, long a_bs1, long b_bs0, long b_bs1, long o_bs0, long o_bs1,
+                               long bias_bs0, long bias_bs1,
+                               int out_f16, int out_trans, int act, float alpha, void* stream) {
+    WC_CHECK_ARG(A && B && out && nb0 > 0 && nb1 > 0);
+    GemmProblem p;
+    p.M = M; p.N = N; p.K = K; p.nb0 = nb0; p.nb1 = nb1;
+    p.A = {reinterpret_cast<const h16*>(A), M, lda, a_bs0, a_bs1};
+    p.B = {reinterpret_cast<const h16*>(B), N, ldb, b_bs0, b_bs1};
+    p.epi.mode = GM_STORE; p.epi.act = act; p.epi.alpha = alpha; p.epi.bias = bias;
+    p.epi.bias_bs0 = bias_bs0; p.epi.bias_bs1 = bias_bs1;
+    p.epi.out = out; p.epi.out_f16 = out_f16; p.epi.out_trans = out_trans; p.epi.ldo = ldo;
+    p.epi.out_bs0 = o_bs0; p.epi.out_bs1 = o_bs1;
+    p.epi.resid = resid; p.epi.ldr = ldo; p.epi.resid_bs0 = o_bs0; p.epi.resid_bs1 = o_bs1;
+    return launch_gemm(p, as_stream(stream));
+}

@@ -93,7 +93,23 @@ class Engine:
         w.logit_scale_exp = float(sd["encoder.logit_scale"].float().exp())
         self.load_decoder_state_dict(sd)
 
+    def refresh_decoder(self, sd):
+        """Copy new decoder weights into the EXISTING device buffers (addresses stay fixed)."""
+        shadow = Engine.__new__(Engine)
+        shadow.device, shadow._keep, shadow.dec, shadow.num_classes = self.device, [], DecW(), self.num_classes
+        n0 = len(self._keep) - self._n_dec
+        shadow.load_decoder_state_dict(sd)
+        old = self._keep[n0:]
+        assert len(old) == len(shadow._keep)
+        for dst, src in zip(old, shadow._keep):
+            dst.copy_(src)
+
     def load_decoder_state_dict(self, sd):
+        n_before = len(self._keep)
+        self._load_decoder(sd)
+        self._n_dec = len(self._keep) - n_before
+
+    def _load_decoder(self, sd):
         d, f = self.dec, "decoder_fts_fuse.linears_modulelist"
         d.fuse_w1 = self._bf(torch.stack([sd[f"{f}.{i}.proj.weight"] for i in range(N_TAPS)]))
         d.fuse_b1 = self._f32(torch.stack([sd[f"{f}.{i}.proj.bias"] for i in range(N_TAPS)]))

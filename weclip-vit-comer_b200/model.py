@@ -7,8 +7,13 @@ Same ``forward(img, img_names, mode) -> (seg, cam_labels, attn_pred)`` contract,
 
 Out of scope by SURVEY.md §2 (init-time only): the CLIP text tower / tokenizer.  ``fg_text_features`` /
 ``bg_text_features`` are therefore inputs (ctor kwargs or attributes), not computed here.
-Forward-only: ``seg`` / ``attn_pred`` carry no autograd graph (training the decoder through this module is
-SURVEY.md §8f-2, "next").
+
+Trainable decoder: ``decoder_fts_fuse`` and ``decoder`` are sub-modules holding live ``nn.Parameter``s
+(``get_param_groups()[3]``, ``state_dict()``); under grad mode ``seg`` and ``attn_pred`` come from
+``train.DecoderFunction`` (tcgen05 forward + hand-written backward, Dropout2d(0.1) while ``self.training``) and carry an
+autograd graph, so scripts/dist_clip_voc.py:246-267 (loss, backward, optimizer.step) runs against this module.  Under
+``torch.no_grad()`` the fused inference kernels run (wc_decoder_fwd).  The CLIP encoder is frozen (the reference never
+steps it: its parameter groups 0-2 are empty, model_attn_aff_voc.py:94-103).
 """
 from __future__ import annotations
 
@@ -23,6 +28,7 @@ import torch.nn as nn
 from . import _lib
 from .engine import Engine
 from .par import PAR, argmax_lut
+from .train import DecoderFunction, DecoderTransformer, SegFormerHead, decoder_parameters, make_dropout_mask
 
 _DATASETS = {
     # window, box threshold, RFM switch iteration, label sub-directory   (clip_tool.py:155,179 / :277,301;
@@ -117,8 +123,11 @@ class WeCLIP(nn.Module):
         self.keep_intermediates = False      # debugging / test hook: keep raw CAMs, box masks, refined CAMs in self.last
         self.last: dict = {}
         self._device = torch.device(device)
-        self._sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+        self._sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()      # frozen encoder weights (reference key names)
         self.engine: Optional[Engine] = None
+        self.decoder_fts_fuse = SegFormerHead()
+        self.decoder = DecoderTransformer(output_dim=num_classes or 21)
+        self._dec_versions = None
         if state_dict is None and clip_model is not None:
             clip_sd = load_clip_checkpoint(clip_model)
             state_dict = {("encoder." + k.replace("module.", "")): v for k, v in clip_sd.items()
@@ -127,33 +136,68 @@ class WeCLIP(nn.Module):
             self.load_state_dict(state_dict, strict=False)
 
     # ---- state dict with the reference's key names -------------------------------------------------------
+    def _decoder_state(self) -> "OrderedDict[str, torch.Tensor]":
+        sd = OrderedDict()
+        for prefix, mod in (("decoder_fts_fuse.", self.decoder_fts_fuse), ("decoder.", self.decoder)):
+            for k, v in mod.state_dict().items():
+                sd[prefix + k] = v
+        return sd
+
     def state_dict(self, *args, **kwargs):
         sd = OrderedDict(self._sd)
+        sd.update({k: v.detach() for k, v in self._decoder_state().items()})
         sd["par.kernel"] = self.par.kernel
         return sd
 
     def load_state_dict(self, state_dict, strict: bool = False):
         """test_msc_flip_voc.py:196 loads with strict=False; encoder keys may come from the CLIP checkpoint."""
-        known = {k: v for k, v in state_dict.items() if k.startswith(("encoder.visual.", "encoder.logit_scale",
-                                                                      "decoder_fts_fuse.", "decoder."))}
-        self._sd.update({k: v.detach().float().cpu() for k, v in known.items()})
-        need = ("encoder.visual.conv1.weight", "decoder.linear_pred.weight", "decoder_fts_fuse.linear_fuse.weight")
-        if all(k in self._sd for k in need) and torch.cuda.is_available():
-            self.engine = Engine(self._sd, self.num_classes, self._device)
+        enc = {k: v for k, v in state_dict.items() if k.startswith(("encoder.visual.", "encoder.logit_scale"))}
+        dec = {k: v for k, v in state_dict.items() if k.startswith(("decoder_fts_fuse.", "decoder."))}
+        self._sd.update({k: v.detach().float().cpu() for k, v in enc.items()})
+        if "decoder.linear_pred.weight" in dec and dec["decoder.linear_pred.weight"].shape[0] != self.decoder.linear_pred.out_channels:
+            self.decoder = DecoderTransformer(output_dim=int(dec["decoder.linear_pred.weight"].shape[0]))
+        own = self._decoder_state()
+        loaded = set()
+        with torch.no_grad():
+            for k, v in dec.items():
+                if k in own and own[k].shape == v.shape:
+                    own[k].copy_(v.detach().to(own[k].dtype))
+                    loaded.add(k)
+        self._dec_loaded = getattr(self, "_dec_loaded", set()) | loaded
+        need = ("encoder.visual.conv1.weight",)
+        have_dec = {"decoder.linear_pred.weight", "decoder_fts_fuse.linear_fuse.weight"} <= self._dec_loaded
+        if all(k in self._sd for k in need) and have_dec and torch.cuda.is_available():
+            self.decoder_fts_fuse.to(self._device)
+            self.decoder.to(self._device)
+            full = OrderedDict(self._sd)
+            full.update(self._decoder_state())
+            self.engine = Engine(full, self.num_classes, self._device)
             self.num_classes = self.engine.num_classes
-        missing = [k for k in need if k not in self._sd]
-        unexpected = [k for k in state_dict if k not in known and k != "par.kernel"]
+            self._dec_versions = self._param_versions()
+        missing = [k for k in ("encoder.visual.conv1.weight",) if k not in self._sd] + \
+                  [k for k in ("decoder.linear_pred.weight", "decoder_fts_fuse.linear_fuse.weight") if k not in self._dec_loaded]
+        unexpected = [k for k in state_dict if k not in enc and k not in loaded and k != "par.kernel"]
         if strict and (missing or unexpected):
             raise RuntimeError(f"missing {missing}, unexpected {unexpected}")
         return nn.modules.module._IncompatibleKeys(missing, unexpected)
 
     def get_param_groups(self):
-        """model_attn_aff_voc.py:94-103: [[], [], [], decoder + fuse parameters]."""
+        """model_attn_aff_voc.py:94-103: [[], [], [], decoder + fuse parameters] — the live nn.Parameters."""
         groups = [[], [], [], []]
-        for k, v in self._sd.items():
-            if k.startswith(("decoder.", "decoder_fts_fuse.")):
-                groups[3].append(v)
+        groups[3] += list(self.decoder.parameters())
+        groups[3] += list(self.decoder_fts_fuse.parameters())
         return groups
+
+    def _param_versions(self):
+        return tuple((p.data_ptr(), p._version) for p in decoder_parameters(self.decoder_fts_fuse, self.decoder))
+
+    def _sync_decoder_weights(self):
+        """The fused inference kernels read fp16 device copies of the decoder weights: refresh them (in place, same
+        addresses, so captured CUDA graphs stay valid) after an optimiser step or a manual edit of the parameters."""
+        ver = self._param_versions()
+        if ver != self._dec_versions:
+            self.engine.refresh_decoder(self._decoder_state())
+            self._dec_versions = ver
 
     # ---- forward ---------------------------------------------------------------------------------------------
     def _label_path(self, name) -> str:
@@ -222,9 +266,19 @@ class WeCLIP(nn.Module):
         n_cam, nl = m.n_cam, m.nl
         taps, x_last, attn = eng.encoder(img, n_attn=(nl - 1) if m.cam_path else 0, attn_slots=nl if m.cam_path else 0,
                                          attn_imgs=n_cam if m.cam_path else None)
-        seg, attn_pred, _ = eng.decoder(taps, N, h, w)
+        params = decoder_parameters(self.decoder_fts_fuse, self.decoder)
+        if torch.is_grad_enabled() and any(p.requires_grad for p in params):
+            # training step (scripts/dist_clip_voc.py:246-267): seg / attn_pred carry the autograd graph of the decoder
+            mask = make_dropout_mask(N, self.decoder_fts_fuse.dropout.p, self.training and self.decoder_fts_fuse.training,
+                                     eng.device)
+            seg, attn_pred_g = DecoderFunction.apply(taps, (N, h, w), mask, *params)
+            attn_pred = attn_pred_g.detach()          # the CAM / PAR branch is detached (clip_tool.py:169-175)
+        else:
+            self._sync_decoder_weights()
+            seg, attn_pred, _ = eng.decoder(taps, N, h, w)
+            attn_pred_g = attn_pred
         if not m.cam_path:
-            return seg, None, attn_pred
+            return seg, None, attn_pred_g
         # the text rows are gathered on the device from a cached [fg; bg] table with the index vector of prepare()
         table, _, _ = self._text_table(eng.device)
         text = table.index_select(0, m.rows)
@@ -238,7 +292,7 @@ class WeCLIP(nn.Module):
         par_in = eng.cam_upsample_bg(refined, m.k_off, n_cam, h, w, Hc, Wc, float(self.cam_bg_thres))
         par_out = self.par.refine_ragged(img[:n_cam], par_in, m.ch_off)
         labels = argmax_lut(par_out, m.lut, m.ch_off)
-        return seg, labels, attn_pred
+        return seg, labels, attn_pred_g
 
     def forward(self, img, img_names="2007_000032", mode="train"):
         _lib.require_device()
