@@ -30,7 +30,7 @@ extern "C" {
 #define WC_ERR_WORKSPACE (-3)
 #define WC_ERR_UNSUPPORTED (-4)
 
-#define WC_ABI_VERSION 10
+#define WC_ABI_VERSION 11
 #define WC_PAR_MAX_DIL 8
 
 /* ABI version (bumped whenever a signature changes) and last error text. */
@@ -318,6 +318,36 @@ int wc_act_bwd(int kind, const float* dy, const void* aux, void* out, long n, fl
 int wc_sigmoid_gram_bwd(const float* dA, const float* S, void* G, int N, int P, int Pp, float alpha, void* stream);
 /* Dropout2d (segformer_head.py:79): y[n][p][c] = x[n][p][c] * mask[n][c], mask = 0 or 1/(1-p); y fp32 and/or h16. */
 int wc_dropout2d(const float* x, const float* mask, float* y, void* y_f16, int N, int P, int C, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Input pipeline: baseline JPEG -> normalised CHW fp32 on the device, label map -> label set.
+ * Replaces imageio.imread + normalize_img + HWC->CHW (datasets/voc.py:48-67,253-271, datasets/transforms.py:8-15) and
+ * np.unique on the label PNG (clip/clip_tool.py:111-118).  The decoded pixels are bit-identical to PIL / libjpeg's
+ * defaults (integer "islow" IDCT, fancy chroma up-sampling, fixed-point YCbCr->RGB): see csrc/jpeg.cu.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct wc_jpeg_info {
+    int width, height, ncomp;            /* ncomp 1 (grey) or 3 (YCbCr) */
+    int hs[3], vs[3], hmax, vmax;        /* sampling factors */
+    int mcus_x, mcus_y;
+    int blocks_w[3], blocks_h[3];        /* 8x8 blocks per component (padded to whole MCUs) */
+    long coef_off[3], coef_count;        /* int16 coefficients: component c starts at coef_off[c]; block-major, natural order */
+    int comp_qt[3], restart_interval;
+    uint16_t qt[4][64];                  /* quantisation tables, natural order */
+} wc_jpeg_info;
+/* HOST: parse the markers of a JPEG byte stream (WC_ERR_UNSUPPORTED for progressive / arithmetic / 12-bit / CMYK). */
+int wc_jpeg_parse(const uint8_t* data_host, size_t n, wc_jpeg_info* info_host);
+/* HOST: sequential Huffman decode into coef_host (info.coef_count int16; pinned memory recommended). Thread-safe. */
+int wc_jpeg_entropy_decode(const uint8_t* data_host, size_t n, int16_t* coef_host, long coef_cap);
+/* DEVICE: de-quantise + inverse DCT + chroma up-sampling + colour conversion.  coef: DEVICE copy of the coefficients.
+ * rgb_hwc (uint8 [H,W,3], optional) = exactly what PIL returns; chw (fp32 [3,H,W], optional) = (rgb - mean) / std per
+ * channel evaluated in fp64 and rounded to fp32 like numpy (mean / std: 3 host doubles). */
+size_t wc_jpeg_workspace_bytes(const wc_jpeg_info* info_host);
+int wc_jpeg_reconstruct(const wc_jpeg_info* info_host, const int16_t* coef, uint8_t* rgb_hwc, float* chw,
+                        const double* mean_host, const double* std_host, void* workspace, size_t workspace_bytes, void* stream);
+/* uint8 HWC image already on the device -> normalised fp32 CHW (datasets/transforms.py:8-15 + the transpose of voc.py:236). */
+int wc_normalize_u8(const uint8_t* hwc, float* chw, int H, int W, const double* mean_host, const double* std_host, void* stream);
+/* present256[v] = 1 iff value v occurs in the uint8 label map (np.unique of clip/clip_tool.py:113 as a presence table). */
+int wc_label_presence(const uint8_t* label, long n, int* present256, void* stream);
 
 #ifdef __cplusplus
 }
