@@ -211,9 +211,10 @@ def grad_cam(x11: Tensor, text: Tensor, targets: Sequence[int], sd: Dict[str, Te
     cams = []
     probs = attn_last = None
     for k in targets:
-        A = layer_norm(x11, sd[p + ".ln_1.weight"], sd[p + ".ln_1.bias"]).detach().requires_grad_(True)
-        probs, attn_last = forward_last_layer(x11.detach(), text, sd, mimic_fp16, ln1_out=A)
-        probs[:, k].sum().backward()
+        with torch.enable_grad():       # the reference runs Grad-CAM with autograd on whatever the caller's grad mode is
+            A = layer_norm(x11, sd[p + ".ln_1.weight"], sd[p + ".ln_1.bias"]).detach().requires_grad_(True)
+            probs, attn_last = forward_last_layer(x11.detach(), text, sd, mimic_fp16, ln1_out=A)
+            probs[:, k].sum().backward()
         # .cpu(): the reference's own device -> host round trips (activations_and_gradients.py:24,35)
         act = A.detach()[1:, 0, :].float().reshape(h, w, -1).permute(2, 0, 1).cpu().numpy()       # [768,h,w]
         grd = A.grad[1:, 0, :].float().reshape(h, w, -1).permute(2, 0, 1).cpu().numpy()

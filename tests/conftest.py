@@ -17,3 +17,13 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN
+
+
+@pytest.fixture(autouse=True)
+def _inference_tests_run_without_autograd(request):
+    """Everything except the training tests exercises the inference path: run it under torch.no_grad() (with grad mode on,
+    WeCLIP.forward takes the trainable-decoder path and returns tensors that carry an autograd graph)."""
+    import torch
+    needs_grad = request.module.__name__.rsplit(".", 1)[-1] in ("test_train_gpu", "test_training_gpu", "test_training_cpu")
+    with torch.set_grad_enabled(needs_grad):
+        yield

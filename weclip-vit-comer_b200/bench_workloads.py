@@ -297,10 +297,12 @@ class PseudoLabelVoc(MscFlipVoc):
         self.d2h = self.labels_h.numel() * 8
         self.launches = None
 
+    @torch.no_grad()       # the pseudo-label step itself (forward); the decoder's training backward is not part of cfg-2
     def step_device(self, record=False):
         self.model.iter_num = 20000            # RFM branch of clip_tool.py:152-175
         return self.model(self.imgs_d, self.names, mode="train")
 
+    @torch.no_grad()
     def step_e2e(self):
         img = self.imgs_h.to(self.dev, non_blocking=True)
         self.model.iter_num = 20000

@@ -233,6 +233,7 @@ class MscFlipEvaluator:
             return seg_pred[0], msc_pred[0], (cam[0] if cam is not None else None), msc[0]
         return None
 
+    @torch.no_grad()      # evaluation never differentiates: keeps WeCLIP on its fused inference kernels (no autograd tape)
     def process_batch(self, names: Sequence[str], inputs: torch.Tensor, labels: torch.Tensor, want_preds: bool = False):
         """B same-size dataset images per model call (the reference loops image by image; images are independent,
         so a (H,W) bucket is run as one [2B,3,H,W] forward per scale: B plain images followed by their B flipped
@@ -305,6 +306,7 @@ class MscFlipEvaluator:
         self._slot = (self._slot + 1) % len(self._slots)
         return slot
 
+    @torch.no_grad()
     def _graph_step(self, slot, ent):
         """The step as it is captured: every launch goes to the slot's streams, forked from / joined to its launch stream."""
         launch, side, acc = slot["launch"], slot["side"], slot["acc"]
