@@ -30,7 +30,7 @@ extern "C" {
 #define WC_ERR_WORKSPACE (-3)
 #define WC_ERR_UNSUPPORTED (-4)
 
-#define WC_ABI_VERSION 11
+#define WC_ABI_VERSION 12
 #define WC_PAR_MAX_DIL 8
 
 /* ABI version (bumped whenever a signature changes) and last error text. */
@@ -158,10 +158,13 @@ typedef struct wc_decoder_weights {         /* SegFormerHead (segformer_head.py:
  *   attn_avg  fp32 [n_attn(+slack), attn_imgs, L, L]  head-averaged attention (myAtt.py:323-326) of the LAST n_attn
  *             encoder blocks, oldest first, for the first attn_imgs images of the batch (0 = all N): the CAM path only
  *             runs for the images that have a name (model_attn_aff_voc.py:139); may be NULL when n_attn == 0
+ *   attn_sums fp64 [n_attn(+slack), attn_imgs] or NULL: sum of attn_avg[l][n][1:, 1:], accumulated by the kernel that writes
+ *             the map (the RFM layer score of clip_tool.py:158-160; saves wc_affinity_refine one pass over every map)
  * ---------------------------------------------------------------------------------------------- */
 size_t wc_encoder_workspace_bytes(int N, int H, int W);
 int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, int H, int W, void* taps, float* x_last,
-                   float* attn_avg, int n_attn, int attn_imgs, void* workspace, size_t workspace_bytes, void* stream);
+                   float* attn_avg, double* attn_sums, int n_attn, int attn_imgs, void* workspace, size_t workspace_bytes,
+                   void* stream);
 
 /* Decoder: 11 per-layer MLPs + concat + linear_fuse (segformer_head.py:69-80), attn_pred = sigmoid(F^T F)
  * (model_attn_aff_voc.py:134-137), 3 transformer blocks + linear_pred (TransDecoder.py:113-125).
@@ -196,12 +199,13 @@ int wc_attention_fwd(const void* q, const void* k, const void* vt, void* o, floa
  *   text_off_host int [N+1]      row offsets into text;  k_off_host int [N+1]  instance offsets (K_i = diff)
  *   cams       fp32 [sumK,h*w]   raw Grad-CAMs, ReLU'd and min-max normalised twice
  *   attn_last  fp32 [N,L,L]      head-averaged attention of block 12
+ *   attn_last_sum fp64 [N] or NULL  sum of attn_last[n][1:, 1:] (see wc_encoder_fwd)
  *   probs      fp32 [sumT] or NULL  softmax(logit_scale * cos) per image
  * ---------------------------------------------------------------------------------------------- */
 size_t wc_gradcam_workspace_bytes(int N, int h, int w, int total_inst, int max_k);
 int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int h, int wd, const float* text,
-               const int* text_off_host, const int* k_off_host, float* cams, float* attn_last, float* probs,
-               void* workspace, size_t workspace_bytes, void* stream);
+               const int* text_off_host, const int* k_off_host, float* cams, float* attn_last, double* attn_last_sum,
+               float* probs, void* workspace, size_t workspace_bytes, void* stream);
 
 /* The reference runs the out-projection of every attention block in fp16 (clip/myAtt.py:321), hence its autograd backward
  * too: with near-uniform class probabilities the gradient there (~1e-7) falls into fp16's subnormal range and the
@@ -219,14 +223,15 @@ int wc_gradcam_debug_offsets(int N, int h, int w, int total_inst, int max_k, siz
  * selection against attn_pred (use_rfm=1; nl = 6 VOC / 10 COCO) or plain mean of the nl maps (use_rfm=0,
  * nl = 8), compute_trans_mat (:64-80), scoremap2bbox box mask (clip/utils.py:115-142; box_thr 0.4 / 0.7) and
  * cam' = (T * mask) @ cam.
- *   attn fp32 [nl,N,L,L] (oldest first, block 12 last); attn_pred fp32 [N,P,P]; cams / cams_refined fp32 [sumK,P];
+ *   attn fp32 [nl,N,L,L] (oldest first, block 12 last); attn_sums fp64 [nl,N] = sum of attn[l][n][1:,1:] from the producers
+ *   (NULL: computed here with one more pass over the maps); attn_pred fp32 [N,P,P]; cams / cams_refined fp32 [sumK,P];
  *   box_masks fp32 [sumK,P] or NULL (exported for the parity tests).  box_thr is a double: the reference evaluates
  *   int(thr * max(uint8)) in float64 (clip/utils.py:118-121); 0.7f * 250 would give 174 instead of 175.
  *   rfm_sel fp32 [N,2,nl] or NULL (test hook): per image the 0/1 layer selection of clip_tool.py:161-165 and the margins
  *   d_l - mean(d) it was decided by.  The layer sums are accumulated in fp64 here; the reference's fp32 torch.sum over
  *   P^2 ~ 1e6 terms resolves ~0.1-0.25 at that magnitude, which is the size of the margins. */
 size_t wc_affinity_workspace_bytes(int N, int h, int w, int total_inst, int nl);
-int wc_affinity_refine(const float* attn, int nl, const float* attn_pred, int N, int h, int wd, int use_rfm,
+int wc_affinity_refine(const float* attn, int nl, const double* attn_sums, const float* attn_pred, int N, int h, int wd, int use_rfm,
                        const float* cams, const int* k_off_host, double box_thr, float* cams_refined,
                        float* box_masks, float* rfm_sel, void* workspace, size_t workspace_bytes, void* stream);
 

@@ -23,7 +23,7 @@ def _refine(attn_pp: np.ndarray, cams: np.ndarray, h: int, w: int, thr: float):
     attn, cams_d = attn.cuda(), torch.from_numpy(np.ascontiguousarray(cams, np.float32)).reshape(K, P).cuda()
     out, masks = torch.empty(K, P, device="cuda"), torch.empty(K, P, device="cuda")
     ws = torch.empty(L.wc_affinity_workspace_bytes(1, h, w, K, 1), dtype=torch.uint8, device="cuda")
-    rc = L.wc_affinity_refine(_lib.ptr(attn), 1, None, 1, h, w, 0, _lib.ptr(cams_d), _lib.int_array([0, K]),
+    rc = L.wc_affinity_refine(_lib.ptr(attn), 1, None, None, 1, h, w, 0, _lib.ptr(cams_d), _lib.int_array([0, K]),
                               ctypes.c_double(thr), _lib.ptr(out), _lib.ptr(masks), None, _lib.ptr(ws),
                               ctypes.c_size_t(ws.numel()), _lib.stream_ptr())
     _lib.check(rc, "wc_affinity_refine")

@@ -72,7 +72,7 @@ def refine_case(h, pk):
     ws = torch.empty(L.wc_affinity_workspace_bytes(N, h, h, N * K, nl), dtype=torch.uint8, device="cuda")
 
     def run():
-        rc = L.wc_affinity_refine(_lib.ptr(attn), nl, _lib.ptr(ap), N, h, h, 1, _lib.ptr(cams), _lib.int_array(k_off),
+        rc = L.wc_affinity_refine(_lib.ptr(attn), nl, None, _lib.ptr(ap), N, h, h, 1, _lib.ptr(cams), _lib.int_array(k_off),
                                   ctypes.c_double(0.4), _lib.ptr(out), None, None, _lib.ptr(ws), ctypes.c_size_t(ws.numel()),
                                   _lib.stream_ptr())
         _lib.check(rc, "wc_affinity_refine")

@@ -45,16 +45,20 @@ __global__ void __launch_bounds__(256) aff_layer_sums_kernel(const float* __rest
 __global__ void __launch_bounds__(256) aff_build_kernel(const float* __restrict__ attn, const float* __restrict__ ap,
                                                         const double* __restrict__ sums, float* __restrict__ Bm,
                                                         float* __restrict__ colz, int nl, int N, int L, int use_rfm,
-                                                        float* __restrict__ sel_out) {
+                                                        float* __restrict__ sel_out, int sums_layer_major) {
     __shared__ float wl[16];
     const int P = L - 1, img = blockIdx.y, r0 = blockIdx.x * 16, r1 = min(r0 + 16, P);
     if (threadIdx.x == 0) {
         if (use_rfm) {
-            // attn_diff_l = sum(seg_attn - W_l); keep layers with diff <= mean(diff)
+            // attn_diff_l = sum(seg_attn - W_l); keep layers with diff <= mean(diff).  sum(seg_attn) is the same for every
+            // layer and cancels in diff_l - mean(diff), so only the layer sums S_l matter: d_l - mean = mean(S) - S_l
+            // (sums: [img][nl+1] from aff_layer_sums_kernel, or [nl][N] accumulated by the head-mean kernel)
             float d[16], mean = 0.f;
-            const double sap = sums[(size_t)img * (nl + 1) + nl];
-            for (int l = 0; l < nl; ++l) { d[l] = (float)(sap - sums[(size_t)img * (nl + 1) + l]); mean += d[l]; }
-            mean /= (float)nl;
+            double sbar = 0.0;
+            for (int l = 0; l < nl; ++l) sbar += sums_layer_major ? sums[(size_t)l * N + img] : sums[(size_t)img * (nl + 1) + l];
+            sbar /= (double)nl;
+            for (int l = 0; l < nl; ++l)
+                d[l] = (float)(sbar - (sums_layer_major ? sums[(size_t)l * N + img] : sums[(size_t)img * (nl + 1) + l]));
             float cnt = 0.f;
             for (int l = 0; l < nl; ++l) { wl[l] = (d[l] <= mean) ? 1.f : 0.f; cnt += wl[l]; }
             if (sel_out && blockIdx.x == 0)        // test hook: which layers were kept, and the margins they were kept by
@@ -71,7 +75,8 @@ __global__ void __launch_bounds__(256) aff_build_kernel(const float* __restrict_
         float cs = 0.f;
         for (int i = r0; i < r1; ++i) {
             float v = 0.f;
-            for (int l = 0; l < nl; ++l) v = fmaf(wl[l], attn_row(attn, l, img, N, L, i)[j], v);
+            for (int l = 0; l < nl; ++l)
+                if (wl[l] != 0.f) v = fmaf(wl[l], attn_row(attn, l, img, N, L, i)[j], v);      // dropped layers are not read
             if (use_rfm) v *= ap[((size_t)img * P + i) * P + j];
             Bm[((size_t)img * P + i) * P + j] = v;
             cs += v;
@@ -88,8 +93,16 @@ __global__ void __launch_bounds__(256) aff_row_pass_kernel(const float* __restri
     const float* row = Bm + ((size_t)img * P + i) * P;
     const float* zz = z + (size_t)img * P;
     float s = 0.f;
-    for (int j = lane; j < P; j += 32) s += row[j] / zz[j];
-    s = warp_sum(s);
+    float s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int j = lane;
+    for (; j + 96 < P; j += 128) {          // four independent streams; 1/z by reciprocal + multiply (<= 1 ulp from the division)
+        s = fmaf(row[j], __frcp_rn(zz[j]), s);
+        s1 = fmaf(row[j + 32], __frcp_rn(zz[j + 32]), s1);
+        s2 = fmaf(row[j + 64], __frcp_rn(zz[j + 64]), s2);
+        s3 = fmaf(row[j + 96], __frcp_rn(zz[j + 96]), s3);
+    }
+    for (; j < P; j += 32) s = fmaf(row[j], __frcp_rn(zz[j]), s);
+    s = warp_sum((s + s1) + (s2 + s3));
     if (lane == 0) r[(size_t)img * P + i] = 1.f / s;
 }
 
@@ -192,7 +205,7 @@ __global__ void __launch_bounds__(256) tsym_row_kernel(const float* __restrict__
 #pragma unroll
     for (int k = 0; k < AFF_KMAX; ++k) acc[k] = 0.f;
     for (int j = lane; j < P; j += 32) {
-        const float b = row[j] / zz[j];
+        const float b = row[j] * __frcp_rn(zz[j]);
 #pragma unroll
         for (int k = 0; k < AFF_KMAX; ++k)
             if (k < kn) acc[k] = fmaf(b, x[(size_t)(k0 + k) * P + j], acc[k]);
@@ -299,7 +312,7 @@ extern "C" size_t wc_affinity_workspace_bytes(int N, int h, int w, int total_ins
            sizeof(double) * (size_t)N * (nl + 1) + 2048;
 }
 
-extern "C" int wc_affinity_refine(const float* attn, int nl, const float* attn_pred, int N, int h, int wd, int use_rfm,
+extern "C" int wc_affinity_refine(const float* attn, int nl, const double* attn_sums, const float* attn_pred, int N, int h, int wd, int use_rfm,
                                   const float* cams, const int* k_off_host, double box_thr, float* cams_refined,
                                   float* box_masks, float* rfm_sel, void* workspace, size_t workspace_bytes, void* stream) {
     WC_CHECK_ARG(attn && cams && k_off_host && cams_refined && workspace && nl >= 1 && nl <= 16);
@@ -322,13 +335,14 @@ extern "C" int wc_affinity_refine(const float* attn, int nl, const float* attn_p
     float* v0 = r + (size_t)N * P;
     float* v1 = v0 + (size_t)total * P;
     const size_t NP = (size_t)N * P;
-    if (use_rfm) {
+    if (use_rfm && !attn_sums) {      // no sums from the producers: one extra pass over the nl maps
         WC_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * N * (nl + 1), st));
-        aff_layer_sums_kernel<<<dim3(ceil_div(P, 32), nl + 1, N), 256, 0, st>>>(attn, attn_pred, sums, nl, N, L);
+        aff_layer_sums_kernel<<<dim3(ceil_div(P, 32), nl, N), 256, 0, st>>>(attn, attn_pred, sums, nl, N, L);
         WC_LAUNCH_CHECK();
     }
     WC_CUDA(cudaMemsetAsync(z, 0, sizeof(float) * NP, st));
-    aff_build_kernel<<<dim3(ceil_div(P, 16), N), 256, 0, st>>>(attn, attn_pred, sums, Bm, z, nl, N, L, use_rfm, rfm_sel);
+    aff_build_kernel<<<dim3(ceil_div(P, 16), N), 256, 0, st>>>(attn, attn_pred, attn_sums ? attn_sums : sums, Bm, z, nl, N, L, use_rfm, rfm_sel,
+                                                                attn_sums ? 1 : 0);
     WC_LAUNCH_CHECK();
     for (int round = 0; round < 3; ++round) {   // clip_tool.py:67-72
         if (round > 0) {

@@ -403,6 +403,7 @@ struct MeanArgs {
     int L, heads;
     const float* lse2;
     float* avg;
+    double* sums;      // optional [n_img]: += sum of avg[img][1:, 1:] (the RFM layer score, clip_tool.py:158-160)
 };
 
 __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __grid_constant__ CUtensorMap mapQ,
@@ -504,6 +505,18 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __gr
         // mean over heads, transposed through the warp's swizzled 32x32 block so that each store is one row x 32 keys
         const float inv_h = 1.f / (float)a.heads;
         const int row0 = qt * AT_BM + q * 32;
+        if (a.sums) {
+            // sum of this warp's part of avg[1:, 1:] (class-token row and column excluded), one fp64 atomic per warp: the
+            // RFM layer selection needs it and would otherwise re-read every map from HBM
+            float part = 0.f;
+            if (grow >= 1 && grow < a.L) {
+                const int key0 = kt * AT_BN + half * 64;
+#pragma unroll
+                for (int i = 0; i < 64; ++i) part += (key0 + i >= 1 && key0 + i < a.L) ? acc[i] : 0.f;
+            }
+            part = warp_sum(part);
+            if (lane == 0 && part != 0.f) atomicAdd(a.sums + img, (double)(part * inv_h));
+        }
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
             const int key = kt * AT_BN + half * 64 + c * 32 + lane;
@@ -820,13 +833,14 @@ int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, floa
 }
 
 int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* avg, int n_img, int heads, int L,
-                         cudaStream_t st) {
+                         cudaStream_t st, double* sums) {
     WC_CHECK_ARG(q && k && lse2 && avg && n_img > 0 && heads > 0 && L > 0 && n_img <= 65535);
     WC_SET_MAX_SMEM(attn_headmean_kernel, MeanSmem::TOTAL);
     CUtensorMap mq, mk;
     int rc = attn_maps(q, k, nullptr, n_img * heads, L, 0, AT_HD, &mq, &mk, nullptr);
     if (rc) return rc;
-    MeanArgs a{L, heads, lse2, avg};
+    if (sums) WC_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * n_img, st));
+    MeanArgs a{L, heads, lse2, avg, sums};
     dim3 grid(ceil_div(L, AT_BN), ceil_div(L, AT_BM), n_img);
     ProfScope prof(PK_SOFTMAX, 4.0 * n_img * (double)L * L, st);
     if (g_prof_on) prof_tag(L, n_img, heads, 1);

@@ -15,8 +15,9 @@ int launch_attention_fwd(const h16* q, const h16* k, const h16* v_or_vt, h16* o,
 
 // avg[n, i, j] = mean over heads of softmax(q k^T)[n, h, i, j] (myAtt.py:323-326), fp32 [N, L, L], each element written
 // once.  Needs lse2 from launch_attention_fwd.
+// sums (optional, [n_img] fp64, overwritten): sum of avg[n][1:, 1:] per image, accumulated while the tiles are in registers.
 int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* avg, int n_img, int heads, int L,
-                         cudaStream_t st);
+                         cudaStream_t st, double* sums = nullptr);
 
 // Grad-CAM attention backward reduced to column sums (see attention.cu / gradcam.cu headers).
 //   dOT: fp16 [n_inst*heads, 80, Lp] = rows 0..63 dO^T of the head, row 64 / 65 = -delta (hi / lo fp16 split), rest zero.

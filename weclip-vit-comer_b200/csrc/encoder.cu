@@ -32,7 +32,7 @@ int run_block(const wc_block_weights& w, const BlockBuffers& b, int n_img, int L
         if (b.attn_avg && (hd != 64 || !b.lse))
             return fail(WC_ERR_UNSUPPORTED, "%s: the head-mean map needs head_dim 64 and an lse buffer", __func__);
         if ((rc = launch_attention_fwd(b.q, b.k, hd == 64 ? b.v : b.vt, b.o, b.lse, n_img, heads, L, (int)Lp, hd, st))) return rc;
-        if (b.attn_avg && (rc = launch_attn_headmean(b.q, b.k, b.lse, b.attn_avg, b.attn_imgs > 0 ? b.attn_imgs : n_img, heads, L, st))) return rc;
+        if (b.attn_avg && (rc = launch_attn_headmean(b.q, b.k, b.lse, b.attn_avg, b.attn_imgs > 0 ? b.attn_imgs : n_img, heads, L, st, b.attn_sum))) return rc;
     } else {
         // S = q k^T (myAtt.py:56), fp32 [N*heads, L, Lp]
         {
@@ -128,7 +128,8 @@ extern "C" size_t wc_encoder_workspace_bytes(int N, int H, int W) {
 }
 
 extern "C" int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, int H, int W, void* taps_, float* x_last,
-                              float* attn_avg, int n_attn, int attn_imgs, void* workspace, size_t workspace_bytes, void* stream) {
+                              float* attn_avg, double* attn_sums, int n_attn, int attn_imgs, void* workspace,
+                              size_t workspace_bytes, void* stream) {
     WC_CHECK_ARG(w && img && taps_ && x_last && workspace && N > 0 && H >= 16 && W >= 16);
     WC_CHECK_ARG(n_attn >= 0 && n_attn <= 11 && (n_attn == 0 || attn_avg) && attn_imgs >= 0 && attn_imgs <= N);
     if (attn_imgs == 0) attn_imgs = N;
@@ -161,6 +162,7 @@ extern "C" int wc_encoder_fwd(const wc_vit_weights* w, const float* img, int N, 
         const int slot = i - (11 - n_attn);
         b.attn_avg = (slot >= 0) ? attn_avg + (size_t)slot * attn_imgs * L * L : nullptr;
         b.attn_imgs = attn_imgs;
+        b.attn_sum = (slot >= 0 && attn_sums) ? attn_sums + (size_t)slot * attn_imgs : nullptr;
         // tap i = fp16 copy of block i's output: blocks 0..9 add their MLP output into x in place (L2 reduction, no second
         // epilogue output), so the next block's ln_1 - which reads x anyway - writes the copy; block 10 writes its own
         b.tap_in = (i > 0) ? taps + (size_t)(i - 1) * M * E : nullptr;

@@ -40,6 +40,7 @@ struct BlockBuffers {
     h16* u;            // [M,4E]  QuickGELU(c_fc)
     h16* u_pre;        // optional [M,4E] pre-activation
     float* attn_avg;    // optional [N,L,L]
+    double* attn_sum = nullptr;   // optional [attn_imgs]: sum of attn_avg[n][1:,1:] (fused path only)
     h16* tap;          // optional h16 copy of x_out
     h16* tap_in;       // optional h16 copy of x_in, written by ln_1 (the previous block's tap when its c_proj adds in place)
 };

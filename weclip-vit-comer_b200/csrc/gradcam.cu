@@ -527,8 +527,8 @@ extern "C" int wc_gradcam_debug_offsets(int N, int h, int w, int total_inst, int
 }
 
 extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int h, int wd, const float* text,
-                          const int* text_off_host, const int* k_off_host, float* cams, float* attn_last, float* probs,
-                          void* workspace, size_t workspace_bytes, void* stream) {
+                          const int* text_off_host, const int* k_off_host, float* cams, float* attn_last,
+                          double* attn_last_sum, float* probs, void* workspace, size_t workspace_bytes, void* stream) {
     WC_CHECK_ARG(w && x11 && text && text_off_host && k_off_host && cams && attn_last && workspace);
     WC_CHECK_ARG(N > 0 && N <= GC_MAX_IMG && h > 0 && wd > 0);
     cudaStream_t st = as_stream(stream);
@@ -556,7 +556,7 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
         BlockBuffers b{};
         b.x_in = x11; b.x_mid = g.x1; b.x_out = g.x2;
         b.a = g.a; b.a_f32 = g.a32; b.q = g.q; b.k = g.k; b.v = g.v; b.vt = g.vt; b.lse = g.lse; b.o = g.o;   // fused attention
-        b.u = g.u; b.u_pre = g.upre; b.attn_avg = attn_last;
+        b.u = g.u; b.u_pre = g.upre; b.attn_avg = attn_last; b.attn_sum = attn_last_sum;
         if ((rc = run_block(w->blocks[11], b, N, L, E, GC_HEADS, st))) return rc;
     }
     // ---- pooled head + its Jacobian for every (image, class)

@@ -22,6 +22,7 @@
 #include "common.cuh"
 
 #include <math.h>
+#include <stdlib.h>
 #include <vector>
 
 namespace wc {
@@ -490,6 +491,220 @@ __global__ void __launch_bounds__(PT_THREADS, 2) par_iter_tile_kernel(const AffT
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Pipelined propagation step (fp16 affinity): persistent CTAs, one per SM, walk 64x16-pixel tiles.
+//   warp 8       weight producer: the 8 weights x 64 pixels of one (tile row, dilation) are ONE contiguous KB in the blocked
+//                layout; 16 lanes each issue a cp.async.bulk (TMA unit, no registers, no LSU issue slots) into a 3-stage
+//                ring of [16 rows][8][64] blocks, completion counted on the stage's mbarrier
+//   warps 9-15   tile producers: the NEXT tile's mask planes + 24-pixel halo (double-buffered) with cp.async, completion
+//                signalled through cp.async.mbarrier.arrive
+//   warps 0-7    consumers: thread = 4 pixels of one row; per dilation 8 LDS.64 weights + the aligned LDS.128 mask vectors,
+//                FFMA2 accumulation; they never wait on HBM latency themselves (the register-prefetch kernel above spent
+//                35 % of its stall samples on exactly that, ncu r02) and the tile fill of tile i+1 runs under tile i.
+// Shared memory: 2 x 3 planes x 28 KB + 3 x 16 KB ring + barriers = 216 KB.
+// ---------------------------------------------------------------------------------------------------
+constexpr int PP_TH = 16;
+constexpr int PP_SH = PP_TH + 2 * PT_HALO;                       // 64
+constexpr int PP_PLANE = PP_SH * PT_SW;                          // floats per plane
+constexpr int PP_NST = 3;
+constexpr int PP_STAGE_HALVES = PP_TH * 8 * PB;                  // fp16 elements per ring stage (16 KB)
+constexpr int PP_CONSUMERS = 256;
+constexpr int PP_FILL_WARPS = 7;
+constexpr int PP_THREADS = PP_CONSUMERS + 32 + 32 * PP_FILL_WARPS;
+constexpr size_t PP_SMEM = (size_t)2 * PT_KC * PP_PLANE * sizeof(float) + (size_t)PP_NST * PP_STAGE_HALVES * sizeof(__half) + 256 + 128;
+
+__device__ __forceinline__ uint32_t pp_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void pp_mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(pp_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void pp_mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(pp_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void pp_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pp_smem_u32(bar)), "r"(bytes) : "memory");
+}
+// A protocol bug must fault, never hang the GPU: trap after ~2 s of spinning.
+__device__ __forceinline__ void pp_mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = pp_smem_u32(bar);
+    uint32_t done = 0;
+    long long t0 = 0;
+    int spins = 0;
+    while (true) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (done) break;
+        if (++spins == 64) t0 = clock64();
+        if (spins > 64 && clock64() - t0 > 4000000000LL) {
+            printf("wc: PAR pipeline mbarrier timeout (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+            __trap();
+        }
+    }
+}
+__device__ __forceinline__ void pp_bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar, uint64_t pol) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(pp_smem_u32(dst)), "l"(src), "r"(bytes), "r"(pp_smem_u32(bar)), "l"(pol) : "memory");
+}
+
+struct PipeArgs {
+    int tiles_x, tiles_y, n_tiles;
+    int dbg;       // timing experiments only (WC_PAR_DBG): bit 0 = no weight copies, bit 1 = no tile fill (results are garbage)
+};
+
+template <int KC, int DD>
+__device__ __forceinline__ void pp_dilation(float (&acc)[KC][4], const float* sc, const __half* wrow) {
+    AffIO<__half>::Raw wr[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) wr[j] = *reinterpret_cast<const uint2*>(wrow + j * PB);
+    accumulate_dilation<__half, KC, PP_SH, DD>(acc, sc, wr);
+}
+
+template <int KC>
+__device__ __forceinline__ void pp_consume_tile(const float* planes, const __half* ring, uint64_t* w_full, uint64_t* w_empty,
+                                                int& g, int tx4, int ty, int lane, float (&acc)[KC][4]) {
+    const float* sc = planes + (ty + PT_HALO) * PT_SW + PT_HALO + 4 * tx4;
+#pragma unroll
+    for (int k = 0; k < KC; ++k) acc[k][0] = acc[k][1] = acc[k][2] = acc[k][3] = 0.f;
+#pragma unroll
+    for (int d = 0; d < 6; ++d) {
+        const int s = g % PP_NST;
+        pp_mbar_wait(&w_full[s], (g / PP_NST) & 1);
+        const __half* wrow = ring + (size_t)s * PP_STAGE_HALVES + ty * (8 * PB) + 4 * tx4;
+        if (d == 0) pp_dilation<KC, 1>(acc, sc, wrow);
+        else if (d == 1) pp_dilation<KC, 2>(acc, sc, wrow);
+        else if (d == 2) pp_dilation<KC, 4>(acc, sc, wrow);
+        else if (d == 3) pp_dilation<KC, 8>(acc, sc, wrow);
+        else if (d == 4) pp_dilation<KC, 12>(acc, sc, wrow);
+        else pp_dilation<KC, 24>(acc, sc, wrow);
+        __syncwarp();
+        if (lane == 0) pp_mbar_arrive(&w_empty[s]);
+        ++g;
+    }
+}
+
+__global__ void __launch_bounds__(PP_THREADS, 1) par_iter_pipe_kernel(const __half* __restrict__ aff, const float* __restrict__ in,
+                                                                       float* __restrict__ out, const __grid_constant__ TileArgs a,
+                                                                       const __grid_constant__ ParChunks ch,
+                                                                       const __grid_constant__ PipeArgs pa) {
+    extern __shared__ __align__(128) uint8_t pp_smem[];
+    float* planes = reinterpret_cast<float*>(pp_smem);                                                   // [2][PT_KC][PP_PLANE]
+    __half* ring = reinterpret_cast<__half*>(pp_smem + (size_t)2 * PT_KC * PP_PLANE * sizeof(float));      // [PP_NST][16][8][64]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(ring) + (size_t)PP_NST * PP_STAGE_HALVES * sizeof(__half));
+    uint64_t* w_full = bars;                    // [PP_NST]  weights of a (tile, dilation) have landed
+    uint64_t* w_empty = w_full + PP_NST;        // [PP_NST]  ... have been read by all 8 consumer warps
+    uint64_t* t_full = w_empty + PP_NST;        // [2]       mask planes of a tile are in shared memory
+    uint64_t* t_empty = t_full + 2;             // [2]       ... have been read by all 8 consumer warps
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int H = a.H, W = a.W;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < PP_NST; ++s) { pp_mbar_init(&w_full[s], 1); pp_mbar_init(&w_empty[s], 8); }
+        for (int b = 0; b < 2; ++b) { pp_mbar_init(&t_full[b], 32 * PP_FILL_WARPS); pp_mbar_init(&t_empty[b], 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const int per_chunk = pa.tiles_x * pa.tiles_y;
+    const size_t iplane = (size_t)H * a.in_pitch, oplane = (size_t)H * a.out_pitch;
+    const size_t arow = (size_t)a.wb * (48 * PB);
+
+    if (warp == 8) {
+        // ---- weight producer
+        const uint64_t pol = a.evict_first ? l2_evict_first_policy() : l2_evict_normal_policy();
+        int g = 0;
+        for (int w = blockIdx.x; w < pa.n_tiles; w += gridDim.x) {
+            const int c = w / per_chunk, r = w - c * per_chunk, tyi = r / pa.tiles_x, txi = r - tyi * pa.tiles_x;
+            const int y0 = tyi * PP_TH, rows = min(PP_TH, H - y0);
+            const __half* base = aff + ((size_t)ch.b[c] * H * a.wb + txi) * (48 * PB);
+            for (int d = 0; d < 6; ++d, ++g) {
+                const int s = g % PP_NST;
+                if (lane == 0) {
+                    pp_mbar_wait(&w_empty[s], ((g / PP_NST) & 1) ^ 1);
+                    if (pa.dbg & 1) pp_mbar_arrive(&w_full[s]);
+                    else pp_mbar_expect_tx(&w_full[s], (uint32_t)rows * 8 * PB * sizeof(__half));
+                }
+                __syncwarp();
+                if (lane < rows && !(pa.dbg & 1))
+                    pp_bulk_load(ring + (size_t)s * PP_STAGE_HALVES + lane * (8 * PB), base + (size_t)(y0 + lane) * arow + d * (8 * PB),
+                                 8 * PB * sizeof(__half), &w_full[s], pol);
+            }
+        }
+    } else if (warp > 8) {
+        // ---- tile producers (PP_FILL_WARPS warps: two could keep only ~10 B/clk of cp.async in flight): planes of tile i into
+        //      buffer i & 1
+        int i = 0;
+        const int pw = warp - 9;
+        for (int w = blockIdx.x; w < pa.n_tiles; w += gridDim.x, ++i) {
+            const int c = w / per_chunk, r = w - c * per_chunk, tyi = r / pa.tiles_x, txi = r - tyi * pa.tiles_x;
+            const int x0 = txi * PT_W, y0 = tyi * PP_TH, buf = i & 1, kc = ch.cnt[c];
+            pp_mbar_wait(&t_empty[buf], ((i >> 1) & 1) ^ 1);
+            float* tile = planes + (size_t)buf * PT_KC * PP_PLANE;
+            const float* src = in + (size_t)ch.ch0[c] * iplane;
+            if (lane < PT_SW / 4 && !(pa.dbg & 2)) {
+                const int gx = x0 - PT_HALO + 4 * lane;
+                const bool fast = a.in_vec && gx >= 0 && gx + 3 < W;
+                const int c0 = min(max(gx, 0), W - 1), c1 = min(max(gx + 1, 0), W - 1), c2 = min(max(gx + 2, 0), W - 1),
+                          c3 = min(max(gx + 3, 0), W - 1);
+                const int rows = kc * PP_SH;
+                for (int rk = pw; rk < rows; rk += PP_FILL_WARPS) {
+                    const int k = rk / PP_SH, rr = rk - k * PP_SH;
+                    const int gy = min(max(y0 - PT_HALO + rr, 0), H - 1);
+                    const float* rowp = src + (size_t)k * iplane + (size_t)gy * a.in_pitch;
+                    const uint32_t d32 = pp_smem_u32(tile + (size_t)k * PP_PLANE + (size_t)rr * PT_SW + 4 * lane);
+                    if (fast) {
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d32), "l"(rowp + gx) : "memory");
+                    } else {
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d32), "l"(rowp + c0) : "memory");
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d32 + 4), "l"(rowp + c1) : "memory");
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d32 + 8), "l"(rowp + c2) : "memory");
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d32 + 12), "l"(rowp + c3) : "memory");
+                    }
+                }
+            }
+            // arrives on t_full[buf] once every cp.async this thread has issued so far has completed (every lane arrives)
+            asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(pp_smem_u32(&t_full[buf])) : "memory");
+        }
+    } else {
+        // ---- consumers
+        const int tx4 = threadIdx.x & 15, ty = threadIdx.x >> 4;
+        int g = 0, i = 0;
+        for (int w = blockIdx.x; w < pa.n_tiles; w += gridDim.x, ++i) {
+            const int c = w / per_chunk, r = w - c * per_chunk, tyi = r / pa.tiles_x, txi = r - tyi * pa.tiles_x;
+            const int x = txi * PT_W + 4 * tx4, y = tyi * PP_TH + ty, buf = i & 1, kc = ch.cnt[c];
+            const float* tile = planes + (size_t)buf * PT_KC * PP_PLANE;
+            pp_mbar_wait(&t_full[buf], (i >> 1) & 1);
+            float acc[PT_KC][4];
+            if (kc == 1) {
+                float a1[1][4];
+                pp_consume_tile<1>(tile, ring, w_full, w_empty, g, tx4, ty, lane, a1);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) acc[0][e] = a1[0][e];
+            } else if (kc == 2) {
+                float a2[2][4];
+                pp_consume_tile<2>(tile, ring, w_full, w_empty, g, tx4, ty, lane, a2);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { acc[0][e] = a2[0][e]; acc[1][e] = a2[1][e]; }
+            } else {
+                pp_consume_tile<3>(tile, ring, w_full, w_empty, g, tx4, ty, lane, acc);
+            }
+            __syncwarp();
+            if (lane == 0) pp_mbar_arrive(&t_empty[buf]);             // the planes may be overwritten by tile i+2
+            if (x < W && y < H) {
+                float* op = out + (size_t)ch.ch0[c] * oplane + (size_t)y * a.out_pitch + x;
+#pragma unroll
+                for (int k = 0; k < PT_KC; ++k) {
+                    if (k < kc) {
+                        if (a.out_vec && x + 3 < W) {
+                            *reinterpret_cast<float4*>(op + (size_t)k * oplane) = make_float4(acc[k][0], acc[k][1], acc[k][2], acc[k][3]);
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e)
+                                if (x + e < W) op[(size_t)k * oplane + e] = acc[k][e];
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
 // Affinity build on a 64x24 tile: the 3 image planes + halo live in shared memory (96.8 KB, 2 CTAs per SM); 192 threads,
 // each walks 8 pixels (lanes = consecutive x: conflict-free scalar LDS), TWO passes over the 48 compile-time neighbour
 // offsets: (1) sum and sum of squares of d = v - centre per channel -> unbiased variance (shifted two-moment form: exact
@@ -573,9 +788,34 @@ __global__ void argmax_lut_kernel(const float* __restrict__ masks, const int64_t
     labels[(size_t)b * hw + i] = lut[ch0 + arg];
 }
 
+// fp16 propagation kernel: 0 = register-prefetch tile kernel (default), 1 = the TMA-pipelined persistent kernel (WC_PAR_PIPE=1).
+// Measured on B200 (16 x 512^2, Kc = 3 / 2, one step): register-prefetch 129 / 93 us; pipelined 175 / 136 us — its tile fill
+// (86 KB of 16-byte cp.async per 64x16 tile from 7 warps) is not hidden behind the 8 consumer warps' 96 us of LDS + FFMA2
+// work, and with the fill removed altogether it only ties (129 us).  Kept selectable as the measured alternative.
+static int g_par_pipe = -1;
+
+static int launch_iter_pipe(const __half* aff, const float* src, float* dst, const TileArgs& ta, const ParChunks& chunks, int n,
+                            cudaStream_t st) {
+    WC_SET_MAX_SMEM(par_iter_pipe_kernel, PP_SMEM);
+    PipeArgs pa;
+    pa.tiles_x = ceil_div(ta.W, PT_W); pa.tiles_y = ceil_div(ta.H, PP_TH); pa.n_tiles = pa.tiles_x * pa.tiles_y * n;
+    { const char* e = getenv("WC_PAR_DBG"); pa.dbg = e ? atoi(e) : 0; }
+    int dev = 0, sms = 148;
+    WC_CUDA(cudaGetDevice(&dev));
+    WC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int grid = pa.n_tiles < sms ? pa.n_tiles : sms;
+    par_iter_pipe_kernel<<<grid, PP_THREADS, PP_SMEM, st>>>(aff, src, dst, ta, chunks, pa);
+    WC_LAUNCH_CHECK();
+    return WC_OK;
+}
+
 template <typename AffT>
 static int launch_iter_tile(const AffT* aff, const float* src, float* dst, const TileArgs& ta, const ParChunks& chunks,
                             int n, int max_cnt, cudaStream_t st) {
+    if (sizeof(AffT) == 2) {
+        if (g_par_pipe < 0) { const char* e = getenv("WC_PAR_PIPE"); g_par_pipe = (e && e[0] == '1') ? 1 : 0; }
+        if (g_par_pipe) return launch_iter_pipe(reinterpret_cast<const __half*>(aff), src, dst, ta, chunks, n, st);
+    }
     constexpr int PLANE = (PT_TH + 2 * PT_HALO) * PT_SW * (int)sizeof(float);
     WC_SET_MAX_SMEM(par_iter_tile_kernel<AffT>, PT_KC * PLANE);
     dim3 grid(ceil_div(ta.W, PT_W), ceil_div(ta.H, PT_TH), n);

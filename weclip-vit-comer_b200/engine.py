@@ -154,9 +154,12 @@ class Engine:
         slots = attn_slots if attn_slots is not None else n_attn
         n_ai = N if attn_imgs is None else int(attn_imgs)
         attn = torch.empty(max(slots, 1), n_ai, Lt, Lt, dtype=torch.float32, device=self.device) if slots else None
+        # per (map, image) sum of attn[l][n][1:, 1:], accumulated by the kernel that writes the map (RFM layer score)
+        self.last_attn_sums = torch.zeros(max(slots, 1), n_ai, dtype=torch.float64, device=self.device) if slots else None
         ws = self._workspace("enc", L.wc_encoder_workspace_bytes(N, H, W))
         rc = L.wc_encoder_fwd(byref(self.vit), _lib.ptr(img), N, H, W, _lib.ptr(taps), _lib.ptr(x_last),
-                              _lib.ptr(attn), n_attn, n_ai, _lib.ptr(ws), c_size_t(ws.numel()), _lib.stream_ptr())
+                              _lib.ptr(attn), _lib.ptr(self.last_attn_sums), n_attn, n_ai, _lib.ptr(ws), c_size_t(ws.numel()),
+                              _lib.stream_ptr())
         _lib.check(rc, "wc_encoder_fwd")
         return taps, x_last, attn
 
@@ -174,7 +177,8 @@ class Engine:
         return seg, attn_pred, fts
 
     def gradcam(self, x_last: torch.Tensor, N: int, h: int, w: int, text: torch.Tensor, text_off: Sequence[int],
-                k_off: Sequence[int], attn_last_out: Optional[torch.Tensor] = None, want_probs: bool = False):
+                k_off: Sequence[int], attn_last_out: Optional[torch.Tensor] = None, want_probs: bool = False,
+                attn_last_sum: Optional[torch.Tensor] = None):
         """forward_last_layer + Grad-CAM for every (image, class).  text fp32 [sumT,512] (per image: its K fg rows
         then the bg rows).  Returns (cams fp32 [sumK,h,w], attn_last fp32 [N,L,L], probs|None)."""
         L = _lib.lib()
@@ -189,13 +193,14 @@ class Engine:
         probs = torch.empty(int(text_off[-1]), dtype=torch.float32, device=self.device) if want_probs else None
         ws = self._workspace("gc", L.wc_gradcam_workspace_bytes(N, h, w, total, max_k))
         rc = L.wc_gradcam(byref(self.vit), _lib.ptr(x_last), N, h, w, _lib.ptr(text), _lib.int_array(text_off),
-                          _lib.int_array(k_off), _lib.ptr(cams), _lib.ptr(attn_last), _lib.ptr(probs),
+                          _lib.int_array(k_off), _lib.ptr(cams), _lib.ptr(attn_last), _lib.ptr(attn_last_sum), _lib.ptr(probs),
                           _lib.ptr(ws), c_size_t(ws.numel()), _lib.stream_ptr())
         _lib.check(rc, "wc_gradcam")
         return cams, attn_last, probs
 
     def affinity_refine(self, attn: torch.Tensor, nl: int, attn_pred: torch.Tensor, N: int, h: int, w: int,
-                        use_rfm: bool, cams: torch.Tensor, k_off: Sequence[int], box_thr: float, want_masks=False):
+                        use_rfm: bool, cams: torch.Tensor, k_off: Sequence[int], box_thr: float, want_masks=False,
+                        attn_sums: Optional[torch.Tensor] = None):
         """clip_tool.py:152-191.  attn fp32 [nl,N,L,L]; returns (cams_refined [sumK,h,w], box masks|None); with want_masks the
         RFM layer selection + margins [N,2,nl] are kept in ``self.last_rfm_sel`` (test hook)."""
         L = _lib.lib()
@@ -205,7 +210,8 @@ class Engine:
         sel = torch.zeros(N, 2, nl, dtype=torch.float32, device=self.device) if want_masks else None
         self.last_rfm_sel = sel
         ws = self._workspace("aff", L.wc_affinity_workspace_bytes(N, h, w, total, nl))
-        rc = L.wc_affinity_refine(_lib.ptr(attn), nl, _lib.ptr(attn_pred), N, h, w, int(use_rfm), _lib.ptr(cams),
+        assert attn_sums is None or (attn_sums.dtype == torch.float64 and attn_sums.shape[0] >= nl and attn_sums.shape[1] == N)
+        rc = L.wc_affinity_refine(_lib.ptr(attn), nl, _lib.ptr(attn_sums), _lib.ptr(attn_pred), N, h, w, int(use_rfm), _lib.ptr(cams),
                                   _lib.int_array(k_off), c_double(box_thr), _lib.ptr(out), _lib.ptr(masks),
                                   _lib.ptr(sel), _lib.ptr(ws), c_size_t(ws.numel()), _lib.stream_ptr())
         _lib.check(rc, "wc_affinity_refine")

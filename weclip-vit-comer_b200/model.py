@@ -282,9 +282,11 @@ class WeCLIP(nn.Module):
         # the text rows are gathered on the device from a cached [fg; bg] table with the index vector of prepare()
         table, _, _ = self._text_table(eng.device)
         text = table.index_select(0, m.rows)
-        cams, _, _ = eng.gradcam(x_last, n_cam, h, w, text, m.text_off, m.k_off, attn_last_out=attn[nl - 1])
+        sums = eng.last_attn_sums
+        cams, _, _ = eng.gradcam(x_last, n_cam, h, w, text, m.text_off, m.k_off, attn_last_out=attn[nl - 1],
+                                 attn_last_sum=sums[nl - 1])
         refined, bmasks = eng.affinity_refine(attn, nl, attn_pred, n_cam, h, w, m.require_seg_trans, cams, m.k_off,
-                                              cfg["box_thr"], want_masks=self.keep_intermediates)
+                                              cfg["box_thr"], want_masks=self.keep_intermediates, attn_sums=sums)
         if self.keep_intermediates:
             self.last = dict(cams=cams, box_masks=bmasks, refined=refined, k_off=m.k_off, ids=m.ids_all,
                              rfm_sel=eng.last_rfm_sel)
