@@ -8,6 +8,10 @@ from weclip_b200.bench_workloads import WORKLOADS, prof_summary
 def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "mscflip"
     wl = WORKLOADS[name](0, torch.device("cuda", 0))
+    ev = getattr(wl, "ev", None)
+    if ev is not None:           # every kernel alone on the device, launched eagerly (the profiler brackets launches)
+        ev.overlap_scales = False
+        ev.use_graphs = False
     for _ in range(2):
         wl.step_device()
     torch.cuda.synchronize()

@@ -204,7 +204,20 @@ __global__ void __launch_bounds__(256) tsym_row_kernel(const float* __restrict__
     float acc[AFF_KMAX];
 #pragma unroll
     for (int k = 0; k < AFF_KMAX; ++k) acc[k] = 0.f;
-    for (int j = lane; j < P; j += 32) {
+    // four independent column groups per trip (loads of the next groups in flight under the FMAs of the first)
+    int j = lane;
+    for (; j + 96 < P; j += 128) {
+        float b[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) b[u] = row[j + 32 * u] * __frcp_rn(zz[j + 32 * u]);
+#pragma unroll
+        for (int k = 0; k < AFF_KMAX; ++k)
+            if (k < kn) {
+                const float* xk = x + (size_t)(k0 + k) * P + j;
+                acc[k] = fmaf(b[0], xk[0], fmaf(b[1], xk[32], fmaf(b[2], xk[64], fmaf(b[3], xk[96], acc[k]))));
+            }
+    }
+    for (; j < P; j += 32) {
         const float b = row[j] * __frcp_rn(zz[j]);
 #pragma unroll
         for (int k = 0; k < AFF_KMAX; ++k)

@@ -350,7 +350,8 @@ class MscFlipEvaluator:
         launch.synchronize()
         self._hist.copy_(saved)
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g, pool=slot["pool"], stream=launch):
+        # thread_local: other threads of the process (the NCCL watchdog polls events) must not invalidate the capture
+        with torch.cuda.graph(g, pool=slot["pool"], stream=launch, capture_error_mode="thread_local"):
             self._graph_step(slot, ent)
         ent["graph"] = g
         self._graphs[key] = ent
