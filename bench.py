@@ -229,14 +229,16 @@ def run_reference(args, rank, world):
     dt = time.perf_counter() - t0
     v = statistics.mean(vals)
     cfg = _config(cls, world)        # the same keys and values as our arm's line
-    line = {"impl": "reference", "metric": METRIC, "value": round(v, 4), "unit": "images/s", "n_gpus": args.gpus,
+    unit = getattr(cls, "unit", "images/s")
+    kind = getattr(cls, "cpu_kind", "port")
+    line = {"impl": "reference", "metric": getattr(cls, "metric", METRIC), "value": round(v, 4), "unit": unit, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * dt / args.steps, 2),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": cfg,
             "note": "one CPU process on rank 0 using all host cores; not multiplied by --gpus",
-            "cpu_baseline": {"value": round(v, 4), "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
-                             "sample": sample},
-            "e2e": {"value": round(v, 4), "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            "cpu_baseline": {"value": round(v, 4), "unit": unit, "cores": getattr(cls, "cpu_cores", None) or torch.get_num_threads(),
+                             "kind": kind, "sample": sample},
+            "e2e": {"value": round(v, 4), "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
@@ -362,18 +364,21 @@ def main():
 
     if rank == 0:
         units = wl.units * world * args.steps
+        unit = getattr(wl, "unit", "images/s")
         line = {
-            "metric": METRIC, "value": round(units / (ms_dev * 1e-3), 2), "unit": "images/s", "n_gpus": world,
+            "metric": getattr(wl, "metric", METRIC), "value": round(units / (ms_dev * 1e-3), 2), "unit": unit, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_dev / args.steps, 4),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": getattr(wl, "dtype", "f32"),
             "data": "synthetic (seeded images / CAMs / random-init weights; no datasets or checkpoints offline)",
             "config": _config(wl, world),
             "clocks": clocks,
-            "e2e": {"value": round(units / (ms_e2e * 1e-3), 2), "unit": "images/s",
+            "e2e": {"value": round(units / (ms_e2e * 1e-3), 2), "unit": unit,
                     "h2d_bytes_per_step": wl.h2d, "d2h_bytes_per_step": wl.d2h},
             "gpu_launches": int(wl.launches) * args.steps,
             "roofline": wl.roofline(peaks),
         }
+        if hasattr(wl, "graphs"):
+            line["config"]["cuda_graphs"] = bool(wl.graphs)
         if ms_live is not None:
             line["value_live_outputs"] = round(units / (ms_live * 1e-3), 2)
             line["value_live_outputs_note"] = ("same step, cam_passes='live': 1 CAM/PAR pass per dataset image instead of the "
@@ -402,8 +407,9 @@ def main():
         if world == 1:
             torch.set_num_threads(os.cpu_count() or 1)
             v, sample = wl.cpu_sample()
-            line["cpu_baseline"] = {"value": round(v, 4), "unit": "images/s", "cores": torch.get_num_threads(),
-                                    "kind": "port", "sample": sample}
+            line["cpu_baseline"] = {"value": round(v, 4), "unit": unit,
+                                    "cores": getattr(wl, "cpu_cores", None) or torch.get_num_threads(),
+                                    "kind": getattr(wl, "cpu_kind", "port"), "sample": sample}
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()

@@ -147,3 +147,40 @@ def test_dropout2d_masks_whole_channels_when_training():
     _, _, ap3 = model(img.cuda(), names)
     _, _, ap4 = model(img.cuda(), names)
     assert torch.equal(ap3, ap4) and ap3.requires_grad
+
+
+def test_graphed_train_step_follows_the_eager_step():
+    """train.TrainStep: the CUDA-graph replay of the optimisation step (first batch eager + capture, then replays with refreshed
+    inputs and label tables) against the same steps launched eagerly on a second model: same losses, same weights."""
+    from weclip_b200.train import TrainStep
+    torch.manual_seed(0)
+    runs = []
+    for use_graphs in (False, True):
+        model, sd, img, names = _setup(2, 96, 112, 21)
+        model.decoder_fts_fuse.dropout.p = 0.0
+        opt = torch.optim.AdamW(model.get_param_groups()[3], lr=torch.tensor(1e-3, device="cuda"), weight_decay=0.01,
+                                capturable=True)
+        step = TrainStep(model, opt, radius=2, use_graphs=use_graphs)
+        assert step.use_graphs == use_graphs
+        losses = []
+        for i in range(4):
+            model.iter_num = 20000
+            x = (img + 0.01 * i).cuda()                     # new pixels every step: the replay must see the refreshed input
+            losses.append(float(step(x, names)))
+        runs.append((losses, {k: v.detach().clone() for k, v in model.named_parameters()}, step))
+    (l0, p0, _), (l1, p1, st) = runs
+    assert st.graph_captures == 1 and st.graph_replays == 3
+    assert len(set(round(v, 4) for v in l1)) > 1            # the loss moves: the optimiser step inside the graph is live
+    for a, b in zip(l0, l1):
+        assert abs(a - b) < 2e-3 * abs(a), (l0, l1)
+    for k in p0:
+        d = (p0[k] - p1[k]).abs().max().item()
+        assert d <= 4 * 2e-3 + 1e-4, (k, d)                 # Adam: an element whose gradient is rounding noise may move 2 lr apart per step
+        # (the key third of every in_proj_bias has an exactly zero gradient: Adam moves those elements by +-lr per step on rounding
+        # noise alone, see the test above)
+        assert (p0[k] - p1[k]).abs().mean().item() < (3e-3 if k.endswith("in_proj_bias") else 4e-4), k
+    # an optimiser without device-side state cannot be captured: the step then runs eagerly
+    model, sd, img, names = _setup(1, 96, 112, 22)
+    plain = TrainStep(model, torch.optim.AdamW(model.get_param_groups()[3], lr=1e-3), use_graphs=True)
+    assert plain.use_graphs is False
+    assert torch.isfinite(plain(img.cuda(), names))

@@ -331,4 +331,211 @@ class PseudoLabelVoc(MscFlipVoc):
                             "oracle port of WeCLIP.forward(mode='train'), torch CPU fp32")
 
 
-WORKLOADS = {"mscflip": MscFlipVoc, "mscflip_coco": MscFlipCoco, "cfg2": PseudoLabelVoc}
+class TrainStepVoc(PseudoLabelVoc):
+    """ONE optimisation step of the reference's training loop (scripts/dist_clip_voc.py:238-267) at its own
+    configuration (configs/voc_attn_reg.yaml: samples_per_gpu 4, crop 320, AdamW lr 2e-4 / wd 0.01): WeCLIP.forward in train mode
+    under autograd (frozen encoder + CAM / refinement / PAR pseudo-labels on the inference kernels, trainable decoder through
+    train.DecoderFunction), F.interpolate of the logits, affinity + segmentation loss on the device (losses.py), backward through
+    the decoder (tcgen05 dgrad / wgrad GEMMs + train.cu), AdamW step (torch's fused element-wise optimiser: plumbing).
+    Unit = one crop."""
+    name = ("train: scripts/dist_clip_voc.py optimisation step, batch 4 at 320x320 crop (samples_per_gpu 4), 21 classes: forward "
+            "mode='train' (RFM branch) + pseudo-labels + aff / seg loss + decoder backward + AdamW")
+    metric = "WeCLIP decoder training step crops/sec"
+    unit = "crops/s"
+    BATCH = 4
+    units = BATCH
+    l2_note = ("4 crops: 26 MB of fp16 MLP activations per encoder block, 39 MB of PAR affinities; smaller than L2, as the "
+               "reference's own step is; L2 is not flushed between steps")
+
+    def __init__(self, rank: int, device):
+        super().__init__(rank, device)
+        from .train import TrainStep
+        self.graphs = os.environ.get("WC_BENCH_GRAPHS", "1") != "0"
+        # optimiser state on the device (capturable) with a tensor learning rate: the whole step can live in a CUDA graph
+        self.opt = torch.optim.AdamW(self.model.get_param_groups()[3], lr=torch.tensor(2e-4, device=device), weight_decay=0.01,
+                                     betas=(0.9, 0.999), capturable=True)
+        self.step = TrainStep(self.model, self.opt, radius=8, aff_weight=0.1, use_graphs=self.graphs)
+        self.loss_h = torch.zeros(1).pin_memory()
+        self.d2h = 4
+
+    def _train_step(self, img):
+        self.model.iter_num = 20000                                            # RFM branch of clip_tool.py:152-175
+        return self.step(img, self.names)
+
+    def step_device(self, record=False):
+        return self._train_step(self.imgs_d)
+
+    def profile(self, steps: int):
+        on, self.step.use_graphs = self.step.use_graphs, False                 # the profiler brackets launches, not graph nodes
+        try:
+            return super().profile(steps)
+        finally:
+            self.step.use_graphs = on
+
+    def step_e2e(self):
+        loss = self._train_step(self.imgs_h.to(self.dev, non_blocking=True))
+        self.loss_h.copy_(loss.reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self.loss_h
+
+    def cpu_sample(self, n_img=2):
+        import torch.nn.functional as F
+        from oracle import weclip_oracle as O
+        n_img = min(n_img, 2)
+        img = self.imgs_h[:n_img].clone()
+        labs = [np.asarray(l) for l in self.labs[:n_img]]
+        keys = [k for k in self.sd if k.startswith("decoder.") or k.startswith("decoder_fts_fuse.")]
+        sd = {k: v.clone() for k, v in self.sd.items()}
+        leaves = {k: sd[k].float().clone().requires_grad_(True) for k in keys}
+        sd.update(leaves)
+        opt = torch.optim.AdamW(list(leaves.values()), lr=2e-4, weight_decay=0.01)
+        h = w = self.H // 16
+        t0 = time.perf_counter()
+        with torch.no_grad():        # pseudo-labels (encoder, Grad-CAM re-enables grad itself, refinement, PAR)
+            _, cam, _ = O.weclip_forward(img, labs, self.sd, self.fg, self.bg, mode="train", iter_num=20001, dataset=self.dataset)
+            taps, _ = O.encode_image(img, self.sd)
+        cam = torch.as_tensor(np.asarray(cam)).long()
+        fts = O.decoder_fts_fuse([t.detach() for t in taps], sd, h, w)
+        seg = O.decoder(fts, sd)
+        attn_pred = O.attn_pred_from_fts(fts)
+        segs = F.interpolate(seg, size=cam.shape[1:], mode="bilinear", align_corners=False)
+        aff_label = O.affinity_label(cam, O.mask_by_radius(h, w, 8), 255)
+        pos, neg = aff_label == 1, aff_label == 0
+        attn_loss = 0.5 * (1 - attn_pred)[pos].sum() / (pos.sum() + 1) + 0.5 * attn_pred[neg].sum() / (neg.sum() + 1)
+        nll = -torch.log_softmax(segs, dim=1).gather(1, cam.clamp(0, self.n_classes - 1).unsqueeze(1)).squeeze(1)
+        valid = cam != 255
+        bgm, fgm = valid & (cam == 0), valid & (cam != 0)
+        loss = 0.5 * (nll[bgm].sum() / bgm.sum().clamp_min(1) + nll[fgm].sum() / fgm.sum().clamp_min(1)) + 0.1 * attn_loss
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        dt = time.perf_counter() - t0
+        return n_img / dt, (f"{n_img} of the step's {self.BATCH} crops: oracle port of the same step (forward incl. pseudo-labels; the "
+                            "frozen encoder runs twice because the oracle's forward does not return its taps; decoder forward + "
+                            "torch autograd backward + AdamW), torch CPU fp32")
+
+
+class InputPipelineVoc:
+    """the dataset side of the evaluation loop (datasets/voc.py:25-95: PIL.Image.open -> np.asarray ->
+    normalize_img -> transpose): baseline JPEGs of VOC-like sizes (4:2:0, quality 90) -> fp32 [3,H,W] on the device.
+    `value`: Huffman-decoded coefficient blocks already resident in HBM (the device half: dequantise + islow IDCT, fancy
+    up-sampling, fixed-point colour conversion, fp64-exact normalise); `e2e`: compressed bytes in host memory -> host marker
+    parser + Huffman decoder (C, one thread) -> pinned coefficients -> H2D -> device half -> one pixel read back.
+    Unit = one image."""
+    name = "io: VOC12SegDataset JPEG decode + normalise, 16 baseline 4:2:0 JPEGs of VOC-like sizes (long side 500), quality 90"
+    metric = "JPEG decode + normalise images/sec"
+    cpu_kind = "reference"      # PIL / libjpeg + numpy is the reference's own code path for this row
+    cpu_cores = 2               # test_msc_flip_voc.py:36 DataLoader(num_workers=2); our host half uses two threads as well
+    host_threads = 2
+    units = 16
+    dtype = "i16/u8"
+    cam_passes_per_image = 0
+    l2_note = "16 images: 18 MB of coefficients + 36 MB of fp32 output per step (smaller than L2; not flushed)"
+
+    def __init__(self, rank: int, device):
+        from . import dataio
+        self.dev, self.dataio = device, dataio
+        self.streams = self._make_streams(500 + rank, self.units)
+        self.infos, self.coef_h, self.coef_d = [], [], []
+        for data in self.streams:
+            info, coef = dataio.jpeg_entropy_decode(data)
+            self.infos.append(info); self.coef_h.append(coef); self.coef_d.append(coef.to(device))
+        L = _lib.lib()
+        self.out = [torch.empty(3, i.height, i.width, dtype=torch.float32, device=device) for i in self.infos]
+        self.ws = [torch.empty(int(L.wc_jpeg_workspace_bytes(ctypes.byref(i))), dtype=torch.uint8, device=device) for i in self.infos]
+        self.mean = (ctypes.c_double * 3)(*dataio.IMAGENET_MEAN)
+        self.std = (ctypes.c_double * 3)(*dataio.IMAGENET_STD)
+        self.h2d = sum(c.numel() * 2 for c in self.coef_h)
+        self.d2h = 4 * self.units
+        self.px = sum(i.height * i.width for i in self.infos)
+        self.pix_h = torch.zeros(self.units).pin_memory()
+        self.launches = 0
+        self._ms_dev = None
+
+    @staticmethod
+    def _make_streams(seed, n):
+        """n synthetic photographs-like images (smooth structure + sensor noise) of VOC-like sizes as baseline 4:2:0 JPEGs."""
+        import io
+        from PIL import Image
+        rng = np.random.default_rng(seed)
+        out = []
+        for i, (H, W) in enumerate(synth.draw_voc_like_sizes(rng, n)):
+            y, x = np.mgrid[0:H, 0:W]
+            base = np.stack([127 + 100 * np.sin(x / 37.0 + i), 127 + 100 * np.cos(y / 29.0 - i), (x + y) % 256], -1)
+            img = np.clip(base + rng.normal(0, 12, (H, W, 3)), 0, 255).astype(np.uint8)
+            buf = io.BytesIO()
+            Image.fromarray(img).save(buf, format="JPEG", quality=90, subsampling=2)
+            out.append(buf.getvalue())
+        return out
+
+    def _reconstruct(self, i, coef):
+        L = _lib.lib()
+        rc = L.wc_jpeg_reconstruct(ctypes.byref(self.infos[i]), _lib.ptr(coef), ctypes.c_void_p(0), _lib.ptr(self.out[i]), self.mean,
+                                   self.std, _lib.ptr(self.ws[i]), ctypes.c_size_t(self.ws[i].numel()), _lib.stream_ptr())
+        _lib.check(rc, "wc_jpeg_reconstruct")
+
+    def step_device(self, record=False):
+        for i in range(self.units):
+            self._reconstruct(i, self.coef_d[i])
+
+    def step_e2e(self):
+        if not hasattr(self, "_pool"):
+            from concurrent.futures import ThreadPoolExecutor
+            self._pool = ThreadPoolExecutor(self.host_threads)
+        # host half on `host_threads` threads (the C decoder runs without the GIL), into a pinned ring reused once the step has synced
+        futs = [self._pool.submit(self.dataio.jpeg_entropy_decode, data, True, self.coef_h[i]) for i, data in enumerate(self.streams)]
+        for i, f in enumerate(futs):
+            info, coef = f.result()
+            self._reconstruct(i, coef.to(self.dev, non_blocking=True))
+            self.pix_h[i:i + 1].copy_(self.out[i][0, 0, :1], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self.pix_h
+
+    def profile(self, steps: int):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            self.step_device()
+        e1.record(); torch.cuda.synchronize()
+        self._ms_dev = e0.elapsed_time(e1) / steps
+        self.launches = 3 * self.units          # IDCT (all components), up-sample + colour, normalise: per image
+
+    def roofline(self, peaks):
+        # algorithmic bytes per image (4:2:0): coefficients 2 B x 1.5 samples / px in, u8 planes 1.5 B / px written and read back by
+        # the colour pass, fp32 [3,H,W] out
+        by = self.px * (2 * 1.5 + 1.5 + 1.5 + 12)
+        a = by / (self._ms_dev * 1e-3) / 1e9
+        return {"bound": "hbm", "kernel": "jpeg_idct + jpeg_color (wc_jpeg_reconstruct)", "achieved": round(a, 1),
+                "peak": peaks["hbm_gbs"], "peak_source": peaks["source"] + " (copy)", "unit": "GB/s",
+                "frac": round(a / peaks["hbm_gbs"], 4), "traffic": None,
+                "note": "18 B per pixel (4:2:0): 3 B coefficients + 3 B planes + 12 B fp32 output; images of ~0.19 MP each are "
+                        "launch-bound (3 launches of a few microseconds per image)"}
+
+    @classmethod
+    def cpu(cls):
+        return cls.__new__(cls)
+
+    def cpu_sample(self, n_img=16):
+        import io
+        from PIL import Image
+        if not hasattr(self, "streams"):
+            self.streams = self._make_streams(500, self.units)
+        mean = np.array([123.675, 116.28, 103.53]); std = np.array([58.395, 57.12, 57.375])
+        from concurrent.futures import ThreadPoolExecutor
+        reps = 20
+
+        def load(data):
+            arr = np.asarray(Image.open(io.BytesIO(data)).convert("RGB")).astype(np.float32)
+            return np.ascontiguousarray(np.transpose((arr - mean) / std, (2, 0, 1)))
+        with ThreadPoolExecutor(self.cpu_cores) as pool:
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                list(pool.map(load, self.streams))
+            dt = time.perf_counter() - t0
+        return reps * len(self.streams) / dt, (f"{reps} x {len(self.streams)} images: PIL (libjpeg-turbo) decode + the reference's numpy "
+                                              f"normalise / transpose (datasets/voc.py), {self.cpu_cores} host threads as the "
+                                              "reference's DataLoader(num_workers=2) — the reference's own code path")
+
+
+WORKLOADS = {"mscflip": MscFlipVoc, "mscflip_coco": MscFlipCoco, "cfg2": PseudoLabelVoc, "train": TrainStepVoc,
+             "io": InputPipelineVoc}

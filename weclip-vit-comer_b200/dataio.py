@@ -31,13 +31,20 @@ class JpegInfo(ctypes.Structure):
                 ("qt", (ctypes.c_uint16 * 64) * 4)]
 
 
-def jpeg_entropy_decode(data: bytes, pinned: bool = True) -> Tuple[JpegInfo, torch.Tensor]:
-    """HOST half: parse the stream and Huffman-decode it -> (info, int16 coefficients [coef_count], pinned host tensor)."""
+def jpeg_entropy_decode(data: bytes, pinned: bool = True, out: torch.Tensor = None) -> Tuple[JpegInfo, torch.Tensor]:
+    """HOST half: parse the stream and Huffman-decode it -> (info, int16 coefficients [coef_count], pinned host tensor).
+    ``out``: a caller-owned (pinned) int16 buffer to decode into — allocating pinned memory costs more than decoding a VOC-sized
+    image, so a loader keeps a small ring of them; the returned tensor is then a view of its first ``coef_count`` elements."""
     L = _lib.lib()
     buf = (ctypes.c_uint8 * len(data)).from_buffer_copy(data)
     info = JpegInfo()
     _lib.check(L.wc_jpeg_parse(buf, ctypes.c_size_t(len(data)), ctypes.byref(info)), "wc_jpeg_parse")
-    coef = torch.empty(int(info.coef_count), dtype=torch.int16, pin_memory=pinned and torch.cuda.is_available())
+    if out is not None:
+        if out.dtype != torch.int16 or out.numel() < int(info.coef_count) or not out.is_contiguous():
+            raise ValueError("out must be a contiguous int16 tensor of at least coef_count elements")
+        coef = out.view(-1)[: int(info.coef_count)]
+    else:
+        coef = torch.empty(int(info.coef_count), dtype=torch.int16, pin_memory=pinned and torch.cuda.is_available())
     rc = L.wc_jpeg_entropy_decode(buf, ctypes.c_size_t(len(data)), ctypes.c_void_p(coef.data_ptr()), ctypes.c_long(coef.numel()))
     _lib.check(rc, "wc_jpeg_entropy_decode")
     return info, coef

@@ -292,13 +292,21 @@ class DecoderFunction(torch.autograd.Function):
         wf, bf = next(it), next(it)
         blocks = [tuple(next(it) for _ in range(12)) for _ in range(N_BLOCKS)]
         wp, bp = next(it), next(it)
-        # power-of-two loss scale: the gradient operands of the tensor-core products are fp16
-        amax = 0.0
-        if dseg is not None:
-            amax = max(amax, float(dseg.abs().max()))
-        if dattn is not None:
-            amax = max(amax, float(dattn.abs().max()))
-        sc = 2.0 ** (8 - math.ceil(math.log2(amax))) if amax > 0 and math.isfinite(amax) else 1.0
+        # power-of-two loss scale: the gradient operands of the tensor-core products are fp16.  Eagerly it follows this step's
+        # incoming gradients (one host read); a captured step (TrainStep) runs with the scale of the eager step it was captured
+        # after — |d loss / d seg| ~ 1 / pixels moves little between batches and max -> 2^8 leaves 2^7 of headroom either way —
+        # and leaves the maximum on the device so that the host can look at it now and then.
+        am = None
+        for t in (dseg, dattn):
+            if t is not None:
+                a = t.detach().abs().max()
+                am = a if am is None else torch.maximum(am, a)
+        DecoderFunction.last_amax = am
+        if DecoderFunction.scale_override is not None:
+            sc = DecoderFunction.scale_override
+        else:
+            sc = loss_scale_for(float(am) if am is not None else 0.0)
+            DecoderFunction.last_scale = sc
         inv = 1.0 / sc
         grads = {}
         zeros = lambda *shape: torch.zeros(*shape, dtype=torch.float32, device=dev)
@@ -412,9 +420,150 @@ class DecoderFunction(torch.autograd.Function):
         return (None, None, None, *out)
 
 
+DecoderFunction.scale_override = None      # float: run backward with this loss scale, no host read (set by TrainStep for a capture)
+DecoderFunction.last_scale = 1.0           # the scale the last eager backward chose
+DecoderFunction.last_amax = None           # device scalar: max |incoming gradient| of the last backward
+
+
+def loss_scale_for(amax: float) -> float:
+    """Power of two that brings the largest incoming gradient to [2^7, 2^8]."""
+    return 2.0 ** (8 - math.ceil(math.log2(amax))) if amax > 0 and math.isfinite(amax) else 1.0
+
+
 def make_dropout_mask(N: int, p: float, training: bool, device) -> torch.Tensor:
     """Dropout2d(p) channel mask [N, 256] holding 0 or 1/(1-p) (ones when not training)."""
     if not training or p <= 0:
         return torch.ones(N, D, dtype=torch.float32, device=device)
     keep = (torch.rand(N, D, device=device) >= p).float()
     return keep / (1.0 - p)
+
+
+class TrainStep:
+    """One optimisation step of the reference's training loop (scripts/dist_clip_voc.py:238-267) behind one call:
+
+        step = TrainStep(model, optimizer)          # optimizer over model.get_param_groups()[3]
+        loss = step(img, img_names)                 # forward mode='train', aff / seg loss, backward, optimizer.step()
+
+    The step is ~300 kernel launches of a few microseconds each; launched from Python it is host-bound (measured 10-16 ms of
+    host time for 4.3 ms of device work at batch 4 x 320^2).  With ``use_graphs`` the device half — WeCLIP.run (frozen encoder,
+    pseudo-labels, trainable decoder), F.interpolate, the two losses, the whole backward and the optimiser step — is captured
+    into a CUDA graph per (batch shape, label-set signature) and replayed; the host half (label PNGs -> class lists,
+    WeCLIP.prepare) stays outside and its index vectors are copied into the graph's buffers before each replay.  The first
+    batch of a signature runs eagerly (it is a real step) and is captured for the next one.  Graph mode needs an optimiser
+    whose state lives on the device (``capturable=True``; a tensor ``lr`` lets a scheduler keep working); otherwise the step
+    runs eagerly.  The returned loss is a device scalar (no host synchronisation)."""
+
+    def __init__(self, model, optimizer, radius: int = 8, aff_weight: float = 0.1, ignore_index: int = 255,
+                 use_graphs: bool = True, max_graphs: int = 32):
+        self.model, self.opt = model, optimizer
+        self.radius, self.aff_weight, self.ignore_index = radius, aff_weight, ignore_index
+        capturable = all(g.get("capturable", False) for g in optimizer.param_groups)
+        self.use_graphs = bool(use_graphs and capturable)
+        self.max_graphs = max_graphs
+        if self.use_graphs:
+            # the parameters' AccumulateGrad nodes were created on the caller's stream, the step runs on its own: torch orders the
+            # two with events (captured as graph edges) and would warn about it on every backward
+            setter = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
+            if setter is not None:
+                setter(False)
+        self._graphs = {}
+        self._stream = None
+        self._pool = None
+        self.graph_captures = self.graph_replays = 0
+
+    def _device_step(self, img, meta):
+        import torch.nn.functional as F
+        from . import losses as LS
+        segs, cam, attn_pred = self.model.run(img, meta)                                             # dist_clip_voc.py:246
+        segs_up = F.interpolate(segs, size=cam.shape[1:], mode="bilinear", align_corners=False)      # :250
+        attn_loss, _, _ = LS.aff_loss_from_labels(attn_pred, cam, radius=self.radius, ignore_index=self.ignore_index)
+        seg_loss = LS.get_seg_loss(segs_up, cam, ignore_index=self.ignore_index)                     # :256
+        loss = seg_loss + self.aff_weight * attn_loss                                                # :258
+        self.opt.zero_grad(set_to_none=True)
+        loss.backward()
+        self.opt.step()
+        return loss.detach()
+
+    def _device_meta(self, meta_h, dev):
+        from .model import ForwardMeta
+        m = ForwardMeta()
+        m.__dict__.update(meta_h.__dict__)
+        m.rows = torch.empty(meta_h.rows_host.shape, dtype=torch.int64, device=dev)
+        m.lut = torch.empty(meta_h.lut_host.shape, dtype=torch.int64, device=dev)
+        return m
+
+    @staticmethod
+    def _refresh(ent, img, meta_h):
+        ent["img"].copy_(img, non_blocking=True)
+        ent["meta"].rows.copy_(meta_h.rows_host.pin_memory(), non_blocking=True)
+        ent["meta"].lut.copy_(meta_h.lut_host.pin_memory(), non_blocking=True)
+
+    def __call__(self, img, img_names):
+        _lib.require_device()
+        model = self.model
+        eng = model.engine
+        if eng is None:
+            raise _lib.WeclipError("WeCLIP weights are not loaded (encoder + decoder state dict required)")
+        dev = eng.device
+        img = img.to(dev, torch.float32)
+        N, _, H, W = img.shape
+        model.iter_num += 1
+        if not self.use_graphs:
+            with torch.enable_grad():
+                return self._device_step(img, model.prepare(img_names, "train", N, H, W))
+        meta_h = model.prepare(img_names, "train", N, H, W, device_tensors=False)
+        if not meta_h.cam_path:
+            raise _lib.WeclipError("the training step needs the pseudo-label path (one name per image)")
+        model._text_table(dev)
+        key = (N, H, W, meta_h.signature(), id(eng), eng.generation, getattr(model, "_text_key", None), model.training,
+               float(model.decoder_fts_fuse.dropout.p))
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(dev)
+            self._pool = torch.cuda.graph_pool_handle()
+        caller = torch.cuda.current_stream(dev)
+        st = self._stream
+        st.wait_stream(caller)
+        ent = self._graphs.get(key)
+        with torch.cuda.stream(st):
+            if ent is None:
+                ent = dict(img=torch.empty_like(img), meta=self._device_meta(meta_h, dev))
+                self._refresh(ent, img, meta_h)
+                with torch.enable_grad():
+                    loss = self._device_step(ent["img"], ent["meta"])          # the real step for this batch (and the warm-up)
+                    loss = loss.clone()
+                    st.synchronize()
+                    if len(self._graphs) >= self.max_graphs:
+                        self._graphs.pop(next(iter(self._graphs)))
+                    g = torch.cuda.CUDAGraph()
+                    self.opt.zero_grad(set_to_none=True)      # gradients of the captured step live in the graph's own pool
+                    ent["scale"] = DecoderFunction.scale_override = DecoderFunction.last_scale
+                    try:
+                        with torch.cuda.graph(g, pool=self._pool, stream=st, capture_error_mode="thread_local"):
+                            ent["loss"] = self._device_step(ent["img"], ent["meta"])
+                    finally:
+                        DecoderFunction.scale_override = None
+                    ent["amax"] = DecoderFunction.last_amax                    # static tensor of the captured backward
+                    ent["amax_h"] = torch.zeros(1).pin_memory()
+                    ent["amax_ev"] = None
+                ent["graph"] = g
+                self._graphs[key] = ent
+                self.graph_captures += 1
+            else:
+                self._refresh(ent, img, meta_h)
+                ent["graph"].replay()
+                self.graph_replays += 1
+                loss = ent["loss"]
+                # loss-scale watch: every 32 replays the gradient maximum travels to the host (asynchronously); a graph whose
+                # captured scale has drifted more than 2^4 from what that maximum asks for is dropped and captured again
+                if ent["amax_ev"] is not None and ent["amax_ev"].query():
+                    want = loss_scale_for(float(ent["amax_h"][0]))
+                    ent["amax_ev"] = None
+                    if not (2.0 ** -4 <= want / ent["scale"] <= 2.0 ** 4):
+                        self._graphs.pop(key, None)
+                elif ent["amax_ev"] is None and self.graph_replays % 32 == 0 and ent["amax"] is not None:
+                    ent["amax_h"].copy_(ent["amax"].reshape(1), non_blocking=True)
+                    ent["amax_ev"] = torch.cuda.Event()
+                    ent["amax_ev"].record(st)
+        img.record_stream(st)
+        caller.wait_stream(st)
+        return loss
