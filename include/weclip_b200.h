@@ -30,7 +30,7 @@ extern "C" {
 #define WC_ERR_WORKSPACE (-3)
 #define WC_ERR_UNSUPPORTED (-4)
 
-#define WC_ABI_VERSION 12
+#define WC_ABI_VERSION 13
 #define WC_PAR_MAX_DIL 8
 
 /* ABI version (bumped whenever a signature changes) and last error text. */
@@ -291,6 +291,17 @@ int wc_aff_loss(const float* inputs, const int64_t* targets, long n, float* loss
 int wc_aff_loss_fused(const float* attn_pred, const int64_t* cam_label, int B, int H, int W, int radius,
                       int ignore_index, float* loss, int64_t* counts, float* grad, void* workspace,
                       size_t workspace_bytes, void* stream);
+/* wc_aff_loss_fused without a workspace argument and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  Same inputs, outputs and results as wc_aff_loss_fused; the scratch (accumulator + down-sampled patch
+ * labels) is a file-scope static __device__ array of 256 KB + 256 B that every GPU loading the library holds until exit.
+ * Limit: B * (H/16) * (W/16) <= wc_aff_loss_static_max_patches() = 65536 (e.g. 64 crops of 512 x 512); larger calls return
+ * WC_ERR_WORKSPACE with a message.  The device the stream belongs to must be current.  Calls no cudaMalloc / cudaFree; the first
+ * call on a device looks the array's address up (cudaGetSymbolAddress).  All calls share the array: each call clears the
+ * accumulator and rewrites the labels it uses, and two calls that overlap on the GPU (different streams) race. */
+long wc_aff_loss_static_max_patches(void);
+int wc_aff_loss_fused_static(const float* attn_pred, const int64_t* cam_label, int B, int H, int W, int radius,
+                             int ignore_index, float* loss, int64_t* counts, float* grad, void* stream);
 /* get_seg_loss (utils/losses.py:24-33): 0.5 * (CE over label==0 pixels + CE over foreground pixels), each a mean
  * over its own pixels (nan when it has none, like F.cross_entropy).  pred fp32 [B,C,H,W], label int64 [B,H,W];
  * grad fp32 [B,C,H,W] (may be NULL) = d loss / d pred. */

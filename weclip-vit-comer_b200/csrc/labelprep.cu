@@ -10,6 +10,8 @@
 // can hang them on torch autograd.  Sums are accumulated in fp64 (block partials -> one atomicAdd per CTA).
 #include "common.cuh"
 
+#include <atomic>
+
 namespace wc {
 namespace {
 
@@ -349,6 +351,49 @@ extern "C" int wc_aff_loss_fused(const float* attn_pred, const int64_t* cam_labe
     cudaStream_t st = as_stream(stream);
     AffAcc* acc = static_cast<AffAcc*>(workspace);
     int32_t* small = reinterpret_cast<int32_t*>(static_cast<char*>(workspace) + 64);
+    WC_CUDA(cudaMemsetAsync(acc, 0, sizeof(AffAcc), st));
+    label_downsample_kernel<<<grid_for((long)B * P, 256), 256, 0, st>>>(cam_label, small, B, H, W, h, w);
+    WC_LAUNCH_CHECK();
+    return aff_loss_launch<true>(attn_pred, nullptr, small, P, w, radius, ignore_index, (long)B * P * P, acc, loss, counts,
+                                 grad, st);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// wc_aff_loss_fused_static: wc_aff_loss_fused for callers that cannot allocate (CUDA-graph capture, serving loops, harnesses
+// that forbid cudaMalloc).  No counterpart in the reference.  Its scratch (the 64-byte
+// accumulator + the down-sampled patch labels) is this file-scope device array: every GPU that loads the library holds its
+// 256 KB + 256 B until exit.  In host code the array's name is only a stand-in for the symbol, NOT a device address: the address
+// is looked up once per device with cudaGetSymbolAddress (that device current) and that pointer is what the kernels get.
+// All calls share the array and it keeps the last call's contents: the accumulator is cleared by every call, the label part is
+// fully rewritten for the call's B * P patches; two calls that overlap on the GPU (different streams) race.
+// ---------------------------------------------------------------------------------------------------
+constexpr long AFF_STATIC_MAX_PATCHES = 65536;                       // B * (H/16) * (W/16), e.g. 64 crops of 512 x 512
+constexpr size_t AFF_STATIC_BYTES = 256 + AFF_STATIC_MAX_PATCHES * sizeof(int32_t);
+static __device__ __align__(256) unsigned char g_aff_static_scratch[AFF_STATIC_BYTES];
+constexpr int AFF_STATIC_MAX_DEVICES = 64;
+static std::atomic<void*> g_aff_static_ptr[AFF_STATIC_MAX_DEVICES];    // per device: the array's DEVICE address (0 = not looked up)
+
+extern "C" long wc_aff_loss_static_max_patches(void) { return AFF_STATIC_MAX_PATCHES; }
+
+extern "C" int wc_aff_loss_fused_static(const float* attn_pred, const int64_t* cam_label, int B, int H, int W, int radius,
+                                        int ignore_index, float* loss, int64_t* counts, float* grad, void* stream) {
+    WC_CHECK_ARG(attn_pred && cam_label && loss && counts && B > 0 && H >= 16 && W >= 16);
+    const int h = H / 16, w = W / 16, P = h * w;
+    if ((long)B * P > AFF_STATIC_MAX_PATCHES)
+        return fail(WC_ERR_WORKSPACE, "%s: B * (H/16) * (W/16) = %ld patches exceed the static scratch of %ld; use wc_aff_loss_fused "
+                    "with a caller-provided workspace", __func__, (long)B * P, AFF_STATIC_MAX_PATCHES);
+    int dev = 0;
+    WC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= AFF_STATIC_MAX_DEVICES) return fail(WC_ERR_UNSUPPORTED, "%s: device index %ld", __func__, dev);
+    void* base = g_aff_static_ptr[dev].load(std::memory_order_acquire);
+    if (!base) {      // set-up, once per device (racing first calls look up the same address)
+        WC_CUDA(cudaGetSymbolAddress(&base, g_aff_static_scratch));
+        if (!base) return fail(WC_ERR_CUDA, "%s: cudaGetSymbolAddress returned a null address", __func__);
+        g_aff_static_ptr[dev].store(base, std::memory_order_release);
+    }
+    cudaStream_t st = as_stream(stream);
+    AffAcc* acc = static_cast<AffAcc*>(base);
+    int32_t* small = reinterpret_cast<int32_t*>(static_cast<char*>(base) + 256);
     WC_CUDA(cudaMemsetAsync(acc, 0, sizeof(AffAcc), st));
     label_downsample_kernel<<<grid_for((long)B * P, 256), 256, 0, st>>>(cam_label, small, B, H, W, h, w);
     WC_LAUNCH_CHECK();
