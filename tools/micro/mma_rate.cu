@@ -23,14 +23,22 @@ __device__ __forceinline__ void umma_ts(uint32_t tmem_d, uint32_t tmem_a, uint64
 
 // warps 4.. (when launched with more than 128 threads) stream tcgen05.ld over the S columns (and, ldst = 2, tcgen05.st into the P
 // columns) until the issuer is done: what the softmax warps do to the tensor memory while the products run
-__global__ void __launch_bounds__(384, 1) mma_rate_kernel(int mode, int rounds, int ldst, int commits, long long* clk) {
+// data = 1: operands are pseudo-random fp16 in (-1, 1) instead of zeros (real switching activity in the tensor pipe; the first product of
+// every batch overwrites its accumulator as in the attention kernel, so the values stay finite)
+__global__ void __launch_bounds__(384, 1) mma_rate_kernel(int mode, int rounds, int ldst, int commits, int data, long long* clk) {
     extern __shared__ uint8_t raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
     __shared__ uint64_t bar, bar2[2];
     __shared__ uint32_t slot;
     __shared__ volatile int done_flag;
     if (threadIdx.x == 0) done_flag = 0;
-    for (int i = threadIdx.x; i < 96 * 1024 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+    for (int i = threadIdx.x; i < 96 * 1024 / 4; i += blockDim.x) {
+        uint32_t h = (uint32_t)i * 2654435761u + blockIdx.x * 40503u;
+        h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+        // two halves with exponent field <= 14 (|x| < 1), random sign and mantissa
+        const uint32_t v = (h & 0x83ff83ffu) | ((((h >> 10) & 7u) + 7u) << 10) | ((((h >> 26) & 7u) + 7u) << 26);
+        reinterpret_cast<uint32_t*>(smem)[i] = data ? v : 0u;
+    }
     if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_init(&bar2[0], 1); mbar_init(&bar2[1], 1); mbar_fence_init(); }
     if (threadIdx.x < 32) tmem_alloc(&slot, 512);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -38,6 +46,17 @@ __global__ void __launch_bounds__(384, 1) mma_rate_kernel(int mode, int rounds, 
     __syncthreads();
     tc_fence_after();
     const uint32_t tb = slot;
+    if (data && threadIdx.x < 128) {      // the TMEM A operand (P, columns 128..191) gets the same kind of values
+        uint32_t r[32];
+        for (int c = 0; c < 2; ++c) {
+            for (int e = 0; e < 32; ++e) r[e] = reinterpret_cast<uint32_t*>(smem)[(threadIdx.x * 64 + c * 32 + e) & 8191];
+            tmem_st32(tb + ((uint32_t)((threadIdx.x >> 5) * 32) << 16) + 128 + c * 32, r);
+        }
+        tmem_st_wait();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
     if (threadIdx.x == 0) {
         const uint64_t da = make_smem_desc(smem_u32(smem)), db = make_smem_desc(smem_u32(smem + 16384)),
                        dv = make_smem_desc(smem_u32(smem + 32768)), dw = make_smem_desc(smem_u32(smem + 49152));
@@ -47,25 +66,25 @@ __global__ void __launch_bounds__(384, 1) mma_rate_kernel(int mode, int rounds, 
         for (int r = 0; r < rounds; ++r) {
             if (mode == 0 || mode == 4) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) umma_f16(tb, da + 2 * k, db + 2 * k, id_s, 1);
+                for (int k = 0; k < 4; ++k) umma_f16(tb, da + 2 * k, db + 2 * k, id_s, k != 0);
                 if (commits) umma_commit(&bar2[0]);          // (nobody waits: the phase just flips)
             }
             if (mode == 1 || mode == 4) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k) umma_ts(tb + 256, tb + 128 + 8 * k, dv + 128 * k, id_o, 1);
+                for (int k = 0; k < 8; ++k) umma_ts(tb + 256, tb + 128 + 8 * k, dv + 128 * k, id_o, k != 0);
                 if (commits) umma_commit(&bar2[1]);
             }
             if (mode == 2) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k) umma_f16(tb + 256, da + 2 * (k & 3), dv + 128 * k, id_o, 1);
+                for (int k = 0; k < 8; ++k) umma_f16(tb + 256, da + 2 * (k & 3), dv + 128 * k, id_o, k != 0);
             }
             if (mode == 3) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k) umma_ts(tb + 256, tb + 128 + 8 * k, dv + 2 * (k & 3), id_ok, 1);
+                for (int k = 0; k < 8; ++k) umma_ts(tb + 256, tb + 128 + 8 * k, dv + 2 * (k & 3), id_ok, k != 0);
             }
             if (mode == 5) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) umma_f16(tb, da + 2 * k, dv + 2 * k, id_g, 1);
+                for (int k = 0; k < 4; ++k) umma_f16(tb, da + 2 * k, dv + 2 * k, id_g, k != 0);
                 if (commits) umma_commit(&bar2[0]);
             }
             (void)dw;
@@ -106,18 +125,20 @@ int main() {
     cudaFuncSetAttribute(mma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
     const char* names[] = {"SS 128x128x16 x4 (scores)", "TS 128x64x16 x8, B MN-major (P V)", "SS 128x64x16 x8, B MN-major",
                            "TS 128x64x16 x8, B K-major", "scores + P V (one attention tile)", "SS 128x256x16 x4 (GEMM k-block)"};
-    for (int cfg = 0; cfg < 7; ++cfg) {
-        const int grid = cfg == 0 ? 1 : 148, ldst = (cfg < 2 || cfg == 5) ? 0 : (cfg == 4 || cfg == 6 ? 2 : 1),
-                  threads = (cfg < 2 || cfg == 5) ? 128 : (cfg == 2 ? 256 : 384), commits = cfg >= 5;
+    for (int cfg = 0; cfg < 9; ++cfg) {
+        const int data = cfg >= 7, c = data ? (cfg == 7 ? 1 : 6) : cfg;       // cfg 7 / 8 = cfg 1 / 6 with random operands
+        const int grid = c == 0 ? 1 : 148, ldst = (c < 2 || c == 5) ? 0 : (c == 4 || c == 6 ? 2 : 1),
+                  threads = (c < 2 || c == 5) ? 128 : (c == 2 ? 256 : 384), commits = c >= 5;
         printf("-- grid %d, %d warps streaming tcgen05.ld%s beside the issuer\n", grid, (threads - 128) / 32, ldst == 2 ? " + st" : "");
         if (commits) printf("   (tcgen05.commit after every batch of 4 / 8)\n");
+        if (data) printf("   (pseudo-random fp16 operands instead of zeros)\n");
         for (int mode = 0; mode < 6; ++mode) {
             const int rounds = 2000;
             cudaEvent_t e0, e1;
             cudaEventCreate(&e0); cudaEventCreate(&e1);
-            mma_rate_kernel<<<grid, threads, 100 * 1024>>>(mode, 10, ldst, commits, clk);
+            mma_rate_kernel<<<grid, threads, 100 * 1024>>>(mode, 10, ldst, commits, data, clk);
             cudaEventRecord(e0);
-            mma_rate_kernel<<<grid, threads, 100 * 1024>>>(mode, rounds, ldst, commits, clk);
+            mma_rate_kernel<<<grid, threads, 100 * 1024>>>(mode, rounds, ldst, commits, data, clk);
             cudaEventRecord(e1);
             cudaError_t err = cudaDeviceSynchronize();
             if (err != cudaSuccess) { printf("mode %d: %s\n", mode, cudaGetErrorString(err)); return 1; }
