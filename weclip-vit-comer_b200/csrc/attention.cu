@@ -37,6 +37,22 @@ __device__ __forceinline__ float ex2_approx(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// 2^x on the FMA / ALU pipes instead of the MUFU (the softmax phase issues one MUFU.EX2 per score at 16 / clk / SM): x = n + f with
+// n = round(x) taken from the low mantissa bits of x + 1.5 * 2^23, 2^f on [-0.5, 0.5] by the degree-4 Taylor polynomial (relative
+// error < 4.3e-5, an order below the fp16 rounding P gets anyway), scaled by adding n into the exponent field.  x <= 127.
+__device__ __forceinline__ float ex2_poly(float x) {
+    x = fmaxf(x, -125.f);
+    const float t = x + 12582912.f;
+    const float f = x - (t - 12582912.f);
+    float p = fmaf(f, 0.0096181291f, 0.055504109f);
+    p = fmaf(p, f, 0.24022651f);
+    p = fmaf(p, f, 0.69314718f);
+    p = fmaf(p, f, 1.f);
+    return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+#ifndef AT_POLY_EVERY
+#define AT_POLY_EVERY 0          // 4: one score in four takes ex2_poly; 0: all MUFU
+#endif
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // -DAT_TRACE (developer builds only, tools/attn_trace.py): clock64 stamps of one softmax warp pair for the second item of CTA 0,
@@ -242,7 +258,8 @@ __global__ void __launch_bounds__(FW_THREADS, 1) attn_fwd_kernel(const __grid_co
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
                 float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * i]), AT_LOG2E, -m_used));
-                float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * i + 1]), AT_LOG2E, -m_used));
+                const float x1 = fmaf(__uint_as_float(r[2 * i + 1]), AT_LOG2E, -m_used);
+                float p1 = (AT_POLY_EVERY && (2 * i + 1) % AT_POLY_EVERY == AT_POLY_EVERY - 1) ? ex2_poly(x1) : ex2_approx(x1);
                 if (nvc < 32) {
                     if (2 * i >= nvc) p0 = 0.f;
                     if (2 * i + 1 >= nvc) p1 = 0.f;
