@@ -128,6 +128,16 @@ class MscFlipVoc:
         """Same step with cam_passes="live": only the CAM / PAR pass whose labels the driver reads."""
         self.ev_live.process_batch(self.names, self.imgs_d, self.labs_d)
 
+    def step_device_fp32_par(self):
+        """Same step as step_device with the PAR affinities stored in fp32 as the reference computes them (PAR.py is fp32 end to
+        end; the pipeline default stores them in fp16: 2.3e-3 vs 2e-5 max error, labels >= 99.5 % either way)."""
+        par = self.model.par
+        keep, par.affinity_dtype = par.affinity_dtype, torch.float32
+        try:
+            self.ev.process_batch(self.names, self.imgs_d, self.labs_d)
+        finally:
+            par.affinity_dtype = keep
+
     def step_b1(self):
         """The step's 8 images ONE PER CALL, as the reference's batch_size-1 loop drives the model."""
         for i in range(IMAGES_PER_STEP):

@@ -378,7 +378,7 @@ class MscFlipEvaluator:
         if any(m.cam_path for m in metas_h):
             self.model._text_table(self.device)           # (re)build the cached text table before it becomes part of the key
         key = (id(slot), B, h0, w0, tuple(labels.shape[-2:]), self.cam_passes, tuple(m.signature() for m in metas_h),
-               id(eng), eng.generation, getattr(self.model, "_text_key", None))
+               id(eng), eng.generation, getattr(self.model, "_text_key", None), str(self.model.par.affinity_dtype))
         with torch.cuda.stream(launch):
             ent = self._graphs.get(key)
             if ent is None:
