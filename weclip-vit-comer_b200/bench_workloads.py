@@ -106,7 +106,7 @@ class MscFlipVoc:
         # size mix (long side 500 -> short sides 384 / 341 / 340 / 287 ... after the resize, mostly not multiples of 16)
         self.ev_b1 = MscFlipEvaluator(self.model, self.n_classes, self.scales, 512, device, overlap_scales=overlap,
                                       cam_passes="reference", use_graphs=graphs,
-                                      graph_slots=int(os.environ.get("WC_GRAPH_SLOTS", "4")))
+                                      graph_slots=int(os.environ.get("WC_GRAPH_SLOTS", "2")))
         voc = synth.make_voc_like_dataset(500 + rank, IMAGES_PER_STEP, self.root, self.subdir, self.n_fg)
         self.voc_items = [(n, im[None].to(device), torch.from_numpy(lab.astype(np.int16)).to(device)) for n, im, lab in voc]
         self.voc_sizes = [tuple(im.shape[-2:]) for _, im, _ in self.voc_items]
