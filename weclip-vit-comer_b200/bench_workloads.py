@@ -284,6 +284,8 @@ class PseudoLabelVoc(MscFlipVoc):
     goes through encoder, decoder, Grad-CAM, affinity refinement (iter_num > 15000: RFM branch), upsample and PAR at crop
     resolution.  Unit = one crop; the step returns (seg, pseudo labels, attn_pred) on the device, e2e copies the labels out."""
     name = "cfg2: WeCLIP VOC CAM+PAR pseudo-label step, batch 32 at 320x320 crop, 21 classes, mode='train' (RFM branch)"
+    metric = "CAM+PAR pseudo-label step crops/sec"
+    unit = "crops/s"
     H = W = 320
     BATCH = 32
     units = BATCH
