@@ -41,6 +41,53 @@ __global__ void __launch_bounds__(256) aff_layer_sums_kernel(const float* __rest
     if (threadIdx.x == 0) atomicAdd(sums + (size_t)img * (nl + 1) + l, (double)s);
 }
 
+// The row loop of aff_build_kernel for NK kept layers (NK = 0: run-time count): 4 rows x (NK + 1) independent loads in flight per
+// thread (the first version issued one row's loads at a time behind a per-layer branch and ran at 1.3-1.6 TB/s).
+template <int NK>
+__device__ __forceinline__ void aff_build_rows(const float* const (&base)[16], const float (&wk)[16], const float* __restrict__ ap,
+                                               float* __restrict__ Bm, float* __restrict__ colz, int img, int P, int L, int r0,
+                                               int r1, int use_rfm, int nk_rt = 0) {
+    const int nk = NK ? NK : nk_rt;
+    const size_t irow = (size_t)img * P;
+    for (int j = threadIdx.x; j < P; j += 256) {
+        float cs = 0.f;
+        int i = r0;
+        for (; i + 4 <= r1; i += 4) {
+            float v[4] = {0.f, 0.f, 0.f, 0.f}, a[4] = {1.f, 1.f, 1.f, 1.f};
+            if (NK) {
+#pragma unroll
+                for (int q = 0; q < (NK ? NK : 1); ++q) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) v[u] = fmaf(wk[q], __ldg(base[q] + (size_t)(i + u) * L + j), v[u]);
+                }
+            } else {
+                for (int q = 0; q < nk; ++q) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) v[u] = fmaf(wk[q], __ldg(base[q] + (size_t)(i + u) * L + j), v[u]);
+                }
+            }
+            if (use_rfm) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) a[u] = __ldg(ap + (irow + i + u) * P + j);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (use_rfm) v[u] *= a[u];
+                Bm[(irow + i + u) * P + j] = v[u];
+                cs += v[u];
+            }
+        }
+        for (; i < r1; ++i) {
+            float v = 0.f;
+            for (int q = 0; q < nk; ++q) v = fmaf(wk[q], __ldg(base[q] + (size_t)i * L + j), v);
+            if (use_rfm) v *= ap[(irow + i) * P + j];
+            Bm[(irow + i) * P + j] = v;
+            cs += v;
+        }
+        atomicAdd(colz + irow + j, cs);
+    }
+}
+
 // B = RFM fusion (clip_tool.py:158-170) or the plain layer mean (:173-174); also the first column sums.
 __global__ void __launch_bounds__(256) aff_build_kernel(const float* __restrict__ attn, const float* __restrict__ ap,
                                                         const double* __restrict__ sums, float* __restrict__ Bm,
@@ -71,17 +118,21 @@ __global__ void __launch_bounds__(256) aff_build_kernel(const float* __restrict_
         }
     }
     __syncthreads();
-    for (int j = threadIdx.x; j < P; j += 256) {
-        float cs = 0.f;
-        for (int i = r0; i < r1; ++i) {
-            float v = 0.f;
-            for (int l = 0; l < nl; ++l)
-                if (wl[l] != 0.f) v = fmaf(wl[l], attn_row(attn, l, img, N, L, i)[j], v);      // dropped layers are not read
-            if (use_rfm) v *= ap[((size_t)img * P + i) * P + j];
-            Bm[((size_t)img * P + i) * P + j] = v;
-            cs += v;
-        }
-        atomicAdd(colz + (size_t)img * P + j, cs);
+    // kept layers, in ascending order (the fmaf chain below adds them in the same order as a loop over all layers would)
+    int nk = 0;
+    const float* base[16];
+    float wk[16];
+    for (int l = 0; l < nl; ++l)
+        if (wl[l] != 0.f) { base[nk] = attn_row(attn, l, img, N, L, 0); wk[nk] = wl[l]; ++nk; }      // dropped layers are not read
+    switch (nk) {
+        case 1: aff_build_rows<1>(base, wk, ap, Bm, colz, img, P, L, r0, r1, use_rfm); break;
+        case 2: aff_build_rows<2>(base, wk, ap, Bm, colz, img, P, L, r0, r1, use_rfm); break;
+        case 3: aff_build_rows<3>(base, wk, ap, Bm, colz, img, P, L, r0, r1, use_rfm); break;
+        case 4: aff_build_rows<4>(base, wk, ap, Bm, colz, img, P, L, r0, r1, use_rfm); break;
+        case 5: aff_build_rows<5>(base, wk, ap, Bm, colz, img, P, L, r0, r1, use_rfm); break;
+        case 6: aff_build_rows<6>(base, wk, ap, Bm, colz, img, P, L, r0, r1, use_rfm); break;
+        case 8: aff_build_rows<8>(base, wk, ap, Bm, colz, img, P, L, r0, r1, use_rfm); break;
+        default: aff_build_rows<0>(base, wk, ap, Bm, colz, img, P, L, r0, r1, use_rfm, nk); break;
     }
 }
 
@@ -94,6 +145,27 @@ __global__ void __launch_bounds__(256) aff_row_pass_kernel(const float* __restri
     const float* zz = z + (size_t)img * P;
     float s = 0.f;
     float s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    if ((P & 3) == 0) {      // 16-byte loads, two per lane in flight (rows start 16-byte aligned when P % 4 == 0)
+        const float4* row4 = reinterpret_cast<const float4*>(row);
+        const float4* z4 = reinterpret_cast<const float4*>(zz);
+        const int n4 = P >> 2;
+        int j = lane;
+        for (; j + 32 < n4; j += 64) {
+            const float4 b0 = __ldg(row4 + j), b1 = __ldg(row4 + j + 32), q0 = __ldg(z4 + j), q1 = __ldg(z4 + j + 32);
+            s = fmaf(b0.x, __frcp_rn(q0.x), s); s1 = fmaf(b0.y, __frcp_rn(q0.y), s1);
+            s2 = fmaf(b0.z, __frcp_rn(q0.z), s2); s3 = fmaf(b0.w, __frcp_rn(q0.w), s3);
+            s = fmaf(b1.x, __frcp_rn(q1.x), s); s1 = fmaf(b1.y, __frcp_rn(q1.y), s1);
+            s2 = fmaf(b1.z, __frcp_rn(q1.z), s2); s3 = fmaf(b1.w, __frcp_rn(q1.w), s3);
+        }
+        for (; j < n4; j += 32) {
+            const float4 b0 = __ldg(row4 + j), q0 = __ldg(z4 + j);
+            s = fmaf(b0.x, __frcp_rn(q0.x), s); s1 = fmaf(b0.y, __frcp_rn(q0.y), s1);
+            s2 = fmaf(b0.z, __frcp_rn(q0.z), s2); s3 = fmaf(b0.w, __frcp_rn(q0.w), s3);
+        }
+        s = warp_sum((s + s1) + (s2 + s3));
+        if (lane == 0) r[(size_t)img * P + i] = 1.f / s;
+        return;
+    }
     int j = lane;
     for (; j + 96 < P; j += 128) {          // four independent streams; 1/z by reciprocal + multiply (<= 1 ulp from the division)
         s = fmaf(row[j], __frcp_rn(zz[j]), s);
@@ -204,6 +276,48 @@ __global__ void __launch_bounds__(256) tsym_row_kernel(const float* __restrict__
     float acc[AFF_KMAX];
 #pragma unroll
     for (int k = 0; k < AFF_KMAX; ++k) acc[k] = 0.f;
+    if ((P & 3) == 0) {      // 16-byte loads (B row, z, x): two per lane in flight
+        const float4* row4 = reinterpret_cast<const float4*>(row);
+        const float4* z4 = reinterpret_cast<const float4*>(zz);
+        const int n4 = P >> 2;
+        auto scaled = [&](int jj) {
+            float4 b = __ldg(row4 + jj);
+            const float4 q = __ldg(z4 + jj);
+            b.x *= __frcp_rn(q.x); b.y *= __frcp_rn(q.y); b.z *= __frcp_rn(q.z); b.w *= __frcp_rn(q.w);
+            return b;
+        };
+        int j = lane;
+        for (; j + 32 < n4; j += 64) {
+            const float4 b0 = scaled(j), b1 = scaled(j + 32);
+#pragma unroll
+            for (int k = 0; k < AFF_KMAX; ++k)
+                if (k < kn) {
+                    const float4* xk = reinterpret_cast<const float4*>(x + (size_t)(k0 + k) * P);
+                    const float4 a0 = __ldg(xk + j), a1 = __ldg(xk + j + 32);
+                    float t0 = fmaf(b0.x, a0.x, fmaf(b0.y, a0.y, fmaf(b0.z, a0.z, b0.w * a0.w)));
+                    float t1 = fmaf(b1.x, a1.x, fmaf(b1.y, a1.y, fmaf(b1.z, a1.z, b1.w * a1.w)));
+                    acc[k] += t0 + t1;
+                }
+        }
+        for (; j < n4; j += 32) {
+            const float4 b0 = scaled(j);
+#pragma unroll
+            for (int k = 0; k < AFF_KMAX; ++k)
+                if (k < kn) {
+                    const float4 a0 = __ldg(reinterpret_cast<const float4*>(x + (size_t)(k0 + k) * P) + j);
+                    acc[k] += fmaf(b0.x, a0.x, fmaf(b0.y, a0.y, fmaf(b0.z, a0.z, b0.w * a0.w)));
+                }
+        }
+        const float ri = r[(size_t)img * P + i];
+#pragma unroll
+        for (int k = 0; k < AFF_KMAX; ++k) {
+            if (k < kn) {
+                const float sk = warp_sum(acc[k]);
+                if (lane == 0) out[(size_t)(k0 + k) * P + i] = 0.5f * ri * sk;
+            }
+        }
+        return;
+    }
     // four independent column groups per trip (loads of the next groups in flight under the FMAs of the first)
     int j = lane;
     for (; j + 96 < P; j += 128) {

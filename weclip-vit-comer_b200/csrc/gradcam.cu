@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msu
     {   // g = mean @ proj  (model.py:414-415)
         // 768 dependent-free loads per thread: four accumulators and a deep unroll keep ~16 L2 requests in flight per thread
         float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll 4
+#pragma unroll 8
         for (int c = 0; c < GC_E; c += 4) {
             s0 = fmaf(mvec[c], __ldg(proj + (size_t)c * GC_EMB + tid), s0);
             s1 = fmaf(mvec[c + 1], __ldg(proj + (size_t)(c + 1) * GC_EMB + tid), s1);
@@ -163,18 +163,30 @@ __global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msu
         const float dot = block_sum(s * g[tid], red);
         dgh[tid] = (s - g[tid] * dot) / gn;          // through the L2 normalisation
         __syncthreads();
-#pragma unroll 2
-        for (int c = warp; c < GC_E; c += 16) {      // d / d mean = proj @ dg ; every patch row gets 1/P of it
-            const float4* pr = reinterpret_cast<const float4*>(proj + (size_t)c * GC_EMB);
-            float a = 0.f;
+        // d / d mean = proj @ dg ; every patch row gets 1/P of it.  Four rows per warp in flight (one CTA per image: the kernel is
+        // bound by the latency of these L2 reads, not by their volume)
+        {
+            float4 d4[GC_EMB / 128];
 #pragma unroll
-            for (int j = 0; j < GC_EMB / 128; ++j) {
-                const float4 w4 = __ldg(pr + lane + 32 * j);
-                const float4 d4 = reinterpret_cast<const float4*>(dgh)[lane + 32 * j];
-                a += w4.x * d4.x + w4.y * d4.y + w4.z * d4.z + w4.w * d4.w;
+            for (int j = 0; j < GC_EMB / 128; ++j) d4[j] = reinterpret_cast<const float4*>(dgh)[lane + 32 * j];
+            for (int c = warp; c < GC_E; c += 64) {
+                float4 w4[4][GC_EMB / 128];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const float4* pr = reinterpret_cast<const float4*>(proj + (size_t)(c + 16 * u) * GC_EMB);
+#pragma unroll
+                    for (int j = 0; j < GC_EMB / 128; ++j) w4[u][j] = __ldg(pr + lane + 32 * j);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    float a = 0.f;
+#pragma unroll
+                    for (int j = 0; j < GC_EMB / 128; ++j)
+                        a += w4[u][j].x * d4[j].x + w4[u][j].y * d4[j].y + w4[u][j].z * d4[j].z + w4[u][j].w * d4[j].w;
+                    a = warp_sum(a);
+                    if (lane == 0) dm[(size_t)inst * GC_E + c + 16 * u] = a / (float)P;
+                }
             }
-            a = warp_sum(a);
-            if (lane == 0) dm[(size_t)inst * GC_E + c] = a / (float)P;
         }
         __syncthreads();
         // power-of-two gradient scale: the backward chain runs through fp16 GEMM operands and dp_k/dy is ~1e-6 for
@@ -364,28 +376,54 @@ __global__ void __launch_bounds__(256) do_prep_kernel(const h16* __restrict__ dO
 // ---------------------------------------------------------------------------------------------------
 // Row sums of dQ, dK, dV over the patch tokens -> dqkv[inst][2304] (see file header).  One CTA per (head, inst).
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) qkv_grad_sum_kernel(const float* __restrict__ colsum, const float* __restrict__ ds0,
-                                                           const h16* __restrict__ q, const h16* __restrict__ k,
-                                                           const float* __restrict__ p0, const h16* __restrict__ dO,
-                                                           float* __restrict__ dqkv, const __grid_constant__ InstTable it,
-                                                           int L, int Lp, float qscale) {
-    __shared__ float part[3][4][GC_HD];
+// 16 row groups of 64 threads, four rows per group in flight (the first version walked the rows with 4 groups and one row at a
+// time: 180 CTAs of latency-bound 2-byte loads, 0.48 TB/s).
+constexpr int QS_GROUPS = 16;
+__global__ void __launch_bounds__(64 * QS_GROUPS) qkv_grad_sum_kernel(const float* __restrict__ colsum, const float* __restrict__ ds0,
+                                                                     const h16* __restrict__ q, const h16* __restrict__ k,
+                                                                     const float* __restrict__ p0, const h16* __restrict__ dO,
+                                                                     float* __restrict__ dqkv, const __grid_constant__ InstTable it,
+                                                                     int L, int Lp, float qscale) {
+    __shared__ float part[3][QS_GROUPS][GC_HD];
     const int h = blockIdx.x, inst = blockIdx.y, d = threadIdx.x & 63, grp = threadIdx.x >> 6;
     const int img = it.img[inst];
     const size_t hb = (size_t)(img * GC_HEADS + h);
     const float* cs = colsum + (size_t)(inst * GC_HEADS + h) * L;
     const float* d0 = ds0 + (size_t)(inst * GC_HEADS + h) * L;
+    const float* pp = p0 + (size_t)(inst * GC_HEADS + h) * L;
+    const h16* kp = k + hb * L * GC_HD + d;
+    const h16* qp = q + hb * L * GC_HD + d;
+    const h16* op = dO + (size_t)inst * L * GC_E + h * GC_HD + d;
     float gq = 0.f, gk = 0.f, gv = 0.f;
-    for (int i = grp; i < L; i += 4) {
-        gq = fmaf(cs[i], __half2float(k[(hb * L + i) * GC_HD + d]), gq);
-        gk = fmaf(-d0[i], __half2float(q[(hb * L + i) * GC_HD + d]), gk);
-        const float pi0 = p0[(size_t)(inst * GC_HEADS + h) * L + i];
-        gv = fmaf(1.f - pi0, __half2float(dO[((size_t)inst * L + i) * GC_E + h * GC_HD + d]), gv);
+    int i = grp;
+    for (; i + 3 * QS_GROUPS < L; i += 4 * QS_GROUPS) {
+        float a[4], b[4], c[4], kv[4], qv[4], ov[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int r = i + u * QS_GROUPS;
+            a[u] = __ldg(cs + r); b[u] = __ldg(d0 + r); c[u] = __ldg(pp + r);
+            kv[u] = __half2float(kp[(size_t)r * GC_HD]);
+            qv[u] = __half2float(qp[(size_t)r * GC_HD]);
+            ov[u] = __half2float(op[(size_t)r * GC_E]);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            gq = fmaf(a[u], kv[u], gq);
+            gk = fmaf(-b[u], qv[u], gk);
+            gv = fmaf(1.f - c[u], ov[u], gv);
+        }
+    }
+    for (; i < L; i += QS_GROUPS) {
+        gq = fmaf(cs[i], __half2float(kp[(size_t)i * GC_HD]), gq);
+        gk = fmaf(-d0[i], __half2float(qp[(size_t)i * GC_HD]), gk);
+        gv = fmaf(1.f - pp[i], __half2float(op[(size_t)i * GC_E]), gv);
     }
     part[0][grp][d] = gq; part[1][grp][d] = gk; part[2][grp][d] = gv;
     __syncthreads();
     if (grp < 3) {
-        const float s = part[grp][0][d] + part[grp][1][d] + part[grp][2][d] + part[grp][3][d];
+        float s = 0.f;
+#pragma unroll
+        for (int g = 0; g < QS_GROUPS; ++g) s += part[grp][g][d];
         dqkv[(size_t)inst * 3 * GC_E + grp * GC_E + h * GC_HD + d] = (grp == 0) ? s * qscale : s;
     }
 }
@@ -629,7 +667,7 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
             for (int c = 0; c < n_inst; ++c) bt.img[c] = it.img[c];
             if ((rc = launch_attn_bwd_colsum(g.q, g.k, g.v, g.dOT, g.lse, g.colsum, bt, n_inst, N, GC_HEADS, L, (int)Lp, st))) return rc;
         }
-        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, qkv_grad_sum_kernel<<<dim3(GC_HEADS, n_inst), 256, 0, st>>>(g.colsum, g.ds0, g.q, g.k, g.p0, g.dO,
+        WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, qkv_grad_sum_kernel<<<dim3(GC_HEADS, n_inst), 64 * QS_GROUPS, 0, st>>>(g.colsum, g.ds0, g.q, g.k, g.p0, g.dO,
                                                                     g.dqkv + (long)it.inst0 * 3 * E, it, L, (int)Lp, qscale));
         WC_LAUNCH_CHECK();
         WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, cam_weight_kernel<<<dim3(E / 64, n_inst), 256, 0, st>>>(g.dqkv + (long)it.inst0 * 3 * E, w->w_in_f32,

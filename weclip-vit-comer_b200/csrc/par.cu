@@ -774,8 +774,13 @@ __global__ void __launch_bounds__(PA_THREADS, 2) par_aff_tile_kernel(const float
 
 
 // ---------------------------------------------------------------------------------------------------
+constexpr int AL_MAX_IMG = 64;               // images per launch (channel offsets travel by value)
+struct ArgmaxTab { int ch0[AL_MAX_IMG + 1]; };
+// blockIdx.y = image of the launch's group; 4 pixels per thread when the plane size allows 16-byte accesses
 __global__ void argmax_lut_kernel(const float* __restrict__ masks, const int64_t* __restrict__ lut,
-                                  int64_t* __restrict__ labels, int ch0, int kc, int b, size_t hw) {
+                                  int64_t* __restrict__ labels, const __grid_constant__ ArgmaxTab tab, int b0, size_t hw) {
+    const int bi = blockIdx.y;
+    const int ch0 = tab.ch0[bi], kc = tab.ch0[bi + 1] - ch0;
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= hw) return;
     const float* m = masks + (size_t)ch0 * hw + i;
@@ -785,7 +790,7 @@ __global__ void argmax_lut_kernel(const float* __restrict__ masks, const int64_t
         const float v = m[(size_t)k * hw];
         if (v > best || (v != v && best == best)) { best = v; arg = k; }   // first max wins; NaN propagates like torch
     }
-    labels[(size_t)b * hw + i] = lut[ch0 + arg];
+    labels[(size_t)(b0 + bi) * hw + i] = lut[ch0 + arg];
 }
 
 // fp16 propagation kernel: 0 = register-prefetch tile kernel (default), 1 = the TMA-pipelined persistent kernel (WC_PAR_PIPE=1).
@@ -985,9 +990,13 @@ extern "C" int wc_argmax_lut(const float* masks, const int64_t* lut, int64_t* la
     WC_CHECK_ARG(check_ragged(ch_off, B) == 0);
     const size_t hw = (size_t)H * W;
     ProfScope prof(PK_CAM_UPSAMPLE, 0.0, as_stream(stream));
-    for (int b = 0; b < B; ++b) {
-        argmax_lut_kernel<<<(unsigned)ceil_div(hw, (size_t)256), 256, 0, as_stream(stream)>>>(
-            masks, lut, labels, ch_off[b], ch_off[b + 1] - ch_off[b], b, hw);
+    for (int b0 = 0; b0 < B; b0 += AL_MAX_IMG) {       // one launch per group of up to 64 images (was: one per image)
+        const int nb = (B - b0 < AL_MAX_IMG) ? B - b0 : AL_MAX_IMG;
+        ArgmaxTab tab;
+        for (int i = 0; i <= nb; ++i) tab.ch0[i] = ch_off[b0 + i];
+        for (int i = nb + 1; i <= AL_MAX_IMG; ++i) tab.ch0[i] = tab.ch0[nb];
+        dim3 grid((unsigned)ceil_div(hw, (size_t)256), (unsigned)nb);
+        argmax_lut_kernel<<<grid, 256, 0, as_stream(stream)>>>(masks, lut, labels, tab, b0, hw);
         WC_LAUNCH_CHECK();
     }
     return WC_OK;
