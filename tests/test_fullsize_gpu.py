@@ -73,6 +73,37 @@ def test_cfg3_msc_flip_voc_512_matches_oracle():
     assert np.array_equal(h[2], O.fast_hist(labs[0], cam.cpu().numpy(), C))        # integer work: exact
 
 
+def test_cfg3_voc_sized_image_short_side_not_a_multiple_of_16_matches_oracle_eager_and_graph():
+    """A dataset image of a real VOC size (333 x 500): the loop resizes it to 340 x 512 and runs 255 x 384 / 340 x 512 /
+    425 x 640 pairs — none of the short sides is a multiple of the 16-pixel patch (the conv drops the remainder,
+    clip/model.py:267) — with labels at the ORIGINAL 333 x 500.  Eager call against oracle.msc_flip_image, then the same image
+    through the CUDA-graph path twice (capture, replay): the same histograms."""
+    torch.set_num_threads(os.cpu_count() or 1)
+    model, sd, fg, bg, names, labs, imgs, C = _setup("voc", 1, 333, 500, seed=53)
+    ev = MscFlipEvaluator(model, C, (1.0, 0.75, 1.25), resize_long=512, cam_passes="reference")
+    gt = torch.from_numpy(labs[0].astype(np.int16)).cuda()
+    seg_pred, msc_pred, cam, msc = ev.process(names[0], imgs.cuda(), gt, want_preds=True)
+    seg_o, msc_o, cam_o, msc_segs_o = O.msc_flip_image(imgs, labs[0], sd, fg, bg, (1.0, 0.75, 1.25), 512, "voc")
+    assert tuple(msc.shape[-2:]) == (21, 32) and tuple(seg_pred.shape[-2:]) == (333, 500)
+    assert _norm_err(msc, msc_segs_o[0]) < TOL
+    assert (seg_pred.cpu() == seg_o).float().mean().item() >= AGREE
+    assert (msc_pred.cpu() == msc_o).float().mean().item() >= AGREE
+    assert (cam.cpu() == cam_o).float().mean().item() >= AGREE
+    h = ev.hist.cpu().numpy()
+    assert np.array_equal(h[2], O.fast_hist(labs[0], cam.cpu().numpy(), C))
+    evg = MscFlipEvaluator(model, C, (1.0, 0.75, 1.25), resize_long=512, cam_passes="reference", use_graphs=True,
+                           graph_slots=1)
+    for _ in range(2):
+        evg.process(names[0], imgs.cuda(), gt)
+    evg.join()
+    torch.cuda.synchronize()
+    assert evg.graph_captures == 1 and evg.graph_replays == 2
+    hg = evg.hist.cpu().numpy()
+    assert np.array_equal(hg[:2], 2 * h[:2])                      # segmentation outputs: bit-identical
+    # CAM pseudo-labels: the refinement accumulates column sums with fp32 atomics, whose order is not fixed
+    assert hg[2].sum() == 2 * h[2].sum() and np.abs(hg[2] - 2 * h[2]).sum() <= 2e-3 * hg[2].sum()
+
+
 def test_cfg4_msc_flip_coco_512_matches_oracle():
     """BASELINE configs[3]: 81 classes; COCO val returns before the CAM path (model_attn_aff_coco.py:131-132)."""
     torch.set_num_threads(os.cpu_count() or 1)

@@ -8,16 +8,18 @@ from weclip_b200.bench_workloads import WORKLOADS, prof_summary
 def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "mscflip"
     wl = WORKLOADS[name](0, torch.device("cuda", 0))
-    ev = getattr(wl, "ev", None)
-    if ev is not None:           # every kernel alone on the device, launched eagerly (the profiler brackets launches)
-        ev.overlap_scales = False
-        ev.use_graphs = False
+    b1 = len(sys.argv) > 2 and sys.argv[2] == "b1"       # the one-image-per-call step (8 images of 512 x 512, one call each)
+    step = wl.step_b1 if b1 else wl.step_device
+    for ev in (getattr(wl, "ev", None), getattr(wl, "ev_b1", None)):
+        if ev is not None:       # every kernel alone on the device, launched eagerly (the profiler brackets launches)
+            ev.overlap_scales = False
+            ev.use_graphs = False
     for _ in range(2):
-        wl.step_device()
+        step()
     torch.cuda.synchronize()
     L = _lib.lib()
     L.wc_prof_reset(); L.wc_prof_enable(1)
-    wl.step_device()
+    step()
     summ = prof_summary()
     cap = 1 << 16
     kind = (ctypes.c_int * cap)(); ms = (ctypes.c_double * cap)(); work = (ctypes.c_double * cap)(); tags = (ctypes.c_int * (4 * cap))()
