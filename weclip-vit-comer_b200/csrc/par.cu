@@ -318,6 +318,67 @@ __device__ __forceinline__ void fill_tile(float* tile, const float* __restrict__
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
 
+// Storage type of the mask tile in shared memory.  -DWC_PAR_MASK16=1 holds the masks of one step as fp16 in the tile when the
+// AFFINITIES are fp16 (values in [0, 1] rounded once per step at the fill, fp32 accumulation, fp32 in global memory): half the
+// shared-memory bytes.  Measured on B200 (16 x 512^2, one step, parity green): Kc = 2 / 3 / 6: 87.7 / 129.1 / 241.8 us against
+// 93 / 129 / 254 us with fp32 tiles — the step is not bound by shared-memory BYTES but by the latency of its LDS -> FFMA2 chains
+// at 4 warps per scheduler (ncu r02 stall samples: MIO throttle 24 %, long scoreboard 21 %, short scoreboard 15 %; time is linear
+// in Kc at ~40 us per channel), so the default keeps fp32 tiles and their exact arithmetic.
+#ifndef WC_PAR_MASK16
+#define WC_PAR_MASK16 0
+#endif
+template <typename AffT> struct MaskTile { using T = float; };
+#if WC_PAR_MASK16
+template <> struct MaskTile<__half> { using T = __half; };
+#endif
+__device__ __forceinline__ float4 ldm4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float4 ldm4(const __half* p) {
+    const uint2 u = *reinterpret_cast<const uint2*>(p);
+    const float2 lo = __half22float2(*reinterpret_cast<const __half2*>(&u.x));
+    const float2 hi = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+    return make_float4(lo.x, lo.y, hi.x, hi.y);
+}
+
+// fp16 tile: the same window, through registers (cp.async cannot convert): four rows per warp in flight
+template <int SH, int NT>
+__device__ __forceinline__ void fill_tile(__half* tile, const float* __restrict__ src, size_t plane, int pitch, int planes,
+                                          int x0, int y0, int H, int W, int vec) {
+    constexpr int NW = NT / 32;
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    if (lane < PT_SW / 4) {
+        const int gx = x0 - PT_HALO + 4 * lane;
+        const bool fast = vec && gx >= 0 && gx + 3 < W;
+        const int c0 = min(max(gx, 0), W - 1), c1 = min(max(gx + 1, 0), W - 1), c2 = min(max(gx + 2, 0), W - 1),
+                  c3 = min(max(gx + 3, 0), W - 1);
+        const int rows = planes * SH;
+        for (int rk0 = wrp; rk0 < rows; rk0 += 4 * NW) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int rk = rk0 + u * NW;
+                if (rk < rows) {
+                    const int k = rk / SH, r = rk - k * SH;
+                    const int gy = min(max(y0 - PT_HALO + r, 0), H - 1);
+                    const float* rowp = src + (size_t)k * plane + (size_t)gy * pitch;
+                    if (fast) v[u] = __ldg(reinterpret_cast<const float4*>(rowp + gx));
+                    else v[u] = make_float4(__ldg(rowp + c0), __ldg(rowp + c1), __ldg(rowp + c2), __ldg(rowp + c3));
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int rk = rk0 + u * NW;
+                if (rk < rows) {
+                    const __half2 lo = __floats2half2_rn(v[u].x, v[u].y), hi = __floats2half2_rn(v[u].z, v[u].w);
+                    uint2 pk;
+                    pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+                    pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+                    *reinterpret_cast<uint2*>(tile + (size_t)rk * PT_SW + 4 * lane) = pk;
+                }
+            }
+        }
+    }
+}
+
 // Two fp32 FMAs in one instruction (FFMA2, sm_100): halves the issue slots and fma-pipe cycles of the 48 x Kc x 4 products
 // a thread accumulates per pass.  The operand pairs are adjacent registers (LDS.128 results, accumulator pairs), so the
 // mov.b64 packs below are register renames.
@@ -342,8 +403,8 @@ __device__ __forceinline__ void fma4p(float (&acc)[KC][4], int k, const float4& 
 }
 
 // One dilation DD: 8 neighbours x KC channels for 4 consecutive pixels.  sc -> centre pixel 0 of channel 0 in the tile.
-template <typename AffT, int KC, int SH, int DD>
-__device__ __forceinline__ void accumulate_dilation(float (&acc)[KC][4], const float* sc,
+template <typename AffT, int KC, int SH, int DD, typename MT = float>
+__device__ __forceinline__ void accumulate_dilation(float (&acc)[KC][4], const MT* sc,
                                                     const typename AffIO<AffT>::Raw (&wr)[8]) {
     float4 w[8];
 #pragma unroll
@@ -352,22 +413,22 @@ __device__ __forceinline__ void accumulate_dilation(float (&acc)[KC][4], const f
     for (int k = 0; k < KC; ++k) {
 #pragma unroll
         for (int r = -1; r <= 1; ++r) {
-            const float* rowp = sc + k * (SH * PT_SW) + r * DD * PT_SW;
+            const MT* rowp = sc + k * (SH * PT_SW) + r * DD * PT_SW;
             const int jl = (r == -1) ? 0 : (r == 0) ? 3 : 5;      // neighbour index of (r, -1)
             const int jr = (r == -1) ? 2 : (r == 0) ? 4 : 7;      // neighbour index of (r, +1)
             if (DD % 4 == 0) {
-                const float4 L = *reinterpret_cast<const float4*>(rowp - DD);
-                const float4 R = *reinterpret_cast<const float4*>(rowp + DD);
+                const float4 L = ldm4(rowp - DD);
+                const float4 R = ldm4(rowp + DD);
                 fma4p<KC>(acc, k, w[jl], L.x, L.y, L.z, L.w);
                 fma4p<KC>(acc, k, w[jr], R.x, R.y, R.z, R.w);
                 if (r != 0) {
-                    const float4 C = *reinterpret_cast<const float4*>(rowp);
+                    const float4 C = ldm4(rowp);
                     fma4p<KC>(acc, k, w[jl + 1], C.x, C.y, C.z, C.w);
                 }
             } else {
-                const float4 L = *reinterpret_cast<const float4*>(rowp - 4);
-                const float4 C = *reinterpret_cast<const float4*>(rowp);
-                const float4 R = *reinterpret_cast<const float4*>(rowp + 4);
+                const float4 L = ldm4(rowp - 4);
+                const float4 C = ldm4(rowp);
+                const float4 R = ldm4(rowp + 4);
                 if (DD == 1) {      // shifted by one: the value pairs straddle register pairs -> scalar FMAs
                     fma4<KC>(acc, k, w[jl], L.w, C.x, C.y, C.z);
                     fma4<KC>(acc, k, w[jr], C.y, C.z, C.w, R.x);
@@ -392,8 +453,10 @@ constexpr int PT_KC = 3;                 // channels per chunk on the tile path:
 constexpr int PT_TH = 32;
 
 template <typename AffT, int KC, int TH>
-__device__ __forceinline__ void par_iter_tile_body(float* par_tile, const AffT* __restrict__ aff, const float* __restrict__ in,
+__device__ __forceinline__ void par_iter_tile_body(typename MaskTile<AffT>::T* par_tile, const AffT* __restrict__ aff,
+                                                   const float* __restrict__ in,
                                                    float* __restrict__ out, const TileArgs& a, const ParChunks& ch) {
+    using MT = typename MaskTile<AffT>::T;
     constexpr int SH = TH + 2 * PT_HALO;
     const int c = blockIdx.z;
     const int x0 = blockIdx.x * PT_W, y0 = blockIdx.y * TH;
@@ -430,35 +493,35 @@ __device__ __forceinline__ void par_iter_tile_body(float* par_tile, const AffT* 
         const AffT* ap = abase + (size_t)y * arow;
         const bool more = pass + 1 < TH / 16 && y + 16 < H;
         const AffT* apn = ap + 16 * arow;
-        const float* sc = par_tile + (ty + PT_HALO) * PT_SW + PT_HALO + 4 * tx4;
+        const MT* sc = par_tile + (ty + PT_HALO) * PT_SW + PT_HALO + 4 * tx4;
         float acc[KC][4];
 #pragma unroll
         for (int k = 0; k < KC; ++k) acc[k][0] = acc[k][1] = acc[k][2] = acc[k][3] = 0.f;
         if constexpr (THREE) {
-            accumulate_dilation<AffT, KC, SH, 1>(acc, sc, wa);
+            accumulate_dilation<AffT, KC, SH, 1, MT>(acc, sc, wa);
             load_weights<AffT>(wa, ap, 3, pol);
-            accumulate_dilation<AffT, KC, SH, 2>(acc, sc, wb);
+            accumulate_dilation<AffT, KC, SH, 2, MT>(acc, sc, wb);
             load_weights<AffT>(wb, ap, 4, pol);
-            accumulate_dilation<AffT, KC, SH, 4>(acc, sc, wc);
+            accumulate_dilation<AffT, KC, SH, 4, MT>(acc, sc, wc);
             load_weights<AffT>(wc, ap, 5, pol);
-            accumulate_dilation<AffT, KC, SH, 8>(acc, sc, wa);
+            accumulate_dilation<AffT, KC, SH, 8, MT>(acc, sc, wa);
             if (more) load_weights<AffT>(wa, apn, 0, pol);
-            accumulate_dilation<AffT, KC, SH, 12>(acc, sc, wb);
+            accumulate_dilation<AffT, KC, SH, 12, MT>(acc, sc, wb);
             if (more) load_weights<AffT>(wb, apn, 1, pol);
-            accumulate_dilation<AffT, KC, SH, 24>(acc, sc, wc);
+            accumulate_dilation<AffT, KC, SH, 24, MT>(acc, sc, wc);
             if (more) load_weights<AffT>(wc, apn, 2, pol);
         } else {
-            accumulate_dilation<AffT, KC, SH, 1>(acc, sc, wa);
+            accumulate_dilation<AffT, KC, SH, 1, MT>(acc, sc, wa);
             load_weights<AffT>(wa, ap, 2, pol);
-            accumulate_dilation<AffT, KC, SH, 2>(acc, sc, wb);
+            accumulate_dilation<AffT, KC, SH, 2, MT>(acc, sc, wb);
             load_weights<AffT>(wb, ap, 3, pol);
-            accumulate_dilation<AffT, KC, SH, 4>(acc, sc, wa);
+            accumulate_dilation<AffT, KC, SH, 4, MT>(acc, sc, wa);
             load_weights<AffT>(wa, ap, 4, pol);
-            accumulate_dilation<AffT, KC, SH, 8>(acc, sc, wb);
+            accumulate_dilation<AffT, KC, SH, 8, MT>(acc, sc, wb);
             load_weights<AffT>(wb, ap, 5, pol);
-            accumulate_dilation<AffT, KC, SH, 12>(acc, sc, wa);
+            accumulate_dilation<AffT, KC, SH, 12, MT>(acc, sc, wa);
             if (more) load_weights<AffT>(wa, apn, 0, pol);
-            accumulate_dilation<AffT, KC, SH, 24>(acc, sc, wb);
+            accumulate_dilation<AffT, KC, SH, 24, MT>(acc, sc, wb);
             if (more) load_weights<AffT>(wb, apn, 1, pol);
         }
         float* op = out + (size_t)ch0 * oplane + (size_t)y * a.out_pitch + x;
@@ -483,7 +546,8 @@ __global__ void __launch_bounds__(PT_THREADS, 2) par_iter_tile_kernel(const AffT
                                                                        float* __restrict__ out,
                                                                        const __grid_constant__ TileArgs a,
                                                                        const __grid_constant__ ParChunks ch) {
-    extern __shared__ __align__(16) float par_tile[];
+    extern __shared__ __align__(16) unsigned char par_tile_raw[];
+    typename MaskTile<AffT>::T* par_tile = reinterpret_cast<typename MaskTile<AffT>::T*>(par_tile_raw);
     switch (ch.cnt[blockIdx.z]) {
         case 1: par_iter_tile_body<AffT, 1, PT_TH>(par_tile, aff, in, out, a, ch); break;
         case 2: par_iter_tile_body<AffT, 2, PT_TH>(par_tile, aff, in, out, a, ch); break;
@@ -821,7 +885,7 @@ static int launch_iter_tile(const AffT* aff, const float* src, float* dst, const
         if (g_par_pipe < 0) { const char* e = getenv("WC_PAR_PIPE"); g_par_pipe = (e && e[0] == '1') ? 1 : 0; }
         if (g_par_pipe) return launch_iter_pipe(reinterpret_cast<const __half*>(aff), src, dst, ta, chunks, n, st);
     }
-    constexpr int PLANE = (PT_TH + 2 * PT_HALO) * PT_SW * (int)sizeof(float);
+    constexpr int PLANE = (PT_TH + 2 * PT_HALO) * PT_SW * (int)sizeof(typename MaskTile<AffT>::T);
     WC_SET_MAX_SMEM(par_iter_tile_kernel<AffT>, PT_KC * PLANE);
     dim3 grid(ceil_div(ta.W, PT_W), ceil_div(ta.H, PT_TH), n);
     par_iter_tile_kernel<AffT><<<grid, PT_THREADS, max_cnt * PLANE, st>>>(aff, src, dst, ta, chunks);
