@@ -136,7 +136,10 @@ template <> struct AffIO<__half> {
         return __half2float(__ushort_as_half(u));
     }
     using Raw = uint2;                // 4 x fp16 stay packed until they are used (2 registers per neighbour)
-    static constexpr int LOOKAHEAD = 2;
+#ifndef WC_PAR_LOOKAHEAD16
+#define WC_PAR_LOOKAHEAD16 1     // weight sets prefetched beyond the one in use (1: two sets of 16 registers; 2: three)
+#endif
+    static constexpr int LOOKAHEAD = WC_PAR_LOOKAHEAD16;
     static __device__ __forceinline__ Raw ld4(const __half* p, uint64_t pol) {
         uint2 v;
         asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u32 {%0, %1}, [%2], %3;"
@@ -318,14 +321,20 @@ __device__ __forceinline__ void fill_tile(float* tile, const float* __restrict__
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
 
-// Storage type of the mask tile in shared memory.  -DWC_PAR_MASK16=1 holds the masks of one step as fp16 in the tile when the
-// AFFINITIES are fp16 (values in [0, 1] rounded once per step at the fill, fp32 accumulation, fp32 in global memory): half the
-// shared-memory bytes.  Measured on B200 (16 x 512^2, one step, parity green): Kc = 2 / 3 / 6: 87.7 / 129.1 / 241.8 us against
-// 93 / 129 / 254 us with fp32 tiles — the step is not bound by shared-memory BYTES but by the latency of its LDS -> FFMA2 chains
-// at 4 warps per scheduler (ncu r02 stall samples: MIO throttle 24 %, long scoreboard 21 %, short scoreboard 15 %; time is linear
-// in Kc at ~40 us per channel), so the default keeps fp32 tiles and their exact arithmetic.
+// Storage type of the mask tile in shared memory.  With fp16 AFFINITIES (the pipeline's approximate mode) the masks of one step
+// are also held as fp16 in the tile: values in [0, 1] rounded once per step at the fill (<= 2^-12 absolute), fp32 accumulation,
+// fp32 in global memory.  That halves the tile (53.8 KB at Kc = 3) so that THREE CTAs fit per SM, compiled for 80 registers with
+// two prefetched weight sets instead of three: the step is bound by the latency of its LDS -> FFMA2 chains (ncu r02 stall
+// samples: MIO throttle 24 %, long scoreboard 21 %, short scoreboard 15 %; time linear in Kc), so resident warps are what helps.
+// Measured on B200 (16 x 512^2, one step, us at Kc = 2 / 3 / 6):
+//     fp32 tiles, 2 CTAs / SM, 3 weight sets (round-2 kernel until this change)   93 / 129 / 254
+//     fp16 tiles, 2 CTAs / SM, 3 weight sets                                       88 / 129 / 242   (bytes alone do not help)
+//     fp32 tiles, 3 CTAs / SM where they fit (Kc <= 2), 2 weight sets              99 / 140 / 261
+//     fp16 tiles, 3 CTAs / SM, 2 weight sets (default)                             87 / 118 / 222
+// fp32 affinities keep fp32 tiles, 2 CTAs / SM and exact arithmetic.  -DWC_PAR_MASK16=0 -DWC_PAR_CTAS16=2 -DWC_PAR_LOOKAHEAD16=2
+// restores the previous fp16-affinity kernel.
 #ifndef WC_PAR_MASK16
-#define WC_PAR_MASK16 0
+#define WC_PAR_MASK16 1
 #endif
 template <typename AffT> struct MaskTile { using T = float; };
 #if WC_PAR_MASK16
@@ -469,10 +478,10 @@ __device__ __forceinline__ void par_iter_tile_body(typename MaskTile<AffT>::T* p
     const int x = x0 + 4 * tx4;
     const bool active = x < W;             // (the affinity blocks are padded to 64 pixels: loads beyond W stay in bounds)
     const AffT* abase = aff + ((size_t)ch.b[c] * H * a.wb + blockIdx.x) * (48 * PB) + 4 * tx4;
-    // Software pipeline over (row pass, dilation): three weight sets rotate, each refilled as soon as its dilation has been
-    // accumulated — the refills at the end of a pass already fetch the NEXT row's first three dilations, and the very first
-    // three are requested before the tile fill, so no pass starts with an exposed HBM round trip.
-    // (fp16 weights: three sets of 16 registers; fp32: two sets of 32)
+    // Software pipeline over (row pass, dilation): two (LOOKAHEAD 1) or three (LOOKAHEAD 2) weight sets rotate, each refilled as
+    // soon as its dilation has been accumulated — the refills at the end of a pass already fetch the NEXT row's first
+    // dilations, and the very first ones are requested before the tile fill, so no pass starts with an exposed HBM round trip.
+    // (fp16 weights: sets of 16 registers, two by default so that three CTAs fit per SM; fp32: two sets of 32)
     constexpr bool THREE = AffIO<AffT>::LOOKAHEAD == 2;
     typename AffIO<AffT>::Raw wa[8], wb[8], wc[THREE ? 8 : 1];
     if (active && y0 + tyb < H) {
@@ -541,7 +550,10 @@ __device__ __forceinline__ void par_iter_tile_body(typename MaskTile<AffT>::T* p
 // One launch per propagation step: blockIdx.z = chunk (image, first channel, 1..PT_KC channels); the channel count is
 // CTA-uniform, each count has its own fully unrolled body.
 template <typename AffT>
-__global__ void __launch_bounds__(PT_THREADS, 2) par_iter_tile_kernel(const AffT* __restrict__ aff,
+#ifndef WC_PAR_CTAS16
+#define WC_PAR_CTAS16 3          // resident CTAs per SM the fp16-affinity step is compiled for (3: <= 85 registers)
+#endif
+__global__ void __launch_bounds__(PT_THREADS, (sizeof(AffT) == 2 ? WC_PAR_CTAS16 : 2)) par_iter_tile_kernel(const AffT* __restrict__ aff,
                                                                        const float* __restrict__ in,
                                                                        float* __restrict__ out,
                                                                        const __grid_constant__ TileArgs a,
