@@ -565,6 +565,141 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_headmean_kernel(const __gr
 }
 
 // ---------------------------------------------------------------------------------------------------
+// attn_headmean64_kernel — the same map from 128 x 64 tiles with TWO CTAs resident per SM.  The 128 x 128 kernel above keeps one
+// CTA per SM, so its per-tile prologue (barrier init, TMEM allocation, first TMA round trip) and epilogue (transposed store of the
+// 64 KB tile) run with the MUFU idle: 107 of its 286 us at L = 1601 do not depend on the head count (tools/hm_slope.py).  Here a
+// CTA holds half a tile (thread = row x 32 keys: 32 accumulators, < 102 registers), so two CTAs share an SM and one's
+// prologue / epilogue runs under the other's head loop.  Q is loaded once per 64 keys instead of once per 128 (L2 traffic x1.5).
+// ---------------------------------------------------------------------------------------------------
+constexpr int HM_BN = 64, HM_STAGES = 3;
+constexpr int HM_STAGE_BYTES = AT_TILE_BYTES + AT_TILE_BYTES / 2;            // Q_h [128][64] + K_h [64][64] fp16
+struct Mean64Smem {
+    static constexpr int RING = 0;
+    static constexpr int STG = HM_STAGES * HM_STAGE_BYTES;                   // 8 warps x 4 KB transposition blocks
+    static constexpr int BARS = STG + AT_SM_WARPS * 32 * 32 * 4;
+    static constexpr int TOTAL = BARS + 256 + 1024;
+};
+
+__global__ void __launch_bounds__(AT_THREADS, 2) attn_headmean64_kernel(const __grid_constant__ CUtensorMap mapQ,
+                                                                         const __grid_constant__ CUtensorMap mapK,
+                                                                         const __grid_constant__ MeanArgs a) {
+    extern __shared__ uint8_t at_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Mean64Smem::BARS);
+    uint64_t* full = bars;                         // [STAGES]
+    uint64_t* empty = full + HM_STAGES;            // [STAGES]
+    uint64_t* s_full = empty + HM_STAGES;          // [2]
+    uint64_t* s_empty = s_full + 2;                // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int kt = blockIdx.x, qt = blockIdx.y, img = blockIdx.z;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&mapQ); prefetch_tmap(&mapK);
+        for (int s = 0; s < HM_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], AT_SM_WARPS); }
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 2 * HM_BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int h = 0; h < a.heads; ++h) {
+                const int s = h % HM_STAGES;
+                mbar_wait(&empty[s], ((h / HM_STAGES) & 1) ^ 1);
+                uint8_t* sq = smem + Mean64Smem::RING + s * HM_STAGE_BYTES;
+                mbar_expect_tx(&full[s], HM_STAGE_BYTES);
+                tma_load_4d(sq, &mapQ, &full[s], 0, qt * AT_BM, img * a.heads + h, 0);
+                tma_load_4d(sq + AT_TILE_BYTES, &mapK, &full[s], 0, kt * HM_BN, img * a.heads + h, 0);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_s = make_idesc(AT_BM, HM_BN);
+            for (int h = 0; h < a.heads; ++h) {
+                const int s = h % HM_STAGES, b = h & 1;
+                {   // both barrier round trips in flight together
+                    const uint32_t ok_f = mbar_try(&full[s], (h / HM_STAGES) & 1);
+                    const uint32_t ok_e = mbar_try(&s_empty[b], ((h >> 1) & 1) ^ 1);
+                    if (!ok_f) mbar_wait(&full[s], (h / HM_STAGES) & 1);
+                    if (!ok_e) mbar_wait(&s_empty[b], ((h >> 1) & 1) ^ 1);
+                }
+                tc_fence_after();
+                const uint32_t sq = smem_u32(smem + Mean64Smem::RING + s * HM_STAGE_BYTES);
+                const uint64_t dq = make_smem_desc(sq), dk = make_smem_desc(sq + AT_TILE_BYTES);
+#pragma unroll
+                for (int k = 0; k < AT_HD / 16; ++k) umma_f16(tmem_base + b * HM_BN, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+                umma_commit(&s_full[b]);
+                umma_commit(&empty[s]);
+            }
+        }
+    } else {
+        const int q = warp & 3;                              // TMEM lane quarter
+        const int half = (warp - 2) >> 2;                    // which 32 key columns this warp accumulates
+        const int row = q * 32 + lane, grow = qt * AT_BM + row;
+        const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16) + half * 32;
+        float* stg = reinterpret_cast<float*>(smem + Mean64Smem::STG) + (warp - 2) * 32 * 32;
+        float acc[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+        uint32_t r0[32];
+        float lse = (grow < a.L) ? __ldg(a.lse2 + (size_t)(img * a.heads) * a.L + grow) : 0.f;
+        for (int h = 0; h < a.heads; ++h) {
+            const int b = h & 1;
+            const float lse_next = (grow < a.L && h + 1 < a.heads) ? __ldg(a.lse2 + (size_t)(img * a.heads + h + 1) * a.L + grow) : 0.f;
+            mbar_wait(&s_full[b], (h >> 1) & 1);
+            tc_fence_after();
+            tmem_ld32_issue(tlane + b * HM_BN, r0);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_empty[b]);         // S[b] is in registers: the MMA of head h + 2 may overwrite it
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[i] += ex2_approx(fmaf(__uint_as_float(r0[i]), AT_LOG2E, -lse));
+            lse = lse_next;
+        }
+        const float inv_h = 1.f / (float)a.heads;
+        const int row0 = qt * AT_BM + q * 32;
+        const int key0 = kt * HM_BN + half * 32;
+        if (a.sums) {
+            float part = 0.f;
+            if (grow >= 1 && grow < a.L) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) part += (key0 + i >= 1 && key0 + i < a.L) ? acc[i] : 0.f;
+            }
+            part = warp_sum(part);
+            if (lane == 0 && part != 0.f) atomicAdd(a.sums + img, (double)(part * inv_h));
+        }
+        // mean over heads, transposed through the warp's swizzled 32x32 block so that each store is one row x 32 keys
+        const int key = key0 + lane;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) =
+                make_float4(acc[4 * j] * inv_h, acc[4 * j + 1] * inv_h, acc[4 * j + 2] * inv_h, acc[4 * j + 3] * inv_h);
+        __syncwarp();
+        if (key < a.L) {
+            float* dst = a.avg + ((size_t)img * a.L + row0) * a.L + key;
+#pragma unroll 4
+            for (int rr = 0; rr < 32; ++rr) {
+                if (row0 + rr >= a.L) break;
+                dst[(size_t)rr * a.L] = stg[rr * 32 + (((lane >> 2) ^ (rr & 7)) << 2) + (lane & 3)];
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 2 * HM_BN);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
 // attn_bwd_colsum_kernel — the only L x L work of the Grad-CAM backward (gradcam.cu header):
 //     colsum[j] = sum_{i>=1} dS_ij,   dS = P * (dP - delta),  dP = dO V^T,  delta_i = dO_i . O_i
 //               = V'_j . W'_j         with  W' = P~^T dO'   (P~ = P without the class-token query row,
@@ -869,9 +1004,21 @@ int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* a
     if (rc) return rc;
     if (sums) WC_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * n_img, st));
     MeanArgs a{L, heads, lse2, avg, sums};
-    dim3 grid(ceil_div(L, AT_BN), ceil_div(L, AT_BM), n_img);
     ProfScope prof(PK_SOFTMAX, 4.0 * n_img * (double)L * L, st);
     if (g_prof_on) prof_tag(L, n_img, heads, 1);
+    static const bool tile64 = [] { const char* e = getenv("WC_HEADMEAN64"); return !(e && e[0] == '0'); }();
+    if (tile64) {        // 128 x 64 tiles, two CTAs per SM (WC_HEADMEAN64=0: the 128 x 128 kernel)
+        WC_SET_MAX_SMEM(attn_headmean64_kernel, Mean64Smem::TOTAL);
+        CUtensorMap mk64;
+        int u0, u1;
+        GemmOperand ok{k, L, AT_HD, (long)L * AT_HD, 0};
+        if ((rc = make_tma_map(&mk64, ok, AT_HD, n_img * heads, 1, HM_BN, &u0, &u1))) return rc;
+        dim3 grid64(ceil_div(L, HM_BN), ceil_div(L, AT_BM), n_img);
+        attn_headmean64_kernel<<<grid64, AT_THREADS, Mean64Smem::TOTAL, st>>>(mq, mk64, a);
+        WC_LAUNCH_CHECK();
+        return WC_OK;
+    }
+    dim3 grid(ceil_div(L, AT_BN), ceil_div(L, AT_BM), n_img);
     attn_headmean_kernel<<<grid, AT_THREADS, MeanSmem::TOTAL, st>>>(mq, mk, a);
     WC_LAUNCH_CHECK();
     return WC_OK;
