@@ -8,9 +8,10 @@ from weclip_b200 import ops
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["0", "1"], ids=["attn_fwd_kernel", "attn_fwd2_kernel"], autouse=True)
+@pytest.fixture(params=["0", "1", "2"], ids=["attn_fwd_kernel", "attn_fwd2_kernel", "attn_fwd3_kernel"], autouse=True)
 def head_dim_64_kernel(request, monkeypatch):
-    """Both head_dim-64 forward kernels (attention.cu and the two-tile TMEM-operand kernel of attention2.cu, WC_ATTN2=1) run every
+    """The head_dim-64 forward kernels (attention.cu, the two-tile TMEM-operand kernel of attention2.cu, WC_ATTN2=1, and the
+    two-CTAs-per-SM kernel of attention3.cu, WC_ATTN2=2) run every
     case; the selection is read per launch."""
     monkeypatch.setenv("WC_ATTN2", request.param)
 

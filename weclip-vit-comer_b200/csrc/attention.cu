@@ -969,6 +969,9 @@ static int launch_fwd_hd(const CUtensorMap& mq, const CUtensorMap& mk, const CUt
 // second-generation head_dim-64 forward (attention2.cu)
 int launch_attention_fwd2(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, h16* o, float* lse2, int n_img,
                           int heads, int L, int sms, cudaStream_t st);
+// third variant (attention3.cu): 64-key tiles, two CTAs per SM (WC_ATTN2=2)
+int launch_attention_fwd3(const CUtensorMap& mq, const h16* k, const h16* v, h16* o, float* lse2, int n_img, int heads, int L,
+                          cudaStream_t st);
 // head_dim 64: attn_fwd_kernel<64> unless WC_ATTN2=1 (read per launch, so that the tests can run both): the second kernel is within
 // 2% of the first at the encoder's shapes (profiles/r02_attention.txt) and owns two query tiles per item, which is the coarser
 // granularity at the evaluation driver's batch of two.
@@ -991,6 +994,7 @@ int launch_attention_fwd(const h16* q, const h16* k, const h16* vt, h16* o, floa
     ProfScope prof(PK_ATTENTION, 4.0 * L * L * hd * heads * n_img, st);
     if (g_prof_on) prof_tag(L, n_img, heads, hd);
     const char* sel = hd == 64 ? getenv("WC_ATTN2") : nullptr;
+    if (sel && sel[0] == '2') return launch_attention_fwd3(mq, k, vt, o, lse2, n_img, heads, L, st);
     if (sel && sel[0] == '1') return launch_attention_fwd2(mq, mk, mv, o, lse2, n_img, heads, L, sms, st);
     return hd == 64 ? launch_fwd_hd<64>(mq, mk, mv, a, grid, st) : launch_fwd_hd<32>(mq, mk, mv, a, grid, st);
 }
