@@ -259,7 +259,7 @@ def _small_dataset(root, seed=21):
 def test_cuda_graph_buckets_equal_the_eager_driver():
     """use_graphs: one CUDA graph per (image size, label size, classes-per-image) bucket and replay slot holds the whole
     step; replays (incl. re-used buckets, both slots, several images in flight) give the eager driver's histograms —
-    bit-identical for the segmentation outputs, within the fp-atomics tolerance for the CAM pseudo-labels."""
+    bit-identical, CAM pseudo-labels included (every reduction on the path has a fixed order)."""
     sd = synth.make_state_dict(0, 21)
     fg, bg = synth.make_text_features(7, 20, 25)
     root = tempfile.mkdtemp()
@@ -277,9 +277,7 @@ def test_cuda_graph_buckets_equal_the_eager_driver():
     he, hg = eager.hist, graphed.hist
     assert graphed.n_images == eager.n_images == 12 and graphed.graph_replays == 12
     assert 3 <= graphed.graph_captures <= 12              # buckets x 2 slots at most; far fewer captures than images
-    assert torch.equal(he[:2], hg[:2])
-    assert int(he[2].sum()) == int(hg[2].sum())
-    assert int((he[2] - hg[2]).abs().sum()) <= 2e-3 * int(he[2].sum())
+    assert torch.equal(he, hg)                # all three histograms: the path has no floating-point atomics
     before = graphed.graph_captures
     for name, img, lab in items:                          # third pass: every bucket / slot pair that recurs is a pure replay
         graphed.process(name, img[None].cuda(), torch.from_numpy(lab.astype(np.int16)).cuda())

@@ -84,7 +84,7 @@ __device__ __forceinline__ void aff_build_rows(const float* const (&base)[16], c
             Bm[(irow + i) * P + j] = v;
             cs += v;
         }
-        atomicAdd(colz + irow + j, cs);
+        (void)cs; (void)colz;      // (the first column sums come from aff_col_pass_kernel: no floating-point atomics on the path)
     }
 }
 
@@ -178,17 +178,37 @@ __global__ void __launch_bounds__(256) aff_row_pass_kernel(const float* __restri
     if (lane == 0) r[(size_t)img * P + i] = 1.f / s;
 }
 
-// z_j += sum_{i in chunk} r_i B_ij      (column sums of diag(r) B)
+// z_j = sum_i r_i B_ij      (column sums of diag(r) B; r == nullptr: plain column sums)
+// One CTA owns a strip of 32 columns over ALL rows: lane = column, the 8 warps interleave the rows, eight 128-byte row segments
+// per warp in flight, and the eight partial sums are added in a fixed order — every z_j is the same bits on every run (the first
+// version added row-chunk partials with atomicAdd, whose order is not fixed).
 __global__ void __launch_bounds__(256) aff_col_pass_kernel(const float* __restrict__ Bm, const float* __restrict__ r,
                                                            float* __restrict__ z, int P) {
-    __shared__ float rr[32];
-    const int img = blockIdx.y, r0 = blockIdx.x * 32, n = min(32, P - r0);
-    if (threadIdx.x < n) rr[threadIdx.x] = r[(size_t)img * P + r0 + threadIdx.x];
+    __shared__ float part[8][32];
+    const int img = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31, j = blockIdx.x * 32 + lane;
+    const bool ok = j < P;
+    const float* col = Bm + (size_t)img * P * P + (ok ? j : 0);
+    const float* rr = r ? r + (size_t)img * P : nullptr;
+    float s0 = 0.f, s1 = 0.f;
+    int i = warp;
+    for (; i + 56 < P; i += 64) {
+        float b[8], w[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            b[u] = __ldg(col + (size_t)(i + 8 * u) * P);
+            w[u] = rr ? __ldg(rr + i + 8 * u) : 1.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u += 2) { s0 = fmaf(w[u], b[u], s0); s1 = fmaf(w[u + 1], b[u + 1], s1); }
+    }
+    for (; i < P; i += 8) s0 = fmaf(rr ? __ldg(rr + i) : 1.f, __ldg(col + (size_t)i * P), s0);
+    part[warp][lane] = s0 + s1;
     __syncthreads();
-    for (int j = threadIdx.x; j < P; j += 256) {
-        float s = 0.f;
-        for (int i = 0; i < n; ++i) s = fmaf(rr[i], Bm[((size_t)img * P + r0 + i) * P + j], s);
-        atomicAdd(z + (size_t)img * P + j, s);
+    if (warp == 0 && ok) {
+        float t = part[0][lane];
+#pragma unroll
+        for (int w8 = 1; w8 < 8; ++w8) t += part[w8][lane];
+        z[(size_t)img * P + j] = t;
     }
 }
 
@@ -347,33 +367,51 @@ __global__ void __launch_bounds__(256) tsym_row_kernel(const float* __restrict__
     }
 }
 
-// out_jk += 0.5 / z_j * sum_{i in chunk} B_ij r_i x_ik   (column half of T_s x; accumulates)
+// out_jk += 0.5 / z_j * sum_i B_ij r_i x_ik   (column half of T_s x; adds to the row half written by tsym_row_kernel)
+// Same strip scheme as aff_col_pass_kernel (32 columns x all rows per CTA, fixed summation order, one writer per element).
 __global__ void __launch_bounds__(256) tsym_col_kernel(const float* __restrict__ Bm, const float* __restrict__ r,
                                                        const float* __restrict__ z, const float* __restrict__ x,
                                                        float* __restrict__ out, const __grid_constant__ AffTable tab,
                                                        int P, int kbase) {
-    __shared__ float rx[32][AFF_KMAX];
-    const int img = blockIdx.y, r0 = blockIdx.x * 32, n = min(32, P - r0);
+    __shared__ float part[8][AFF_KMAX][32];
+    const int img = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31, j = blockIdx.x * 32 + lane;
     const int k0 = tab.k_off[img] + kbase, kn = min(AFF_KMAX, tab.k_off[img + 1] - k0);
     if (kn <= 0) return;
-    for (int t = threadIdx.x; t < 32 * AFF_KMAX; t += 256) {
-        const int i = t / AFF_KMAX, k = t % AFF_KMAX;
-        rx[i][k] = (i < n && k < kn) ? r[(size_t)img * P + r0 + i] * x[(size_t)(k0 + k) * P + r0 + i] : 0.f;
-    }
-    __syncthreads();
-    for (int j = threadIdx.x; j < P; j += 256) {
-        float acc[AFF_KMAX];
+    const bool ok = j < P;
+    const float* col = Bm + (size_t)img * P * P + (ok ? j : 0);
+    const float* rr = r + (size_t)img * P;
+    float acc[AFF_KMAX];
 #pragma unroll
-        for (int k = 0; k < AFF_KMAX; ++k) acc[k] = 0.f;
-        for (int i = 0; i < n; ++i) {
-            const float b = Bm[((size_t)img * P + r0 + i) * P + j];
+    for (int k = 0; k < AFF_KMAX; ++k) acc[k] = 0.f;
+    int i = warp;
+    for (; i + 24 < P; i += 32) {
+        float b[4];
 #pragma unroll
-            for (int k = 0; k < AFF_KMAX; ++k) acc[k] = fmaf(b, rx[i][k], acc[k]);
-        }
-        const float cj = 0.5f / z[(size_t)img * P + j];
+        for (int u = 0; u < 4; ++u) b[u] = __ldg(col + (size_t)(i + 8 * u) * P) * __ldg(rr + i + 8 * u);
 #pragma unroll
         for (int k = 0; k < AFF_KMAX; ++k)
-            if (k < kn) atomicAdd(out + (size_t)(k0 + k) * P + j, cj * acc[k]);
+            if (k < kn) {
+                const float* xk = x + (size_t)(k0 + k) * P + i;       // warp-uniform addresses: broadcast loads
+                acc[k] = fmaf(b[0], __ldg(xk), fmaf(b[1], __ldg(xk + 8), fmaf(b[2], __ldg(xk + 16), fmaf(b[3], __ldg(xk + 24), acc[k]))));
+            }
+    }
+    for (; i < P; i += 8) {
+        const float b = __ldg(col + (size_t)i * P) * __ldg(rr + i);
+#pragma unroll
+        for (int k = 0; k < AFF_KMAX; ++k)
+            if (k < kn) acc[k] = fmaf(b, __ldg(x + (size_t)(k0 + k) * P + i), acc[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < AFF_KMAX; ++k) part[warp][k][lane] = acc[k];
+    __syncthreads();
+    if (ok) {
+        const float cj = 0.5f / z[(size_t)img * P + j];
+        for (int k = warp; k < kn; k += 8) {
+            float t = part[0][k][lane];
+#pragma unroll
+            for (int w8 = 1; w8 < 8; ++w8) t += part[w8][k][lane];
+            out[(size_t)(k0 + k) * P + j] += cj * t;
+        }
     }
 }
 
@@ -461,22 +499,17 @@ extern "C" int wc_affinity_refine(const float* attn, int nl, const double* attn_
     float* r = z + (size_t)N * P;
     float* v0 = r + (size_t)N * P;
     float* v1 = v0 + (size_t)total * P;
-    const size_t NP = (size_t)N * P;
     if (use_rfm && !attn_sums) {      // no sums from the producers: one extra pass over the nl maps
         WC_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * N * (nl + 1), st));
         aff_layer_sums_kernel<<<dim3(ceil_div(P, 32), nl, N), 256, 0, st>>>(attn, attn_pred, sums, nl, N, L);
         WC_LAUNCH_CHECK();
     }
-    WC_CUDA(cudaMemsetAsync(z, 0, sizeof(float) * NP, st));
     aff_build_kernel<<<dim3(ceil_div(P, 16), N), 256, 0, st>>>(attn, attn_pred, attn_sums ? attn_sums : sums, Bm, z, nl, N, L, use_rfm, rfm_sel,
                                                                 attn_sums ? 1 : 0);
     WC_LAUNCH_CHECK();
     for (int round = 0; round < 3; ++round) {   // clip_tool.py:67-72
-        if (round > 0) {
-            WC_CUDA(cudaMemsetAsync(z, 0, sizeof(float) * NP, st));
-            aff_col_pass_kernel<<<dim3(ceil_div(P, 32), N), 256, 0, st>>>(Bm, r, z, P);
-            WC_LAUNCH_CHECK();
-        }
+        aff_col_pass_kernel<<<dim3(ceil_div(P, 32), N), 256, 0, st>>>(Bm, round ? r : nullptr, z, P);
+        WC_LAUNCH_CHECK();
         aff_row_pass_kernel<<<dim3(ceil_div(P, 8), N), 256, 0, st>>>(Bm, z, r, P);
         WC_LAUNCH_CHECK();
     }

@@ -986,6 +986,12 @@ static int launch_pair(const GemmProblem& p, cudaStream_t st) {
 int launch_gemm(const GemmProblem& p, cudaStream_t st) {
     WC_CHECK_ARG(p.M > 0 && p.N > 0 && p.K > 0 && p.nb0 > 0 && p.nb1 > 0 && p.A.ptr && p.B.ptr);
     if (p.epi.mode == GM_QKV) WC_CHECK_ARG(p.N % 32 == 0 && p.epi.hd % 32 == 0 && p.epi.bias && aligned(p.epi.bias, 16));
+    {   // developer override (tools/gemm_bench.py): WC_GEMM_FORCE_BN = 256 / 128 / 64 runs every problem on cta_group::1 tiles of that width
+        static const int force = [] { const char* e = getenv("WC_GEMM_FORCE_BN"); return e ? atoi(e) : 0; }();
+        if (force == 256 && p.N > 128) return launch_cfg<256>(p, st);
+        if (force == 128 && p.N > 64) return launch_cfg<128>(p, st);
+        if (force == 64 && p.N > 32) return launch_cfg<64>(p, st);
+    }
     if (p.N <= 32) return launch_cfg<32>(p, st);
     if (p.N <= 64) return launch_cfg<64>(p, st);
     if (p.N <= 128) return launch_cfg<128>(p, st);

@@ -49,7 +49,8 @@ __global__ void inst_map_kernel(const __grid_constant__ InstTable it, int* __res
 }
 
 // ---------------------------------------------------------------------------------------------------
-// ln_post + column sums over the patch rows (clip/model.py:411-412).  msum[img][c] += sum_rows LN(x2)[row][c]
+// ln_post + column sums over the patch rows (clip/model.py:411-412).  mpart[img][block][c] = sum over the block's 32 rows of
+// LN(x2)[row][c]; head_kernel adds the blocks in order (no floating-point atomics: the same bits on every run)
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) lnpost_mean_kernel(const float* __restrict__ x2, const float* __restrict__ gw,
                                                           const float* __restrict__ gb, float* __restrict__ msum, int L) {
@@ -93,7 +94,7 @@ __global__ void __launch_bounds__(256) lnpost_mean_kernel(const float* __restric
         float s = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) s += part[w][c];
-        atomicAdd(msum + (size_t)img * GC_E + c, s);
+        msum[((size_t)img * gridDim.x + blockIdx.x) * GC_E + c] = s;
     }
 }
 
@@ -102,7 +103,7 @@ __global__ void __launch_bounds__(256) lnpost_mean_kernel(const float* __restric
 // (clip/model.py:411-427 and the softmax / L2-norm / proj Jacobians).  One CTA (512 threads) per image.
 //   dm[inst][c] = d p_k / d y[l][c] for every patch row l  ( = (proj @ dg)[c] / P )
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msum, const float* __restrict__ proj,
+__global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msum, int n_part, const float* __restrict__ proj,
                                                    const float* __restrict__ text, const __grid_constant__ ImgTable tab,
                                                    float logit_scale, int P, float* __restrict__ dm,
                                                    float* __restrict__ gscale, float* __restrict__ probs_out) {
@@ -113,7 +114,11 @@ __global__ void __launch_bounds__(512) head_kernel(const float* __restrict__ msu
     const int img = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int t0 = tab.text_off[img], T = tab.text_off[img + 1] - t0;
     const int K = tab.k_off[img + 1] - tab.k_off[img];
-    for (int c = tid; c < GC_E; c += 512) mvec[c] = msum[(size_t)img * GC_E + c] / (float)P;
+    for (int c = tid; c < GC_E; c += 512) {
+        float sum = 0.f;
+        for (int b = 0; b < n_part; ++b) sum += msum[((size_t)img * n_part + b) * GC_E + c];
+        mvec[c] = sum / (float)P;
+    }
     __syncthreads();
     {   // g = mean @ proj  (model.py:414-415)
         // 768 dependent-free loads per thread: four accumulators and a deep unroll keep ~16 L2 requests in flight per thread
@@ -512,7 +517,7 @@ static void gc_layout(Arena& ar, GcLayout& g, int N, int L, int total_inst, int 
     const long M = (long)N * L, Lp = round8(L), E = GC_E;
     g.a32 = ar.get<float>(M * E); g.x1 = ar.get<float>(M * E); g.x2 = ar.get<float>(M * E);
     g.lse = ar.get<float>((long)N * GC_HEADS * L);
-    g.msum = ar.get<float>((long)N * E); g.dm = ar.get<float>((long)total_inst * E);
+    g.msum = ar.get<float>((long)N * ceil_div(L - 1, 32) * E); g.dm = ar.get<float>((long)total_inst * E);
     g.dqkv = ar.get<float>((long)total_inst * 3 * E); g.wvec = ar.get<float>((long)total_inst * E);
     g.gscale = ar.get<float>((long)total_inst);
     g.a = ar.get<h16>(M * E); g.q = ar.get<h16>(M * E); g.k = ar.get<h16>(M * E); g.v = ar.get<h16>(M * E);
@@ -598,10 +603,9 @@ extern "C" int wc_gradcam(const wc_vit_weights* w, const float* x11, int N, int 
         if ((rc = run_block(w->blocks[11], b, N, L, E, GC_HEADS, st))) return rc;
     }
     // ---- pooled head + its Jacobian for every (image, class)
-    WC_CUDA(cudaMemsetAsync(g.msum, 0, sizeof(float) * N * E, st));
     WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, lnpost_mean_kernel<<<dim3(ceil_div(P, 32), N), 256, 0, st>>>(g.x2, w->ln_post_w, w->ln_post_b, g.msum, L));
     WC_LAUNCH_CHECK();
-    WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, head_kernel<<<N, 512, 0, st>>>(g.msum, w->proj, text, tab, w->logit_scale_exp, P, g.dm, g.gscale, probs));
+    WC_PROF_LAUNCH(PK_GRADCAM_MISC, 0.0, st, head_kernel<<<N, 512, 0, st>>>(g.msum, ceil_div(P, 32), w->proj, text, tab, w->logit_scale_exp, P, g.dm, g.gscale, probs));
     WC_LAUNCH_CHECK();
     // ---- backward, in chunks of whole images holding <= chunk instances
     const float qscale = 1.f / sqrtf((float)GC_HD);
