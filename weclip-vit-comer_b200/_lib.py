@@ -77,7 +77,7 @@ def stream_ptr() -> c_void_p:
     object (device-index lookups, ~14 us measured); the raw getter is two orders of magnitude cheaper."""
     import torch
     raw = getattr(torch._C, "_cuda_getCurrentRawStream", None)
-    if raw is not None and not os.environ.get("WC_OLD_STREAM"):
+    if raw is not None:
         return c_void_p(raw(torch.cuda.current_device()))
     return c_void_p(torch.cuda.current_stream().cuda_stream)
 
