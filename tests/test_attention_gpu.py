@@ -25,7 +25,7 @@ def _ref(q, k, v):
 
 
 @pytest.mark.parametrize("N,heads,L", [(1, 1, 128), (1, 2, 401), (2, 12, 577), (1, 3, 1025), (1, 2, 1601), (2, 1, 50)])
-def test_attention_matches_torch(N, heads, L):
+def test_attention_matches_torch(N, heads, L, monkeypatch):
     g = torch.Generator(device="cuda").manual_seed(L + heads)
     q = (torch.randn(N, heads, L, 64, device="cuda", generator=g) * 0.125 * 2.0).half()
     k = (torch.randn(N, heads, L, 64, device="cuda", generator=g) * 1.5).half()
@@ -36,6 +36,10 @@ def test_attention_matches_torch(N, heads, L):
     assert (o.float() - o_ref).abs().max().item() < 4e-3
     assert (avg - avg_ref).abs().max().item() < 2e-5
     assert (avg.sum(-1) - 1).abs().max().item() < 1e-4
+    # the head-mean map from the 128 x 128 one-CTA-per-SM kernel (default: 128 x 64 tiles, two CTAs per SM): the same bits
+    monkeypatch.setenv("WC_HEADMEAN64", "0")
+    _, avg128 = ops.attention_fwd(q, k, v)
+    assert torch.equal(avg128, avg)
 
 
 @pytest.mark.parametrize("N,heads,L", [(1, 1, 64), (2, 8, 400), (1, 8, 576), (1, 3, 1024), (2, 8, 1600), (1, 2, 37)])

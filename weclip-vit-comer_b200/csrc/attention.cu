@@ -1010,8 +1010,8 @@ int launch_attn_headmean(const h16* q, const h16* k, const float* lse2, float* a
     MeanArgs a{L, heads, lse2, avg, sums};
     ProfScope prof(PK_SOFTMAX, 4.0 * n_img * (double)L * L, st);
     if (g_prof_on) prof_tag(L, n_img, heads, 1);
-    static const bool tile64 = [] { const char* e = getenv("WC_HEADMEAN64"); return !(e && e[0] == '0'); }();
-    if (tile64) {        // 128 x 64 tiles, two CTAs per SM (WC_HEADMEAN64=0: the 128 x 128 kernel)
+    const char* hm = getenv("WC_HEADMEAN64");            // read per launch, so that the tests can run both kernels
+    if (!(hm && hm[0] == '0')) {        // 128 x 64 tiles, two CTAs per SM (WC_HEADMEAN64=0: the 128 x 128 kernel)
         WC_SET_MAX_SMEM(attn_headmean64_kernel, Mean64Smem::TOTAL);
         CUtensorMap mk64;
         int u0, u1;
