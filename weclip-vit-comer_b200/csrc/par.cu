@@ -331,6 +331,7 @@ __device__ __forceinline__ void fill_tile(float* tile, const float* __restrict__
 //     fp16 tiles, 2 CTAs / SM, 3 weight sets                                       88 / 129 / 242   (bytes alone do not help)
 //     fp32 tiles, 3 CTAs / SM where they fit (Kc <= 2), 2 weight sets              99 / 140 / 261
 //     fp16 tiles, 3 CTAs / SM, 2 weight sets (default)                             87 / 118 / 222
+//     fp16 tiles, 4 CTAs / SM (64 registers: 444 B of spills)                      94 / 163 / 298
 // fp32 affinities keep fp32 tiles, 2 CTAs / SM and exact arithmetic.  -DWC_PAR_MASK16=0 -DWC_PAR_CTAS16=2 -DWC_PAR_LOOKAHEAD16=2
 // restores the previous fp16-affinity kernel.
 #ifndef WC_PAR_MASK16
